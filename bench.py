@@ -1,0 +1,409 @@
+#!/usr/bin/env python
+"""bench.py -- getSegmentList queries/s (BASELINE.json metric) on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A step = one batched getSegmentList pass (list form) over BASELINE.json configs[1]: one VOD
+playlist of 3 levels x 1000 fragments and 10^6 random (playlist, level, beginTime, duration)
+queries.  With N > 1 every rank owns its own playlist shard and query batch (weak scaling, no
+collective on the data path); `value` is total queries / max-over-ranks device time.
+
+  value     inputs resident in HBM, K launches timed with CUDA events on the launch stream
+  e2e       the same step through the C ABI's HOST-pointer entry point on pinned host
+            buffers: H2D of the queries and D2H of offsets + hits are inside the timed region
+  roofline  algorithmic bytes (28 B/query + 12 B/hit + the tables once) / mean launch time,
+            against the measured HBM copy peak of MEASURED_PEAKS.json
+  cpu_baseline  the C restatement of media-map.js:42-51 (oracle/) on the host cores, timed on
+            rank 0 -- "port": no JavaScript engine exists on these boxes
+
+--impl reference times that CPU restatement alone with every host thread (the reference is
+JavaScript) and prints the same line with "impl": "reference".
+"""
+import argparse
+import json
+import os
+import shutil
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "getSegmentList queries/s"
+UNIT = "queries/s"
+L2_BYTES = 126 * 1024 * 1024
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--queries", type=int, default=1_000_000)
+    ap.add_argument("--e2e-steps", type=int, default=8)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def host_threads():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def node_version():
+    exe = shutil.which("node") or shutil.which("nodejs")
+    if not exe:
+        return None
+    try:
+        return subprocess.check_output([exe, "--version"], timeout=10).decode().strip()
+    except Exception:
+        return None
+
+
+def workload_config(args, world):
+    return {"workload": "BASELINE.json configs[1]: VOD playlist, 3 levels x 1000 fragments, "
+                        "%d random (playlist, level, beginTime, duration) queries per GPU, list form"
+                        % args.queries,
+            "queries_per_step_per_gpu": args.queries, "levels": 3, "fragments_per_level": 1000,
+            "sharding": "by playlist, one shard per GPU, no collective" if world > 1 else "single GPU"}
+
+
+# ---------------------------------------------------------------------------------------------
+#  CPU arm: the restated reference filter on the host cores
+# ---------------------------------------------------------------------------------------------
+def cpu_filter_rate(tables, q, threads, min_seconds, max_reps=50):
+    import oracle
+    oracle.build()
+    reps, t0 = 0, time.perf_counter()
+    hits = 0
+    while True:
+        hits, _ = oracle.bench_get_segment_list(tables.playlist_base, tables.track_off,
+                                                tables.track_state, tables.start, tables.sn,
+                                                q.playlist, q.level, q.begin, q.duration, threads)
+        reps += 1
+        dt = time.perf_counter() - t0
+        if dt >= min_seconds or reps >= max_reps:
+            break
+    return reps * len(q) / dt, reps, dt, hits
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if rank != 0:
+        return 0
+    from hlsjs_p2p_wrapper_b200 import synth
+    import oracle
+    oracle.build()
+    tables, q = synth.config2(seed=2, n_queries=args.queries)
+    threads = host_threads()
+
+    def step():
+        return oracle.bench_get_segment_list(tables.playlist_base, tables.track_off, tables.track_state,
+                                             tables.start, tables.sn, q.playlist, q.level, q.begin,
+                                             q.duration, threads)
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        hits, _ = step()
+    dt = time.perf_counter() - t0
+    value = args.steps * len(q) / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": workload_config(args, world),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": "every step = the full %d-query batch through the C restatement of "
+                                   "media-map.js:42-51 (linear filter + list push), %d pthreads; the "
+                                   "reference JS itself cannot run: node is %s"
+                                   % (len(q), threads, node_version() or "absent")},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "hits_per_query": hits / len(q), "node": node_version(),
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------
+#  clocks sampling during the timed region
+# ---------------------------------------------------------------------------------------------
+class ClockSampler:
+    """Samples SM clock and throttle reasons through NVML every ~2 ms while the timed region
+    runs (nvidia-smi is far too slow to land a sample inside a few-ms region)."""
+
+    def __init__(self, uuid=None, index=0):
+        self.uuid, self.index = uuid, index
+        self.samples = []          # (t, sm_mhz, reasons_bitmask)
+        self.window = None         # (t0, t1) of the timed region
+        self._stop = threading.Event()
+        self._t = None
+        self.max_mhz = None
+        self.err = None
+
+    def _run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = None
+            if self.uuid:
+                for u in (self.uuid, "GPU-" + self.uuid):
+                    try:
+                        h = nv.nvmlDeviceGetHandleByUUID(u)
+                        break
+                    except Exception:
+                        h = None
+            if h is None:
+                h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+                nv.nvmlDeviceGetCurrentClocksThrottleReasons
+            while not self._stop.is_set():
+                self.samples.append((time.perf_counter(),
+                                     float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)),
+                                     int(get_reasons(h))))
+                self._stop.wait(0.002)
+        except Exception as e:          # no NVML: report that instead of inventing clocks
+            self.err = repr(e)
+
+    def start(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._t:
+            self._t.join(timeout=10)
+        bits = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "sw_thermal_slowdown": 0x20,
+                "hw_thermal_slowdown": 0x40, "hw_power_brake_slowdown": 0x80}
+        t0, t1 = self.window or (0.0, float("inf"))
+        inside = [s for s in self.samples if t0 <= s[0] <= t1] or self.samples
+        sm = [s[1] for s in inside]
+        mask = 0
+        for s in inside:
+            mask |= s[2]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(k for k, b in bits.items() if mask & b),
+                "samples_in_timed_region": len([s for s in self.samples if t0 <= s[0] <= t1]),
+                "samples": len(self.samples), "error": self.err}
+
+
+# ---------------------------------------------------------------------------------------------
+#  GPU arm
+# ---------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import hlsjs_p2p_wrapper_b200 as pk
+    from hlsjs_p2p_wrapper_b200 import synth
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: this engine has no CPU path")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier(device_ids=[local])
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    ctx = pk.Context(local)
+    # every rank owns its own playlist (seeded by rank): sharding by playlist, no exchange
+    tables, q0 = synth.config2(seed=2 + 1000 * rank, n_queries=args.queries)
+    dmap = ctx.upload(tables)
+    info = dmap.info()
+    nq = args.queries
+
+    # Rotating query/result buffer sets: successive steps stream through distinct memory
+    # whose total is > 3x L2, so no step finds its inputs or outputs in L2.
+    sets = []
+    per_step_bytes = None
+    n_sets = 0
+    while True:
+        q = q0
+        if n_sets > 0:   # the same queries in another order: distinct memory, same tables
+            rng = synth._stream(7000 + rank, n_sets)
+            perm = np.argsort(rng.u32(nq), kind="stable")
+            q = pk.QueryBatch(q0.playlist[perm], q0.level[perm], q0.begin[perm], q0.duration[perm])
+        _, total = dmap.count_segments(q.playlist, q.level, q.begin, q.duration)
+        cap = int(total)
+        s = {"q": q, "hits": cap,
+             "pl": torch.from_numpy(q.playlist).to(dev), "lv": torch.from_numpy(q.level).to(dev),
+             "bg": torch.from_numpy(q.begin).to(dev), "du": torch.from_numpy(q.duration).to(dev),
+             "off": torch.empty(nq + 1, dtype=torch.int32, device=dev),
+             "sn": torch.empty(cap, dtype=torch.int32, device=dev),
+             "tm": torch.empty(cap, dtype=torch.float64, device=dev)}
+        sets.append(s)
+        n_sets += 1
+        per_step_bytes = 28 * nq + 12 * cap
+        if n_sets * per_step_bytes >= 3 * L2_BYTES and n_sets >= 3:
+            break
+    torch.cuda.synchronize()
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def launch(s):
+        dmap.get_segment_list_dev(nq, s["pl"].data_ptr(), s["lv"].data_ptr(), s["bg"].data_ptr(),
+                                  s["du"].data_ptr(), s["off"].data_ptr(), s["sn"].data_ptr(),
+                                  s["tm"].data_ptr(), s["hits"], stream=stream)
+
+    for i in range(args.warmup):
+        launch(sets[i % n_sets])
+    chk = dmap.last_result(stream)
+    assert chk.total_hits == sets[(args.warmup - 1) % n_sets]["hits"] if args.warmup else True
+
+    try:
+        uuid = str(torch.cuda.get_device_properties(local).uuid)
+    except Exception:
+        uuid = None
+    sampler = ClockSampler(uuid, local)
+    if rank == 0:
+        sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+          for _ in range(args.steps)]
+    t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    w0 = time.perf_counter()
+    t_begin.record()
+    hits_timed = 0
+    for i in range(args.steps):
+        s = sets[i % n_sets]
+        ev[i][0].record()
+        launch(s)
+        ev[i][1].record()
+        hits_timed += s["hits"]
+    t_end.record()
+    barrier()
+    sampler.window = (w0, time.perf_counter())
+    region_ms = max_over_ranks(t_begin.elapsed_time(t_end))
+    kernel_ms = [a.elapsed_time(b) for a, b in ev]
+    clocks = sampler.stop() if rank == 0 else None
+    total_queries = sum_over_ranks(float(nq * args.steps))
+    value = total_queries / (region_ms * 1e-3)
+
+    # roofline of the dominant (only) kernel: algorithmic bytes / mean launch duration
+    table_bytes = 12 * info["n_fragments"]
+    alg_bytes = 28.0 * nq + 12.0 * (hits_timed / args.steps) + table_bytes
+    mean_kernel_ms = float(np.mean(kernel_ms))
+    achieved = alg_bytes / (mean_kernel_ms * 1e-3) / 1e9
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get("resolve_search_kernel_dram_bytes_per_launch")
+        except Exception:
+            traffic = None
+
+    # end to end through the host-pointer C ABI call on pinned buffers
+    s0 = sets[0]
+    pins = {k: ctx.pinned(shape, dt) for k, shape, dt in (
+        ("pl", nq, np.int32), ("lv", nq, np.int32), ("bg", nq, np.float64), ("du", nq, np.float64),
+        ("off", nq + 1, np.int32), ("sn", s0["hits"], np.int32), ("tm", s0["hits"], np.float64))}
+    pins["pl"].array[:] = s0["q"].playlist
+    pins["lv"].array[:] = s0["q"].level
+    pins["bg"].array[:] = s0["q"].begin
+    pins["du"].array[:] = s0["q"].duration
+
+    def e2e_step():
+        return dmap.get_segment_list_into(pins["pl"].array, pins["lv"].array, pins["bg"].array,
+                                          pins["du"].array, pins["off"].array, pins["sn"].array,
+                                          pins["tm"].array)
+    for _ in range(3):
+        r = e2e_step()
+    e2e_launches = r.kernel_launches
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.e2e_steps):
+        r = e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    e2e_value = sum_over_ranks(float(nq * args.e2e_steps)) / e2e_s
+    assert int(pins["off"].array[-1]) == s0["hits"] == r.total_hits
+    h2d = 24 * nq
+    d2h = 4 * (nq + 1) + 12 * s0["hits"]
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        threads = host_threads()
+        rate, reps, dt, _ = cpu_filter_rate(tables, q0, threads, min_seconds=3.0)
+        cpu = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
+               "sample": "%d x the full %d-query batch (%.1f s wall) through the C restatement of "
+                         "media-map.js:42-51 with %d pthreads; node on this box: %s"
+                         % (reps, nq, dt, threads, node_version() or "absent")}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": region_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": dict(workload_config(args, world),
+                           l2_policy="rotating %d distinct query/result buffer sets, %.0f MB per step, "
+                                     "%.0f MB per rotation (> 3x the 126 MB L2): no step finds its "
+                                     "inputs or outputs in L2" % (n_sets, per_step_bytes / 1e6,
+                                                                  n_sets * per_step_bytes / 1e6),
+                           hits_per_query=hits_timed / args.steps / nq, kernel="resolve_search_kernel",
+                           stage_all=info["stage_all"]),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                         "frac_of_nominal_8TBs": achieved / 8000.0,
+                         "algorithmic_bytes_per_launch": alg_bytes,
+                         "kernel_ms_mean": mean_kernel_ms, "kernel_ms_min": float(np.min(kernel_ms))},
+            "cpu_baseline": cpu,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "steps": args.e2e_steps,
+                    "ms_per_step": 1e3 * e2e_s / args.e2e_steps,
+                    "api": "hlsmap_get_segment_list (host pointers, pinned)",
+                    "kernel_launches_per_step": e2e_launches},
+            "gpu_launches": args.steps, "clocks": clocks, "node": node_version(),
+        }
+        print(json.dumps(line))
+    for p in pins.values():
+        p.free()
+    dmap.close()
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

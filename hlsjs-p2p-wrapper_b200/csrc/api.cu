@@ -1,0 +1,999 @@
+// api.cu -- the extern "C" boundary of libhlsmap: contexts, table upload, and the
+// host-pointer / device-pointer entry points declared in include/hlsmap.h.
+//
+// No CPU fallback lives here: every entry point either runs the CUDA kernels of
+// resolve.cu / views.cu or fails with a message.
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <limits>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+
+using namespace hlsmap;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string &msg)
+{
+    g_err = msg;
+    return code;
+}
+
+#define CK(call)                                                                         \
+    do {                                                                                 \
+        cudaError_t e_ = (call);                                                         \
+        if (e_ != cudaSuccess)                                                           \
+            return fail(HLSMAP_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+constexpr int kSlots = 12;
+
+}  // namespace
+
+struct hlsmap_ctx {
+    int device = 0;
+    int sm_count = 0;
+    int max_smem_optin = 0;
+    cudaStream_t stream = nullptr;      // compute + copies of the host-pointer variants
+    ScanCounters *ctr = nullptr;        // scan scratch header
+    DeviceResult *d_result = nullptr;
+    DeviceResult *h_result = nullptr;   // pinned
+    unsigned long long *tile_status = nullptr;
+    int64_t tile_cap = 0;
+    unsigned epoch = 0;
+    int last_launches = 0;
+    int last_path = 0;
+    bool have_last = false;
+    void *slot[kSlots] = {};            // grow-only device staging of the host variants
+    int64_t slot_bytes[kSlots] = {};
+};
+
+struct hlsmap_map {
+    hlsmap_ctx *ctx = nullptr;
+    int32_t n_playlists = 0, n_tracks = 0;
+    int64_t n_frag = 0, n_frag_padded = 0;
+    TrackDesc *d_desc = nullptr;
+    int *d_playlist_base = nullptr;
+    double *d_start = nullptr;
+    int *d_sn = nullptr;
+    double *d_dur0 = nullptr;
+    std::vector<int32_t> h_playlist_base;
+    std::vector<int32_t> h_url_count;
+    std::vector<uint8_t> h_monotone;
+    hlsmap_map_info info{};
+    int path = HLSMAP_PATH_AUTO;
+    int stage_elems = 0;
+    size_t stage_smem = 0;
+    int grid_search = 0, grid_filter = 0;
+};
+
+namespace {
+
+int use_ctx(hlsmap_ctx *ctx)
+{
+    if (!ctx) return fail(HLSMAP_ERR_INVALID, "null context");
+    CK(cudaSetDevice(ctx->device));
+    return HLSMAP_OK;
+}
+
+int ensure_slot(hlsmap_ctx *ctx, int i, int64_t bytes, void **out)
+{
+    if (bytes < 16) bytes = 16;
+    if (ctx->slot_bytes[i] < bytes) {
+        if (ctx->slot[i]) {
+            CK(cudaStreamSynchronize(ctx->stream));
+            CK(cudaFree(ctx->slot[i]));
+            ctx->slot[i] = nullptr;
+            ctx->slot_bytes[i] = 0;
+        }
+        const int64_t want = bytes + bytes / 4 + 256;
+        cudaError_t e = cudaMalloc(&ctx->slot[i], (size_t)want);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            return fail(HLSMAP_ERR_NOMEM, "cudaMalloc of " + std::to_string(want) + " bytes failed");
+        }
+        ctx->slot_bytes[i] = want;
+    }
+    *out = ctx->slot[i];
+    return HLSMAP_OK;
+}
+
+// Scratch for a scan batch of n_tiles tiles; bumps the launch epoch.
+int prepare_scan(hlsmap_ctx *ctx, int64_t n_tiles, cudaStream_t s)
+{
+    if (n_tiles > ctx->tile_cap) {
+        CK(cudaStreamSynchronize(ctx->stream));
+        if (s != ctx->stream) CK(cudaStreamSynchronize(s));
+        if (ctx->tile_status) CK(cudaFree(ctx->tile_status));
+        ctx->tile_status = nullptr;
+        const int64_t cap = n_tiles + n_tiles / 2 + 1024;
+        cudaError_t e = cudaMalloc(&ctx->tile_status, (size_t)cap * 8);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            ctx->tile_cap = 0;
+            return fail(HLSMAP_ERR_NOMEM, "cudaMalloc of tile status failed");
+        }
+        ctx->tile_cap = cap;
+        CK(cudaMemsetAsync(ctx->tile_status, 0, (size_t)cap * 8, s));
+    }
+    ctx->epoch++;
+    if (ctx->epoch > kEpochMask) {  // epoch 0 means "never written": wipe and restart
+        CK(cudaMemsetAsync(ctx->tile_status, 0, (size_t)ctx->tile_cap * 8, s));
+        CK(cudaMemsetAsync(ctx->ctr, 0, sizeof(ScanCounters), s));
+        ctx->epoch = 1;
+    }
+    return HLSMAP_OK;
+}
+
+int fetch_result(hlsmap_ctx *ctx, cudaStream_t s, hlsmap_result *out)
+{
+    CK(cudaMemcpyAsync(ctx->h_result, ctx->d_result, sizeof(DeviceResult), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    out->total_hits = ctx->h_result->total_hits;
+    out->n_unparsed = ctx->h_result->n_unparsed;
+    out->n_missing = ctx->h_result->n_missing;
+    out->kernel_launches = ctx->last_launches;
+    out->path = ctx->last_path;
+    if (ctx->h_result->overflow)
+        return fail(HLSMAP_ERR_OVERFLOW, "batch produced more than INT32_MAX hits; split it");
+    return HLSMAP_OK;
+}
+
+int pick_path(const hlsmap_map *m)
+{
+    if (m->path == HLSMAP_PATH_FILTER) return HLSMAP_PATH_FILTER;
+    if (m->path == HLSMAP_PATH_SEARCH) return HLSMAP_PATH_SEARCH;
+    return m->info.all_monotone ? HLSMAP_PATH_SEARCH : HLSMAP_PATH_FILTER;
+}
+
+inline bool al16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+}  // namespace
+
+extern "C" {
+
+const char *hlsmap_last_error(void) { return g_err.c_str(); }
+int hlsmap_version(void) { return 100; }
+
+int hlsmap_device_count(void)
+{
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(HLSMAP_ERR_CUDA, std::string("cudaGetDeviceCount: ") + cudaGetErrorString(e));
+    }
+    return n;
+}
+
+int hlsmap_ctx_create(int device, hlsmap_ctx **out)
+{
+    if (!out) return fail(HLSMAP_ERR_INVALID, "null out pointer");
+    *out = nullptr;
+    int n = hlsmap_device_count();
+    if (n < 0) return n;
+    if (n == 0) return fail(HLSMAP_ERR_CUDA, "no CUDA device: libhlsmap has no CPU path");
+    if (device < 0 || device >= n) return fail(HLSMAP_ERR_INVALID, "device ordinal out of range");
+    CK(cudaSetDevice(device));
+    hlsmap_ctx *c = new (std::nothrow) hlsmap_ctx();
+    if (!c) return fail(HLSMAP_ERR_NOMEM, "out of host memory");
+    c->device = device;
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) {
+        delete c;
+        return fail(HLSMAP_ERR_CUDA, "libhlsmap is built for sm_100a (Blackwell B200) only");
+    }
+    c->sm_count = prop.multiProcessorCount;
+    c->max_smem_optin = (int)prop.sharedMemPerBlockOptin;
+    CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CK(cudaMalloc(&c->ctr, sizeof(ScanCounters)));
+    CK(cudaMalloc(&c->d_result, sizeof(DeviceResult)));
+    CK(cudaMemset(c->ctr, 0, sizeof(ScanCounters)));
+    CK(cudaMemset(c->d_result, 0, sizeof(DeviceResult)));
+    CK(cudaHostAlloc(&c->h_result, sizeof(DeviceResult), cudaHostAllocDefault));
+    memset(c->h_result, 0, sizeof(DeviceResult));
+    *out = c;
+    return HLSMAP_OK;
+}
+
+void hlsmap_ctx_destroy(hlsmap_ctx *c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    for (int i = 0; i < kSlots; i++)
+        if (c->slot[i]) cudaFree(c->slot[i]);
+    if (c->tile_status) cudaFree(c->tile_status);
+    if (c->ctr) cudaFree(c->ctr);
+    if (c->d_result) cudaFree(c->d_result);
+    if (c->h_result) cudaFreeHost(c->h_result);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int hlsmap_ctx_device(const hlsmap_ctx *ctx) { return ctx ? ctx->device : -1; }
+
+int hlsmap_ctx_synchronize(hlsmap_ctx *ctx)
+{
+    int r = use_ctx(ctx);
+    if (r) return r;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return HLSMAP_OK;
+}
+
+int hlsmap_host_alloc(hlsmap_ctx *ctx, int64_t bytes, void **out)
+{
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (!out || bytes < 0) return fail(HLSMAP_ERR_INVALID, "bad host_alloc arguments");
+    CK(cudaHostAlloc(out, (size_t)(bytes > 0 ? bytes : 1), cudaHostAllocPortable));
+    return HLSMAP_OK;
+}
+
+int hlsmap_host_free(hlsmap_ctx *ctx, void *p)
+{
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (p) CK(cudaFreeHost(p));
+    return HLSMAP_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+//  table upload
+// ---------------------------------------------------------------------------------------
+int hlsmap_map_create(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *playlist_track_base,
+                      int32_t n_tracks, const int64_t *track_offset, const uint8_t *track_state,
+                      const int32_t *url_count, const double *start, const int32_t *sn,
+                      const double *duration, hlsmap_map **out)
+{
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (!out) return fail(HLSMAP_ERR_INVALID, "null out pointer");
+    *out = nullptr;
+    if (n_playlists < 0 || n_tracks < 0 || !playlist_track_base || !track_offset ||
+        (n_tracks > 0 && !track_state))
+        return fail(HLSMAP_ERR_INVALID, "map_create: missing table arrays");
+    if (playlist_track_base[0] != 0 || playlist_track_base[n_playlists] != n_tracks)
+        return fail(HLSMAP_ERR_INVALID, "map_create: playlist_track_base must span [0, n_tracks]");
+    for (int32_t p = 0; p < n_playlists; p++)
+        if (playlist_track_base[p + 1] < playlist_track_base[p])
+            return fail(HLSMAP_ERR_INVALID, "map_create: playlist_track_base not monotone");
+    if (track_offset[0] != 0) return fail(HLSMAP_ERR_INVALID, "map_create: track_offset[0] != 0");
+    for (int32_t t = 0; t < n_tracks; t++) {
+        const int64_t len = track_offset[t + 1] - track_offset[t];
+        if (len < 0 || len > 0x7fffffff)
+            return fail(HLSMAP_ERR_INVALID, "map_create: bad track length");
+        if (track_state[t] > HLSMAP_TRACK_PARSED)
+            return fail(HLSMAP_ERR_INVALID, "map_create: bad track_state");
+    }
+    const int64_t nf = track_offset[n_tracks];
+    if (nf > 0 && (!start || !sn)) return fail(HLSMAP_ERR_INVALID, "map_create: null start/sn");
+
+    hlsmap_map *m = new (std::nothrow) hlsmap_map();
+    if (!m) return fail(HLSMAP_ERR_NOMEM, "out of host memory");
+    m->ctx = ctx;
+    m->n_playlists = n_playlists;
+    m->n_tracks = n_tracks;
+    m->n_frag = nf;
+    m->n_frag_padded = ((nf + 3) & ~3ll) + 4;  // bulk copies round spans to 4 elements
+    m->h_playlist_base.assign(playlist_track_base, playlist_track_base + n_playlists + 1);
+    m->h_url_count.resize(n_tracks);
+    for (int32_t t = 0; t < n_tracks; t++) m->h_url_count[t] = url_count ? url_count[t] : 1;
+
+    std::vector<TrackDesc> desc((size_t)n_tracks);
+    std::vector<double> dur0((size_t)n_tracks, std::numeric_limits<double>::quiet_NaN());
+    int parsed = 0;
+    for (int32_t t = 0; t < n_tracks; t++) {
+        desc[t].off = track_offset[t];
+        desc[t].len = (int)(track_offset[t + 1] - track_offset[t]);
+        desc[t].flags = track_state[t];
+        if (track_state[t] == HLSMAP_TRACK_PARSED) {
+            parsed++;
+            if (duration && desc[t].len > 0) dur0[t] = duration[track_offset[t]];
+        }
+    }
+
+    auto bail = [&](int code) {
+        hlsmap_map_destroy(m);
+        return code;
+    };
+#define CKM(call)                                                                             \
+    do {                                                                                      \
+        cudaError_t e_ = (call);                                                              \
+        if (e_ != cudaSuccess) {                                                              \
+            cudaGetLastError();                                                               \
+            return bail(fail(e_ == cudaErrorMemoryAllocation ? HLSMAP_ERR_NOMEM : HLSMAP_ERR_CUDA, \
+                             std::string(#call) + ": " + cudaGetErrorString(e_)));            \
+        }                                                                                     \
+    } while (0)
+
+    cudaStream_t s = ctx->stream;
+    CKM(cudaMalloc(&m->d_desc, sizeof(TrackDesc) * (size_t)(n_tracks + 1)));
+    CKM(cudaMalloc(&m->d_playlist_base, sizeof(int) * (size_t)(n_playlists + 1)));
+    CKM(cudaMalloc(&m->d_start, sizeof(double) * (size_t)m->n_frag_padded));
+    CKM(cudaMalloc(&m->d_sn, sizeof(int) * (size_t)m->n_frag_padded));
+    CKM(cudaMalloc(&m->d_dur0, sizeof(double) * (size_t)(n_tracks + 1)));
+    // padding reads as NaN: it can never pass either comparison of the filter
+    CKM(cudaMemsetAsync(m->d_start, 0xff, sizeof(double) * (size_t)m->n_frag_padded, s));
+    CKM(cudaMemsetAsync(m->d_sn, 0, sizeof(int) * (size_t)m->n_frag_padded, s));
+    if (n_tracks) {
+        CKM(cudaMemcpyAsync(m->d_desc, desc.data(), sizeof(TrackDesc) * (size_t)n_tracks,
+                            cudaMemcpyHostToDevice, s));
+        CKM(cudaMemcpyAsync(m->d_dur0, dur0.data(), sizeof(double) * (size_t)n_tracks,
+                            cudaMemcpyHostToDevice, s));
+    }
+    CKM(cudaMemcpyAsync(m->d_playlist_base, playlist_track_base, sizeof(int) * (size_t)(n_playlists + 1),
+                        cudaMemcpyHostToDevice, s));
+    if (nf) {
+        CKM(cudaMemcpyAsync(m->d_start, start, sizeof(double) * (size_t)nf, cudaMemcpyHostToDevice, s));
+        CKM(cudaMemcpyAsync(m->d_sn, sn, sizeof(int) * (size_t)nf, cudaMemcpyHostToDevice, s));
+    }
+    // monotonicity of every start column, proven on the device (hard part 2)
+    CKM(launch_monotone_check(m->d_start, m->d_desc, n_tracks, s));
+    if (n_tracks)
+        CKM(cudaMemcpyAsync(desc.data(), m->d_desc, sizeof(TrackDesc) * (size_t)n_tracks,
+                            cudaMemcpyDeviceToHost, s));
+    CKM(cudaStreamSynchronize(s));
+
+    m->h_monotone.resize(n_tracks);
+    int mono = 0;
+    for (int32_t t = 0; t < n_tracks; t++) {
+        m->h_monotone[t] = (desc[t].flags & kTrackMonotone) ? 1 : 0;
+        mono += m->h_monotone[t];
+    }
+    m->info.n_playlists = n_playlists;
+    m->info.n_tracks = n_tracks;
+    m->info.n_fragments = nf;
+    m->info.n_monotone_tracks = mono;
+    m->info.n_parsed_tracks = parsed;
+    m->info.all_monotone = (mono == parsed) ? 1 : 0;
+    m->info.device_bytes = (int64_t)(sizeof(TrackDesc) * (size_t)(n_tracks + 1) +
+                                     sizeof(int) * (size_t)(n_playlists + 1) +
+                                     12 * (size_t)m->n_frag_padded + 8 * (size_t)(n_tracks + 1));
+
+    // shared-memory staging plan: whole column when it is small, else a per-tile window
+    int64_t stage_all_limit = 96 * 1024, window = 64 * 1024;
+    if (const char *e = getenv("HLSMAP_STAGE_ALL_KB")) stage_all_limit = atoll(e) * 1024;
+    if (const char *e = getenv("HLSMAP_STAGE_WINDOW_KB")) window = atoll(e) * 1024;
+    const int64_t smem_budget = (int64_t)ctx->max_smem_optin - 24 * 1024;
+    if (stage_all_limit > smem_budget) stage_all_limit = smem_budget;
+    if (window > smem_budget) window = smem_budget;
+    const int64_t col_bytes = m->n_frag_padded * 8;
+    if (col_bytes <= stage_all_limit) {
+        m->info.stage_all = 1;
+        m->stage_elems = (int)m->n_frag_padded;
+        m->stage_smem = (size_t)col_bytes;
+    } else {
+        m->info.stage_all = 0;
+        m->stage_elems = (int)(window / 8) & ~3;
+        m->stage_smem = (size_t)m->stage_elems * 8;
+    }
+    m->grid_search = resolve_search_max_grid(m->stage_smem);
+    m->grid_filter = resolve_filter_max_grid();
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess)
+        return bail(fail(HLSMAP_ERR_CUDA, std::string("kernel attribute set-up: ") + cudaGetErrorString(e)));
+#undef CKM
+    *out = m;
+    return HLSMAP_OK;
+}
+
+void hlsmap_map_destroy(hlsmap_map *m)
+{
+    if (!m) return;
+    if (m->ctx) {
+        cudaSetDevice(m->ctx->device);
+        cudaStreamSynchronize(m->ctx->stream);
+    }
+    if (m->d_desc) cudaFree(m->d_desc);
+    if (m->d_playlist_base) cudaFree(m->d_playlist_base);
+    if (m->d_start) cudaFree(m->d_start);
+    if (m->d_sn) cudaFree(m->d_sn);
+    if (m->d_dur0) cudaFree(m->d_dur0);
+    delete m;
+}
+
+int hlsmap_map_get_info(const hlsmap_map *map, hlsmap_map_info *info)
+{
+    if (!map || !info) return fail(HLSMAP_ERR_INVALID, "null argument");
+    *info = map->info;
+    return HLSMAP_OK;
+}
+
+int hlsmap_map_get_monotone(const hlsmap_map *map, uint8_t *flags)
+{
+    if (!map || !flags) return fail(HLSMAP_ERR_INVALID, "null argument");
+    if (map->n_tracks) memcpy(flags, map->h_monotone.data(), (size_t)map->n_tracks);
+    return HLSMAP_OK;
+}
+
+int hlsmap_map_set_path(hlsmap_map *map, int path)
+{
+    if (!map) return fail(HLSMAP_ERR_INVALID, "null map");
+    if (path != HLSMAP_PATH_AUTO && path != HLSMAP_PATH_SEARCH && path != HLSMAP_PATH_FILTER)
+        return fail(HLSMAP_ERR_INVALID, "unknown path");
+    if (path == HLSMAP_PATH_SEARCH && !map->info.all_monotone)
+        return fail(HLSMAP_ERR_INVALID,
+                    "search path refused: a start column is not sorted / NaN-free, only the "
+                    "filter kernel is exact for this map");
+    map->path = path;
+    return HLSMAP_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+//  getSegmentList
+// ---------------------------------------------------------------------------------------
+int hlsmap_get_segment_list_dev(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
+                                const int32_t *d_level, const double *d_begin,
+                                const double *d_duration, int32_t *d_offsets, int32_t *d_sn_out,
+                                double *d_time_out, int64_t hit_capacity, uint8_t *d_status,
+                                void *stream, hlsmap_result *result)
+{
+    if (!map) return fail(HLSMAP_ERR_INVALID, "null map");
+    hlsmap_ctx *ctx = map->ctx;
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (nq < 0 || !d_offsets || (nq > 0 && (!d_level || !d_begin || !d_duration)))
+        return fail(HLSMAP_ERR_INVALID, "get_segment_list: null query/offset arrays");
+    if ((d_sn_out == nullptr) != (d_time_out == nullptr))
+        return fail(HLSMAP_ERR_INVALID, "get_segment_list: sn_out and time_out go together");
+    if (hit_capacity < 0) return fail(HLSMAP_ERR_INVALID, "negative hit capacity");
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    const int path = pick_path(map);
+    ctx->last_path = path;
+    ctx->last_launches = 0;
+    ctx->have_last = true;
+
+    if (nq == 0) {
+        CK(cudaMemsetAsync(d_offsets, 0, sizeof(int32_t), s));
+        CK(cudaMemsetAsync(ctx->d_result, 0, sizeof(DeviceResult), s));
+        if (result) return fetch_result(ctx, s, result);
+        return HLSMAP_OK;
+    }
+
+    const int tile_q = path == HLSMAP_PATH_SEARCH ? kSearchTileQueries : kFilterTileQueries;
+    const int64_t n_tiles = (nq + tile_q - 1) / tile_q;
+    if (n_tiles > 0x7fffffff) return fail(HLSMAP_ERR_INVALID, "batch too large: split it");
+    r = prepare_scan(ctx, n_tiles, s);
+    if (r) return r;
+
+    ResolveParams p{};
+    p.desc = map->d_desc;
+    p.playlist_base = map->d_playlist_base;
+    p.n_playlists = map->n_playlists;
+    p.start = map->d_start;
+    p.sn = map->d_sn;
+    p.n_frag_padded = map->n_frag_padded;
+    p.nq = nq;
+    p.q_playlist = d_playlist;
+    p.q_level = d_level;
+    p.q_begin = d_begin;
+    p.q_duration = d_duration;
+    p.offsets = d_offsets;
+    p.sn_out = d_sn_out;
+    p.time_out = d_time_out;
+    p.capacity = d_sn_out ? hit_capacity : 0;
+    p.status = d_status;
+    p.tile_status = ctx->tile_status;
+    p.ctr = ctx->ctr;
+    p.result = ctx->d_result;
+    p.epoch = ctx->epoch;
+    p.n_tiles = (int)n_tiles;
+    p.stage_elems = map->stage_elems;
+    p.stage_all = map->info.stage_all;
+    p.vec_ok = al16(d_level) && al16(d_begin) && al16(d_duration) && al16(d_offsets) &&
+               (!d_playlist || al16(d_playlist)) &&
+               (!d_status || (reinterpret_cast<uintptr_t>(d_status) & 3u) == 0);
+
+    if (path == HLSMAP_PATH_SEARCH) {
+        const int grid = (int)(n_tiles < map->grid_search ? n_tiles : map->grid_search);
+        CK(launch_resolve_search(p, grid, map->stage_smem, s));
+    } else {
+        const int grid = (int)(n_tiles < map->grid_filter ? n_tiles : map->grid_filter);
+        CK(launch_resolve_filter(p, grid, s));
+    }
+    ctx->last_launches = 1;
+
+    if (result) {
+        r = fetch_result(ctx, s, result);
+        if (r) return r;
+        if (d_sn_out && result->total_hits > hit_capacity)
+            return fail(HLSMAP_ERR_CAPACITY, "hit buffers too small: need " +
+                                                 std::to_string(result->total_hits) + " entries");
+    }
+    return HLSMAP_OK;
+}
+
+int hlsmap_ctx_last_result(hlsmap_ctx *ctx, void *stream, hlsmap_result *result)
+{
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (!result) return fail(HLSMAP_ERR_INVALID, "null result");
+    if (!ctx->have_last) return fail(HLSMAP_ERR_INVALID, "no batch has been issued");
+    return fetch_result(ctx, stream ? (cudaStream_t)stream : ctx->stream, result);
+}
+
+int hlsmap_get_segment_list(hlsmap_map *map, int64_t nq, const int32_t *playlist,
+                            const int32_t *level, const double *begin, const double *duration,
+                            int32_t *offsets, int32_t *sn_out, double *time_out,
+                            int64_t hit_capacity, uint8_t *status, hlsmap_result *result)
+{
+    if (!map) return fail(HLSMAP_ERR_INVALID, "null map");
+    hlsmap_ctx *ctx = map->ctx;
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (nq < 0 || !offsets || (nq > 0 && (!level || !begin || !duration)))
+        return fail(HLSMAP_ERR_INVALID, "get_segment_list: null query/offset arrays");
+    if ((sn_out == nullptr) != (time_out == nullptr))
+        return fail(HLSMAP_ERR_INVALID, "get_segment_list: sn_out and time_out go together");
+    cudaStream_t s = ctx->stream;
+    const bool fill = sn_out != nullptr;
+
+    int *d_pl = nullptr, *d_lv = nullptr, *d_off = nullptr, *d_sn = nullptr;
+    double *d_bg = nullptr, *d_du = nullptr, *d_tm = nullptr;
+    uint8_t *d_st = nullptr;
+    void *v;
+    const int64_t n1 = nq > 0 ? nq : 1;
+    if (playlist) { if ((r = ensure_slot(ctx, 0, n1 * 4, &v))) return r; d_pl = (int *)v; }
+    if ((r = ensure_slot(ctx, 1, n1 * 4, &v))) return r; d_lv = (int *)v;
+    if ((r = ensure_slot(ctx, 2, n1 * 8, &v))) return r; d_bg = (double *)v;
+    if ((r = ensure_slot(ctx, 3, n1 * 8, &v))) return r; d_du = (double *)v;
+    if ((r = ensure_slot(ctx, 4, (n1 + 1) * 4, &v))) return r; d_off = (int *)v;
+    if (status) { if ((r = ensure_slot(ctx, 5, n1, &v))) return r; d_st = (uint8_t *)v; }
+    if (nq) {
+        if (playlist) CK(cudaMemcpyAsync(d_pl, playlist, (size_t)nq * 4, cudaMemcpyHostToDevice, s));
+        CK(cudaMemcpyAsync(d_lv, level, (size_t)nq * 4, cudaMemcpyHostToDevice, s));
+        CK(cudaMemcpyAsync(d_bg, begin, (size_t)nq * 8, cudaMemcpyHostToDevice, s));
+        CK(cudaMemcpyAsync(d_du, duration, (size_t)nq * 8, cudaMemcpyHostToDevice, s));
+    }
+
+    hlsmap_result res{};
+    int launches = 0;
+    int64_t dev_cap = 0;
+    if (fill) {
+        // device hit buffers: grow-only; first guess 8 hits per query, bounded by the caller
+        dev_cap = ctx->slot_bytes[6] / 4 < ctx->slot_bytes[7] / 8 ? ctx->slot_bytes[6] / 4
+                                                                 : ctx->slot_bytes[7] / 8;
+        int64_t want = nq * 8 + 1024;
+        if (want > hit_capacity) want = hit_capacity;
+        if (dev_cap < want) dev_cap = want;
+        if (dev_cap > hit_capacity) dev_cap = hit_capacity;
+        if ((r = ensure_slot(ctx, 6, dev_cap * 4, &v))) return r; d_sn = (int *)v;
+        if ((r = ensure_slot(ctx, 7, dev_cap * 8, &v))) return r; d_tm = (double *)v;
+    }
+    r = hlsmap_get_segment_list_dev(map, nq, d_pl, d_lv, d_bg, d_du, d_off, d_sn, d_tm, dev_cap,
+                                    d_st, s, &res);
+    launches += ctx->last_launches;
+    if (r == HLSMAP_ERR_CAPACITY && res.total_hits <= hit_capacity) {
+        // the guess was too small but the caller's buffers are not: grow and rerun
+        dev_cap = res.total_hits;
+        if ((r = ensure_slot(ctx, 6, dev_cap * 4, &v))) return r; d_sn = (int *)v;
+        if ((r = ensure_slot(ctx, 7, dev_cap * 8, &v))) return r; d_tm = (double *)v;
+        r = hlsmap_get_segment_list_dev(map, nq, d_pl, d_lv, d_bg, d_du, d_off, d_sn, d_tm,
+                                        dev_cap, d_st, s, &res);
+        launches += ctx->last_launches;
+    }
+    res.kernel_launches = launches;
+    ctx->last_launches = launches;
+    if (result) *result = res;
+    if (r != HLSMAP_OK && r != HLSMAP_ERR_CAPACITY) return r;
+
+    CK(cudaMemcpyAsync(offsets, d_off, (size_t)(nq + 1) * 4, cudaMemcpyDeviceToHost, s));
+    if (status && nq) CK(cudaMemcpyAsync(status, d_st, (size_t)nq, cudaMemcpyDeviceToHost, s));
+    const bool fits = fill && res.total_hits <= hit_capacity;
+    if (fits && res.total_hits > 0) {
+        CK(cudaMemcpyAsync(sn_out, d_sn, (size_t)res.total_hits * 4, cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(time_out, d_tm, (size_t)res.total_hits * 8, cudaMemcpyDeviceToHost, s));
+    }
+    CK(cudaStreamSynchronize(s));
+    if (fill && !fits)
+        return fail(HLSMAP_ERR_CAPACITY, "hit buffers too small: need " +
+                                             std::to_string(res.total_hits) + " entries");
+    return HLSMAP_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+//  range form
+// ---------------------------------------------------------------------------------------
+int hlsmap_get_segment_range_dev(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
+                                 const int32_t *d_level, const double *d_begin,
+                                 const double *d_duration, int32_t *d_first, int32_t *d_count,
+                                 uint8_t *d_status, void *stream)
+{
+    if (!map) return fail(HLSMAP_ERR_INVALID, "null map");
+    hlsmap_ctx *ctx = map->ctx;
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (nq < 0 || (nq > 0 && (!d_level || !d_begin || !d_duration || !d_first || !d_count)))
+        return fail(HLSMAP_ERR_INVALID, "get_segment_range: null arrays");
+    if (nq == 0) return HLSMAP_OK;
+    RangeParams p{};
+    p.desc = map->d_desc;
+    p.playlist_base = map->d_playlist_base;
+    p.n_playlists = map->n_playlists;
+    p.start = map->d_start;
+    p.nq = nq;
+    p.q_playlist = d_playlist;
+    p.q_level = d_level;
+    p.q_begin = d_begin;
+    p.q_duration = d_duration;
+    p.first = d_first;
+    p.count = d_count;
+    p.status = d_status;
+    CK(launch_range(p, stream ? (cudaStream_t)stream : ctx->stream));
+    ctx->last_launches = 1;
+    return HLSMAP_OK;
+}
+
+int hlsmap_get_segment_range(hlsmap_map *map, int64_t nq, const int32_t *playlist,
+                             const int32_t *level, const double *begin, const double *duration,
+                             int32_t *first, int32_t *count, uint8_t *status)
+{
+    if (!map) return fail(HLSMAP_ERR_INVALID, "null map");
+    hlsmap_ctx *ctx = map->ctx;
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (nq < 0 || (nq > 0 && (!level || !begin || !duration || !first || !count)))
+        return fail(HLSMAP_ERR_INVALID, "get_segment_range: null arrays");
+    if (nq == 0) return HLSMAP_OK;
+    cudaStream_t s = ctx->stream;
+    void *v;
+    int *d_pl = nullptr, *d_lv, *d_first, *d_count;
+    double *d_bg, *d_du;
+    uint8_t *d_st = nullptr;
+    if (playlist) { if ((r = ensure_slot(ctx, 0, nq * 4, &v))) return r; d_pl = (int *)v; }
+    if ((r = ensure_slot(ctx, 1, nq * 4, &v))) return r; d_lv = (int *)v;
+    if ((r = ensure_slot(ctx, 2, nq * 8, &v))) return r; d_bg = (double *)v;
+    if ((r = ensure_slot(ctx, 3, nq * 8, &v))) return r; d_du = (double *)v;
+    if ((r = ensure_slot(ctx, 4, nq * 4, &v))) return r; d_first = (int *)v;
+    if ((r = ensure_slot(ctx, 6, nq * 4, &v))) return r; d_count = (int *)v;
+    if (status) { if ((r = ensure_slot(ctx, 5, nq, &v))) return r; d_st = (uint8_t *)v; }
+    if (playlist) CK(cudaMemcpyAsync(d_pl, playlist, (size_t)nq * 4, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d_lv, level, (size_t)nq * 4, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d_bg, begin, (size_t)nq * 8, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d_du, duration, (size_t)nq * 8, cudaMemcpyHostToDevice, s));
+    r = hlsmap_get_segment_range_dev(map, nq, d_pl, d_lv, d_bg, d_du, d_first, d_count, d_st, s);
+    if (r) return r;
+    CK(cudaMemcpyAsync(first, d_first, (size_t)nq * 4, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(count, d_count, (size_t)nq * 4, cudaMemcpyDeviceToHost, s));
+    if (status) CK(cudaMemcpyAsync(status, d_st, (size_t)nq, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return HLSMAP_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+//  getSegmentDuration / getTrackList
+// ---------------------------------------------------------------------------------------
+int hlsmap_get_segment_duration_dev(hlsmap_map *map, int64_t n, const int32_t *d_playlist,
+                                    const int32_t *d_level, double *d_out, uint8_t *d_status,
+                                    void *stream)
+{
+    if (!map) return fail(HLSMAP_ERR_INVALID, "null map");
+    hlsmap_ctx *ctx = map->ctx;
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (n < 0 || (n > 0 && (!d_level || !d_out)))
+        return fail(HLSMAP_ERR_INVALID, "get_segment_duration: null arrays");
+    if (n == 0) return HLSMAP_OK;
+    CK(launch_segment_duration(map->d_desc, map->d_playlist_base, map->n_playlists, map->d_dur0, n,
+                               d_playlist, d_level, d_out, d_status,
+                               stream ? (cudaStream_t)stream : ctx->stream));
+    ctx->last_launches = 1;
+    return HLSMAP_OK;
+}
+
+int hlsmap_get_segment_duration(hlsmap_map *map, int64_t n, const int32_t *playlist,
+                                const int32_t *level, double *out, uint8_t *status)
+{
+    if (!map) return fail(HLSMAP_ERR_INVALID, "null map");
+    hlsmap_ctx *ctx = map->ctx;
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (n < 0 || (n > 0 && (!level || !out)))
+        return fail(HLSMAP_ERR_INVALID, "get_segment_duration: null arrays");
+    if (n == 0) return HLSMAP_OK;
+    cudaStream_t s = ctx->stream;
+    void *v;
+    int *d_pl = nullptr, *d_lv;
+    double *d_out;
+    uint8_t *d_st = nullptr;
+    if (playlist) { if ((r = ensure_slot(ctx, 0, n * 4, &v))) return r; d_pl = (int *)v; }
+    if ((r = ensure_slot(ctx, 1, n * 4, &v))) return r; d_lv = (int *)v;
+    if ((r = ensure_slot(ctx, 2, n * 8, &v))) return r; d_out = (double *)v;
+    if (status) { if ((r = ensure_slot(ctx, 5, n, &v))) return r; d_st = (uint8_t *)v; }
+    if (playlist) CK(cudaMemcpyAsync(d_pl, playlist, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d_lv, level, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+    r = hlsmap_get_segment_duration_dev(map, n, d_pl, d_lv, d_out, d_st, s);
+    if (r) return r;
+    CK(cudaMemcpyAsync(out, d_out, (size_t)n * 8, cudaMemcpyDeviceToHost, s));
+    if (status) CK(cudaMemcpyAsync(status, d_st, (size_t)n, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return HLSMAP_OK;
+}
+
+int hlsmap_get_track_list(const hlsmap_map *map, int32_t playlist, int32_t *level_out,
+                          int32_t *url_id_out, int64_t capacity, int64_t *n_out)
+{
+    if (!map || !n_out) return fail(HLSMAP_ERR_INVALID, "null argument");
+    if (playlist < 0 || playlist >= map->n_playlists)
+        return fail(HLSMAP_ERR_INVALID, "playlist out of range");
+    if ((level_out == nullptr) != (url_id_out == nullptr))
+        return fail(HLSMAP_ERR_INVALID, "level_out and url_id_out go together");
+    const int32_t b = map->h_playlist_base[playlist], e = map->h_playlist_base[playlist + 1];
+    int64_t k = 0;
+    for (int32_t t = b; t < e; t++)              // for i in levels          (media-map.js:66)
+        for (int32_t j = 0; j < map->h_url_count[t]; j++) {  // for j in level.url (:68)
+            if (level_out && k < capacity) {
+                level_out[k] = t - b;
+                url_id_out[k] = j;
+            }
+            k++;
+        }
+    *n_out = k;
+    if (level_out && k > capacity) return fail(HLSMAP_ERR_CAPACITY, "track list buffers too small");
+    return HLSMAP_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+//  views
+// ---------------------------------------------------------------------------------------
+#define VIEW_PRELUDE(cond)                                                     \
+    int r = use_ctx(ctx);                                                      \
+    if (r) return r;                                                           \
+    if (n < 0 || (n > 0 && !(cond))) return fail(HLSMAP_ERR_INVALID, "null view arrays"); \
+    if (n == 0) return HLSMAP_OK;                                              \
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;              \
+    ctx->last_launches = 1;
+
+int hlsmap_view_pack_dev(hlsmap_ctx *ctx, int64_t n, const int32_t *d_level,
+                         const int32_t *d_url_id, const int32_t *d_sn, uint32_t *d_wire,
+                         void *stream)
+{
+    VIEW_PRELUDE(d_level && d_url_id && d_sn && d_wire)
+    CK(launch_view_pack(n, d_level, d_url_id, d_sn, d_wire, s));
+    return HLSMAP_OK;
+}
+
+int hlsmap_view_unpack_dev(hlsmap_ctx *ctx, int64_t n, const uint32_t *d_wire, uint32_t *d_level,
+                           uint32_t *d_url_id, uint32_t *d_sn, void *stream)
+{
+    VIEW_PRELUDE(d_level && d_url_id && d_sn && d_wire)
+    CK(launch_view_unpack(n, d_wire, d_level, d_url_id, d_sn, s));
+    return HLSMAP_OK;
+}
+
+int hlsmap_view_is_equal_dev(hlsmap_ctx *ctx, int64_t n, const int32_t *al, const int32_t *au,
+                             const int32_t *as, const int32_t *bl, const int32_t *bu,
+                             const int32_t *bs, uint8_t *d_out, void *stream)
+{
+    VIEW_PRELUDE(al && au && as && bl && bu && bs && d_out)
+    CK(launch_view_is_equal(n, al, au, as, bl, bu, bs, d_out, s));
+    return HLSMAP_OK;
+}
+
+int hlsmap_view_is_in_track_dev(hlsmap_ctx *ctx, int64_t n, const int32_t *d_level,
+                                const int32_t *d_url_id, const int32_t *d_t_level,
+                                const int32_t *d_t_url_id, uint8_t *d_out, void *stream)
+{
+    VIEW_PRELUDE(d_level && d_url_id && d_t_level && d_t_url_id && d_out)
+    CK(launch_view_is_in_track(n, d_level, d_url_id, d_t_level, d_t_url_id, d_out, s));
+    return HLSMAP_OK;
+}
+
+int hlsmap_view_roundtrip_dev(hlsmap_ctx *ctx, int64_t n, const int32_t *d_level,
+                              const int32_t *d_url_id, const int32_t *d_sn, uint32_t *d_wire,
+                              uint8_t *d_equal, void *stream)
+{
+    VIEW_PRELUDE(d_level && d_url_id && d_sn && d_wire && d_equal)
+    CK(launch_view_roundtrip(n, d_level, d_url_id, d_sn, d_wire, d_equal, s));
+    return HLSMAP_OK;
+}
+
+int hlsmap_view_format_dev(hlsmap_ctx *ctx, int64_t n, const int32_t *d_level,
+                           const int32_t *d_url_id, const int32_t *d_sn, int with_sn,
+                           int32_t *d_offsets, char *d_chars, int64_t capacity, void *stream,
+                           int64_t *total_out)
+{
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (n < 0 || !d_offsets || capacity < 0 ||
+        (n > 0 && (!d_level || !d_url_id || (with_sn && !d_sn) || (capacity > 0 && !d_chars))))
+        return fail(HLSMAP_ERR_INVALID, "view_format: null arrays");
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    ctx->have_last = true;
+    ctx->last_path = 0;
+    ctx->last_launches = 0;
+    if (n == 0) {
+        CK(cudaMemsetAsync(d_offsets, 0, sizeof(int32_t), s));
+        if (total_out) *total_out = 0;
+        return HLSMAP_OK;
+    }
+    const int64_t n_tiles = (n + kFormatTileViews - 1) / kFormatTileViews;
+    if (n_tiles > 0x7fffffff) return fail(HLSMAP_ERR_INVALID, "batch too large: split it");
+    r = prepare_scan(ctx, n_tiles, s);
+    if (r) return r;
+    FormatParams p{};
+    p.n = n;
+    p.level = d_level;
+    p.url_id = d_url_id;
+    p.sn = d_sn;
+    p.with_sn = with_sn ? 1 : 0;
+    p.offsets = d_offsets;
+    p.chars = d_chars;
+    p.capacity = capacity;
+    p.tile_status = ctx->tile_status;
+    p.ctr = ctx->ctr;
+    p.result = ctx->d_result;
+    p.epoch = ctx->epoch;
+    p.n_tiles = (int)n_tiles;
+    const int maxg = view_format_max_grid();
+    CK(launch_view_format(p, (int)(n_tiles < maxg ? n_tiles : maxg), s));
+    ctx->last_launches = 1;
+    if (total_out) {
+        hlsmap_result res{};
+        r = fetch_result(ctx, s, &res);
+        if (r) return r;
+        *total_out = res.total_hits;
+        if (res.total_hits > capacity)
+            return fail(HLSMAP_ERR_CAPACITY, "character buffer too small: need " +
+                                                 std::to_string(res.total_hits) + " bytes");
+    }
+    return HLSMAP_OK;
+}
+
+// ---- host-pointer view variants: copy in, run the kernel, copy out -----------------------
+namespace {
+struct Cols {
+    const void *h;
+    int64_t bytes;
+    void *d;
+};
+int stage_in(hlsmap_ctx *ctx, Cols *c, int n, int first_slot)
+{
+    for (int i = 0; i < n; i++) {
+        int r = ensure_slot(ctx, first_slot + i, c[i].bytes, &c[i].d);
+        if (r) return r;
+        if (c[i].h) CK(cudaMemcpyAsync(c[i].d, c[i].h, (size_t)c[i].bytes, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    return HLSMAP_OK;
+}
+}  // namespace
+
+int hlsmap_view_pack(hlsmap_ctx *ctx, int64_t n, const int32_t *level, const int32_t *url_id,
+                     const int32_t *sn, uint32_t *wire)
+{
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (n < 0 || (n > 0 && !(level && url_id && sn && wire)))
+        return fail(HLSMAP_ERR_INVALID, "null view arrays");
+    if (n == 0) return HLSMAP_OK;
+    Cols c[4] = {{level, n * 4, nullptr}, {url_id, n * 4, nullptr}, {sn, n * 4, nullptr},
+                 {nullptr, n * 12, nullptr}};
+    if ((r = stage_in(ctx, c, 4, 0))) return r;
+    r = hlsmap_view_pack_dev(ctx, n, (int *)c[0].d, (int *)c[1].d, (int *)c[2].d, (uint32_t *)c[3].d,
+                             ctx->stream);
+    if (r) return r;
+    CK(cudaMemcpyAsync(wire, c[3].d, (size_t)n * 12, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return HLSMAP_OK;
+}
+
+int hlsmap_view_unpack(hlsmap_ctx *ctx, int64_t n, const uint32_t *wire, uint32_t *level,
+                       uint32_t *url_id, uint32_t *sn)
+{
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (n < 0 || (n > 0 && !(level && url_id && sn && wire)))
+        return fail(HLSMAP_ERR_INVALID, "null view arrays");
+    if (n == 0) return HLSMAP_OK;
+    Cols c[4] = {{wire, n * 12, nullptr}, {nullptr, n * 4, nullptr}, {nullptr, n * 4, nullptr},
+                 {nullptr, n * 4, nullptr}};
+    if ((r = stage_in(ctx, c, 4, 0))) return r;
+    r = hlsmap_view_unpack_dev(ctx, n, (uint32_t *)c[0].d, (uint32_t *)c[1].d, (uint32_t *)c[2].d,
+                               (uint32_t *)c[3].d, ctx->stream);
+    if (r) return r;
+    CK(cudaMemcpyAsync(level, c[1].d, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(url_id, c[2].d, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(sn, c[3].d, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return HLSMAP_OK;
+}
+
+int hlsmap_view_is_equal(hlsmap_ctx *ctx, int64_t n, const int32_t *a_level,
+                         const int32_t *a_url_id, const int32_t *a_sn, const int32_t *b_level,
+                         const int32_t *b_url_id, const int32_t *b_sn, uint8_t *out)
+{
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (n < 0 || (n > 0 && !(a_level && a_url_id && a_sn && b_level && b_url_id && b_sn && out)))
+        return fail(HLSMAP_ERR_INVALID, "null view arrays");
+    if (n == 0) return HLSMAP_OK;
+    Cols c[7] = {{a_level, n * 4, nullptr}, {a_url_id, n * 4, nullptr}, {a_sn, n * 4, nullptr},
+                 {b_level, n * 4, nullptr}, {b_url_id, n * 4, nullptr}, {b_sn, n * 4, nullptr},
+                 {nullptr, n, nullptr}};
+    if ((r = stage_in(ctx, c, 7, 0))) return r;
+    r = hlsmap_view_is_equal_dev(ctx, n, (int *)c[0].d, (int *)c[1].d, (int *)c[2].d, (int *)c[3].d,
+                                 (int *)c[4].d, (int *)c[5].d, (uint8_t *)c[6].d, ctx->stream);
+    if (r) return r;
+    CK(cudaMemcpyAsync(out, c[6].d, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return HLSMAP_OK;
+}
+
+int hlsmap_view_is_in_track(hlsmap_ctx *ctx, int64_t n, const int32_t *level,
+                            const int32_t *url_id, const int32_t *t_level,
+                            const int32_t *t_url_id, uint8_t *out)
+{
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (n < 0 || (n > 0 && !(level && url_id && t_level && t_url_id && out)))
+        return fail(HLSMAP_ERR_INVALID, "null view arrays");
+    if (n == 0) return HLSMAP_OK;
+    Cols c[5] = {{level, n * 4, nullptr}, {url_id, n * 4, nullptr}, {t_level, n * 4, nullptr},
+                 {t_url_id, n * 4, nullptr}, {nullptr, n, nullptr}};
+    if ((r = stage_in(ctx, c, 5, 0))) return r;
+    r = hlsmap_view_is_in_track_dev(ctx, n, (int *)c[0].d, (int *)c[1].d, (int *)c[2].d,
+                                    (int *)c[3].d, (uint8_t *)c[4].d, ctx->stream);
+    if (r) return r;
+    CK(cudaMemcpyAsync(out, c[4].d, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return HLSMAP_OK;
+}
+
+int hlsmap_view_roundtrip(hlsmap_ctx *ctx, int64_t n, const int32_t *level,
+                          const int32_t *url_id, const int32_t *sn, uint32_t *wire,
+                          uint8_t *equal)
+{
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (n < 0 || (n > 0 && !(level && url_id && sn && wire && equal)))
+        return fail(HLSMAP_ERR_INVALID, "null view arrays");
+    if (n == 0) return HLSMAP_OK;
+    Cols c[5] = {{level, n * 4, nullptr}, {url_id, n * 4, nullptr}, {sn, n * 4, nullptr},
+                 {nullptr, n * 12, nullptr}, {nullptr, n, nullptr}};
+    if ((r = stage_in(ctx, c, 5, 0))) return r;
+    r = hlsmap_view_roundtrip_dev(ctx, n, (int *)c[0].d, (int *)c[1].d, (int *)c[2].d,
+                                  (uint32_t *)c[3].d, (uint8_t *)c[4].d, ctx->stream);
+    if (r) return r;
+    CK(cudaMemcpyAsync(wire, c[3].d, (size_t)n * 12, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(equal, c[4].d, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return HLSMAP_OK;
+}
+
+int hlsmap_view_format(hlsmap_ctx *ctx, int64_t n, const int32_t *level, const int32_t *url_id,
+                       const int32_t *sn, int with_sn, int32_t *offsets, char *chars,
+                       int64_t capacity, int64_t *total_out)
+{
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (n < 0 || !offsets || capacity < 0 ||
+        (n > 0 && (!level || !url_id || (with_sn && !sn) || (capacity > 0 && !chars))))
+        return fail(HLSMAP_ERR_INVALID, "view_format: null arrays");
+    const int64_t n1 = n > 0 ? n : 1;
+    Cols c[5] = {{level, n1 * 4, nullptr}, {url_id, n1 * 4, nullptr},
+                 {with_sn ? sn : nullptr, n1 * 4, nullptr}, {nullptr, (n1 + 1) * 4, nullptr},
+                 {nullptr, capacity > 0 ? capacity : 16, nullptr}};
+    if (n == 0) c[0].h = c[1].h = c[2].h = nullptr;
+    if ((r = stage_in(ctx, c, 5, 0))) return r;
+    int64_t total = 0;
+    r = hlsmap_view_format_dev(ctx, n, (int *)c[0].d, (int *)c[1].d, (int *)c[2].d, with_sn,
+                               (int *)c[3].d, (char *)c[4].d, capacity, ctx->stream, &total);
+    if (total_out) *total_out = total;
+    if (r != HLSMAP_OK && r != HLSMAP_ERR_CAPACITY) return r;
+    CK(cudaMemcpyAsync(offsets, c[3].d, (size_t)(n + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (r == HLSMAP_OK && total > 0)
+        CK(cudaMemcpyAsync(chars, c[4].d, (size_t)total, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return r;
+}
+
+}  // extern "C"

@@ -1,0 +1,144 @@
+// common.cuh -- shared declarations of libhlsmap (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "hlsmap.h"
+
+namespace hlsmap {
+
+// One fragment table = one (playlist, level).  16 bytes so a query fetches it with a
+// single LDG.128.  flags: bits 0-1 = HLSMAP_TRACK_*, bit 2 = start column is monotone
+// non-decreasing and NaN-free (established on the GPU at upload).
+struct __align__(16) TrackDesc {
+    long long off;   // first fragment in the start[] / sn[] columns
+    int len;         // fragments in this track
+    unsigned flags;
+};
+constexpr unsigned kTrackStateMask = 3u;
+constexpr unsigned kTrackMonotone = 4u;
+
+// Per-context scratch header for the single-pass scan kernels.  ticket[] is double
+// buffered by launch parity so that late ticket fetches of launch e never see the reset
+// done for launch e+1.
+struct ScanCounters {
+    unsigned int ticket[2];
+    unsigned int done;
+    unsigned int pad;
+    unsigned long long n_unparsed;
+    unsigned long long n_missing;
+};
+
+// What the last tile of a batch leaves behind for the host.
+struct DeviceResult {
+    long long total_hits;
+    long long n_unparsed;
+    long long n_missing;
+    long long overflow;  // 1 if the running hit count passed INT32_MAX
+};
+
+// Tile status word of the decoupled look-back: [epoch:22][state:2][value:40].
+constexpr unsigned long long kStateAggregate = 1ull;
+constexpr unsigned long long kStatePrefix = 2ull;
+constexpr int kValueBits = 40;
+constexpr unsigned kEpochMask = (1u << 22) - 1u;
+
+__host__ __device__ inline unsigned long long make_status(unsigned epoch, unsigned long long state,
+                                                          unsigned long long value)
+{
+    return ((unsigned long long)(epoch & kEpochMask) << 42) | (state << kValueBits) |
+           (value & ((1ull << kValueBits) - 1ull));
+}
+
+struct ResolveParams {
+    // tables
+    const TrackDesc *desc;
+    const int *playlist_base;
+    int n_playlists;
+    const double *start;
+    const int *sn;
+    long long n_frag_padded;  // elements readable in start[] (multiple of 4)
+    // queries
+    long long nq;
+    const int *q_playlist;  // nullable
+    const int *q_level;
+    const double *q_begin;
+    const double *q_duration;
+    // outputs
+    int *offsets;           // [nq+1]
+    int *sn_out;            // nullable (count only)
+    double *time_out;
+    long long capacity;
+    unsigned char *status;  // nullable
+    // scratch
+    unsigned long long *tile_status;
+    ScanCounters *ctr;
+    DeviceResult *result;
+    unsigned epoch;
+    int n_tiles;
+    // staging
+    int stage_elems;  // capacity of the shared-memory copy of start[], in doubles
+    int stage_all;    // the whole column fits: stage once per CTA
+    int vec_ok;       // query/offset pointers are 16-byte aligned
+};
+
+struct RangeParams {
+    const TrackDesc *desc;
+    const int *playlist_base;
+    int n_playlists;
+    const double *start;
+    long long nq;
+    const int *q_playlist;
+    const int *q_level;
+    const double *q_begin;
+    const double *q_duration;
+    int *first;
+    int *count;
+    unsigned char *status;
+};
+
+// launchers (resolve.cu)
+cudaError_t launch_resolve_search(const ResolveParams &p, int grid, size_t smem, cudaStream_t s);
+cudaError_t launch_resolve_filter(const ResolveParams &p, int grid, cudaStream_t s);
+cudaError_t launch_range(const RangeParams &p, cudaStream_t s);
+cudaError_t launch_monotone_check(const double *start, TrackDesc *desc, int n_tracks,
+                                  cudaStream_t s);
+cudaError_t launch_segment_duration(const TrackDesc *desc, const int *playlist_base,
+                                    int n_playlists, const double *dur0, long long n,
+                                    const int *q_playlist, const int *q_level, double *out,
+                                    unsigned char *status, cudaStream_t s);
+int resolve_search_max_grid(size_t smem);
+int resolve_filter_max_grid();
+constexpr int kSearchTileQueries = 1024;  // 256 threads x 4 queries
+constexpr int kFilterTileQueries = 256;   // 8 warps x 32 queries
+
+// launchers (views.cu)
+struct FormatParams {
+    long long n;
+    const int *level, *url_id, *sn;
+    int with_sn;
+    int *offsets;
+    char *chars;
+    long long capacity;
+    unsigned long long *tile_status;
+    ScanCounters *ctr;
+    DeviceResult *result;
+    unsigned epoch;
+    int n_tiles;
+};
+constexpr int kFormatTileViews = 1024;
+cudaError_t launch_view_pack(long long n, const int *level, const int *url_id, const int *sn,
+                             unsigned *wire, cudaStream_t s);
+cudaError_t launch_view_unpack(long long n, const unsigned *wire, unsigned *level,
+                               unsigned *url_id, unsigned *sn, cudaStream_t s);
+cudaError_t launch_view_is_equal(long long n, const int *al, const int *au, const int *as,
+                                 const int *bl, const int *bu, const int *bs, unsigned char *out,
+                                 cudaStream_t s);
+cudaError_t launch_view_is_in_track(long long n, const int *al, const int *au, const int *tl,
+                                    const int *tu, unsigned char *out, cudaStream_t s);
+cudaError_t launch_view_roundtrip(long long n, const int *level, const int *url_id, const int *sn,
+                                  unsigned *wire, unsigned char *equal, cudaStream_t s);
+cudaError_t launch_view_format(const FormatParams &p, int grid, cudaStream_t s);
+int view_format_max_grid();
+
+}  // namespace hlsmap

@@ -1,0 +1,135 @@
+// scan.cuh -- persistent-tile scheduling and a CTA-wide decoupled look-back.
+//
+// Variable-length output (hits per query, characters per view) needs an exclusive prefix
+// over tiles.  All tiles of a batch are processed by ONE kernel: a tile publishes its
+// aggregate, then the whole CTA (not one warp) inspects up to THREADS predecessors at
+// once, so a batch of ~1000 simultaneously running tiles resolves in <= 4 L2 round trips
+// instead of a 30-deep chain of 32-wide windows.  Status words carry the launch epoch,
+// so no clearing pass runs between launches.
+#pragma once
+#include "common.cuh"
+
+namespace hlsmap {
+
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long *p)
+{
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(unsigned long long *p, unsigned long long v)
+{
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+template <int THREADS>
+struct TileScan {
+    static constexpr int NW = THREADS / 32;
+    struct Smem {
+        int tile;
+        int warp_first[NW];
+        unsigned long long warp_sum[NW];
+    };
+
+    // Tickets hand out tiles in order, so every predecessor of a tile is already owned
+    // by a running CTA (forward progress of the look-back does not depend on blockIdx).
+    __device__ static int next_tile(Smem &s, ScanCounters *ctr, unsigned epoch)
+    {
+        __syncthreads();  // previous tile fully consumed (shared buffers, s.tile)
+        if (threadIdx.x == 0) s.tile = (int)atomicAdd(&ctr->ticket[epoch & 1u], 1u);
+        __syncthreads();
+        return s.tile;
+    }
+
+    // CTA-wide sum of a per-thread value; result valid in every thread.
+    __device__ static unsigned long long block_sum(Smem &s, unsigned long long v)
+    {
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+        __syncthreads();
+        if (lane == 0) s.warp_sum[warp] = v;
+        __syncthreads();
+        unsigned long long t = 0;
+#pragma unroll
+        for (int w = 0; w < NW; w++) t += s.warp_sum[w];
+        return t;
+    }
+
+    // Publishes `aggregate` for `tile` and returns the sum of the aggregates of all
+    // earlier tiles.  Must be called by every thread of the CTA.
+    __device__ static unsigned long long exclusive_prefix(Smem &s, unsigned long long *status,
+                                                          unsigned epoch, int tile,
+                                                          unsigned long long aggregate)
+    {
+        const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+        if (tile == 0) {
+            if (tid == 0) st_relaxed_u64(&status[0], make_status(epoch, kStatePrefix, aggregate));
+            return 0ull;
+        }
+        if (tid == 0) st_relaxed_u64(&status[tile], make_status(epoch, kStateAggregate, aggregate));
+
+        unsigned long long running = 0;
+        int top = tile - 1;
+        for (;;) {
+            const int idx = top - tid;
+            unsigned long long val = 0;
+            bool is_prefix = true;  // idx < 0: the virtual tile -1 holds prefix 0
+            if (idx >= 0) {
+                unsigned long long w;
+                do {
+                    w = ld_relaxed_u64(&status[idx]);
+                } while ((unsigned)(w >> 42) != (epoch & kEpochMask));
+                val = w & ((1ull << kValueBits) - 1ull);
+                is_prefix = ((w >> kValueBits) & 3ull) == kStatePrefix;
+            }
+            const unsigned ball = __ballot_sync(0xffffffffu, is_prefix);
+            __syncthreads();  // s.warp_first / s.warp_sum free for reuse
+            if (lane == 0) s.warp_first[warp] = ball ? warp * 32 + (__ffs(ball) - 1) : 0x7fffffff;
+            __syncthreads();
+            int first = 0x7fffffff;
+#pragma unroll
+            for (int w = 0; w < NW; w++) first = min(first, s.warp_first[w]);
+            unsigned long long c = (tid <= first) ? val : 0ull;
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
+            if (lane == 0) s.warp_sum[warp] = c;
+            __syncthreads();
+#pragma unroll
+            for (int w = 0; w < NW; w++) running += s.warp_sum[w];
+            if (first != 0x7fffffff) break;
+            top -= THREADS;
+        }
+        if (tid == 0)
+            st_relaxed_u64(&status[tile], make_status(epoch, kStatePrefix, running + aggregate));
+        return running;
+    }
+
+    // Call once per finished tile, after its global writes.  Returns true in thread 0 of
+    // exactly one CTA: the one that finished the batch's last outstanding tile.
+    __device__ static bool tile_done(ScanCounters *ctr, int n_tiles)
+    {
+        __syncthreads();
+        if (threadIdx.x != 0) return false;
+        __threadfence();
+        const unsigned old = atomicAdd(&ctr->done, 1u);
+        if (old != (unsigned)(n_tiles - 1)) return false;
+        __threadfence();
+        return true;
+    }
+
+    // Run by the thread tile_done() elected: hand the counters to the host-visible
+    // result and re-arm the scratch header for the next launch.
+    __device__ static void finish_batch(ScanCounters *ctr, DeviceResult *result, unsigned epoch)
+    {
+        result->n_unparsed = (long long)atomicAdd(&ctr->n_unparsed, 0ull);
+        result->n_missing = (long long)atomicAdd(&ctr->n_missing, 0ull);
+        ctr->n_unparsed = 0ull;
+        ctr->n_missing = 0ull;
+        ctr->done = 0u;
+        ctr->ticket[(epoch + 1u) & 1u] = 0u;  // untouched by this launch's late fetches
+        __threadfence();
+    }
+};
+
+}  // namespace hlsmap

@@ -1,0 +1,102 @@
+"""Sharding by playlist across GPUs: a query touches exactly one
+playlist's one level (media-map.js:28,41), playlists share nothing, so each GPU holds a
+contiguous playlist range and the only cross-GPU step is a host-side gather.  No NCCL.
+
+`plan` / `split` / `merge` are pure host logic (tested on CPU with gloo, world_size 2);
+`ShardedMap` drives one Context per GPU from one process with a thread per GPU.
+"""
+import threading
+
+import numpy as np
+
+from .tables import FragmentTables, QueryBatch
+
+
+def plan(tables: FragmentTables, queries: QueryBatch, n_shards: int):
+    """Contiguous playlist ranges balanced by bytes moved: 12 B per fragment of the shard's
+    tables + 76 B per query.  Returns playlist boundaries, length n_shards+1."""
+    p = tables.n_playlists
+    frag_per_pl = np.diff(tables.track_off[tables.playlist_base].astype(np.int64))
+    inb = (queries.playlist >= 0) & (queries.playlist < p)
+    q_per_pl = np.bincount(queries.playlist[inb], minlength=p)[:p]
+    w = 12.0 * frag_per_pl + 76.0 * q_per_pl + 1e-9
+    c = np.concatenate([[0.0], np.cumsum(w)])
+    targets = c[-1] * np.arange(1, n_shards) / n_shards
+    cuts = np.searchsorted(c, targets, side="left")
+    bounds = np.concatenate([[0], cuts, [p]]).astype(np.int64)
+    return np.maximum.accumulate(bounds)
+
+
+def split(tables: FragmentTables, queries: QueryBatch, bounds):
+    """-> (shards, order): shards[i] = (tables_i, queries_i) with playlist ids re-based;
+    `order` is the permutation that groups the original queries shard by shard.  Queries on
+    playlists outside [0, P) go to shard 0 (they resolve to 'missing' there too)."""
+    n = len(bounds) - 1
+    pl = queries.playlist.astype(np.int64)
+    shard_of = np.clip(np.searchsorted(bounds, pl, side="right") - 1, 0, n - 1)
+    outside = (pl < 0) | (pl >= tables.n_playlists)
+    shard_of[outside] = 0
+    order = np.argsort(shard_of, kind="stable")
+    counts = np.bincount(shard_of, minlength=n)
+    starts = np.concatenate([[0], np.cumsum(counts)])
+    shards = []
+    for i in range(n):
+        idx = order[starts[i]:starts[i + 1]]
+        p0, p1 = int(bounds[i]), int(bounds[i + 1])
+        lp = pl[idx] - p0
+        if i == 0:
+            lp = np.where(outside[idx], -1, lp)
+        q = QueryBatch(lp.astype(np.int32), queries.level[idx].copy(), queries.begin[idx].copy(),
+                       queries.duration[idx].copy())
+        shards.append((tables.slice_playlists(p0, p1), q))
+    return shards, order
+
+
+def merge(results, order):
+    """Host-side gather: per-shard list-form results (offsets, status, sn, time) back into
+    the original query order."""
+    counts = np.concatenate([np.diff(r[0]).astype(np.int64) for r in results])
+    status = np.concatenate([r[1] for r in results])
+    sn = np.concatenate([r[2] for r in results])
+    tm = np.concatenate([r[3] for r in results])
+    nq = len(order)
+    inv = np.empty(nq, np.int64)
+    inv[order] = np.arange(nq)
+    src_off = np.concatenate([[0], np.cumsum(counts)])
+    out_counts = counts[inv]
+    out_off = np.concatenate([[0], np.cumsum(out_counts)])
+    # gather each query's run of hits
+    take = np.repeat(src_off[:-1][inv] - out_off[:-1], out_counts) + np.arange(out_off[-1])
+    return out_off, status[inv], sn[take], tm[take]
+
+
+class ShardedMap:
+    """Tables of many playlists spread over several GPUs of one box, one Context each."""
+
+    def __init__(self, contexts, tables: FragmentTables, queries_hint: QueryBatch = None):
+        self.contexts = list(contexts)
+        hint = queries_hint or QueryBatch(np.zeros(0, np.int32), np.zeros(0, np.int32),
+                                          np.zeros(0), np.zeros(0))
+        self.bounds = plan(tables, hint, len(self.contexts))
+        self.tables = tables
+        self.maps = [c.upload(tables.slice_playlists(int(self.bounds[i]), int(self.bounds[i + 1])))
+                     for i, c in enumerate(self.contexts)]
+
+    def get_segment_list(self, queries: QueryBatch):
+        shards, order = split(self.tables, queries, self.bounds)
+        out = [None] * len(self.maps)
+
+        def work(i):
+            q = shards[i][1]
+            r = self.maps[i].get_segment_list(q.playlist, q.level, q.begin, q.duration)
+            out[i] = (r.offsets.astype(np.int64), r.status, r.sn, r.time)
+        threads = [threading.Thread(target=work, args=(i,)) for i in range(len(self.maps))]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        return merge(out, order)
+
+    def close(self):
+        for m in self.maps:
+            m.close()

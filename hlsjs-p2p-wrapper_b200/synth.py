@@ -1,0 +1,215 @@
+"""Synthetic playlists and query batches for the BASELINE.json configs.
+
+One integer-only 32-bit generator (mulberry32: imul, shifts, xors) drives everything, so
+the same streams can be regenerated in JavaScript (`Math.imul`, `>>> 0`) and C.  All
+doubles are dyadic rationals (ticks of 1/1024 s), so every `start` column -- a running sum
+of durations -- is exact in fp64 whatever the summation order.  Reference data shape:
+`hls.levels[l].details.fragments[i] = {sn, start, duration}` (media-map.js:41-48).
+"""
+import numpy as np
+
+from .tables import FragmentTables, QueryBatch, TRACK_PARSED
+
+TICK = 1024  # ticks per second
+_M32 = np.uint64(0xFFFFFFFF)
+
+
+def _imul(a, b):
+    return (a * b) & _M32
+
+
+class Mulberry32:
+    """Vectorised mulberry32; `u32(n)` returns the next n outputs of the JS generator."""
+
+    def __init__(self, seed):
+        self.a = np.uint64(seed & 0xFFFFFFFF)
+
+    def u32(self, n):
+        k = np.arange(1, n + 1, dtype=np.uint64)
+        a = (self.a + k * np.uint64(0x6D2B79F5)) & _M32
+        self.a = np.uint64((int(self.a) + n * 0x6D2B79F5) & 0xFFFFFFFF)
+        t = _imul(a ^ (a >> np.uint64(15)), a | np.uint64(1))
+        t = ((t + _imul(t ^ (t >> np.uint64(7)), t | np.uint64(61))) & _M32) ^ t
+        return (t ^ (t >> np.uint64(14))) & _M32          # uint64 holding u32 values
+
+    def below(self, n, bound):
+        """n integers uniform in [0, bound) (modulo bias is irrelevant here)."""
+        return self.u32(n) % np.uint64(bound)
+
+
+def _stream(seed, k):
+    return Mulberry32((seed * 0x9E3779B1 + k * 0x85EBCA6B + 0x1234567) & 0xFFFFFFFF)
+
+
+def _vod_tracks(rng, lens):
+    """Durations uniform in {2 .. 10 s} in 1/1024 s steps; start = running sum from 0."""
+    lens = np.asarray(lens, np.int64)
+    off = np.zeros(len(lens) + 1, np.int64)
+    np.cumsum(lens, out=off[1:])
+    nf = int(off[-1])
+    dur_t = (2 * TICK + rng.below(nf, 8 * TICK + 1)).astype(np.int64)   # ticks
+    csum = np.cumsum(dur_t)
+    excl = csum - dur_t                                      # running sum before fragment i
+    first = np.minimum(off[:-1], max(nf - 1, 0))
+    track_base = excl[first] if nf else np.zeros(len(lens), np.int64)
+    start_t = excl - np.repeat(track_base, lens)             # restart at 0 per track
+    total_t = np.zeros(len(lens), np.int64)
+    nz = lens > 0
+    total_t[nz] = csum[off[1:][nz] - 1] - track_base[nz]
+    sn = (np.arange(nf, dtype=np.int64) - np.repeat(off[:-1], lens)).astype(np.int32)
+    return off, start_t.astype(np.float64) / TICK, sn, dur_t.astype(np.float64) / TICK, total_t
+
+
+def _adversarial(rng, n, tables, track, begin, dur):
+    """Edge queries: exact boundary hits, rounding sums, negatives, NaN, Inf, -0."""
+    kind = rng.below(n, 10).astype(np.int64)
+    pick = rng.u32(n).astype(np.int64)
+    off = tables.track_off
+    for i in range(n):
+        t = int(track[i])
+        o, ln = int(off[t]), int(off[t + 1] - off[t])
+        s = tables.start[o + pick[i] % ln] if ln else 0.0
+        k = int(kind[i])
+        if k == 0:      # begin == a start exactly
+            begin[i], dur[i] = s, 30.0
+        elif k == 1:    # begin + duration == a start exactly
+            begin[i], dur[i] = s - 30.0, 30.0
+        elif k == 2:    # a sum that rounds (0.1 + 0.2 style operands are not dyadic)
+            begin[i], dur[i] = s - 0.3, 0.1 + 0.2
+        elif k == 3:    # negative duration -> empty
+            begin[i], dur[i] = s, -1.0
+        elif k == 4:
+            begin[i], dur[i] = float("nan"), 30.0
+        elif k == 5:
+            begin[i], dur[i] = s, float("nan")
+        elif k == 6:
+            begin[i], dur[i] = s, float("inf")
+        elif k == 7:    # -Inf + Inf = NaN upper bound
+            begin[i], dur[i] = float("-inf"), float("inf")
+        elif k == 8:
+            begin[i], dur[i] = -0.0, s
+        else:
+            begin[i], dur[i] = float("-inf"), 1e308
+
+
+def _queries(rng, tables, playlist, level, total_t, adversarial=True):
+    """Query mix of SURVEY 8(d) config 2 for already chosen (playlist, level) pairs."""
+    n = len(level)
+    track = tables.playlist_base[playlist].astype(np.int64) + level
+    tt = total_t[track].astype(np.uint64)
+    span = tt + tt // np.uint64(10)                                  # 110 % of the timeline
+    begin_t = ((rng.u32(n) * span) >> np.uint64(32)).astype(np.int64) - (tt // np.uint64(20)).astype(np.int64)
+    begin = begin_t.astype(np.float64) / TICK
+    mix = rng.below(n, 100).astype(np.int64)
+    r = rng.u32(n)
+    look = (30 * TICK - TICK + (r % np.uint64(2 * TICK + 1)).astype(np.int64)).astype(np.float64) / TICK
+    wide = (r % np.uint64(300 * TICK + 1)).astype(np.float64) / TICK
+    dur = np.where(mix < 70, look, np.where(mix < 90, wide, 0.0))
+    if adversarial:
+        idx = np.nonzero(mix >= 95)[0]
+        if len(idx):
+            b, d = begin[idx].copy(), dur[idx].copy()
+            _adversarial(rng, len(idx), tables, track[idx], b, d)
+            begin[idx], dur[idx] = b, d
+    return QueryBatch(playlist.astype(np.int32), level.astype(np.int32), begin, dur)
+
+
+def config2(seed=2, n_levels=3, n_frag=1000, n_queries=1_000_000, adversarial=True):
+    """VOD playlist, 3 levels x 1k fragments, 10^6 random queries (BASELINE.json configs[1])."""
+    rng = _stream(seed, 0)
+    off, start, sn, dur, total_t = _vod_tracks(rng, [n_frag] * n_levels)
+    tables = FragmentTables(
+        np.asarray([0, n_levels], np.int32), off, np.full(n_levels, TRACK_PARSED, np.uint8),
+        np.full(n_levels, 2, np.int32), start, sn, dur).validate()
+    q = _stream(seed, 1)
+    level = q.below(n_queries, n_levels).astype(np.int64)
+    playlist = np.zeros(n_queries, np.int64)
+    return tables, _queries(q, tables, playlist, level, total_t, adversarial)
+
+
+def config3(seed=3, n_players=100_000, n_levels=3, window=6):
+    """Live sliding windows: sn offset uniform in [0, 2^31 - 7), 6-fragment window.  Per
+    player one query over the whole window and one over the next 30 s."""
+    rng = _stream(seed, 0)
+    nt = n_players * n_levels
+    nf = nt * window
+    target = np.asarray([2, 4, 6, 10], np.int64)[rng.below(n_players, 4).astype(np.int64)] * TICK
+    sn0 = rng.below(n_players, (1 << 31) - 7).astype(np.int64)
+    t0 = rng.below(n_players, 86400 * TICK).astype(np.int64)
+    jitter = rng.below(nf, TICK // 2 + 1).astype(np.int64) - TICK // 4
+    i = np.tile(np.arange(window, dtype=np.int64), nt)
+    per_track_target = np.repeat(target, n_levels * window)
+    start_t = np.repeat(t0, n_levels * window) + i * per_track_target + jitter
+    sn = (np.repeat(sn0, n_levels * window) + i).astype(np.int32)
+    tables = FragmentTables(
+        (np.arange(n_players + 1, dtype=np.int64) * n_levels).astype(np.int32),
+        np.arange(nt + 1, dtype=np.int64) * window, np.full(nt, TRACK_PARSED, np.uint8),
+        np.full(nt, 1, np.int32), start_t.astype(np.float64) / TICK, sn,
+        per_track_target.astype(np.float64) / TICK).validate()
+    q = _stream(seed, 1)
+    playlist = np.repeat(np.arange(n_players, dtype=np.int64), 2)
+    level = np.repeat(q.below(n_players, n_levels).astype(np.int64), 2)
+    first = tables.start[(playlist * n_levels + level) * window]
+    begin = first.copy()
+    dur = np.empty(2 * n_players)
+    dur[0::2] = (target * window).astype(np.float64) / TICK + 1.0     # the whole window
+    dur[1::2] = 30.0                                                  # the next 30 s
+    begin[1::2] += (q.below(n_players, 20 * TICK).astype(np.float64) / TICK)
+    return tables, QueryBatch(playlist.astype(np.int32), level.astype(np.int32), begin, dur)
+
+
+def config4(seed=4, n_levels=8, n_frag=10_000, n_views=1_000_000, perturbed_pct=1):
+    """8 levels x 10k fragments; views drawn as getSegmentList hits (uniform level, index);
+    returns (tables, views dict, perturbed copy) for pack -> parse -> isEqual."""
+    rng = _stream(seed, 0)
+    off, start, sn, dur, _ = _vod_tracks(rng, [n_frag] * n_levels)
+    sn = sn + np.int32(1000)
+    tables = FragmentTables(
+        np.asarray([0, n_levels], np.int32), off, np.full(n_levels, TRACK_PARSED, np.uint8),
+        np.full(n_levels, 2, np.int32), start, sn, dur).validate()
+    q = _stream(seed, 1)
+    level = q.below(n_views, n_levels).astype(np.int64)
+    idx = q.below(n_views, n_frag).astype(np.int64)
+    url = q.below(n_views, 2).astype(np.int32)
+    views = {"level": level.astype(np.int32), "urlId": url, "sn": sn[off[level] + idx],
+             "time": start[off[level] + idx]}
+    other = {k: v.copy() for k, v in views.items()}
+    which = q.below(n_views, 100).astype(np.int64) < perturbed_pct
+    field = q.below(n_views, 3).astype(np.int64)
+    other["level"][which & (field == 0)] += 1
+    other["urlId"][which & (field == 1)] ^= 1
+    other["sn"][which & (field == 2)] += 1535
+    return tables, views, other
+
+
+def config5(seed=5, n_playlists=1_000_000, n_levels=3, queries_per_playlist=100,
+            adversarial=True):
+    """Many playlists, fragments per level piecewise log-uniform in [6, 1024], queries
+    grouped by playlist (BASELINE.json configs[4]; scale n_playlists down for tests)."""
+    rng = _stream(seed, 0)
+    nt = n_playlists * n_levels
+    octave = rng.below(nt, 8).astype(np.int64)
+    base = 6 << octave
+    lens = np.minimum(base + (rng.u32(nt).astype(np.int64) % base), 1024)
+    off, start, sn, dur, total_t = _vod_tracks(rng, lens)
+    tables = FragmentTables(
+        (np.arange(n_playlists + 1, dtype=np.int64) * n_levels).astype(np.int32), off,
+        np.full(nt, TRACK_PARSED, np.uint8), np.full(nt, 2, np.int32), start, sn, dur).validate()
+    q = _stream(seed, 1)
+    nq = n_playlists * queries_per_playlist
+    playlist = np.repeat(np.arange(n_playlists, dtype=np.int64), queries_per_playlist)
+    level = q.below(nq, n_levels).astype(np.int64)
+    return tables, _queries(q, tables, playlist, level, total_t, adversarial)
+
+
+def hls_mock_tables(level_number=3, defined_level=1, live=False):
+    """SoA form of the reference fixture HlsMock(levelNumber, live, definedLevel)
+    (test/mocks/hls.js:5-45): sn 25..199, start = 10*sn, no duration, 2 URLs per level."""
+    levels = []
+    frags = [{"sn": f, "start": f * 10} for f in range(25, 200)]
+    for i in range(level_number):
+        lvl = {"url": ["http://foo.bar/%d/0/playlist.m3u8" % i, "http://foo.bar/%d/1/playlist.m3u8" % i]}
+        if live is not None and i == defined_level:
+            lvl["details"] = {"live": live, "fragments": frags}
+        levels.append(lvl)
+    return FragmentTables.from_hls_levels([levels if level_number > 0 else None])

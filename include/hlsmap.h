@@ -1,0 +1,220 @@
+/*
+ * hlsmap.h -- C ABI of the B200-native MediaMap batch engine (libhlsmap.so).
+ *
+ * This is the drop-in boundary for ONE path of streamroot-hlsjs-p2p-wrapper: the
+ * MediaMap / SegmentView / TrackView mapping layer (lib/integration/mapping/*.js).  The
+ * reference has no FFI of its own (it is pure JavaScript); the entry points below are
+ * what an N-API addon bound under the reference's JS classes calls -- see
+ * INTEGRATION.md for that stub.  Every function cites the reference code it replaces
+ * (paths relative to the reference checkout).
+ *
+ * Conventions
+ *   - plain C types only; no exceptions cross the boundary;
+ *   - every function returns an int status: 0 = OK, negative = misuse / CUDA failure, and
+ *     hlsmap_last_error() then returns a thread-local message;
+ *   - per-query outcomes (level missing / not parsed yet) are DATA (HLSMAP_ST_*), not
+ *     errors: the JS binding turns them into the reference's throw / console.warn;
+ *   - `*_dev` variants take DEVICE pointers and a cudaStream_t (as void*) and do no
+ *     host<->device copies; the un-suffixed variants take HOST pointers, copy in and out,
+ *     and block until the result is in the caller's buffers;
+ *   - a context is bound to one GPU and used by one thread at a time; batches issued
+ *     through one context share its scratch memory and must not overlap on the GPU;
+ *   - there is no CPU fallback: without a usable CUDA device every call fails.
+ */
+#ifndef HLSMAP_H
+#define HLSMAP_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HLSMAP_OK 0
+#define HLSMAP_ERR_INVALID (-1)   /* bad argument */
+#define HLSMAP_ERR_CUDA (-2)      /* CUDA runtime failure (message has the detail) */
+#define HLSMAP_ERR_NOMEM (-3)
+#define HLSMAP_ERR_CAPACITY (-4)  /* hit buffers too small; result.total_hits = needed */
+#define HLSMAP_ERR_OVERFLOW (-5)  /* more than INT32_MAX hits in one batch: split it */
+
+/* per-query status */
+#define HLSMAP_ST_OK 0
+#define HLSMAP_ST_UNPARSED 1 /* level has no details: warn + [] (media-map.js:34-37) */
+#define HLSMAP_ST_MISSING 2  /* no such level: the reference throws (media-map.js:30-32) */
+#define HLSMAP_ST_EMPTY 3    /* getSegmentDuration on an empty list (media-map.js:86) */
+#define HLSMAP_ST_SCATTERED 4 /* range form only: hits are not one contiguous run */
+
+/* track_state values for hlsmap_map_create */
+#define HLSMAP_TRACK_MISSING 0  /* hls.levels[i] is falsy */
+#define HLSMAP_TRACK_UNPARSED 1 /* level.details is falsy */
+#define HLSMAP_TRACK_PARSED 2
+
+/* resolve kernel selection (hlsmap_map_set_path) */
+#define HLSMAP_PATH_AUTO 0
+#define HLSMAP_PATH_SEARCH 1 /* binary search; only legal when every track is monotone */
+#define HLSMAP_PATH_FILTER 2 /* the reference's linear filter, any table */
+
+typedef struct hlsmap_ctx hlsmap_ctx; /* one GPU: streams, scratch, staging buffers */
+typedef struct hlsmap_map hlsmap_map; /* uploaded fragment tables of many playlists */
+
+typedef struct hlsmap_result {
+    int64_t total_hits;      /* H: SegmentViews the batch produced */
+    int64_t n_unparsed;      /* queries with HLSMAP_ST_UNPARSED */
+    int64_t n_missing;       /* queries with HLSMAP_ST_MISSING  */
+    int32_t kernel_launches; /* CUDA kernels this call launched */
+    int32_t path;            /* HLSMAP_PATH_SEARCH or HLSMAP_PATH_FILTER actually run */
+} hlsmap_result;
+
+typedef struct hlsmap_map_info {
+    int32_t n_playlists;
+    int32_t n_tracks;
+    int64_t n_fragments;
+    int32_t n_monotone_tracks; /* parsed tracks whose start column is sorted and NaN-free */
+    int32_t n_parsed_tracks;
+    int32_t all_monotone;      /* 1 => the search kernel is exact for every track */
+    int32_t stage_all;         /* 1 => the whole start column is staged in shared memory */
+    int64_t device_bytes;      /* HBM held by this map */
+} hlsmap_map_info;
+
+/* ---- library / context ------------------------------------------------------------ */
+const char *hlsmap_last_error(void);
+int hlsmap_version(void);
+/* Number of CUDA devices visible, or a negative error. */
+int hlsmap_device_count(void);
+
+int hlsmap_ctx_create(int device, hlsmap_ctx **out);
+void hlsmap_ctx_destroy(hlsmap_ctx *ctx);
+int hlsmap_ctx_device(const hlsmap_ctx *ctx);
+/* Block until everything issued through the context's own stream has finished. */
+int hlsmap_ctx_synchronize(hlsmap_ctx *ctx);
+
+/* Pinned host memory for bindings that want zero-staging copies (N-API external
+ * ArrayBuffers, the Python test binding).  Optional: every host-pointer entry point also
+ * accepts pageable memory. */
+int hlsmap_host_alloc(hlsmap_ctx *ctx, int64_t bytes, void **out);
+int hlsmap_host_free(hlsmap_ctx *ctx, void *p);
+
+/* ---- table upload: `new MediaMap(hls)` (media-map.js:6-8) ------------------------- */
+/* The reference keeps a live reference to hls.levels; here the level tables of
+ * n_playlists players are copied to HBM as SoA columns (input shape: media-map.js:28,41,
+ * 43-48,61,66-69,82-84).
+ *   playlist_track_base[n_playlists+1]  first track of each playlist; a playlist's
+ *                                       `levels.length` is base[p+1]-base[p]
+ *   track_offset[n_tracks+1]            first fragment of each track (monotone, [0]=0)
+ *   track_state[n_tracks]               HLSMAP_TRACK_*
+ *   url_count[n_tracks]                 level.url.length (getTrackList), may be NULL (=1)
+ *   start[F], sn[F]                     fragment.start / fragment.sn in index order
+ *   duration[F]                         fragment.duration, may be NULL (then NaN)
+ * Monotonicity of every start column is established on the GPU at upload. */
+int hlsmap_map_create(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *playlist_track_base,
+                      int32_t n_tracks, const int64_t *track_offset, const uint8_t *track_state,
+                      const int32_t *url_count, const double *start, const int32_t *sn,
+                      const double *duration, hlsmap_map **out);
+void hlsmap_map_destroy(hlsmap_map *map);
+int hlsmap_map_get_info(const hlsmap_map *map, hlsmap_map_info *info);
+/* Per-track monotone flags (1/0), n_tracks bytes; what routed AUTO to search or filter. */
+int hlsmap_map_get_monotone(const hlsmap_map *map, uint8_t *flags);
+/* Force a kernel (tests, benchmarks).  SEARCH on a map that is not all-monotone fails. */
+int hlsmap_map_set_path(hlsmap_map *map, int path);
+
+/* ---- getSegmentList (media-map.js:27-54), batched ---------------------------------- */
+/* Query q = (playlist[q], level[q], begin[q], duration[q]); playlist may be NULL (all 0).
+ * `urlId` never takes part in the lookup (media-map.js:28) -- bindings echo it.
+ * List form: offsets[nq+1] is the exclusive prefix of hit counts (offsets[nq] = H); the
+ * hits of query q are sn_out/time_out[offsets[q] .. offsets[q+1]) in fragment index
+ * order: sn = fragment.sn (media-map.js:46), time = fragment.start bit-for-bit (:48).
+ * Keeps fragment i iff begin <= start[i] && start[i] <= fl(begin + duration) (:44).
+ * status (nullable) receives HLSMAP_ST_* per query.  If H > hit_capacity nothing beyond
+ * the capacity is written and HLSMAP_ERR_CAPACITY is returned with result->total_hits
+ * set (call again with larger buffers; sn_out/time_out may be NULL with capacity 0 to
+ * size them).  result may be NULL for the _dev variant: the call is then fully
+ * asynchronous and hlsmap_ctx_last_result() retrieves the counters later. */
+int hlsmap_get_segment_list_dev(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
+                                const int32_t *d_level, const double *d_begin,
+                                const double *d_duration, int32_t *d_offsets, int32_t *d_sn_out,
+                                double *d_time_out, int64_t hit_capacity, uint8_t *d_status,
+                                void *stream, hlsmap_result *result);
+int hlsmap_get_segment_list(hlsmap_map *map, int64_t nq, const int32_t *playlist,
+                            const int32_t *level, const double *begin, const double *duration,
+                            int32_t *offsets, int32_t *sn_out, double *time_out,
+                            int64_t hit_capacity, uint8_t *status, hlsmap_result *result);
+/* Counters of the most recent batch issued through ctx (synchronises its stream). */
+int hlsmap_ctx_last_result(hlsmap_ctx *ctx, void *stream, hlsmap_result *result);
+
+/* Range form: first[q] = index (within its track) of the first kept fragment or -1,
+ * count[q] = number kept.  Exact only where the kept fragments are contiguous: a
+ * non-monotone track yields HLSMAP_ST_SCATTERED with the true count and first hit. */
+int hlsmap_get_segment_range_dev(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
+                                 const int32_t *d_level, const double *d_begin,
+                                 const double *d_duration, int32_t *d_first, int32_t *d_count,
+                                 uint8_t *d_status, void *stream);
+int hlsmap_get_segment_range(hlsmap_map *map, int64_t nq, const int32_t *playlist,
+                             const int32_t *level, const double *begin, const double *duration,
+                             int32_t *first, int32_t *count, uint8_t *status);
+
+/* ---- getSegmentDuration (media-map.js:81-87), batched ------------------------------ */
+/* out[q] = duration of the FIRST fragment of the level, whatever the view's sn. */
+int hlsmap_get_segment_duration_dev(hlsmap_map *map, int64_t n, const int32_t *d_playlist,
+                                    const int32_t *d_level, double *d_out, uint8_t *d_status,
+                                    void *stream);
+int hlsmap_get_segment_duration(hlsmap_map *map, int64_t n, const int32_t *playlist,
+                                const int32_t *level, double *out, uint8_t *status);
+
+/* ---- getTrackList (media-map.js:60-73) --------------------------------------------- */
+/* Level-major, urlId-minor enumeration of one playlist's tracks.  Pass NULL outputs to
+ * get the count in *n_out.  Host-side: it enumerates upload metadata, no arithmetic. */
+int hlsmap_get_track_list(const hlsmap_map *map, int32_t playlist, int32_t *level_out,
+                          int32_t *url_id_out, int64_t capacity, int64_t *n_out);
+
+/* ---- SegmentView / TrackView value types over SoA columns -------------------------- */
+/* A view is (level, urlId, sn, time) (segment-view.js:22-26, track-view.js:3-6). */
+
+/* toArrayBuffer (segment-view.js:59-61): wire[3n] u32 = level, urlId, sn per view. */
+int hlsmap_view_pack_dev(hlsmap_ctx *ctx, int64_t n, const int32_t *d_level,
+                         const int32_t *d_url_id, const int32_t *d_sn, uint32_t *d_wire,
+                         void *stream);
+int hlsmap_view_pack(hlsmap_ctx *ctx, int64_t n, const int32_t *level, const int32_t *url_id,
+                     const int32_t *sn, uint32_t *wire);
+/* fromArrayBuffer (segment-view.js:9-17): the parsed fields are Numbers in [0, 2^32). */
+int hlsmap_view_unpack_dev(hlsmap_ctx *ctx, int64_t n, const uint32_t *d_wire, uint32_t *d_level,
+                           uint32_t *d_url_id, uint32_t *d_sn, void *stream);
+int hlsmap_view_unpack(hlsmap_ctx *ctx, int64_t n, const uint32_t *wire, uint32_t *level,
+                       uint32_t *url_id, uint32_t *sn);
+/* isEqual (segment-view.js:33-39, track-view.js:19-24): sn, level, urlId; not time. */
+int hlsmap_view_is_equal_dev(hlsmap_ctx *ctx, int64_t n, const int32_t *d_a_level,
+                             const int32_t *d_a_url_id, const int32_t *d_a_sn,
+                             const int32_t *d_b_level, const int32_t *d_b_url_id,
+                             const int32_t *d_b_sn, uint8_t *d_out, void *stream);
+int hlsmap_view_is_equal(hlsmap_ctx *ctx, int64_t n, const int32_t *a_level,
+                         const int32_t *a_url_id, const int32_t *a_sn, const int32_t *b_level,
+                         const int32_t *b_url_id, const int32_t *b_sn, uint8_t *out);
+/* isInTrack (segment-view.js:45-47) == TrackView.isEqual (track-view.js:19-24). */
+int hlsmap_view_is_in_track_dev(hlsmap_ctx *ctx, int64_t n, const int32_t *d_level,
+                                const int32_t *d_url_id, const int32_t *d_t_level,
+                                const int32_t *d_t_url_id, uint8_t *d_out, void *stream);
+int hlsmap_view_is_in_track(hlsmap_ctx *ctx, int64_t n, const int32_t *level,
+                            const int32_t *url_id, const int32_t *t_level,
+                            const int32_t *t_url_id, uint8_t *out);
+/* toArrayBuffer -> fromArrayBuffer -> isEqual(original) fused (test/segment-view.js:21-27):
+ * writes the 12-byte wire form and the equality flag (parse is done from registers). */
+int hlsmap_view_roundtrip_dev(hlsmap_ctx *ctx, int64_t n, const int32_t *d_level,
+                              const int32_t *d_url_id, const int32_t *d_sn, uint32_t *d_wire,
+                              uint8_t *d_equal, void *stream);
+int hlsmap_view_roundtrip(hlsmap_ctx *ctx, int64_t n, const int32_t *level,
+                          const int32_t *url_id, const int32_t *sn, uint32_t *wire,
+                          uint8_t *equal);
+/* viewToString (segment-view.js:52-54, track-view.js:11-13): "L{level}U{urlId}S{sn}"
+ * (with_sn = 0: the TrackView form "L{level}U{urlId}").  offsets[n+1] are byte offsets
+ * into chars; HLSMAP_ERR_CAPACITY (with *total_out = bytes needed) if it does not fit. */
+int hlsmap_view_format_dev(hlsmap_ctx *ctx, int64_t n, const int32_t *d_level,
+                           const int32_t *d_url_id, const int32_t *d_sn, int with_sn,
+                           int32_t *d_offsets, char *d_chars, int64_t capacity, void *stream,
+                           int64_t *total_out);
+int hlsmap_view_format(hlsmap_ctx *ctx, int64_t n, const int32_t *level, const int32_t *url_id,
+                       const int32_t *sn, int with_sn, int32_t *offsets, char *chars,
+                       int64_t capacity, int64_t *total_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HLSMAP_H */

@@ -1,0 +1,386 @@
+/*
+ * mediamap_oracle.c -- CPU restatement of the reference's MediaMap / SegmentView /
+ * TrackView path.  TEST INFRASTRUCTURE ONLY.
+ *
+ * This file is the checker, never the product: only tests/, __graft_entry__.smoke()
+ * and bench.py's cpu_baseline / --impl reference legs may load it.  The shipped path
+ * (libhlsmap.so) never links or calls anything here.
+ *
+ * Parity pin: the reference is JavaScript and no JS engine exists in the build
+ * container, so this restatement is pinned against the reference's own known-answer
+ * tests, transcribed as data in tests/golden/reference_vectors.json
+ * (test/media-map.js:8-137, test/segment-view.js:5-73, test/track-view.js:4-41, fixture
+ * test/mocks/hls.js:12-45).  Functions with no reference test (getSegmentDuration, the
+ * exact viewToString text) are restated from the source only and say so below.
+ *
+ * All `file:line` citations are relative to the reference checkout.
+ *
+ * Table model (unpadded SoA, the batch form of `hls.levels[..].details.fragments`,
+ * consumers media-map.js:28,41,43-48):
+ *   playlist_base[P+1]  first track index of each playlist; levels = base[p+1]-base[p]
+ *   track_off[T+1]      first fragment index of each track
+ *   track_state[T]      0 = level slot is empty (falsy), 1 = level has no `details`,
+ *                       2 = parsed
+ *   start[F], sn[F]     fragment.start (fp64) and fragment.sn (int32), index order
+ *   dur0[T]             duration of the track's first fragment (media-map.js:83-85)
+ */
+#include <math.h>
+#include <pthread.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define ST_OK 0
+#define ST_UNPARSED 1 /* media-map.js:34-37: warn + [] */
+#define ST_MISSING 2  /* media-map.js:30-32: throws "getSegmentList: level doesn't exist" */
+
+/* ---- getSegmentList, one query: the linear filter of media-map.js:42-51 ---------- */
+/* Keeps fragment i iff  beginTime <= start[i] && start[i] <= beginTime + duration
+ * (media-map.js:44), both ends inclusive, the sum rounded once to fp64 as JS does.
+ * `volatile` pins the sum to a real fp64 add (no x87 excess precision, no contraction).
+ * Output order is fragment index order.  sn_out/time_out may be NULL to only count. */
+int64_t oracle_filter_one(const double *start, const int32_t *sn, int64_t n, double begin,
+                          double duration, int32_t *sn_out, double *time_out)
+{
+    volatile double upper = begin + duration;
+    double ub = upper;
+    int64_t h = 0;
+    for (int64_t i = 0; i < n; i++) {
+        double s = start[i];
+        if (begin <= s && s <= ub) {
+            if (sn_out) sn_out[h] = sn[i];     /* media-map.js:46 */
+            if (time_out) time_out[h] = s;     /* media-map.js:48 */
+            h++;
+        }
+    }
+    return h;
+}
+
+/* Level lookup of media-map.js:28-37.  Returns the status and, when ST_OK, the track. */
+static int resolve_track(int32_t n_playlists, const int32_t *playlist_base,
+                         const uint8_t *track_state, int32_t playlist, int32_t level,
+                         int32_t *track)
+{
+    if (playlist < 0 || playlist >= n_playlists) return ST_MISSING;
+    int32_t b = playlist_base[playlist], e = playlist_base[playlist + 1];
+    if (level < 0 || level >= e - b) return ST_MISSING; /* levels[level] is undefined */
+    int32_t t = b + level;
+    if (track_state[t] == 0) return ST_MISSING;          /* falsy slot, :30 */
+    if (track_state[t] == 1) return ST_UNPARSED;         /* no details, :34 */
+    *track = t;
+    return ST_OK;
+}
+
+typedef struct {
+    int32_t n_playlists;
+    const int32_t *playlist_base;
+    const int64_t *track_off;
+    const uint8_t *track_state;
+    const double *start;
+    const int32_t *sn;
+    int64_t q0, q1;
+    const int32_t *playlist, *level;
+    const double *begin, *duration;
+    int64_t *offsets; /* pass 1: counts at [q+1]; pass 2: exclusive offsets */
+    uint8_t *status;
+    int32_t *sn_out;
+    double *time_out;
+    int64_t cap;
+    int pass;
+    uint64_t checksum;
+    int64_t hits;
+} job_t;
+
+static void *batch_worker(void *arg)
+{
+    job_t *j = (job_t *)arg;
+    for (int64_t q = j->q0; q < j->q1; q++) {
+        int32_t t = 0;
+        int st = resolve_track(j->n_playlists, j->playlist_base, j->track_state,
+                               j->playlist ? j->playlist[q] : 0, j->level[q], &t);
+        if (j->pass == 1) {
+            if (j->status) j->status[q] = (uint8_t)st;
+            int64_t c = 0;
+            if (st == ST_OK) {
+                int64_t o = j->track_off[t], n = j->track_off[t + 1] - o;
+                c = oracle_filter_one(j->start + o, j->sn + o, n, j->begin[q], j->duration[q],
+                                      NULL, NULL);
+            }
+            j->offsets[q + 1] = c;
+        } else if (st == ST_OK) {
+            int64_t o = j->track_off[t], n = j->track_off[t + 1] - o;
+            int64_t at = j->offsets[q], c = j->offsets[q + 1] - at;
+            if (c > 0 && at + c <= j->cap)
+                oracle_filter_one(j->start + o, j->sn + o, n, j->begin[q], j->duration[q],
+                                  j->sn_out + at, j->time_out + at);
+        }
+    }
+    return NULL;
+}
+
+static void run_threads(job_t *proto, int64_t n_queries, int threads)
+{
+    if (threads < 1) threads = 1;
+    if (threads > 256) threads = 256;
+    pthread_t tid[256];
+    job_t jobs[256];
+    for (int i = 0; i < threads; i++) {
+        jobs[i] = *proto;
+        jobs[i].q0 = n_queries * i / threads;
+        jobs[i].q1 = n_queries * (i + 1) / threads;
+        if (threads == 1) { batch_worker(&jobs[i]); return; }
+        pthread_create(&tid[i], NULL, batch_worker, &jobs[i]);
+    }
+    for (int i = 0; i < threads; i++) pthread_join(tid[i], NULL);
+}
+
+/* ---- getSegmentList, batched list form (media-map.js:27-54 per query) ------------ */
+/* offsets[Q+1] receives the exclusive prefix of hit counts (offsets[Q] = total hits);
+ * hits of query q land at [offsets[q], offsets[q+1]) of sn_out/time_out in fragment
+ * order.  Returns the total hit count; hits are only written when total <= cap. */
+int64_t oracle_get_segment_list_batch(int32_t n_playlists, const int32_t *playlist_base,
+                                      const int64_t *track_off, const uint8_t *track_state,
+                                      const double *start, const int32_t *sn, int64_t n_queries,
+                                      const int32_t *playlist, const int32_t *level,
+                                      const double *begin, const double *duration,
+                                      int64_t *offsets, uint8_t *status, int32_t *sn_out,
+                                      double *time_out, int64_t cap, int threads)
+{
+    job_t j;
+    memset(&j, 0, sizeof j);
+    j.n_playlists = n_playlists; j.playlist_base = playlist_base; j.track_off = track_off;
+    j.track_state = track_state; j.start = start; j.sn = sn;
+    j.playlist = playlist; j.level = level; j.begin = begin; j.duration = duration;
+    j.offsets = offsets; j.status = status; j.sn_out = sn_out; j.time_out = time_out;
+    j.cap = cap;
+    offsets[0] = 0;
+    j.pass = 1;
+    run_threads(&j, n_queries, threads);
+    for (int64_t q = 0; q < n_queries; q++) offsets[q + 1] += offsets[q];
+    int64_t total = offsets[n_queries];
+    if (sn_out && time_out && total <= cap) {
+        j.pass = 2;
+        run_threads(&j, n_queries, threads);
+    }
+    return total;
+}
+
+/* ---- range form helper: (first, count) of the filter on one query ---------------- */
+/* Only meaningful when the hits are contiguous (monotone table); `first` is the index
+ * of the first kept fragment or -1.  Used to check the CUDA range form. */
+void oracle_get_segment_range_batch(int32_t n_playlists, const int32_t *playlist_base,
+                                    const int64_t *track_off, const uint8_t *track_state,
+                                    const double *start, int64_t n_queries,
+                                    const int32_t *playlist, const int32_t *level,
+                                    const double *begin, const double *duration,
+                                    int32_t *first, int32_t *count, uint8_t *status)
+{
+    for (int64_t q = 0; q < n_queries; q++) {
+        int32_t t = 0;
+        int st = resolve_track(n_playlists, playlist_base, track_state,
+                               playlist ? playlist[q] : 0, level[q], &t);
+        if (status) status[q] = (uint8_t)st;
+        first[q] = -1; count[q] = 0;
+        if (st != ST_OK) continue;
+        int64_t o = track_off[t], n = track_off[t + 1] - o;
+        volatile double upper = begin[q] + duration[q];
+        double ub = upper;
+        int32_t c = 0;
+        for (int64_t i = 0; i < n; i++) {
+            double s = start[o + i];
+            if (begin[q] <= s && s <= ub) { if (!c) first[q] = (int32_t)i; c++; }
+        }
+        count[q] = c;
+    }
+}
+
+/* ---- the timed CPU baseline: what the reference does per call -------------------- */
+/* One pass per query, hits pushed onto a per-thread growable list exactly like
+ * `segmentList.push(new SegmentView(...))` (media-map.js:39-51), then folded into a
+ * checksum so the work cannot be elided.  Returns total hits; *checksum_out gets the
+ * xor/sum digest.  This is the "C restatement, not Node" baseline of BASELINE.md. */
+typedef struct { int32_t sn; int32_t level; int32_t url_id; double time; } view_t;
+
+static void *bench_worker(void *arg)
+{
+    job_t *j = (job_t *)arg;
+    size_t capv = 64;
+    view_t *list = (view_t *)malloc(capv * sizeof *list);
+    uint64_t cs = 0; int64_t hits = 0;
+    for (int64_t q = j->q0; q < j->q1; q++) {
+        int32_t t = 0;
+        int st = resolve_track(j->n_playlists, j->playlist_base, j->track_state,
+                               j->playlist ? j->playlist[q] : 0, j->level[q], &t);
+        if (st != ST_OK) continue;
+        int64_t o = j->track_off[t], n = j->track_off[t + 1] - o;
+        const double *s = j->start + o; const int32_t *snp = j->sn + o;
+        double b = j->begin[q];
+        volatile double upper = b + j->duration[q];
+        double ub = upper;
+        size_t len = 0;
+        for (int64_t i = 0; i < n; i++) {
+            if (b <= s[i] && s[i] <= ub) {
+                if (len == capv) { capv *= 2; list = (view_t *)realloc(list, capv * sizeof *list); }
+                list[len].sn = snp[i]; list[len].level = j->level[q]; list[len].url_id = 0;
+                list[len].time = s[i]; len++;
+            }
+        }
+        for (size_t k = 0; k < len; k++) {
+            uint64_t bits; memcpy(&bits, &list[k].time, 8);
+            cs += bits * 0x9E3779B97F4A7C15ull + (uint32_t)list[k].sn;
+        }
+        hits += (int64_t)len;
+    }
+    free(list);
+    j->checksum = cs; j->hits = hits;
+    return NULL;
+}
+
+int64_t oracle_bench_get_segment_list(int32_t n_playlists, const int32_t *playlist_base,
+                                      const int64_t *track_off, const uint8_t *track_state,
+                                      const double *start, const int32_t *sn, int64_t n_queries,
+                                      const int32_t *playlist, const int32_t *level,
+                                      const double *begin, const double *duration, int threads,
+                                      uint64_t *checksum_out)
+{
+    if (threads < 1) threads = 1;
+    if (threads > 256) threads = 256;
+    pthread_t tid[256];
+    job_t jobs[256];
+    for (int i = 0; i < threads; i++) {
+        memset(&jobs[i], 0, sizeof jobs[i]);
+        jobs[i].n_playlists = n_playlists; jobs[i].playlist_base = playlist_base;
+        jobs[i].track_off = track_off; jobs[i].track_state = track_state;
+        jobs[i].start = start; jobs[i].sn = sn; jobs[i].playlist = playlist;
+        jobs[i].level = level; jobs[i].begin = begin; jobs[i].duration = duration;
+        jobs[i].q0 = n_queries * i / threads; jobs[i].q1 = n_queries * (i + 1) / threads;
+        pthread_create(&tid[i], NULL, bench_worker, &jobs[i]);
+    }
+    uint64_t cs = 0; int64_t hits = 0;
+    for (int i = 0; i < threads; i++) {
+        pthread_join(tid[i], NULL);
+        cs += jobs[i].checksum; hits += jobs[i].hits;
+    }
+    if (checksum_out) *checksum_out = cs;
+    return hits;
+}
+
+/* ---- getSegmentDuration (media-map.js:81-87) -- no reference test, source only --- */
+/* Returns the FIRST fragment's duration of the view's level whatever the sn; status 3
+ * = empty fragment list (the reference throws 'All segments should have a duration'). */
+#define ST_EMPTY 3
+void oracle_get_segment_duration_batch(int32_t n_playlists, const int32_t *playlist_base,
+                                       const int64_t *track_off, const uint8_t *track_state,
+                                       const double *dur0, int64_t n, const int32_t *playlist,
+                                       const int32_t *level, double *out, uint8_t *status)
+{
+    for (int64_t q = 0; q < n; q++) {
+        int32_t t = 0;
+        int st = resolve_track(n_playlists, playlist_base, track_state,
+                               playlist ? playlist[q] : 0, level[q], &t);
+        out[q] = NAN;
+        if (st == ST_OK) {
+            if (track_off[t + 1] == track_off[t]) st = ST_EMPTY;
+            else out[q] = dur0[t];
+        }
+        status[q] = (uint8_t)st;
+    }
+}
+
+/* ---- getTrackList (media-map.js:60-73): level-major, urlId-minor ----------------- */
+int64_t oracle_get_track_list(int32_t n_levels, const int32_t *url_count, int32_t *level_out,
+                              int32_t *url_id_out)
+{
+    int64_t k = 0;
+    for (int32_t i = 0; i < n_levels; i++)
+        for (int32_t j = 0; j < url_count[i]; j++) {
+            if (level_out) { level_out[k] = i; url_id_out[k] = j; }
+            k++;
+        }
+    return k;
+}
+
+/* ---- SegmentView wire form (segment-view.js:59-61 / :9-17) ----------------------- */
+/* toArrayBuffer: Uint32Array([level, urlId, sn]) -> 12 bytes, ToUint32 on each value,
+ * little endian on every platform this runs on; `time` is dropped. */
+void oracle_view_pack(int64_t n, const int32_t *level, const int32_t *url_id, const int32_t *sn,
+                      uint32_t *wire)
+{
+    for (int64_t i = 0; i < n; i++) {
+        wire[3 * i + 0] = (uint32_t)level[i];
+        wire[3 * i + 1] = (uint32_t)url_id[i];
+        wire[3 * i + 2] = (uint32_t)sn[i];
+    }
+}
+
+/* fromArrayBuffer: the first three u32 -> {level, urlId, sn}; values are JS Numbers in
+ * [0, 2^32), hence uint32 outputs. */
+void oracle_view_unpack(int64_t n, const uint32_t *wire, uint32_t *level, uint32_t *url_id,
+                        uint32_t *sn)
+{
+    for (int64_t i = 0; i < n; i++) {
+        level[i] = wire[3 * i + 0];
+        url_id[i] = wire[3 * i + 1];
+        sn[i] = wire[3 * i + 2];
+    }
+}
+
+/* isEqual (segment-view.js:33-39 + track-view.js:19-24): sn, level, urlId strictly
+ * equal; `time` is not compared. */
+void oracle_view_is_equal(int64_t n, const int32_t *al, const int32_t *au, const int32_t *as,
+                          const int32_t *bl, const int32_t *bu, const int32_t *bs, uint8_t *out)
+{
+    for (int64_t i = 0; i < n; i++) out[i] = (as[i] == bs[i] && al[i] == bl[i] && au[i] == bu[i]);
+}
+
+/* isInTrack (segment-view.js:45-47): TrackView equality only. */
+void oracle_view_is_in_track(int64_t n, const int32_t *al, const int32_t *au, const int32_t *tl,
+                             const int32_t *tu, uint8_t *out)
+{
+    for (int64_t i = 0; i < n; i++) out[i] = (al[i] == tl[i] && au[i] == tu[i]);
+}
+
+/* pack -> wire -> parse -> isEqual against the original (test/segment-view.js:21-27).
+ * The parsed side holds Numbers in [0, 2^32) while the original holds int32 Numbers, so
+ * a negative field does not survive the trip -- compared here as 64-bit integers. */
+void oracle_view_roundtrip(int64_t n, const int32_t *level, const int32_t *url_id,
+                           const int32_t *sn, uint32_t *wire, uint8_t *equal)
+{
+    oracle_view_pack(n, level, url_id, sn, wire);
+    for (int64_t i = 0; i < n; i++) {
+        int64_t pl = wire[3 * i], pu = wire[3 * i + 1], ps = wire[3 * i + 2];
+        equal[i] = (ps == (int64_t)sn[i] && pl == (int64_t)level[i] && pu == (int64_t)url_id[i]);
+    }
+}
+
+/* viewToString (segment-view.js:52-54, track-view.js:11-13): "L{level}U{urlId}S{sn}",
+ * plain decimal with a leading '-' for negatives (JS Number->String on an int32).
+ * No reference test pins the text -- source only.  offsets[n+1] are byte offsets into
+ * `out`; returns the total length.  out may be NULL to size the buffer. */
+int64_t oracle_view_format(int64_t n, const int32_t *level, const int32_t *url_id,
+                           const int32_t *sn, int with_sn, int64_t *offsets, char *out)
+{
+    int64_t at = 0;
+    char tmp[48];
+    for (int64_t i = 0; i < n; i++) {
+        int len = with_sn ? snprintf(tmp, sizeof tmp, "L%dU%dS%d", level[i], url_id[i], sn[i])
+                          : snprintf(tmp, sizeof tmp, "L%dU%d", level[i], url_id[i]);
+        if (offsets) offsets[i] = at;
+        if (out) memcpy(out + at, tmp, (size_t)len);
+        at += len;
+    }
+    if (offsets) offsets[n] = at;
+    return at;
+}
+
+/* Upload-time check the CUDA side must agree with: is the filter a contiguous range?
+ * True iff start[] is NaN-free and non-decreasing (hard part 2). */
+int oracle_is_monotone(const double *start, int64_t n)
+{
+    for (int64_t i = 0; i < n; i++) {
+        if (start[i] != start[i]) return 0;
+        if (i && start[i] < start[i - 1]) return 0;
+    }
+    return 1;
+}

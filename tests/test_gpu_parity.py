@@ -1,0 +1,277 @@
+"""Bit-exact parity of the CUDA path (through the C ABI) against the CPU oracle on seeded
+synthetic inputs: counts, offsets, per-hit sn (int) and time (fp64 bit pattern) in order,
+statuses; both kernels (search / filter); edge cases; the BASELINE.json configs at sizes
+the oracle finishes in seconds, plus size-independent properties at full size."""
+import ctypes
+
+import numpy as np
+import pytest
+
+import oracle
+import hlsjs_p2p_wrapper_b200 as pk
+from hlsjs_p2p_wrapper_b200 import synth, _native as N
+from hlsjs_p2p_wrapper_b200.tables import FragmentTables, QueryBatch, TRACK_PARSED
+
+pytestmark = pytest.mark.gpu
+
+
+def oracle_list(t, q, threads=8):
+    return oracle.get_segment_list_batch(t.playlist_base, t.track_off, t.track_state, t.start, t.sn,
+                                         q.playlist, q.level, q.begin, q.duration, threads=threads)
+
+
+def assert_same(res, ref, what=""):
+    off, status, sn, tm = ref
+    assert res.total_hits == off[-1], what
+    assert np.array_equal(res.offsets.astype(np.int64), off), what
+    if res.status is not None:
+        assert np.array_equal(res.status, status), what
+    assert np.array_equal(res.sn, sn), what
+    assert np.array_equal(res.time.view(np.uint64), tm.view(np.uint64)), what   # bit patterns
+    assert res.n_unparsed == int((status == 1).sum()) and res.n_missing == int((status == 2).sum()), what
+
+
+def run_both_paths(ctx, t, q, paths=(N.PATH_SEARCH, N.PATH_FILTER)):
+    m = ctx.upload(t)
+    ref = oracle_list(t, q)
+    for path in paths:
+        m.set_path(path)
+        res = m.get_segment_list(q.playlist, q.level, q.begin, q.duration)
+        assert res.path == path and res.kernel_launches >= 1
+        assert_same(res, ref, "path %d" % path)
+    m.close()
+    return ref
+
+
+# ---- config 2: VOD, 3 levels x 1k fragments ------------------------------------------------
+@pytest.mark.parametrize("nq", [1, 3, 4, 31, 255, 1023, 1024, 1025, 4099, 100_000])
+def test_config2_sizes(ctx, nq):
+    t, q = synth.config2(seed=20 + nq % 7, n_queries=nq)
+    run_both_paths(ctx, t, q)
+
+
+def test_config2_full_size_search(ctx):
+    """BASELINE.json configs[1] at full size (10^6 queries), bit-exact against the oracle."""
+    t, q = synth.config2()
+    m = ctx.upload(t)
+    info = m.info()
+    assert info["all_monotone"] == 1 and info["stage_all"] == 1
+    res = m.get_segment_list(q.playlist, q.level, q.begin, q.duration)
+    assert res.path == N.PATH_SEARCH and res.kernel_launches == 1
+    assert_same(res, oracle_list(t, q))
+    # range form agrees with the list form
+    first, count, status = m.get_segment_range(q.playlist, q.level, q.begin, q.duration)
+    assert np.array_equal(count, np.diff(res.offsets))
+    rf, rc, rs = oracle.get_segment_range_batch(t.playlist_base, t.track_off, t.track_state, t.start,
+                                                q.playlist, q.level, q.begin, q.duration)
+    assert np.array_equal(first, rf) and np.array_equal(count, rc) and np.array_equal(status, rs)
+    m.close()
+
+
+def test_empty_batch_and_empty_map(ctx):
+    t, q = synth.config2(n_queries=16)
+    m = ctx.upload(t)
+    res = m.get_segment_list(q.playlist[:0], q.level[:0], q.begin[:0], q.duration[:0])
+    assert res.total_hits == 0 and list(res.offsets) == [0] and len(res.sn) == 0
+    m.close()
+    empty = FragmentTables.from_hls_levels([None, []])          # levels undefined / []
+    m = ctx.upload(empty)
+    res = m.get_segment_list([0, 1, 2, -1], [0, 0, 0, 0], [0.0] * 4, [1.0] * 4)
+    assert list(res.status) == [2, 2, 2, 2] and res.n_missing == 4 and res.total_hits == 0
+    m.close()
+
+
+def test_ragged_levels_and_states(ctx):
+    """Playlists with 0..4 levels, missing / unparsed / empty / one-fragment tracks."""
+    lv = lambda fr: {"url": ["a", "b"], "details": {"fragments": fr}}
+    f = lambda n, s0=0.0: [{"sn": 100 + i, "start": s0 + 2.5 * i, "duration": 2.5} for i in range(n)]
+    playlists = [
+        [lv(f(5)), {"url": ["a"]}, lv([]), lv(f(1, 7.0))],
+        None,
+        [],
+        [None, lv(f(40, -30.0))],
+        [lv(f(3))],
+    ]
+    t = FragmentTables.from_hls_levels(playlists)
+    rng = np.random.default_rng(5)
+    nq = 5000
+    q = QueryBatch(rng.integers(-1, 6, nq).astype(np.int32), rng.integers(-1, 5, nq).astype(np.int32),
+                   rng.integers(-40, 80, nq) / 4.0, rng.integers(-4, 60, nq) / 4.0)
+    ref = run_both_paths(ctx, t, q)
+    assert set(np.unique(ref[1])) == {0, 1, 2}
+    m = ctx.upload(t)
+    out, st = m.get_segment_duration(q.playlist, q.level)
+    eo, es = oracle.get_segment_duration_batch(t.playlist_base, t.track_off, t.track_state, t.dur0(),
+                                               q.playlist, q.level)
+    assert np.array_equal(st, es) and np.array_equal(out, eo, equal_nan=True)
+    assert set(np.unique(es)) == {0, 1, 2, 3}
+    for p in range(len(playlists)):
+        l, u = m.get_track_list(p)
+        b, e = t.playlist_base[p], t.playlist_base[p + 1]
+        el, eu = oracle.get_track_list(t.url_count[b:e])
+        assert np.array_equal(l, el) and np.array_equal(u, eu)
+    m.close()
+
+
+def test_special_values_on_monotone_table(ctx):
+    """NaN / +-Inf / -0 / duplicates / rounding sums as query operands and table entries."""
+    s = 0.1 + 0.2
+    start = np.array([-np.inf, -5.0, -0.0, 0.0, 0.0, 0.3, s, np.nextafter(s, 1), 7.0, 7.0, 7.0, 1e308, np.inf, np.inf])
+    t = FragmentTables(np.array([0, 1], np.int32), np.array([0, len(start)], np.int64),
+                       np.array([TRACK_PARSED], np.uint8), np.array([1], np.int32), start,
+                       np.arange(len(start), dtype=np.int32), np.full(len(start), 1.0))
+    vals = [np.nan, np.inf, -np.inf, 0.0, -0.0, 0.1, 0.2, 0.3, s, 7.0, -5.0, 1e308, -1e308, 5e-324, 1.7e308]
+    b, d = np.meshgrid(vals, vals)
+    q = QueryBatch(np.zeros(b.size, np.int32), np.zeros(b.size, np.int32), b.ravel().copy(), d.ravel().copy())
+    m = ctx.upload(t)
+    assert m.info()["all_monotone"] == 1
+    m.close()
+    run_both_paths(ctx, t, q)
+
+
+def test_non_monotone_tables_use_filter(ctx):
+    """Unsorted and NaN-bearing start columns: only the filter kernel is legal, AUTO picks it,
+    forcing the search path is refused, and results match the reference filter."""
+    rng = np.random.default_rng(11)
+    lens = [0, 1, 2, 33, 64, 65, 200, 1000]
+    cols, sns = [], []
+    for i, n in enumerate(lens):
+        c = rng.integers(0, 400, n) / 4.0
+        if i % 2 == 0 and n > 2:
+            c[rng.integers(0, n, max(1, n // 10))] = np.nan
+        if i == 6:
+            c = np.sort(c)                                      # one sorted track among them
+        cols.append(c)
+        sns.append(rng.integers(0, 1 << 30, n))
+    off = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    t = FragmentTables(np.array([0, 3, 8], np.int32), off, np.full(8, TRACK_PARSED, np.uint8),
+                       np.full(8, 1, np.int32), np.concatenate(cols), np.concatenate(sns).astype(np.int32),
+                       np.ones(int(off[-1])))
+    m = ctx.upload(t)
+    info = m.info()
+    flags = m.monotone_flags()
+    assert info["all_monotone"] == 0
+    assert list(flags) == [int(oracle.is_monotone(c)) for c in cols]
+    with pytest.raises(N.HlsMapError):
+        m.set_path(N.PATH_SEARCH)
+    nq = 20000
+    q = QueryBatch(rng.integers(0, 2, nq).astype(np.int32), rng.integers(0, 5, nq).astype(np.int32),
+                   rng.integers(-20, 420, nq) / 4.0, rng.integers(-8, 200, nq) / 4.0)
+    res = m.get_segment_list(q.playlist, q.level, q.begin, q.duration)
+    assert res.path == N.PATH_FILTER
+    assert_same(res, oracle_list(t, q))
+    first, count, status = m.get_segment_range(q.playlist, q.level, q.begin, q.duration)
+    assert np.array_equal(count, np.diff(res.offsets))
+    assert (status == N.ST_SCATTERED).any()
+    m.close()
+
+
+def test_capacity_contract(ctx):
+    t, q = synth.config2(n_queries=5000)
+    m = ctx.upload(t)
+    off, total = m.count_segments(q.playlist, q.level, q.begin, q.duration)
+    ref = oracle_list(t, q)
+    assert total == ref[0][-1] and np.array_equal(off.astype(np.int64), ref[0])
+    with pytest.raises(N.HlsMapError) as e:
+        m.get_segment_list(q.playlist, q.level, q.begin, q.duration, capacity=total - 1)
+    assert e.value.code == N.ERR_CAPACITY
+    res = m.get_segment_list(q.playlist, q.level, q.begin, q.duration, capacity=total)
+    assert_same(res, ref)
+    m.close()
+
+
+def test_repeated_launches_share_scratch(ctx):
+    """Back-to-back batches of different sizes through one context (epoch-tagged scratch)."""
+    t, q = synth.config2(n_queries=30000)
+    m = ctx.upload(t)
+    ref = oracle_list(t, q)
+    for n in (30000, 7, 2048, 30000, 1, 29999):
+        sub = QueryBatch(q.playlist[:n], q.level[:n], q.begin[:n], q.duration[:n])
+        res = m.get_segment_list(sub.playlist, sub.level, sub.begin, sub.duration)
+        assert np.array_equal(res.offsets.astype(np.int64), ref[0][:n + 1])
+        assert np.array_equal(res.sn, ref[2][:ref[0][n]])
+    m.close()
+
+
+# ---- config 3: live windows ------------------------------------------------------------------
+def test_config3_live_windows(ctx):
+    t, q = synth.config3(n_players=20_000)
+    ref = run_both_paths(ctx, t, q)
+    counts = np.diff(ref[0])
+    assert (counts[0::2] == 6).all()            # the whole-window query keeps all 6 fragments
+    m = ctx.upload(t)
+    assert m.info()["stage_all"] == 0
+    out, st = m.get_segment_duration(q.playlist, q.level)
+    eo, es = oracle.get_segment_duration_batch(t.playlist_base, t.track_off, t.track_state, t.dur0(),
+                                               q.playlist, q.level)
+    assert np.array_equal(out, eo) and np.array_equal(st, es)
+    m.close()
+
+
+# ---- config 5: many playlists, queries grouped by playlist -------------------------------------
+def test_config5_scaled(ctx):
+    t, q = synth.config5(n_playlists=3000, queries_per_playlist=100)
+    run_both_paths(ctx, t, q, paths=(N.PATH_SEARCH,))
+    t, q = synth.config5(seed=6, n_playlists=200, queries_per_playlist=50)
+    run_both_paths(ctx, t, q)
+
+
+def test_config5_shuffled_queries_span_beyond_window(ctx):
+    """Un-grouped queries: a tile's tracks are far apart, so the search falls back to
+    probing L2/HBM directly instead of a staged window."""
+    t, q = synth.config5(seed=7, n_playlists=4000, queries_per_playlist=10)
+    perm = np.random.default_rng(3).permutation(len(q))
+    q = QueryBatch(q.playlist[perm], q.level[perm], q.begin[perm], q.duration[perm])
+    run_both_paths(ctx, t, q, paths=(N.PATH_SEARCH,))
+
+
+def test_huge_counts_take_the_cooperative_expansion(ctx):
+    """Queries that keep whole 10k-fragment tracks (warp output run > 2048 entries)."""
+    t, _, _ = synth.config4(n_views=8)
+    nq = 3000
+    rng = np.random.default_rng(2)
+    q = QueryBatch(np.zeros(nq, np.int32), rng.integers(0, 8, nq).astype(np.int32),
+                   rng.integers(-100, 70000, nq).astype(np.float64),
+                   np.where(rng.random(nq) < 0.1, 1e6, 30.0))
+    run_both_paths(ctx, t, q)
+
+
+# ---- device-pointer entry point, properties at full size ---------------------------------------
+def test_device_pointer_variant_full_size_properties(ctx):
+    import torch
+    t, q = synth.config2()
+    m = ctx.upload(t)
+    dev = torch.device("cuda:0")
+    d_lv = torch.from_numpy(q.level).to(dev)
+    d_bg = torch.from_numpy(q.begin).to(dev)
+    d_du = torch.from_numpy(q.duration).to(dev)
+    nq = len(q)
+    cap = 20 * nq
+    d_off = torch.empty(nq + 1, dtype=torch.int32, device=dev)
+    d_sn = torch.empty(cap, dtype=torch.int32, device=dev)
+    d_tm = torch.empty(cap, dtype=torch.float64, device=dev)
+    torch.cuda.synchronize()
+    s = torch.cuda.current_stream().cuda_stream
+    res = m.get_segment_list_dev(nq, 0, d_lv.data_ptr(), d_bg.data_ptr(), d_du.data_ptr(),
+                                 d_off.data_ptr(), d_sn.data_ptr(), d_tm.data_ptr(), cap,
+                                 stream=s, sync=True)
+    off = d_off.cpu().numpy().astype(np.int64)
+    H = int(res.total_hits)
+    assert off[0] == 0 and off[-1] == H and (np.diff(off) >= 0).all()
+    sn, tm = d_sn[:H].cpu().numpy(), d_tm[:H].cpu().numpy()
+    # every hit satisfies the predicate with its own query, and runs are sorted by time
+    qi = np.repeat(np.arange(nq), np.diff(off))
+    with np.errstate(invalid="ignore"):
+        ub = q.begin + q.duration
+    assert (q.begin[qi] <= tm).all() and (tm <= ub[qi]).all()
+    lvl = q.level[qi].astype(np.int64)
+    assert np.array_equal(t.start[t.track_off[lvl] + sn], tm)      # sn indexes the same fragment
+    # asynchronous form + last_result
+    m.get_segment_list_dev(nq, 0, d_lv.data_ptr(), d_bg.data_ptr(), d_du.data_ptr(),
+                           d_off.data_ptr(), d_sn.data_ptr(), d_tm.data_ptr(), cap, stream=s)
+    again = m.last_result(s)
+    assert again.total_hits == H
+    assert_same_dev = oracle_list(t, q)
+    assert np.array_equal(off, assert_same_dev[0]) and np.array_equal(sn, assert_same_dev[2])
+    assert np.array_equal(tm.view(np.uint64), assert_same_dev[3].view(np.uint64))
+    m.close()
