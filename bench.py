@@ -267,7 +267,11 @@ def run_ours(args):
         if n_sets * per_step_bytes >= 3 * L2_BYTES and n_sets >= 3:
             break
     torch.cuda.synchronize()
-    stream = torch.cuda.current_stream().cuda_stream
+    # an explicit stream: the launches and the CUDA events that time them share it
+    tstream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(tstream)
+    stream = tstream.cuda_stream
+    assert stream != 0
 
     def launch(s):
         dmap.get_segment_list_dev(nq, s["pl"].data_ptr(), s["lv"].data_ptr(), s["bg"].data_ptr(),

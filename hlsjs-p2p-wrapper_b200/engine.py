@@ -18,6 +18,17 @@ def _arr(a, dtype):
     return None if a is None else np.ascontiguousarray(a, dtype=dtype)
 
 
+CUDA_STREAM_LEGACY = 1   # the cudaStreamLegacy handle
+
+
+def _stream(s):
+    """None -> the context's own stream; 0 -> CUDA's legacy default stream (what
+    `torch.cuda.default_stream().cuda_stream` is); anything else is a cudaStream_t."""
+    if s is None:
+        return None
+    return ctypes.c_void_p(CUDA_STREAM_LEGACY if int(s) == 0 else int(s))
+
+
 class SegmentListResult:
     """List form of a getSegmentList batch (media-map.js:27-54 per query)."""
     __slots__ = ("offsets", "sn", "time", "status", "total_hits", "n_unparsed", "n_missing",
@@ -176,7 +187,7 @@ class DeviceMap:
         nq = len(level)
         offsets = np.empty(nq + 1, np.int32)
         status = np.empty(nq, np.uint8) if want_status else None
-        cap = int(capacity) if capacity is not None else 8 * nq + 1024
+        cap = int(capacity) if capacity is not None else 16 * nq + 1024
         res = N.Result()
         for _ in range(2):
             sn = np.empty(max(cap, 1), np.int32)
@@ -219,19 +230,19 @@ class DeviceMap:
         return offsets, res.total_hits
 
     def get_segment_list_dev(self, nq, d_playlist, d_level, d_begin, d_duration, d_offsets,
-                             d_sn_out, d_time_out, capacity, d_status=0, stream=0, sync=False):
+                             d_sn_out, d_time_out, capacity, d_status=0, stream=None, sync=False):
         """Device pointers (ints); asynchronous unless sync=True (then returns the Result)."""
         res = N.Result() if sync else None
         code = self._lib.hlsmap_get_segment_list_dev(
             self._h, int(nq), d_playlist or None, d_level, d_begin, d_duration, d_offsets,
-            d_sn_out or None, d_time_out or None, int(capacity), d_status or None, stream or None,
+            d_sn_out or None, d_time_out or None, int(capacity), d_status or None, _stream(stream),
             ctypes.byref(res) if sync else None)
         N.check(code)
         return res
 
-    def last_result(self, stream=0):
+    def last_result(self, stream=None):
         res = N.Result()
-        N.check(self._lib.hlsmap_ctx_last_result(self.ctx._h, stream or None, ctypes.byref(res)))
+        N.check(self._lib.hlsmap_ctx_last_result(self.ctx._h, _stream(stream), ctypes.byref(res)))
         return res
 
     def get_segment_range(self, playlist, level, begin, duration):

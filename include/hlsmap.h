@@ -15,8 +15,10 @@
  *   - per-query outcomes (level missing / not parsed yet) are DATA (HLSMAP_ST_*), not
  *     errors: the JS binding turns them into the reference's throw / console.warn;
  *   - `*_dev` variants take DEVICE pointers and a cudaStream_t (as void*) and do no
- *     host<->device copies; the un-suffixed variants take HOST pointers, copy in and out,
- *     and block until the result is in the caller's buffers;
+ *     host<->device copies; a NULL stream means the context's own stream (pass
+ *     cudaStreamLegacy / cudaStreamPerThread to name CUDA's default streams); the
+ *     un-suffixed variants take HOST pointers, copy in and out, and block until the result
+ *     is in the caller's buffers;
  *   - a context is bound to one GPU and used by one thread at a time; batches issued
  *     through one context share its scratch memory and must not overlap on the GPU;
  *   - there is no CPU fallback: without a usable CUDA device every call fails.
