@@ -64,6 +64,9 @@ struct hlsmap_map {
     double *d_start = nullptr;
     int *d_sn = nullptr;
     double *d_dur0 = nullptr;
+    TrackHint *d_hint = nullptr;        // SMALL maps: per-track hint-grid parameters
+    unsigned short *d_grid = nullptr;   // SMALL maps: the hint grid itself
+    int grid_padded = 0;
     std::vector<int32_t> h_playlist_base;
     std::vector<int32_t> h_url_count;
     std::vector<uint8_t> h_monotone;
@@ -359,24 +362,53 @@ int hlsmap_map_create(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *playl
                                      sizeof(int) * (size_t)(n_playlists + 1) +
                                      12 * (size_t)m->n_frag_padded + 8 * (size_t)(n_tracks + 1));
 
-    // shared-memory staging plan: whole column when it is small, else a per-tile window
-    int64_t stage_all_limit = 96 * 1024, window = 64 * 1024;
-    if (const char *e = getenv("HLSMAP_STAGE_ALL_KB")) stage_all_limit = atoll(e) * 1024;
+    // Shared-memory plan.  SMALL: every start column is sorted and the whole map (start, sn
+    // and a u16 hint grid of `cells` cells per fragment) fits next to the kernel's own
+    // shared state, so it is staged once per CTA.  Otherwise the search kernel stages, per
+    // tile, the window of the start column its queries touch.
+    int64_t small_limit = 100 * 1024, window = 64 * 1024, cells = 2;
+    if (const char *e = getenv("HLSMAP_SMALL_KB")) small_limit = atoll(e) * 1024;
     if (const char *e = getenv("HLSMAP_STAGE_WINDOW_KB")) window = atoll(e) * 1024;
-    const int64_t smem_budget = (int64_t)ctx->max_smem_optin - 24 * 1024;
-    if (stage_all_limit > smem_budget) stage_all_limit = smem_budget;
+    if (const char *e = getenv("HLSMAP_HINT_CELLS")) cells = atoll(e) > 0 ? atoll(e) : 1;
+    const int64_t smem_budget = (int64_t)ctx->max_smem_optin - 32 * 1024;
+    if (small_limit > smem_budget) small_limit = smem_budget;
     if (window > smem_budget) window = smem_budget;
-    const int64_t col_bytes = m->n_frag_padded * 8;
-    if (col_bytes <= stage_all_limit) {
+    std::vector<TrackHint> hint;
+    int64_t grid_entries = 0;
+    bool small = m->info.all_monotone && nf < 65535 && small_limit > 0;
+    if (small) {
+        hint.resize((size_t)n_tracks);
+        for (int32_t t = 0; t < n_tracks; t++) {
+            const bool live = (desc[t].flags & kTrackStateMask) == HLSMAP_TRACK_PARSED && desc[t].len > 0;
+            hint[t] = TrackHint{};
+            hint[t].ncell = live ? (int)(cells * desc[t].len) : 1;
+            hint[t].grid_off = (int)grid_entries;
+            grid_entries += hint[t].ncell + 1;
+        }
+        grid_entries = (grid_entries + 7) & ~7ll;
+        if (grid_entries < 8) grid_entries = 8;
+        if (m->n_frag_padded * 12 + grid_entries * 2 > small_limit) small = false;
+    }
+    if (small) {
+        m->grid_padded = (int)grid_entries;
+        CKM(cudaMalloc(&m->d_hint, sizeof(TrackHint) * (size_t)(n_tracks + 1)));
+        CKM(cudaMalloc(&m->d_grid, sizeof(unsigned short) * (size_t)grid_entries));
+        CKM(cudaMemsetAsync(m->d_grid, 0, sizeof(unsigned short) * (size_t)grid_entries, s));
+        if (n_tracks)
+            CKM(cudaMemcpyAsync(m->d_hint, hint.data(), sizeof(TrackHint) * (size_t)n_tracks,
+                                cudaMemcpyHostToDevice, s));
+        CKM(launch_build_hint(m->d_start, m->d_desc, m->d_hint, m->d_grid, n_tracks, s));
+        CKM(cudaStreamSynchronize(s));
         m->info.stage_all = 1;
         m->stage_elems = (int)m->n_frag_padded;
-        m->stage_smem = (size_t)col_bytes;
+        m->stage_smem = (size_t)(m->n_frag_padded * 12 + grid_entries * 2);
+        m->info.device_bytes += (int64_t)(sizeof(TrackHint) * (size_t)(n_tracks + 1) + 2 * (size_t)grid_entries);
     } else {
         m->info.stage_all = 0;
         m->stage_elems = (int)(window / 8) & ~3;
         m->stage_smem = (size_t)m->stage_elems * 8;
     }
-    m->grid_search = resolve_search_max_grid(m->stage_smem);
+    m->grid_search = resolve_search_max_grid(m->stage_smem, small);
     m->grid_filter = resolve_filter_max_grid();
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess)
@@ -398,6 +430,8 @@ void hlsmap_map_destroy(hlsmap_map *m)
     if (m->d_start) cudaFree(m->d_start);
     if (m->d_sn) cudaFree(m->d_sn);
     if (m->d_dur0) cudaFree(m->d_dur0);
+    if (m->d_hint) cudaFree(m->d_hint);
+    if (m->d_grid) cudaFree(m->d_grid);
     delete m;
 }
 
@@ -489,6 +523,10 @@ int hlsmap_get_segment_list_dev(hlsmap_map *map, int64_t nq, const int32_t *d_pl
     p.n_tiles = (int)n_tiles;
     p.stage_elems = map->stage_elems;
     p.stage_all = map->info.stage_all;
+    p.small = map->info.stage_all;
+    p.hint = map->d_hint;
+    p.grid = map->d_grid;
+    p.grid_padded = map->grid_padded;
     p.vec_ok = al16(d_level) && al16(d_begin) && al16(d_duration) && al16(d_offsets) &&
                (!d_playlist || al16(d_playlist)) &&
                (!d_status || (reinterpret_cast<uintptr_t>(d_status) & 3u) == 0);

@@ -15,6 +15,14 @@ struct __align__(16) TrackDesc {
     int len;         // fragments in this track
     unsigned flags;
 };
+// Hint grid of one track (SMALL maps only), 32 bytes = two LDG.128.
+struct __align__(16) TrackHint {
+    double t0;     // start[0]
+    double inv;    // ncell / (start[len-1] - start[0]), or 0 when degenerate
+    int grid_off;  // first entry of this track in the u16 grid (ncell + 1 entries)
+    int ncell;
+    int pad[2];
+};
 constexpr unsigned kTrackStateMask = 3u;
 constexpr unsigned kTrackMonotone = 4u;
 
@@ -58,6 +66,10 @@ struct ResolveParams {
     const double *start;
     const int *sn;
     long long n_frag_padded;  // elements readable in start[] (multiple of 4)
+    const TrackHint *hint;        // SMALL maps only
+    const unsigned short *grid;   // SMALL maps only
+    int grid_padded;              // u16 entries in grid (multiple of 8)
+    int small;                    // whole map staged in shared memory + hint grid
     // queries
     long long nq;
     const int *q_playlist;  // nullable
@@ -107,7 +119,9 @@ cudaError_t launch_segment_duration(const TrackDesc *desc, const int *playlist_b
                                     int n_playlists, const double *dur0, long long n,
                                     const int *q_playlist, const int *q_level, double *out,
                                     unsigned char *status, cudaStream_t s);
-int resolve_search_max_grid(size_t smem);
+int resolve_search_max_grid(size_t smem, bool small);
+cudaError_t launch_build_hint(const double *start, const TrackDesc *desc, TrackHint *hint,
+                              unsigned short *grid, int n_tracks, cudaStream_t s);
 int resolve_filter_max_grid();
 constexpr int kSearchTileQueries = 1024;  // 256 threads x 4 queries
 constexpr int kFilterTileQueries = 256;   // 8 warps x 32 queries

@@ -15,6 +15,7 @@
 // Both are single-pass: count -> CTA scan -> decoupled look-back (scan.cuh) -> fill, so
 // queries are read once and hits written once.
 #include <cfloat>
+#include <type_traits>
 
 #include "scan.cuh"
 
@@ -26,30 +27,55 @@ constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
 constexpr int kIpt = 4;                         // queries per thread
 constexpr int kTile = kThreads * kIpt;          // == kSearchTileQueries
-constexpr int kWarpQueries = 32 * kIpt;         // 128
-constexpr int kMaxWarpSpan = 2048;              // outputs a warp expands via the head bitmap
+constexpr int kWindow = 16384;                  // outputs expanded per pass over the tile
+constexpr int kWords = kWindow / 32;            // head-bitmap words per window (2 per thread)
+constexpr int kCntBits = 44;                    // fused scan: [nz:20][count:44]
+constexpr unsigned long long kCntMask = (1ull << kCntBits) - 1ull;
 static_assert(kTile == kSearchTileQueries, "tile size mismatch");
+static_assert(kWords == 2 * kThreads, "two bitmap words per thread");
 
 using Scan = TileScan<kThreads>;
 
-struct __align__(16) ExpRec {  // one query with >= 1 hit, in query order
-    long long src;             // first kept fragment (absolute index into start[]/sn[])
-    int rel;                   // first output slot relative to the warp's output run
-    int cnt;
+// Expansion records: one per query that kept >= 1 fragment, in query order.
+//   rel = first output slot relative to the tile's output run, src = first kept fragment.
+template <bool SMALL>
+struct RecTable;
+template <>
+struct RecTable<true> {   // every fragment index fits an int: one 8-byte record
+    int2 v[kTile];
+    __device__ __forceinline__ void set(int i, int rel, long long src) { v[i] = make_int2(rel, (int)src); }
+    __device__ __forceinline__ void get(int i, int &rel, long long &src) const
+    {
+        const int2 r = v[i];
+        rel = r.x;
+        src = r.y;
+    }
+};
+template <>
+struct RecTable<false> {
+    int rel_[kTile];
+    long long src_[kTile];
+    __device__ __forceinline__ void set(int i, int rel, long long src) { rel_[i] = rel; src_[i] = src; }
+    __device__ __forceinline__ void get(int i, int &rel, long long &src) const
+    {
+        rel = rel_[i];
+        src = src_[i];
+    }
 };
 
-struct WarpExp {
-    ExpRec rec[kWarpQueries];
-    unsigned heads[kMaxWarpSpan / 32];
-};
-
+// Shared state of one CTA.
+template <bool SMALL>
 struct SearchSmem {
     Scan::Smem scan;
     unsigned long long mbar;
     long long red_min[kWarps];
     long long red_max[kWarps];
     unsigned long long warp_cnt[kWarps];
-    WarpExp wexp[kWarps];
+    int warp_heads[kWarps];
+    RecTable<SMALL> rec;
+    // per 32 output slots of the window: .x = bitmap of slots where a record starts,
+    // .y = records that start before this word (tile-wide rank base).  Double buffered.
+    uint2 hb[2][kWords];
 };
 
 __device__ __forceinline__ unsigned smem_u32(const void *p)
@@ -57,7 +83,7 @@ __device__ __forceinline__ unsigned smem_u32(const void *p)
     return (unsigned)__cvta_generic_to_shared(p);
 }
 
-// ---- TMA (bulk async copy) staging of a span of the start column -----------------------
+// ---- TMA (bulk async copy) staging of table columns ------------------------------------
 __device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count)
 {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
@@ -76,6 +102,13 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned by
         "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
         ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar))
         : "memory");
+}
+__device__ __forceinline__ void bulk_g2s_chunked(unsigned char *dst, const void *src,
+                                                 unsigned bytes, unsigned long long *bar)
+{
+    for (unsigned o = 0; o < bytes; o += 32768u)
+        bulk_g2s(dst + o, reinterpret_cast<const unsigned char *>(src) + o,
+                 min(32768u, bytes - o), bar);
 }
 __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity)
 {
@@ -101,6 +134,7 @@ __device__ __forceinline__ int lookup_track(const TrackDesc *desc, const int *pl
     off = 0;
     len = 0;
     flags = 0;
+    if (track) *track = 0;
     if ((unsigned)playlist >= (unsigned)n_playlists) return HLSMAP_ST_MISSING;
     const int b = __ldg(playlist_base + playlist);
     const int e = __ldg(playlist_base + playlist + 1);
@@ -125,11 +159,10 @@ struct GmemCol {
     __device__ __forceinline__ double operator()(int i) const { return __ldg(g + i); }
 };
 
-// First i in [0, len) with  begin <= col(i)  (the filter's left test); len if none.
+// First i in [lo, lo+n) with  begin <= col(i)  (the filter's left test); lo+n if none.
 template <class Col>
-__device__ __forceinline__ int lower_bound_begin(const Col &col, int len, double begin)
+__device__ __forceinline__ int lower_bound_begin(const Col &col, int lo, int n, double begin)
 {
-    int lo = 0, n = len;
     while (n > 0) {
         const int half = n >> 1;
         const bool keep_right = !(begin <= col(lo + half));
@@ -139,8 +172,20 @@ __device__ __forceinline__ int lower_bound_begin(const Col &col, int len, double
     return lo;
 }
 
-// First i in [lo, len) with  !(col(i) <= ub)  (the filter's right test fails); gallops
-// from lo because a look-ahead window keeps only a handful of fragments.
+// First i in [lo, lo+n) with  !(col(i) <= ub)  (the filter's right test fails).
+template <class Col>
+__device__ __forceinline__ int upper_bound_ub(const Col &col, int lo, int n, double ub)
+{
+    while (n > 0) {
+        const int half = n >> 1;
+        const bool keep_right = col(lo + half) <= ub;
+        lo = keep_right ? lo + half + 1 : lo;
+        n = keep_right ? n - half - 1 : half;
+    }
+    return lo;
+}
+
+// Same bound, galloping from lo: a look-ahead window keeps only a handful of fragments.
 template <class Col>
 __device__ __forceinline__ int upper_bound_from(const Col &col, int lo, int len, double ub)
 {
@@ -156,12 +201,7 @@ __device__ __forceinline__ int upper_bound_from(const Col &col, int lo, int len,
             break;
         }
     }
-    while (a < b) {
-        const int m = (a + b) >> 1;
-        if (col(m) <= ub) a = m + 1;
-        else b = m;
-    }
-    return a;
+    return upper_bound_ub(col, a, b - a, ub);
 }
 
 __device__ __forceinline__ int warp_excl_scan(int v, int &total)
@@ -177,39 +217,75 @@ __device__ __forceinline__ int warp_excl_scan(int v, int &total)
     return x - v;
 }
 
+__device__ __forceinline__ unsigned long long warp_excl_scan64(unsigned long long v,
+                                                               unsigned long long &total)
+{
+    const int lane = threadIdx.x & 31;
+    unsigned long long x = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const unsigned long long y = __shfl_up_sync(0xffffffffu, x, d);
+        if (lane >= d) x += y;
+    }
+    total = __shfl_sync(0xffffffffu, x, 31);
+    return x - v;
+}
+
 }  // namespace
 
+// Hint-grid cell of a time value: monotone non-decreasing in x, NaN -> 0, saturating.  The
+// SAME function places table entries (upload) and query bounds (lookup), so for a sorted
+// NaN-free column  cell(s) < cell(x) => s < x  and  cell(s) > cell(x) => s > x : a bound
+// always lies inside [grid[cell], grid[cell+1]] and is finished there with the filter's own
+// comparison.  The grid narrows the search; it never decides a comparison.
+__device__ __forceinline__ int hint_cell(double x, double t0, double inv, int ncell)
+{
+    const int c = __double2int_rd(__dmul_rn(__dsub_rn(x, t0), inv));
+    return min(max(c, 0), ncell - 1);
+}
+
 // =========================================================================================
-//  search kernel
+//  search kernel.  SMALL = the whole map (start, sn, hint grid) lives in shared memory.
 // =========================================================================================
+template <bool SMALL>
 __global__ void __launch_bounds__(kThreads)
 resolve_search_kernel(const ResolveParams p)
 {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
+    __shared__ SearchSmem<SMALL> sm;
     double *s_start = reinterpret_cast<double *>(dyn_smem);
-    __shared__ SearchSmem sm;
+    const int *s_sn = reinterpret_cast<const int *>(dyn_smem + p.n_frag_padded * 8);
+    const unsigned short *s_grid =
+        reinterpret_cast<const unsigned short *>(dyn_smem + p.n_frag_padded * 12);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned lane_le = 0xffffffffu >> (31 - lane);
 
     if (tid == 0) mbar_init(&sm.mbar, 1);
-    for (int i = lane; i < kMaxWarpSpan / 32; i += 32) sm.wexp[warp].heads[i] = 0u;
+#pragma unroll
+    for (int b = 0; b < 2; b++) {
+        sm.hb[b][tid] = make_uint2(0u, 0u);
+        sm.hb[b][tid + kThreads] = make_uint2(0u, 0u);
+    }
     unsigned mbar_phase = 0;
+    unsigned hbuf = 0;                   // which heads[] buffer the next window uses
     long long span_lo = 0, span_hi = 0;  // staged element range of start[]
     __syncthreads();
 
-    if (p.stage_all) {
-        span_lo = 0;
+    bool stage_pending = false;
+    if (SMALL) {
         span_hi = p.n_frag_padded;
         if (tid == 0) {
-            const unsigned bytes = (unsigned)(span_hi * 8);
-            mbar_expect_tx(&sm.mbar, bytes);
-            for (unsigned o = 0; o < bytes; o += 32768u)
-                bulk_g2s(dyn_smem + o, reinterpret_cast<const unsigned char *>(p.start) + o,
-                         min(32768u, bytes - o), &sm.mbar);
+            const unsigned b_start = (unsigned)(p.n_frag_padded * 8);
+            const unsigned b_sn = (unsigned)(p.n_frag_padded * 4);
+            const unsigned b_grid = (unsigned)(p.grid_padded * 2);
+            mbar_expect_tx(&sm.mbar, b_start + b_sn + b_grid);
+            bulk_g2s_chunked(dyn_smem, p.start, b_start, &sm.mbar);
+            bulk_g2s_chunked(dyn_smem + b_start, p.sn, b_sn, &sm.mbar);
+            bulk_g2s_chunked(dyn_smem + b_start + b_sn, p.grid, b_grid, &sm.mbar);
         }
+        stage_pending = true;
     }
-    bool stage_pending = p.stage_all != 0;
 
     for (;;) {
         const int tile = Scan::next_tile(sm.scan, p.ctr, p.epoch);
@@ -247,18 +323,18 @@ resolve_search_kernel(const ResolveParams p)
 
         // ---- resolve (playlist, level) -> fragment table --------------------------------
         long long off[kIpt];
-        int len[kIpt], st[kIpt];
+        int len[kIpt], st[kIpt], trk[kIpt];
         int n_unp = 0, n_mis = 0;
         long long mn = 0x7fffffffffffffffll, mx = -1;
 #pragma unroll
         for (int k = 0; k < kIpt; k++) {
             unsigned fl;
             st[k] = lookup_track(p.desc, p.playlist_base, p.n_playlists, pl[k], lv[k], off[k],
-                                 len[k], fl);
+                                 len[k], fl, &trk[k]);
             const bool in = q0 + k < p.nq;
             n_unp += (in && st[k] == HLSMAP_ST_UNPARSED);
             n_mis += (in && st[k] == HLSMAP_ST_MISSING);
-            if (st[k] == HLSMAP_ST_OK && len[k] > 0) {
+            if (!SMALL && st[k] == HLSMAP_ST_OK && len[k] > 0) {
                 mn = min(mn, off[k]);
                 mx = max(mx, off[k] + len[k]);
             }
@@ -276,10 +352,8 @@ resolve_search_kernel(const ResolveParams p)
         }
 
         // ---- make the needed span of start[] resident in shared memory -------------------
-        bool staged;
-        if (p.stage_all) {
-            staged = true;
-        } else {
+        bool staged = true;
+        if (!SMALL) {
 #pragma unroll
             for (int d = 16; d > 0; d >>= 1) {
                 mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, d));
@@ -298,16 +372,12 @@ resolve_search_kernel(const ResolveParams p)
             } else if (need_lo >= span_lo && need_hi <= span_hi) {
                 staged = true;  // still resident from the previous tile
             } else if (need_hi - need_lo <= (long long)p.stage_elems) {
-                staged = true;
                 span_lo = need_lo;
                 span_hi = need_hi;
                 if (tid == 0) {
                     const unsigned bytes = (unsigned)((span_hi - span_lo) * 8);
-                    const unsigned char *src =
-                        reinterpret_cast<const unsigned char *>(p.start + span_lo);
                     mbar_expect_tx(&sm.mbar, bytes);
-                    for (unsigned o = 0; o < bytes; o += 32768u)
-                        bulk_g2s(dyn_smem + o, src + o, min(32768u, bytes - o), &sm.mbar);
+                    bulk_g2s_chunked(dyn_smem, p.start + span_lo, bytes, &sm.mbar);
                 }
                 stage_pending = true;
             } else {
@@ -320,38 +390,58 @@ resolve_search_kernel(const ResolveParams p)
             stage_pending = false;
         }
 
-        // ---- bounds: [lo, hi) is exactly what the filter keeps ---------------------------
+        // ---- bounds: [lo, lo+cnt) is exactly what the filter keeps -----------------------
         int lo[kIpt], cnt[kIpt];
 #pragma unroll
         for (int k = 0; k < kIpt; k++) {
             // one fp64 add, round-to-nearest, never contracted: JS `beginTime + duration`
             const double ub = __dadd_rn(bg[k], du[k]);
             int l, h;
-            if (staged) {
+            if (SMALL) {
+                // hint grid narrows each bound to one cell; the filter's comparisons finish it
+                const int4 h0 = __ldg(reinterpret_cast<const int4 *>(p.hint + trk[k]));
+                const int4 h1 = __ldg(reinterpret_cast<const int4 *>(p.hint + trk[k]) + 1);
+                const double t0 = __hiloint2double(h0.y, h0.x);
+                const double inv = __hiloint2double(h0.w, h0.z);
+                const int ncell = st[k] == HLSMAP_ST_OK ? h1.y : 1;
+                const unsigned short *g = s_grid + (st[k] == HLSMAP_ST_OK ? h1.x : 0);
+                const SmemCol col{s_start + (int)off[k]};
+                const int cb = hint_cell(bg[k], t0, inv, ncell);
+                const int cu = hint_cell(ub, t0, inv, ncell);
+                const int b0 = g[cb], b1 = g[cb + 1];
+                const int u0 = g[cu], u1 = g[cu + 1];
+                l = lower_bound_begin(col, b0, b1 - b0, bg[k]);
+                if (bg[k] != bg[k]) l = len[k];           // NaN: `begin <= start` never holds
+                h = upper_bound_ub(col, u0, u1 - u0, ub);
+                if (st[k] != HLSMAP_ST_OK) { l = 0; h = 0; }
+            } else if (staged) {
                 const SmemCol col{s_start + (int)(off[k] - span_lo)};
-                l = lower_bound_begin(col, len[k], bg[k]);
+                l = lower_bound_begin(col, 0, len[k], bg[k]);
                 h = upper_bound_from(col, l, len[k], ub);
             } else {
                 const GmemCol col{p.start + off[k]};
-                l = lower_bound_begin(col, len[k], bg[k]);
+                l = lower_bound_begin(col, 0, len[k], bg[k]);
                 h = upper_bound_from(col, l, len[k], ub);
             }
             lo[k] = l;
-            cnt[k] = h - l;
+            cnt[k] = max(h - l, 0);
         }
 
-        // ---- scan counts: thread -> warp -> CTA -> batch ---------------------------------
-        const int tsum = cnt[0] + cnt[1] + cnt[2] + cnt[3];
-        int wtotal;
-        const int texcl = warp_excl_scan(tsum, wtotal);
-        if (lane == 0) sm.warp_cnt[warp] = (unsigned long long)wtotal;
+        // ---- fused scan of (hit count, non-empty flag): thread -> warp -> CTA -> batch ---
+        unsigned long long tval = 0;
+#pragma unroll
+        for (int k = 0; k < kIpt; k++)
+            tval += (unsigned long long)cnt[k] + ((unsigned long long)(cnt[k] > 0) << kCntBits);
+        unsigned long long wtot;
+        const unsigned long long texcl = warp_excl_scan64(tval, wtot);
+        if (lane == 0) sm.warp_cnt[warp] = wtot;
         __syncthreads();
-        unsigned long long wbase = 0, tile_total = 0;
+        unsigned long long wbase = 0, tile_tot = 0;
 #pragma unroll
         for (int w = 0; w < kWarps; w++) {
             const unsigned long long c = sm.warp_cnt[w];
             wbase += (w < warp) ? c : 0ull;
-            tile_total += c;
+            tile_tot += c;
         }
         {   // rare: fold the unparsed / missing tallies (one atomic per warp when non-zero)
             const unsigned any = __ballot_sync(0xffffffffu, (n_unp | n_mis) != 0);
@@ -367,12 +457,14 @@ resolve_search_kernel(const ResolveParams p)
                 }
             }
         }
+        const unsigned long long tile_cnt = tile_tot & kCntMask;
         const unsigned long long tile_base =
-            Scan::exclusive_prefix(sm.scan, p.tile_status, p.epoch, tile, tile_total);
+            Scan::exclusive_prefix(sm.scan, p.tile_status, p.epoch, tile, tile_cnt);
 
         // ---- offsets[q] ------------------------------------------------------------------
-        const unsigned long long my_base = tile_base + wbase + (unsigned long long)texcl;
+        const unsigned long long my_rel = (wbase + texcl) & kCntMask;   // tile-relative
         {
+            const unsigned long long my_base = tile_base + my_rel;
             int4 o4;
             o4.x = (int)my_base;
             o4.y = (int)(my_base + cnt[0]);
@@ -388,75 +480,135 @@ resolve_search_kernel(const ResolveParams p)
             }
         }
         if (tile == p.n_tiles - 1 && tid == kThreads - 1) {
-            const unsigned long long total = tile_base + tile_total;
+            const unsigned long long total = tile_base + tile_cnt;
             p.offsets[p.nq] = (int)total;
             p.result->total_hits = (long long)total;
             p.result->overflow = total > 0x7fffffffull ? 1 : 0;
         }
 
-        // ---- expansion: the warp's hits are one contiguous output run --------------------
-        if (p.sn_out != nullptr && wtotal > 0) {
-            WarpExp &W = sm.wexp[warp];
-            const int nz = (cnt[0] > 0) + (cnt[1] > 0) + (cnt[2] > 0) + (cnt[3] > 0);
-            int nrec;
-            int rank = warp_excl_scan(nz, nrec);
-            const bool bitmap = wtotal <= kMaxWarpSpan;
-            int rel = texcl;
+        // ---- expansion: the tile's hits are ONE contiguous output run, written by the whole
+        //      CTA 256 slots at a time whatever the per-query counts (load balanced) --------
+        if (p.sn_out != nullptr && tile_cnt > 0 && tile_cnt <= 0x7fffffffull) {
+            int rank = (int)((wbase + texcl) >> kCntBits);
+            int rel = (int)my_rel;
 #pragma unroll
             for (int k = 0; k < kIpt; k++) {
                 if (cnt[k] > 0) {
-                    ExpRec r;
-                    r.src = off[k] + lo[k];
-                    r.rel = rel;
-                    r.cnt = cnt[k];
-                    W.rec[rank] = r;
-                    if (bitmap) atomicOr(&W.heads[rel >> 5], 1u << (rel & 31));
+                    sm.rec.set(rank, rel, off[k] + lo[k]);
                     rank++;
                     rel += cnt[k];
                 }
             }
-            __syncwarp();
-            const long long gbase = (long long)(tile_base + wbase);
-            if (bitmap) {
-                int carried = 0;
-                for (int c0 = 0; c0 < wtotal; c0 += 32) {
-                    const unsigned m = W.heads[c0 >> 5];
-                    const int q = c0 + lane;
-                    const int r = carried + __popc(m & lane_le) - 1;
-                    carried += __popc(m);
-                    if (q < wtotal) {
-                        const ExpRec rc = W.rec[r];
-                        const long long src = rc.src + (q - rc.rel);
-                        const long long o = gbase + q;
-                        if (o < p.capacity) {
-                            const double t = staged ? s_start[(int)(src - span_lo)]
-                                                    : __ldg(p.start + src);
-                            __stcs(p.time_out + o, t);            // time = fragment.start (:48)
-                            __stcs(p.sn_out + o, __ldg(p.sn + src));  // sn = fragment.sn (:46)
-                        }
-                    }
-                    __syncwarp();
-                    if (lane == 0) W.heads[c0 >> 5] = 0u;
-                }
-            } else {
-                for (int r = 0; r < nrec; r++) {
-                    const ExpRec rc = W.rec[r];
-                    for (int j = lane; j < rc.cnt; j += 32) {
-                        const long long o = gbase + rc.rel + j;
-                        if (o < p.capacity) {
-                            p.time_out[o] = __ldg(p.start + rc.src + j);
-                            p.sn_out[o] = __ldg(p.sn + rc.src + j);
+            const int total = (int)tile_cnt;
+            int carried = 0;            // records that start before the current window
+            for (int w0 = 0; w0 < total; w0 += kWindow) {
+                uint2 *H = sm.hb[hbuf];
+                {   // mark where this thread's records start inside the window
+                    int r2 = (int)my_rel;
+#pragma unroll
+                    for (int k = 0; k < kIpt; k++) {
+                        if (cnt[k] > 0) {
+                            const unsigned d = (unsigned)(r2 - w0);
+                            if (d < (unsigned)kWindow) atomicOr(&H[d >> 5].x, 1u << (d & 31));
+                            r2 += cnt[k];
                         }
                     }
                 }
+                __syncthreads();
+                {   // rank_base[word] = carried + heads in earlier words (2 words per thread)
+                    const int c0 = __popc(H[2 * tid].x), c1 = __popc(H[2 * tid + 1].x);
+                    int wsum;
+                    const int ex = warp_excl_scan(c0 + c1, wsum);
+                    if (lane == 0) sm.warp_heads[warp] = wsum;
+                    __syncthreads();
+                    int before = carried, all = 0;
+#pragma unroll
+                    for (int w = 0; w < kWarps; w++) {
+                        const int c = sm.warp_heads[w];
+                        before += (w < warp) ? c : 0;
+                        all += c;
+                    }
+                    H[2 * tid].y = (unsigned)(before + ex);
+                    H[2 * tid + 1].y = (unsigned)(before + ex + c0);
+                    carried += all;
+                }
+                __syncthreads();
+                const int wend = min(total - w0, kWindow);
+                const long long obase = (long long)tile_base + w0;
+                for (int q = tid; q < wend; q += kThreads) {
+                    const uint2 hw = H[q >> 5];
+                    const int r = (int)hw.y + __popc(hw.x & lane_le) - 1;
+                    int rrel;
+                    long long src;
+                    sm.rec.get(r, rrel, src);
+                    src += w0 + q - rrel;
+                    const long long o = obase + q;
+                    if (o < p.capacity) {
+                        double t;
+                        int s;
+                        if (SMALL) {
+                            t = s_start[(int)src];
+                            s = s_sn[(int)src];
+                        } else {
+                            t = staged ? s_start[(int)(src - span_lo)] : __ldg(p.start + src);
+                            s = __ldg(p.sn + src);
+                        }
+                        __stcs(p.time_out + o, t);   // time = fragment.start  (media-map.js:48)
+                        __stcs(p.sn_out + o, s);     // sn   = fragment.sn     (media-map.js:46)
+                    }
+                }
+                __syncthreads();
+                H[2 * tid].x = 0u;        // this buffer is next used two windows from now
+                H[2 * tid + 1].x = 0u;
+                hbuf ^= 1u;
             }
-            __syncwarp();
         }
 
         if (Scan::tile_done(p.ctr, p.n_tiles)) Scan::finish_batch(p.ctr, p.result, p.epoch);
     }
     // never leave with a bulk copy still landing in this CTA's shared memory
     if (stage_pending) mbar_wait(&sm.mbar, mbar_phase);
+}
+
+// =========================================================================================
+//  upload-time hint grid (SMALL maps): grid[c] = fragments of the track whose cell < c
+// =========================================================================================
+__global__ void __launch_bounds__(256)
+build_hint_kernel(const double *__restrict__ start, const TrackDesc *__restrict__ desc,
+                  TrackHint *hint, unsigned short *grid, int n_tracks)
+{
+    const int lane = threadIdx.x & 31;
+    const int wpb = blockDim.x >> 5;
+    for (int t = blockIdx.x * wpb + (threadIdx.x >> 5); t < n_tracks; t += gridDim.x * wpb) {
+        const TrackDesc d = desc[t];
+        TrackHint h = hint[t];            // grid_off and ncell were planned on the host
+        const bool live = (d.flags & kTrackStateMask) == HLSMAP_TRACK_PARSED && d.len > 0 &&
+                          (d.flags & kTrackMonotone);
+        double t0 = 0.0, inv = 0.0;
+        if (live) {
+            t0 = start[d.off];
+            const double span = __dsub_rn(start[d.off + d.len - 1], t0);
+            inv = __ddiv_rn((double)h.ncell, span);
+            if (!(span > 0.0) || !(inv > 0.0) || !(inv <= 1.7e308) || !(fabs(t0) <= 1.7e308))
+                inv = 0.0;                // degenerate: every value lands in cell 0
+        }
+        if (lane == 0) {
+            h.t0 = t0;
+            h.inv = inv;
+            hint[t] = h;
+        }
+        const GmemCol col{start + d.off};
+        for (int c = lane; c <= h.ncell; c += 32) {
+            int lo = 0, n = live ? d.len : 0;   // first i with cell(start[i]) >= c
+            while (n > 0) {
+                const int half = n >> 1;
+                const bool keep_right = hint_cell(col(lo + half), t0, inv, h.ncell) < c;
+                lo = keep_right ? lo + half + 1 : lo;
+                n = keep_right ? n - half - 1 : half;
+            }
+            grid[h.grid_off + c] = (unsigned short)(c == h.ncell ? (live ? d.len : 0) : lo);
+        }
+    }
 }
 
 // =========================================================================================
@@ -593,7 +745,7 @@ range_kernel(const RangeParams p)
         if (st == HLSMAP_ST_OK) {
             if (fl & kTrackMonotone) {
                 const GmemCol col{p.start + off};
-                const int l = lower_bound_begin(col, len, bg);
+                const int l = lower_bound_begin(col, 0, len, bg);
                 const int h = upper_bound_from(col, l, len, ub);
                 count = h - l;
                 first = count > 0 ? l : -1;
@@ -679,14 +831,22 @@ static int sm_count()
     return g_sm_count;
 }
 
-int resolve_search_max_grid(size_t smem)
+int resolve_search_max_grid(size_t smem, bool small)
 {
     int per_sm = 0;
-    cudaFuncSetAttribute(resolve_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         (int)smem);
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resolve_search_kernel, kThreads,
-                                                      smem) != cudaSuccess || per_sm < 1)
-        per_sm = 1;
+    cudaError_t e;
+    if (small) {
+        cudaFuncSetAttribute(resolve_search_kernel<true>,
+                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resolve_search_kernel<true>,
+                                                          kThreads, smem);
+    } else {
+        cudaFuncSetAttribute(resolve_search_kernel<false>,
+                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resolve_search_kernel<false>,
+                                                          kThreads, smem);
+    }
+    if (e != cudaSuccess || per_sm < 1) per_sm = 1;
     return per_sm * sm_count();
 }
 
@@ -701,7 +861,8 @@ int resolve_filter_max_grid()
 
 cudaError_t launch_resolve_search(const ResolveParams &p, int grid, size_t smem, cudaStream_t s)
 {
-    resolve_search_kernel<<<grid, kThreads, smem, s>>>(p);
+    if (p.small) resolve_search_kernel<true><<<grid, kThreads, smem, s>>>(p);
+    else resolve_search_kernel<false><<<grid, kThreads, smem, s>>>(p);
     return cudaGetLastError();
 }
 
@@ -729,6 +890,17 @@ cudaError_t launch_monotone_check(const double *start, TrackDesc *desc, int n_tr
     const long long cap = (long long)sm_count() * 8;
     if (blocks > cap) blocks = cap;
     monotone_check_kernel<<<(int)blocks, 256, 0, s>>>(start, desc, n_tracks);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_build_hint(const double *start, const TrackDesc *desc, TrackHint *hint,
+                              unsigned short *grid, int n_tracks, cudaStream_t s)
+{
+    if (n_tracks <= 0) return cudaSuccess;
+    long long blocks = ((long long)n_tracks + 7) / 8;
+    const long long cap = (long long)sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    build_hint_kernel<<<(int)blocks, 256, 0, s>>>(start, desc, hint, grid, n_tracks);
     return cudaGetLastError();
 }
 

@@ -63,6 +63,10 @@ struct TileScan {
                                                           unsigned long long aggregate)
     {
         const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+        // A batch may not produce more than INT32_MAX entries (the host reports OVERFLOW), so
+        // published values saturate far above that instead of wrapping the 40-bit field.
+        const unsigned long long kSat = 1ull << 33;
+        aggregate = aggregate < kSat ? aggregate : kSat;
         if (tile == 0) {
             if (tid == 0) st_relaxed_u64(&status[0], make_status(epoch, kStatePrefix, aggregate));
             return 0ull;
@@ -100,6 +104,7 @@ struct TileScan {
             if (first != 0x7fffffff) break;
             top -= THREADS;
         }
+        running = running < kSat ? running : kSat;
         if (tid == 0)
             st_relaxed_u64(&status[tile], make_status(epoch, kStatePrefix, running + aggregate));
         return running;
