@@ -273,10 +273,14 @@ def run_ours(args):
     stream = tstream.cuda_stream
     assert stream != 0
 
+    count_only = os.environ.get("HLSMAP_BENCH_COUNT_ONLY") == "1"     # experiment switch
+
     def launch(s):
         dmap.get_segment_list_dev(nq, s["pl"].data_ptr(), s["lv"].data_ptr(), s["bg"].data_ptr(),
-                                  s["du"].data_ptr(), s["off"].data_ptr(), s["sn"].data_ptr(),
-                                  s["tm"].data_ptr(), s["hits"], stream=stream)
+                                  s["du"].data_ptr(), s["off"].data_ptr(),
+                                  0 if count_only else s["sn"].data_ptr(),
+                                  0 if count_only else s["tm"].data_ptr(),
+                                  0 if count_only else s["hits"], stream=stream)
 
     for i in range(args.warmup):
         launch(sets[i % n_sets])

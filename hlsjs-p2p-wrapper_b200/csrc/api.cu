@@ -75,6 +75,7 @@ struct hlsmap_map {
     int stage_elems = 0;
     size_t stage_smem = 0;
     int grid_search = 0, grid_filter = 0;
+    int ipt = 4;                        // queries per thread of the SMALL search kernel
 };
 
 namespace {
@@ -408,7 +409,9 @@ int hlsmap_map_create(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *playl
         m->stage_elems = (int)(window / 8) & ~3;
         m->stage_smem = (size_t)m->stage_elems * 8;
     }
-    m->grid_search = resolve_search_max_grid(m->stage_smem, small);
+    m->ipt = 2;   // measured on B200: 512-query tiles at 4 CTAs/SM beat 1024-query tiles at 2-3
+    if (const char *e = getenv("HLSMAP_IPT")) m->ipt = atoi(e) == 4 ? 4 : 2;
+    m->grid_search = resolve_search_max_grid(m->stage_smem, small, m->ipt);
     m->grid_filter = resolve_filter_max_grid();
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess)
@@ -493,7 +496,8 @@ int hlsmap_get_segment_list_dev(hlsmap_map *map, int64_t nq, const int32_t *d_pl
         return HLSMAP_OK;
     }
 
-    const int tile_q = path == HLSMAP_PATH_SEARCH ? kSearchTileQueries : kFilterTileQueries;
+    const int tile_q = path == HLSMAP_PATH_SEARCH ? resolve_search_tile(map->info.stage_all != 0, map->ipt)
+                                                  : kFilterTileQueries;
     const int64_t n_tiles = (nq + tile_q - 1) / tile_q;
     if (n_tiles > 0x7fffffff) return fail(HLSMAP_ERR_INVALID, "batch too large: split it");
     r = prepare_scan(ctx, n_tiles, s);
@@ -524,6 +528,7 @@ int hlsmap_get_segment_list_dev(hlsmap_map *map, int64_t nq, const int32_t *d_pl
     p.stage_elems = map->stage_elems;
     p.stage_all = map->info.stage_all;
     p.small = map->info.stage_all;
+    p.ipt = map->ipt;
     p.hint = map->d_hint;
     p.grid = map->d_grid;
     p.grid_padded = map->grid_padded;
@@ -531,14 +536,35 @@ int hlsmap_get_segment_list_dev(hlsmap_map *map, int64_t nq, const int32_t *d_pl
                (!d_playlist || al16(d_playlist)) &&
                (!d_status || (reinterpret_cast<uintptr_t>(d_status) & 3u) == 0);
 
+    unsigned long long *d_trace = nullptr;
+    const char *trace_path = getenv("HLSMAP_TRACE");     // experiment: per-tile phase timestamps
+    if (trace_path && path == HLSMAP_PATH_SEARCH) {
+        CK(cudaMalloc(&d_trace, (size_t)n_tiles * 64));
+        CK(cudaMemsetAsync(d_trace, 0, (size_t)n_tiles * 64, s));
+        p.trace = d_trace;
+    }
     if (path == HLSMAP_PATH_SEARCH) {
-        const int grid = (int)(n_tiles < map->grid_search ? n_tiles : map->grid_search);
+        int grid = (int)(n_tiles < map->grid_search ? n_tiles : map->grid_search);
+        if (const char *e = getenv("HLSMAP_GRID_PER_SM")) {   // experiment switch
+            const int g = atoi(e) * ctx->sm_count;
+            if (g > 0 && g < grid) grid = g;
+        }
         CK(launch_resolve_search(p, grid, map->stage_smem, s));
     } else {
         const int grid = (int)(n_tiles < map->grid_filter ? n_tiles : map->grid_filter);
         CK(launch_resolve_filter(p, grid, s));
     }
     ctx->last_launches = 1;
+    if (d_trace) {
+        std::vector<unsigned long long> h((size_t)n_tiles * 8);
+        CK(cudaMemcpyAsync(h.data(), d_trace, (size_t)n_tiles * 64, cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+        if (FILE *f = fopen(trace_path, "wb")) {
+            fwrite(h.data(), 8, h.size(), f);
+            fclose(f);
+        }
+        CK(cudaFree(d_trace));
+    }
 
     if (result) {
         r = fetch_result(ctx, s, result);

@@ -70,6 +70,7 @@ struct ResolveParams {
     const unsigned short *grid;   // SMALL maps only
     int grid_padded;              // u16 entries in grid (multiple of 8)
     int small;                    // whole map staged in shared memory + hint grid
+    int ipt;                      // queries per thread of the SMALL kernel (2 or 4)
     // queries
     long long nq;
     const int *q_playlist;  // nullable
@@ -92,6 +93,7 @@ struct ResolveParams {
     int stage_elems;  // capacity of the shared-memory copy of start[], in doubles
     int stage_all;    // the whole column fits: stage once per CTA
     int vec_ok;       // query/offset pointers are 16-byte aligned
+    unsigned long long *trace;  // diagnostics: per-tile phase timestamps (HLSMAP_TRACE=file); NULL normally
 };
 
 struct RangeParams {
@@ -119,11 +121,11 @@ cudaError_t launch_segment_duration(const TrackDesc *desc, const int *playlist_b
                                     int n_playlists, const double *dur0, long long n,
                                     const int *q_playlist, const int *q_level, double *out,
                                     unsigned char *status, cudaStream_t s);
-int resolve_search_max_grid(size_t smem, bool small);
+int resolve_search_max_grid(size_t smem, bool small, int ipt);
+int resolve_search_tile(bool small, int ipt);
 cudaError_t launch_build_hint(const double *start, const TrackDesc *desc, TrackHint *hint,
                               unsigned short *grid, int n_tracks, cudaStream_t s);
 int resolve_filter_max_grid();
-constexpr int kSearchTileQueries = 1024;  // 256 threads x 4 queries
 constexpr int kFilterTileQueries = 256;   // 8 warps x 32 queries
 
 // launchers (views.cu)

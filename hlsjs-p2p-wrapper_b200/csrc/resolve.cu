@@ -25,24 +25,30 @@ namespace {
 
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
-constexpr int kIpt = 4;                         // queries per thread
-constexpr int kTile = kThreads * kIpt;          // == kSearchTileQueries
-constexpr int kWindow = 16384;                  // outputs expanded per pass over the tile
-constexpr int kWords = kWindow / 32;            // head-bitmap words per window (2 per thread)
 constexpr int kCntBits = 44;                    // fused scan: [nz:20][count:44]
 constexpr unsigned long long kCntMask = (1ull << kCntBits) - 1ull;
-static_assert(kTile == kSearchTileQueries, "tile size mismatch");
-static_assert(kWords == 2 * kThreads, "two bitmap words per thread");
 
 using Scan = TileScan<kThreads>;
 
+// Compile-time shape of one search-kernel variant.
+//   IPT     queries per thread (tile = 256 * IPT queries)
+//   WINDOW  output slots expanded per pass over the tile's output run
+template <int IPT>
+struct Shape {
+    static constexpr int kIpt = IPT;
+    static constexpr int kTile = kThreads * IPT;
+    static constexpr int kWindow = IPT >= 4 ? 8192 : 4096;
+    static constexpr int kWords = kWindow / 32;   // <= kThreads: one bitmap word per thread
+    static_assert(kWords <= kThreads, "one bitmap word per thread at most");
+};
+
 // Expansion records: one per query that kept >= 1 fragment, in query order.
 //   rel = first output slot relative to the tile's output run, src = first kept fragment.
-template <bool SMALL>
+template <bool SMALL, int TILE>
 struct RecTable;
-template <>
-struct RecTable<true> {   // every fragment index fits an int: one 8-byte record
-    int2 v[kTile];
+template <int TILE>
+struct RecTable<true, TILE> {   // every fragment index fits an int: one 8-byte record
+    int2 v[TILE];
     __device__ __forceinline__ void set(int i, int rel, long long src) { v[i] = make_int2(rel, (int)src); }
     __device__ __forceinline__ void get(int i, int &rel, long long &src) const
     {
@@ -51,10 +57,10 @@ struct RecTable<true> {   // every fragment index fits an int: one 8-byte record
         src = r.y;
     }
 };
-template <>
-struct RecTable<false> {
-    int rel_[kTile];
-    long long src_[kTile];
+template <int TILE>
+struct RecTable<false, TILE> {
+    int rel_[TILE];
+    long long src_[TILE];
     __device__ __forceinline__ void set(int i, int rel, long long src) { rel_[i] = rel; src_[i] = src; }
     __device__ __forceinline__ void get(int i, int &rel, long long &src) const
     {
@@ -64,7 +70,7 @@ struct RecTable<false> {
 };
 
 // Shared state of one CTA.
-template <bool SMALL>
+template <bool SMALL, int IPT>
 struct SearchSmem {
     Scan::Smem scan;
     unsigned long long mbar;
@@ -72,10 +78,11 @@ struct SearchSmem {
     long long red_max[kWarps];
     unsigned long long warp_cnt[kWarps];
     int warp_heads[kWarps];
-    RecTable<SMALL> rec;
+    int tile_slot[2];              // next tile id, double buffered across iterations
+    RecTable<SMALL, Shape<IPT>::kTile> rec;
     // per 32 output slots of the window: .x = bitmap of slots where a record starts,
     // .y = records that start before this word (tile-wide rank base).  Double buffered.
-    uint2 hb[2][kWords];
+    uint2 hb[2][Shape<IPT>::kWords];
 };
 
 __device__ __forceinline__ unsigned smem_u32(const void *p)
@@ -238,6 +245,20 @@ __device__ __forceinline__ unsigned long long warp_excl_scan64(unsigned long lon
 // NaN-free column  cell(s) < cell(x) => s < x  and  cell(s) > cell(x) => s > x : a bound
 // always lies inside [grid[cell], grid[cell+1]] and is finished there with the filter's own
 // comparison.  The grid narrows the search; it never decides a comparison.
+__device__ __forceinline__ void trace_mark(const ResolveParams &p, int tile, int slot)
+{
+    if (p.trace != nullptr && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        p.trace[(long long)tile * 8 + slot] = t;
+        if (slot == 0) {
+            unsigned smid;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            p.trace[(long long)tile * 8 + 7] = smid;
+        }
+    }
+}
+
 __device__ __forceinline__ int hint_cell(double x, double t0, double inv, int ncell)
 {
     const int c = __double2int_rd(__dmul_rn(__dsub_rn(x, t0), inv));
@@ -246,13 +267,21 @@ __device__ __forceinline__ int hint_cell(double x, double t0, double inv, int nc
 
 // =========================================================================================
 //  search kernel.  SMALL = the whole map (start, sn, hint grid) lives in shared memory.
+//
+//  Software pipeline, one tile deep: an iteration first SEARCHES tile B (bounds, scan, publish
+//  the tile's hit count), then EMITS the tile A it searched one iteration earlier (look-back
+//  for A's batch prefix, offsets, hits).  A's predecessors therefore had a whole search phase
+//  to publish before A asks for them, so the look-back practically never waits, and B's
+//  aggregate is visible to later tiles before A's long emission starts.
 // =========================================================================================
-template <bool SMALL>
+template <bool SMALL, int IPT>
 __global__ void __launch_bounds__(kThreads)
 resolve_search_kernel(const ResolveParams p)
 {
+    using S = Shape<IPT>;
+    constexpr int kIpt = S::kIpt, kTile = S::kTile, kWindow = S::kWindow, kWords = S::kWords;
     extern __shared__ __align__(128) unsigned char dyn_smem[];
-    __shared__ SearchSmem<SMALL> sm;
+    __shared__ SearchSmem<SMALL, IPT> sm;
     double *s_start = reinterpret_cast<double *>(dyn_smem);
     const int *s_sn = reinterpret_cast<const int *>(dyn_smem + p.n_frag_padded * 8);
     const unsigned short *s_grid =
@@ -262,19 +291,17 @@ resolve_search_kernel(const ResolveParams p)
     const unsigned lane_le = 0xffffffffu >> (31 - lane);
 
     if (tid == 0) mbar_init(&sm.mbar, 1);
-#pragma unroll
-    for (int b = 0; b < 2; b++) {
-        sm.hb[b][tid] = make_uint2(0u, 0u);
-        sm.hb[b][tid + kThreads] = make_uint2(0u, 0u);
+    if (tid < kWords) {
+        sm.hb[0][tid] = make_uint2(0u, 0u);
+        sm.hb[1][tid] = make_uint2(0u, 0u);
     }
     unsigned mbar_phase = 0;
-    unsigned hbuf = 0;                   // which heads[] buffer the next window uses
-    long long span_lo = 0, span_hi = 0;  // staged element range of start[]
-    __syncthreads();
+    unsigned hbuf = 0;                   // which hb[] buffer the next window uses
+    long long span_lo = 0, span_hi = 0;  // staged element range of start[] (general kernel)
 
     bool stage_pending = false;
     if (SMALL) {
-        span_hi = p.n_frag_padded;
+        __syncthreads();                 // mbarrier initialised
         if (tid == 0) {
             const unsigned b_start = (unsigned)(p.n_frag_padded * 8);
             const unsigned b_sn = (unsigned)(p.n_frag_padded * 4);
@@ -287,284 +314,430 @@ resolve_search_kernel(const ResolveParams p)
         stage_pending = true;
     }
 
+    // ---- tickets: thread 0 asks for the next tile right after publishing the current one's
+    //      aggregate, so the atomic's L2 round trip hides behind the emission that follows.
+    //      (No deeper look-ahead: a claimed tile is a tile no idle CTA can take.)
+    unsigned t_new = 0;
+    unsigned slot = 0;
+    if (tid == 0) sm.tile_slot[0] = (int)atomicAdd(&p.ctr->ticket[p.epoch & 1u], 1u);
+    __syncthreads();
+    int tileB = sm.tile_slot[0];
+
+    // ---- the tile searched in the previous iteration, waiting to be emitted -----------------
+    int tileA = -1;
+    unsigned long long a_rel = 0, a_cnt_tile = 0;
+    int a_cnt[kIpt];
+    using SrcT = typename std::conditional<SMALL, int, long long>::type;
+    SrcT a_src[kIpt];
+    int a_rank = 0;
+#pragma unroll
+    for (int k = 0; k < kIpt; k++) { a_cnt[k] = 0; a_src[k] = 0; }
+
     for (;;) {
-        const int tile = Scan::next_tile(sm.scan, p.ctr, p.epoch);
-        if (tile >= p.n_tiles) break;
-        const long long q0 = (long long)tile * kTile + (long long)tid * kIpt;
+        const bool haveB = tileB < p.n_tiles;
+        if (!haveB && tileA < 0) break;
 
-        // ---- load this thread's 4 consecutive queries ------------------------------------
-        int pl[kIpt], lv[kIpt];
-        double bg[kIpt], du[kIpt];
-        if (p.vec_ok && q0 + kIpt <= p.nq) {
-            const int4 l4 = __ldcs(reinterpret_cast<const int4 *>(p.q_level + q0));
-            lv[0] = l4.x; lv[1] = l4.y; lv[2] = l4.z; lv[3] = l4.w;
-            if (p.q_playlist) {
-                const int4 p4 = __ldcs(reinterpret_cast<const int4 *>(p.q_playlist + q0));
-                pl[0] = p4.x; pl[1] = p4.y; pl[2] = p4.z; pl[3] = p4.w;
-            } else {
-                pl[0] = pl[1] = pl[2] = pl[3] = 0;
-            }
-            const double2 b0 = __ldcs(reinterpret_cast<const double2 *>(p.q_begin + q0));
-            const double2 b1 = __ldcs(reinterpret_cast<const double2 *>(p.q_begin + q0 + 2));
-            const double2 d0 = __ldcs(reinterpret_cast<const double2 *>(p.q_duration + q0));
-            const double2 d1 = __ldcs(reinterpret_cast<const double2 *>(p.q_duration + q0 + 2));
-            bg[0] = b0.x; bg[1] = b0.y; bg[2] = b1.x; bg[3] = b1.y;
-            du[0] = d0.x; du[1] = d0.y; du[2] = d1.x; du[3] = d1.y;
-        } else {
-#pragma unroll
-            for (int k = 0; k < kIpt; k++) {
-                const bool in = q0 + k < p.nq;
-                lv[k] = in ? __ldcs(p.q_level + q0 + k) : -1;
-                pl[k] = (in && p.q_playlist) ? __ldcs(p.q_playlist + q0 + k) : 0;
-                bg[k] = in ? __ldcs(p.q_begin + q0 + k) : 0.0;
-                du[k] = in ? __ldcs(p.q_duration + q0 + k) : 0.0;
-            }
-        }
-
-        // ---- resolve (playlist, level) -> fragment table --------------------------------
+        // =====================================================================================
+        //  SEARCH tile B
+        // =====================================================================================
         long long off[kIpt];
-        int len[kIpt], st[kIpt], trk[kIpt];
-        int n_unp = 0, n_mis = 0;
-        long long mn = 0x7fffffffffffffffll, mx = -1;
-#pragma unroll
-        for (int k = 0; k < kIpt; k++) {
-            unsigned fl;
-            st[k] = lookup_track(p.desc, p.playlist_base, p.n_playlists, pl[k], lv[k], off[k],
-                                 len[k], fl, &trk[k]);
-            const bool in = q0 + k < p.nq;
-            n_unp += (in && st[k] == HLSMAP_ST_UNPARSED);
-            n_mis += (in && st[k] == HLSMAP_ST_MISSING);
-            if (!SMALL && st[k] == HLSMAP_ST_OK && len[k] > 0) {
-                mn = min(mn, off[k]);
-                mx = max(mx, off[k] + len[k]);
-            }
-        }
-        if (p.status) {
-            if (p.vec_ok && q0 + kIpt <= p.nq) {
-                const unsigned w = (unsigned)st[0] | ((unsigned)st[1] << 8) |
-                                   ((unsigned)st[2] << 16) | ((unsigned)st[3] << 24);
-                *reinterpret_cast<unsigned *>(p.status + q0) = w;
-            } else {
-#pragma unroll
-                for (int k = 0; k < kIpt; k++)
-                    if (q0 + k < p.nq) p.status[q0 + k] = (unsigned char)st[k];
-            }
-        }
-
-        // ---- make the needed span of start[] resident in shared memory -------------------
-        bool staged = true;
-        if (!SMALL) {
-#pragma unroll
-            for (int d = 16; d > 0; d >>= 1) {
-                mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, d));
-                mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, d));
-            }
-            if (lane == 0) { sm.red_min[warp] = mn; sm.red_max[warp] = mx; }
-            __syncthreads();
-#pragma unroll
-            for (int w = 0; w < kWarps; w++) {
-                mn = min(mn, sm.red_min[w]);
-                mx = max(mx, sm.red_max[w]);
-            }
-            const long long need_lo = mn & ~3ll, need_hi = (mx + 3) & ~3ll;
-            if (mx < 0) {
-                staged = true;  // nothing to search in this tile
-            } else if (need_lo >= span_lo && need_hi <= span_hi) {
-                staged = true;  // still resident from the previous tile
-            } else if (need_hi - need_lo <= (long long)p.stage_elems) {
-                span_lo = need_lo;
-                span_hi = need_hi;
-                if (tid == 0) {
-                    const unsigned bytes = (unsigned)((span_hi - span_lo) * 8);
-                    mbar_expect_tx(&sm.mbar, bytes);
-                    bulk_g2s_chunked(dyn_smem, p.start + span_lo, bytes, &sm.mbar);
-                }
-                stage_pending = true;
-            } else {
-                staged = false;  // span larger than shared memory: search in L2/HBM
-            }
-        }
-        if (stage_pending) {
-            mbar_wait(&sm.mbar, mbar_phase);
-            mbar_phase ^= 1u;
-            stage_pending = false;
-        }
-
-        // ---- bounds: [lo, lo+cnt) is exactly what the filter keeps -----------------------
         int lo[kIpt], cnt[kIpt];
+        unsigned long long b_rel = 0, b_cnt_tile = 0;
+        int b_rank = 0;
 #pragma unroll
-        for (int k = 0; k < kIpt; k++) {
-            // one fp64 add, round-to-nearest, never contracted: JS `beginTime + duration`
-            const double ub = __dadd_rn(bg[k], du[k]);
-            int l, h;
-            if (SMALL) {
-                // hint grid narrows each bound to one cell; the filter's comparisons finish it
-                const int4 h0 = __ldg(reinterpret_cast<const int4 *>(p.hint + trk[k]));
-                const int4 h1 = __ldg(reinterpret_cast<const int4 *>(p.hint + trk[k]) + 1);
-                const double t0 = __hiloint2double(h0.y, h0.x);
-                const double inv = __hiloint2double(h0.w, h0.z);
-                const int ncell = st[k] == HLSMAP_ST_OK ? h1.y : 1;
-                const unsigned short *g = s_grid + (st[k] == HLSMAP_ST_OK ? h1.x : 0);
-                const SmemCol col{s_start + (int)off[k]};
-                const int cb = hint_cell(bg[k], t0, inv, ncell);
-                const int cu = hint_cell(ub, t0, inv, ncell);
-                const int b0 = g[cb], b1 = g[cb + 1];
-                const int u0 = g[cu], u1 = g[cu + 1];
-                l = lower_bound_begin(col, b0, b1 - b0, bg[k]);
-                if (bg[k] != bg[k]) l = len[k];           // NaN: `begin <= start` never holds
-                h = upper_bound_ub(col, u0, u1 - u0, ub);
-                if (st[k] != HLSMAP_ST_OK) { l = 0; h = 0; }
-            } else if (staged) {
-                const SmemCol col{s_start + (int)(off[k] - span_lo)};
-                l = lower_bound_begin(col, 0, len[k], bg[k]);
-                h = upper_bound_from(col, l, len[k], ub);
-            } else {
-                const GmemCol col{p.start + off[k]};
-                l = lower_bound_begin(col, 0, len[k], bg[k]);
-                h = upper_bound_from(col, l, len[k], ub);
-            }
-            lo[k] = l;
-            cnt[k] = max(h - l, 0);
-        }
+        for (int k = 0; k < kIpt; k++) { off[k] = 0; lo[k] = 0; cnt[k] = 0; }
 
-        // ---- fused scan of (hit count, non-empty flag): thread -> warp -> CTA -> batch ---
-        unsigned long long tval = 0;
-#pragma unroll
-        for (int k = 0; k < kIpt; k++)
-            tval += (unsigned long long)cnt[k] + ((unsigned long long)(cnt[k] > 0) << kCntBits);
-        unsigned long long wtot;
-        const unsigned long long texcl = warp_excl_scan64(tval, wtot);
-        if (lane == 0) sm.warp_cnt[warp] = wtot;
-        __syncthreads();
-        unsigned long long wbase = 0, tile_tot = 0;
-#pragma unroll
-        for (int w = 0; w < kWarps; w++) {
-            const unsigned long long c = sm.warp_cnt[w];
-            wbase += (w < warp) ? c : 0ull;
-            tile_tot += c;
-        }
-        {   // rare: fold the unparsed / missing tallies (one atomic per warp when non-zero)
-            const unsigned any = __ballot_sync(0xffffffffu, (n_unp | n_mis) != 0);
-            if (any) {
-#pragma unroll
-                for (int d = 16; d > 0; d >>= 1) {
-                    n_unp += __shfl_xor_sync(0xffffffffu, n_unp, d);
-                    n_mis += __shfl_xor_sync(0xffffffffu, n_mis, d);
+        if (haveB) {
+            const long long q0 = (long long)tileB * kTile + (long long)tid * kIpt;
+            const bool full = p.vec_ok && q0 + kIpt <= p.nq;
+            trace_mark(p, tileB, 0);
+
+            // ---- load this thread's consecutive queries -----------------------------------
+            int pl[kIpt], lv[kIpt];
+            double bg[kIpt], du[kIpt];
+            if (full) {
+                if (kIpt == 4) {
+                    const int4 l4 = __ldcs(reinterpret_cast<const int4 *>(p.q_level + q0));
+                    lv[0] = l4.x; lv[1] = l4.y; lv[2] = l4.z; lv[kIpt - 1] = l4.w;
+                    if (p.q_playlist) {
+                        const int4 p4 = __ldcs(reinterpret_cast<const int4 *>(p.q_playlist + q0));
+                        pl[0] = p4.x; pl[1] = p4.y; pl[2] = p4.z; pl[kIpt - 1] = p4.w;
+                    }
+                } else {
+                    const int2 l2 = __ldcs(reinterpret_cast<const int2 *>(p.q_level + q0));
+                    lv[0] = l2.x; lv[1] = l2.y;
+                    if (p.q_playlist) {
+                        const int2 p2 = __ldcs(reinterpret_cast<const int2 *>(p.q_playlist + q0));
+                        pl[0] = p2.x; pl[1] = p2.y;
+                    }
                 }
-                if (lane == 0) {
-                    if (n_unp) atomicAdd(&p.ctr->n_unparsed, (unsigned long long)n_unp);
-                    if (n_mis) atomicAdd(&p.ctr->n_missing, (unsigned long long)n_mis);
+                if (!p.q_playlist) {
+#pragma unroll
+                    for (int k = 0; k < kIpt; k++) pl[k] = 0;
+                }
+#pragma unroll
+                for (int k = 0; k < kIpt; k += 2) {
+                    const double2 b2 = __ldcs(reinterpret_cast<const double2 *>(p.q_begin + q0 + k));
+                    const double2 d2 = __ldcs(reinterpret_cast<const double2 *>(p.q_duration + q0 + k));
+                    bg[k] = b2.x; bg[k + 1] = b2.y;
+                    du[k] = d2.x; du[k + 1] = d2.y;
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < kIpt; k++) {
+                    const bool in = q0 + k < p.nq;
+                    lv[k] = in ? __ldcs(p.q_level + q0 + k) : -1;
+                    pl[k] = (in && p.q_playlist) ? __ldcs(p.q_playlist + q0 + k) : 0;
+                    bg[k] = in ? __ldcs(p.q_begin + q0 + k) : 0.0;
+                    du[k] = in ? __ldcs(p.q_duration + q0 + k) : 0.0;
                 }
             }
-        }
-        const unsigned long long tile_cnt = tile_tot & kCntMask;
-        const unsigned long long tile_base =
-            Scan::exclusive_prefix(sm.scan, p.tile_status, p.epoch, tile, tile_cnt);
 
-        // ---- offsets[q] ------------------------------------------------------------------
-        const unsigned long long my_rel = (wbase + texcl) & kCntMask;   // tile-relative
-        {
-            const unsigned long long my_base = tile_base + my_rel;
-            int4 o4;
-            o4.x = (int)my_base;
-            o4.y = (int)(my_base + cnt[0]);
-            o4.z = (int)(my_base + cnt[0] + cnt[1]);
-            o4.w = (int)(my_base + cnt[0] + cnt[1] + cnt[2]);
-            if (p.vec_ok && q0 + kIpt <= p.nq) {
-                __stcs(reinterpret_cast<int4 *>(p.offsets + q0), o4);
-            } else {
-                if (q0 + 0 < p.nq) p.offsets[q0 + 0] = o4.x;
-                if (q0 + 1 < p.nq) p.offsets[q0 + 1] = o4.y;
-                if (q0 + 2 < p.nq) p.offsets[q0 + 2] = o4.z;
-                if (q0 + 3 < p.nq) p.offsets[q0 + 3] = o4.w;
-            }
-        }
-        if (tile == p.n_tiles - 1 && tid == kThreads - 1) {
-            const unsigned long long total = tile_base + tile_cnt;
-            p.offsets[p.nq] = (int)total;
-            p.result->total_hits = (long long)total;
-            p.result->overflow = total > 0x7fffffffull ? 1 : 0;
-        }
-
-        // ---- expansion: the tile's hits are ONE contiguous output run, written by the whole
-        //      CTA 256 slots at a time whatever the per-query counts (load balanced) --------
-        if (p.sn_out != nullptr && tile_cnt > 0 && tile_cnt <= 0x7fffffffull) {
-            int rank = (int)((wbase + texcl) >> kCntBits);
-            int rel = (int)my_rel;
+            // ---- resolve (playlist, level) -> fragment table -----------------------------
+            int len[kIpt], st[kIpt], trk[kIpt];
+            int n_unp = 0, n_mis = 0;
+            long long mn = 0x7fffffffffffffffll, mx = -1;
 #pragma unroll
             for (int k = 0; k < kIpt; k++) {
-                if (cnt[k] > 0) {
-                    sm.rec.set(rank, rel, off[k] + lo[k]);
-                    rank++;
-                    rel += cnt[k];
+                unsigned fl;
+                st[k] = lookup_track(p.desc, p.playlist_base, p.n_playlists, pl[k], lv[k], off[k],
+                                     len[k], fl, &trk[k]);
+                const bool in = q0 + k < p.nq;
+                n_unp += (in && st[k] == HLSMAP_ST_UNPARSED);
+                n_mis += (in && st[k] == HLSMAP_ST_MISSING);
+                if (!SMALL && st[k] == HLSMAP_ST_OK && len[k] > 0) {
+                    mn = min(mn, off[k]);
+                    mx = max(mx, off[k] + len[k]);
                 }
             }
-            const int total = (int)tile_cnt;
-            int carried = 0;            // records that start before the current window
-            for (int w0 = 0; w0 < total; w0 += kWindow) {
-                uint2 *H = sm.hb[hbuf];
-                {   // mark where this thread's records start inside the window
-                    int r2 = (int)my_rel;
+            if (p.status) {
+                if (full && kIpt == 4) {
+                    const unsigned w = (unsigned)st[0] | ((unsigned)st[1] << 8) |
+                                       ((unsigned)st[2] << 16) | ((unsigned)st[kIpt - 1] << 24);
+                    *reinterpret_cast<unsigned *>(p.status + q0) = w;
+                } else {
+#pragma unroll
+                    for (int k = 0; k < kIpt; k++)
+                        if (q0 + k < p.nq) p.status[q0 + k] = (unsigned char)st[k];
+                }
+            }
+
+            if (SMALL) {
+                // Hint grid: each bound is narrowed to one cell before any table probe; the
+                // per-query chains are written side by side so they overlap (ILP), and the
+                // cell is finished with the filter's own comparisons.
+                int b0[kIpt], bn[kIpt], u0[kIpt], un[kIpt];
+                double ub[kIpt];
+#pragma unroll
+                for (int k = 0; k < kIpt; k++) {
+                    // one fp64 add, round-to-nearest, never contracted: `beginTime + duration`
+                    ub[k] = __dadd_rn(bg[k], du[k]);
+                    const int4 h0 = __ldg(reinterpret_cast<const int4 *>(p.hint + trk[k]));
+                    const int4 h1 = __ldg(reinterpret_cast<const int4 *>(p.hint + trk[k]) + 1);
+                    const double t0 = __hiloint2double(h0.y, h0.x);
+                    const double inv = __hiloint2double(h0.w, h0.z);
+                    const bool ok = st[k] == HLSMAP_ST_OK;
+                    const int ncell = ok ? h1.y : 1;
+                    b0[k] = (ok ? h1.x : 0) + hint_cell(bg[k], t0, inv, ncell);   // grid index
+                    u0[k] = (ok ? h1.x : 0) + hint_cell(ub[k], t0, inv, ncell);
+                }
+                if (stage_pending) {
+                    mbar_wait(&sm.mbar, mbar_phase);
+                    mbar_phase ^= 1u;
+                    stage_pending = false;
+                }
+#pragma unroll
+                for (int k = 0; k < kIpt; k++) {
+                    const int gb0 = s_grid[b0[k]], gb1 = s_grid[b0[k] + 1];
+                    const int gu0 = s_grid[u0[k]], gu1 = s_grid[u0[k] + 1];
+                    b0[k] = gb0; bn[k] = gb1 - gb0;
+                    u0[k] = gu0; un[k] = gu1 - gu0;
+                }
+                // two fixed halving steps settle cells of up to 3 fragments without a loop
+#pragma unroll
+                for (int it = 0; it < 2; it++) {
 #pragma unroll
                     for (int k = 0; k < kIpt; k++) {
-                        if (cnt[k] > 0) {
-                            const unsigned d = (unsigned)(r2 - w0);
-                            if (d < (unsigned)kWindow) atomicOr(&H[d >> 5].x, 1u << (d & 31));
-                            r2 += cnt[k];
+                        const double *col = s_start + (int)off[k];
+                        const int hb_ = bn[k] >> 1, hu_ = un[k] >> 1;
+                        const bool gb = bn[k] > 0 && !(bg[k] <= col[b0[k] + hb_]);
+                        const bool gu = un[k] > 0 && (col[u0[k] + hu_] <= ub[k]);
+                        b0[k] = gb ? b0[k] + hb_ + 1 : b0[k];
+                        bn[k] = gb ? bn[k] - hb_ - 1 : hb_;
+                        u0[k] = gu ? u0[k] + hu_ + 1 : u0[k];
+                        un[k] = gu ? un[k] - hu_ - 1 : hu_;
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < kIpt; k++) {
+                    const SmemCol col{s_start + (int)off[k]};
+                    int l = b0[k], h = u0[k];
+                    if (bn[k] > 0) l = lower_bound_begin(col, l, bn[k], bg[k]);   // crowded cell
+                    if (un[k] > 0) h = upper_bound_ub(col, h, un[k], ub[k]);
+                    if (bg[k] != bg[k]) l = len[k];       // NaN: `begin <= start` never holds
+                    if (st[k] != HLSMAP_ST_OK) { l = 0; h = 0; }
+                    lo[k] = l;
+                    cnt[k] = max(h - l, 0);
+                }
+            } else {
+                // ---- make the span of start[] this tile needs resident in shared memory -------
+                bool staged = true;
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) {
+                    mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, d));
+                    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+                }
+                if (lane == 0) { sm.red_min[warp] = mn; sm.red_max[warp] = mx; }
+                __syncthreads();
+#pragma unroll
+                for (int w = 0; w < kWarps; w++) {
+                    mn = min(mn, sm.red_min[w]);
+                    mx = max(mx, sm.red_max[w]);
+                }
+                const long long need_lo = mn & ~3ll, need_hi = (mx + 3) & ~3ll;
+                if (mx < 0) {
+                    staged = true;  // nothing to search in this tile
+                } else if (need_lo >= span_lo && need_hi <= span_hi) {
+                    staged = true;  // still resident from the previous tile
+                } else if (need_hi - need_lo <= (long long)p.stage_elems) {
+                    span_lo = need_lo;
+                    span_hi = need_hi;
+                    if (tid == 0) {
+                        const unsigned bytes = (unsigned)((span_hi - span_lo) * 8);
+                        mbar_expect_tx(&sm.mbar, bytes);
+                        bulk_g2s_chunked(dyn_smem, p.start + span_lo, bytes, &sm.mbar);
+                    }
+                    mbar_wait(&sm.mbar, mbar_phase);
+                    mbar_phase ^= 1u;
+                } else {
+                    staged = false;  // span larger than shared memory: search in L2/HBM
+                }
+                // ---- bounds: [lo, lo+cnt) is exactly what the filter keeps ----------------
+#pragma unroll
+                for (int k = 0; k < kIpt; k++) {
+                    const double ub = __dadd_rn(bg[k], du[k]);
+                    int l, h;
+                    if (staged) {
+                        const SmemCol col{s_start + (int)(off[k] - span_lo)};
+                        l = lower_bound_begin(col, 0, len[k], bg[k]);
+                        h = upper_bound_from(col, l, len[k], ub);
+                    } else {
+                        const GmemCol col{p.start + off[k]};
+                        l = lower_bound_begin(col, 0, len[k], bg[k]);
+                        h = upper_bound_from(col, l, len[k], ub);
+                    }
+                    lo[k] = l;
+                    cnt[k] = max(h - l, 0);
+                }
+            }
+
+            trace_mark(p, tileB, 1);
+            // ---- fused scan of (hit count, non-empty flag): thread -> warp -> CTA ---------
+            unsigned long long tval = 0;
+#pragma unroll
+            for (int k = 0; k < kIpt; k++)
+                tval += (unsigned long long)cnt[k] + ((unsigned long long)(cnt[k] > 0) << kCntBits);
+            unsigned long long wtot;
+            const unsigned long long texcl = warp_excl_scan64(tval, wtot);
+            if (lane == 0) sm.warp_cnt[warp] = wtot;
+            __syncthreads();     // also: everyone is past the previous emission of rec[]/hb[]
+            unsigned long long wbase = 0, tile_tot = 0;
+#pragma unroll
+            for (int w = 0; w < kWarps; w++) {
+                const unsigned long long c = sm.warp_cnt[w];
+                wbase += (w < warp) ? c : 0ull;
+                tile_tot += c;
+            }
+            b_cnt_tile = tile_tot & kCntMask;
+            Scan::publish_aggregate(p.tile_status, p.epoch, tileB, b_cnt_tile);
+            trace_mark(p, tileB, 2);
+            if (tid == 0) t_new = atomicAdd(&p.ctr->ticket[p.epoch & 1u], 1u);   // lands during emit
+            b_rel = (wbase + texcl) & kCntMask;
+            b_rank = (int)((wbase + texcl) >> kCntBits);
+            {   // rare: fold the unparsed / missing tallies (one atomic per warp when non-zero)
+                const unsigned any = __ballot_sync(0xffffffffu, (n_unp | n_mis) != 0);
+                if (any) {
+#pragma unroll
+                    for (int d = 16; d > 0; d >>= 1) {
+                        n_unp += __shfl_xor_sync(0xffffffffu, n_unp, d);
+                        n_mis += __shfl_xor_sync(0xffffffffu, n_mis, d);
+                    }
+                    if (lane == 0) {
+                        if (n_unp) atomicAdd(&p.ctr->n_unparsed, (unsigned long long)n_unp);
+                        if (n_mis) atomicAdd(&p.ctr->n_missing, (unsigned long long)n_mis);
+                    }
+                }
+            }
+        }
+
+        // =====================================================================================
+        //  EMIT tile A (searched one iteration ago): look-back, offsets, hits
+        // =====================================================================================
+        if (tileA >= 0) {
+            const long long q0 = (long long)tileA * kTile + (long long)tid * kIpt;
+            const bool full = p.vec_ok && q0 + kIpt <= p.nq;
+            trace_mark(p, tileA, 3);
+            const unsigned long long tile_base =
+                Scan::wait_prefix(sm.scan, p.tile_status, p.epoch, tileA, a_cnt_tile);
+            trace_mark(p, tileA, 4);
+
+            // ---- offsets[q] --------------------------------------------------------------
+            {
+                unsigned long long run = tile_base + a_rel;
+                int o[kIpt];
+#pragma unroll
+                for (int k = 0; k < kIpt; k++) {
+                    o[k] = (int)run;
+                    run += (unsigned long long)a_cnt[k];
+                }
+                if (full && kIpt == 4) {
+                    __stcs(reinterpret_cast<int4 *>(p.offsets + q0), make_int4(o[0], o[1], o[2], o[kIpt - 1]));
+                } else if (full && kIpt == 2) {
+                    __stcs(reinterpret_cast<int2 *>(p.offsets + q0), make_int2(o[0], o[1]));
+                } else {
+#pragma unroll
+                    for (int k = 0; k < kIpt; k++)
+                        if (q0 + k < p.nq) p.offsets[q0 + k] = o[k];
+                }
+            }
+            if (tileA == p.n_tiles - 1 && tid == kThreads - 1) {
+                const unsigned long long total_hits = tile_base + a_cnt_tile;
+                p.offsets[p.nq] = (int)total_hits;
+                p.result->total_hits = (long long)total_hits;
+                p.result->overflow = total_hits > 0x7fffffffull ? 1 : 0;
+            }
+
+            // ---- expansion: the tile's hits form ONE contiguous output run; the whole CTA
+            //      writes it 256 slots at a time whatever the per-query counts (load balanced)
+            const bool expand = p.sn_out != nullptr && a_cnt_tile > 0 && a_cnt_tile <= 0x7fffffffull;
+            if (expand) {
+                const int total = (int)a_cnt_tile;
+                {   // records: one per query that kept >= 1 fragment, in query order
+                    int rank = a_rank, rel = (int)a_rel;
+#pragma unroll
+                    for (int k = 0; k < kIpt; k++) {
+                        if (a_cnt[k] > 0) {
+                            sm.rec.set(rank, rel, a_src[k]);
+                            rank++;
+                            rel += a_cnt[k];
                         }
                     }
                 }
-                __syncthreads();
-                {   // rank_base[word] = carried + heads in earlier words (2 words per thread)
-                    const int c0 = __popc(H[2 * tid].x), c1 = __popc(H[2 * tid + 1].x);
-                    int wsum;
-                    const int ex = warp_excl_scan(c0 + c1, wsum);
-                    if (lane == 0) sm.warp_heads[warp] = wsum;
-                    __syncthreads();
-                    int before = carried, all = 0;
-#pragma unroll
-                    for (int w = 0; w < kWarps; w++) {
-                        const int c = sm.warp_heads[w];
-                        before += (w < warp) ? c : 0;
-                        all += c;
-                    }
-                    H[2 * tid].y = (unsigned)(before + ex);
-                    H[2 * tid + 1].y = (unsigned)(before + ex + c0);
-                    carried += all;
-                }
-                __syncthreads();
-                const int wend = min(total - w0, kWindow);
-                const long long obase = (long long)tile_base + w0;
-                for (int q = tid; q < wend; q += kThreads) {
-                    const uint2 hw = H[q >> 5];
+                int carried = 0;            // records that start before the current window
+                // Slot q: the word's rank base + the records starting at or before this lane's
+                // slot name the record; its source fragment follows by offset.
+                auto emit = [&](const uint2 hw, int slot, double &t, int &s) {
                     const int r = (int)hw.y + __popc(hw.x & lane_le) - 1;
                     int rrel;
                     long long src;
                     sm.rec.get(r, rrel, src);
-                    src += w0 + q - rrel;
-                    const long long o = obase + q;
-                    if (o < p.capacity) {
+                    src += slot - rrel;
+                    if (SMALL) {
+                        t = s_start[(int)src];
+                        s = s_sn[(int)src];
+                    } else {
+                        t = __ldg(p.start + src);     // L2-hot: the span was just bulk-copied
+                        s = __ldg(p.sn + src);
+                    }
+                };
+                const bool all_fit = (long long)tile_base + total <= p.capacity;   // CTA-uniform
+                for (int w0 = 0; w0 < total; w0 += kWindow) {
+                    uint2 *H = sm.hb[hbuf];
+                    {   // mark where this thread's records start inside the window, rank words
+                        int r2 = (int)a_rel;
+#pragma unroll
+                        for (int k = 0; k < kIpt; k++) {
+                            if (a_cnt[k] > 0) {
+                                const unsigned d = (unsigned)(r2 - w0);
+                                if (d < (unsigned)kWindow) atomicOr(&H[d >> 5].x, 1u << (d & 31));
+                                r2 += a_cnt[k];
+                            }
+                        }
+                        __syncthreads();
+                        const int c0 = tid < kWords ? __popc(H[tid].x) : 0;
+                        int wsum;
+                        const int ex = warp_excl_scan(c0, wsum);
+                        if (lane == 0) sm.warp_heads[warp] = wsum;
+                        __syncthreads();
+                        int before = carried, all = 0;
+#pragma unroll
+                        for (int w = 0; w < kWarps; w++) {
+                            const int c = sm.warp_heads[w];
+                            before += (w < warp) ? c : 0;
+                            all += c;
+                        }
+                        if (tid < kWords) H[tid].y = (unsigned)(before + ex);
+                        carried += all;
+                        __syncthreads();
+                    }
+                    const int wend = min(total - w0, kWindow);
+                    const uint2 *hp = H + warp;                // this warp's word, 8 words apart
+                    double *tp = p.time_out + ((long long)tile_base + w0 + tid);
+                    int *sp = p.sn_out + ((long long)tile_base + w0 + tid);
+                    int q = tid;
+                    if (all_fit) {
+                        for (; q + 3 * kThreads < wend; q += 4 * kThreads) {
+                            double t[4];
+                            int s[4];
+                            uint2 hw[4];
+#pragma unroll
+                            for (int j = 0; j < 4; j++) hw[j] = hp[j * kWarps];
+#pragma unroll
+                            for (int j = 0; j < 4; j++) emit(hw[j], w0 + q + j * kThreads, t[j], s[j]);
+#pragma unroll
+                            for (int j = 0; j < 4; j++) {
+                                __stcs(tp + j * kThreads, t[j]);   // time = fragment.start (:48)
+                                __stcs(sp + j * kThreads, s[j]);   // sn   = fragment.sn    (:46)
+                            }
+                            hp += 4 * kWarps;
+                            tp += 4 * kThreads;
+                            sp += 4 * kThreads;
+                        }
+                    }
+                    for (; q < wend; q += kThreads) {
                         double t;
                         int s;
-                        if (SMALL) {
-                            t = s_start[(int)src];
-                            s = s_sn[(int)src];
-                        } else {
-                            t = staged ? s_start[(int)(src - span_lo)] : __ldg(p.start + src);
-                            s = __ldg(p.sn + src);
+                        emit(*hp, w0 + q, t, s);
+                        if ((long long)tile_base + w0 + q < p.capacity) {
+                            __stcs(tp, t);
+                            __stcs(sp, s);
                         }
-                        __stcs(p.time_out + o, t);   // time = fragment.start  (media-map.js:48)
-                        __stcs(p.sn_out + o, s);     // sn   = fragment.sn     (media-map.js:46)
+                        hp += kWarps;
+                        tp += kThreads;
+                        sp += kThreads;
                     }
+                    __syncthreads();
+                    if (tid < kWords) H[tid].x = 0u;   // next used two windows from now
+                    hbuf ^= 1u;
                 }
-                __syncthreads();
-                H[2 * tid].x = 0u;        // this buffer is next used two windows from now
-                H[2 * tid + 1].x = 0u;
-                hbuf ^= 1u;
             }
         }
 
-        if (Scan::tile_done(p.ctr, p.n_tiles)) Scan::finish_batch(p.ctr, p.result, p.epoch);
+        // ---- rotate the pipeline: B becomes the pending tile --------------------------------
+        if (tileA >= 0) trace_mark(p, tileA, 5);
+        slot ^= 1u;            // alternate slots: the one read last iteration is not rewritten
+        if (tid == 0) sm.tile_slot[slot] = haveB ? (int)t_new : p.n_tiles;
+        __syncthreads();       // all global writes of tile A issued; next tile id visible
+        if (tid == kThreads - 1 && tileA >= 0) {
+            // completion count off the critical path: only this thread pays for the fence
+            __threadfence();
+            atomicAdd(&p.ctr->done, 1u);
+            if (tileA == p.n_tiles - 1) {                  // the batch's last tile: wrap up
+                while (ld_relaxed_u32(&p.ctr->done) != (unsigned)p.n_tiles) { }
+                __threadfence();
+                Scan::finish_batch(p.ctr, p.result, p.epoch);
+            }
+        }
+        tileA = haveB ? tileB : -1;
+        a_rel = b_rel;
+        a_cnt_tile = b_cnt_tile;
+        a_rank = b_rank;
+#pragma unroll
+        for (int k = 0; k < kIpt; k++) {
+            a_cnt[k] = cnt[k];
+            a_src[k] = (SrcT)(off[k] + lo[k]);
+        }
+        tileB = sm.tile_slot[slot];
     }
     // never leave with a bulk copy still landing in this CTA's shared memory
     if (stage_pending) mbar_wait(&sm.mbar, mbar_phase);
@@ -831,24 +1004,25 @@ static int sm_count()
     return g_sm_count;
 }
 
-int resolve_search_max_grid(size_t smem, bool small)
+template <bool SMALL, int IPT>
+static int max_grid_of(size_t smem)
 {
     int per_sm = 0;
-    cudaError_t e;
-    if (small) {
-        cudaFuncSetAttribute(resolve_search_kernel<true>,
-                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resolve_search_kernel<true>,
-                                                          kThreads, smem);
-    } else {
-        cudaFuncSetAttribute(resolve_search_kernel<false>,
-                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resolve_search_kernel<false>,
-                                                          kThreads, smem);
-    }
-    if (e != cudaSuccess || per_sm < 1) per_sm = 1;
+    cudaFuncSetAttribute(resolve_search_kernel<SMALL, IPT>,
+                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resolve_search_kernel<SMALL, IPT>,
+                                                      kThreads, smem) != cudaSuccess || per_sm < 1)
+        per_sm = 1;
     return per_sm * sm_count();
 }
+
+int resolve_search_max_grid(size_t smem, bool small, int ipt)
+{
+    if (small) return ipt == 2 ? max_grid_of<true, 2>(smem) : max_grid_of<true, 4>(smem);
+    return max_grid_of<false, 4>(smem);
+}
+
+int resolve_search_tile(bool small, int ipt) { return kThreads * ((small && ipt == 2) ? 2 : 4); }
 
 int resolve_filter_max_grid()
 {
@@ -861,8 +1035,9 @@ int resolve_filter_max_grid()
 
 cudaError_t launch_resolve_search(const ResolveParams &p, int grid, size_t smem, cudaStream_t s)
 {
-    if (p.small) resolve_search_kernel<true><<<grid, kThreads, smem, s>>>(p);
-    else resolve_search_kernel<false><<<grid, kThreads, smem, s>>>(p);
+    if (p.small && p.ipt == 2) resolve_search_kernel<true, 2><<<grid, kThreads, smem, s>>>(p);
+    else if (p.small) resolve_search_kernel<true, 4><<<grid, kThreads, smem, s>>>(p);
+    else resolve_search_kernel<false, 4><<<grid, kThreads, smem, s>>>(p);
     return cudaGetLastError();
 }
 

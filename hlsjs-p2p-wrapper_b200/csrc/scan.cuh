@@ -22,6 +22,13 @@ __device__ __forceinline__ void st_relaxed_u64(unsigned long long *p, unsigned l
     asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
+__device__ __forceinline__ unsigned ld_relaxed_u32(const unsigned *p)
+{
+    unsigned v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
 template <int THREADS>
 struct TileScan {
     static constexpr int NW = THREADS / 32;
@@ -56,23 +63,29 @@ struct TileScan {
         return t;
     }
 
-    // Publishes `aggregate` for `tile` and returns the sum of the aggregates of all
-    // earlier tiles.  Must be called by every thread of the CTA.
-    __device__ static unsigned long long exclusive_prefix(Smem &s, unsigned long long *status,
-                                                          unsigned epoch, int tile,
-                                                          unsigned long long aggregate)
+    // A batch may not produce more than INT32_MAX entries (the host reports OVERFLOW), so
+    // published values saturate far above that instead of wrapping the 40-bit field.
+    static constexpr unsigned long long kSat = 1ull << 33;
+
+    // Step 1: make this tile's aggregate visible to later tiles (tile 0 publishes a prefix).
+    __device__ static void publish_aggregate(unsigned long long *status, unsigned epoch, int tile,
+                                             unsigned long long aggregate)
+    {
+        aggregate = aggregate < kSat ? aggregate : kSat;
+        if (threadIdx.x == 0)
+            st_relaxed_u64(&status[tile],
+                           make_status(epoch, tile == 0 ? kStatePrefix : kStateAggregate, aggregate));
+    }
+
+    // Step 2: the sum of the aggregates of all earlier tiles.  Called by every thread of the
+    // CTA after publish_aggregate(); work that does not need the prefix can sit in between.
+    __device__ static unsigned long long wait_prefix(Smem &s, unsigned long long *status,
+                                                     unsigned epoch, int tile,
+                                                     unsigned long long aggregate)
     {
         const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-        // A batch may not produce more than INT32_MAX entries (the host reports OVERFLOW), so
-        // published values saturate far above that instead of wrapping the 40-bit field.
-        const unsigned long long kSat = 1ull << 33;
+        if (tile == 0) return 0ull;
         aggregate = aggregate < kSat ? aggregate : kSat;
-        if (tile == 0) {
-            if (tid == 0) st_relaxed_u64(&status[0], make_status(epoch, kStatePrefix, aggregate));
-            return 0ull;
-        }
-        if (tid == 0) st_relaxed_u64(&status[tile], make_status(epoch, kStateAggregate, aggregate));
-
         unsigned long long running = 0;
         int top = tile - 1;
         for (;;) {
@@ -80,10 +93,11 @@ struct TileScan {
             unsigned long long val = 0;
             bool is_prefix = true;  // idx < 0: the virtual tile -1 holds prefix 0
             if (idx >= 0) {
-                unsigned long long w;
-                do {
+                unsigned long long w = ld_relaxed_u64(&status[idx]);
+                while ((unsigned)(w >> 42) != (epoch & kEpochMask)) {
+                    __nanosleep(256);   // do not flood the few L2 lines every CTA polls
                     w = ld_relaxed_u64(&status[idx]);
-                } while ((unsigned)(w >> 42) != (epoch & kEpochMask));
+                }
                 val = w & ((1ull << kValueBits) - 1ull);
                 is_prefix = ((w >> kValueBits) & 3ull) == kStatePrefix;
             }
@@ -108,6 +122,48 @@ struct TileScan {
         if (tid == 0)
             st_relaxed_u64(&status[tile], make_status(epoch, kStatePrefix, running + aggregate));
         return running;
+    }
+
+    __device__ static unsigned long long exclusive_prefix(Smem &s, unsigned long long *status,
+                                                          unsigned epoch, int tile,
+                                                          unsigned long long aggregate)
+    {
+        publish_aggregate(status, epoch, tile, aggregate);
+        return wait_prefix(s, status, epoch, tile, aggregate);
+    }
+
+    // Ticket prefetch: thread 0 asks for the CTA's next tile while the current one is still
+    // being written, so the L2 round trip of the atomic is off the critical path.
+    __device__ static unsigned prefetch_ticket(ScanCounters *ctr, unsigned epoch)
+    {
+        return threadIdx.x == 0 ? atomicAdd(&ctr->ticket[epoch & 1u], 1u) : 0u;
+    }
+    __device__ static int next_tile_prefetched(Smem &s, unsigned ticket)
+    {
+        __syncthreads();  // previous tile fully consumed (shared buffers, s.tile)
+        if (threadIdx.x == 0) s.tile = (int)ticket;
+        __syncthreads();
+        return s.tile;
+    }
+
+    // Fire-and-forget completion count: no thread waits for the atomic's return value.
+    __device__ static void tile_done_async(ScanCounters *ctr)
+    {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            atomicAdd(&ctr->done, 1u);
+        }
+    }
+    // Called (by all threads) in the CTA that ran the batch's LAST tile, after its own
+    // tile_done_async(): thread 0 waits for every other tile, then publishes the result.
+    __device__ static void finish_when_all_done(ScanCounters *ctr, DeviceResult *result,
+                                                unsigned epoch, int n_tiles)
+    {
+        if (threadIdx.x != 0) return;
+        while (ld_relaxed_u32(&ctr->done) != (unsigned)n_tiles) { }
+        __threadfence();
+        finish_batch(ctr, result, epoch);
     }
 
     // Call once per finished tile, after its global writes.  Returns true in thread 0 of
