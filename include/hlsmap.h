@@ -2,7 +2,7 @@
  * hlsmap.h -- C ABI of the B200-native MediaMap batch engine (libhlsmap.so).
  *
  * This is the drop-in boundary for ONE path of streamroot-hlsjs-p2p-wrapper: the
- * MediaMap / SegmentView / TrackView mapping layer (lib/integration/mapping/*.js).  The
+ * MediaMap / SegmentView / TrackView mapping layer (lib/integration/mapping/, three .js).  The
  * reference has no FFI of its own (it is pure JavaScript); the entry points below are
  * what an N-API addon bound under the reference's JS classes calls -- see
  * INTEGRATION.md for that stub.  Every function cites the reference code it replaces

@@ -1,0 +1,164 @@
+'use strict';
+/*
+ * Drop-in for streamroot-hlsjs-p2p-wrapper's lib/integration/mapping/{media-map,segment-view,
+ * track-view}.js backed by libhlsmap (B200).  Same constructors, methods, return shapes and
+ * error messages; `getSegmentList` runs on the GPU through the N-API addon (js/addon), and
+ * MediaMap gains `getSegmentListBatch`.  One file, CommonJS; `module.exports.MediaMap` etc. are
+ * what the three reference modules default-export.
+ *
+ * Not runnable in the build image (no Node there); the same behaviour is exercised through the
+ * Python mirror hlsjs-p2p-wrapper_b200/mapping.py by tests/test_gpu_media_map.py.
+ */
+const native = require('./addon/build/Release/hlsmap_napi.node');
+
+// ---- value types (host side: these are JS object semantics, not arithmetic) -----------------
+function TrackView(fields) {            // track-view.js:3-6
+  this.level = fields.level;
+  this.urlId = fields.urlId;
+}
+TrackView.prototype.viewToString = function () {            // track-view.js:11-13
+  return 'L' + this.level + 'U' + this.urlId;
+};
+TrackView.prototype.isEqual = function (other) {            // track-view.js:19-24
+  return !!other && other.level === this.level && other.urlId === this.urlId;
+};
+Object.defineProperty(TrackView.prototype, 'type', {        // track-view.js:26-28
+  get() { return 'video'; },
+});
+
+function SegmentView(fields) {          // segment-view.js:22-26 (key order = JSON order)
+  this.sn = fields.sn;
+  this.trackView = new TrackView(fields.trackView);
+  this.time = fields.time;
+}
+SegmentView.fromArrayBuffer = function (buffer) {           // segment-view.js:9-17
+  const words = new Uint32Array(buffer);
+  return new SegmentView({ trackView: new TrackView({ level: words[0], urlId: words[1] }), sn: words[2] });
+};
+SegmentView.prototype.isEqual = function (other) {          // segment-view.js:33-39
+  return !!other && this.sn === other.sn && this.trackView.isEqual(other.trackView);
+};
+SegmentView.prototype.isInTrack = function (trackView) {    // segment-view.js:45-47
+  return this.trackView.isEqual(trackView);
+};
+SegmentView.prototype.viewToString = function () {          // segment-view.js:52-54
+  return this.trackView.viewToString() + 'S' + this.sn;
+};
+SegmentView.prototype.toArrayBuffer = function () {         // segment-view.js:59-61
+  return Uint32Array.of(this.trackView.level, this.trackView.urlId, this.sn).buffer;
+};
+SegmentView.prototype.getId = function () { return this.sn; };   // segment-view.js:63-65
+
+// Batched forms over SoA typed arrays: GPU kernels (views.cu)
+SegmentView.packBatch = (ctx, level, urlId, sn) => native.viewPack(ctx, level, urlId, sn);
+SegmentView.unpackBatch = (ctx, wire) => native.viewUnpack(ctx, wire);
+SegmentView.isEqualBatch = (ctx, a, b) => native.viewIsEqual(ctx, a.level, a.urlId, a.sn, b.level, b.urlId, b.sn);
+SegmentView.viewToStringBatch = (ctx, level, urlId, sn) => native.viewFormat(ctx, level, urlId, sn, true);
+
+// ---- MediaMap --------------------------------------------------------------------------------
+const ST_UNPARSED = 1, ST_MISSING = 2, ST_EMPTY = 3;
+let sharedContext = null;
+
+function snapshotLevels(levels) {
+  // hls.levels[..].details.fragments (AoS of JS objects) -> SoA typed arrays (a13)
+  const nTracks = levels.length;
+  let total = 0;
+  for (const level of levels) if (level && level.details) total += level.details.fragments.length;
+  const t = {
+    playlistBase: Int32Array.of(0, nTracks), trackOffset: new BigInt64Array(nTracks + 1),
+    trackState: new Uint8Array(nTracks), urlCount: new Int32Array(nTracks),
+    start: new Float64Array(total), sn: new Int32Array(total), duration: new Float64Array(total),
+  };
+  let at = 0;
+  levels.forEach((level, i) => {
+    if (level) {
+      t.urlCount[i] = level.url ? level.url.length : 0;
+      t.trackState[i] = level.details ? 2 : 1;
+      if (level.details) {
+        for (const f of level.details.fragments) {
+          t.start[at] = f.start; t.sn[at] = f.sn;
+          t.duration[at] = f.duration === undefined ? NaN : f.duration;
+          at++;
+        }
+      }
+    }
+    t.trackOffset[i + 1] = BigInt(at);
+  });
+  return t;
+}
+
+function levelsSignature(levels) {
+  return levels.map((l) => {
+    const fr = l && l.details ? l.details.fragments : null;
+    const n = fr ? fr.length : -1;
+    return n > 0 ? [n, fr[0].sn, fr[n - 1].sn, fr[n - 1].start].join(':') : String(n);
+  }).join('|');
+}
+
+class MediaMap {
+  constructor(hls, options) {           // media-map.js:6-8
+    this.hls = hls;
+    this._device = options && options.device !== undefined ? options.device : 0;
+    this._map = null;
+    this._signature = null;
+  }
+
+  _deviceMap() {                        // the reference reads hls.levels on every call (:28,41)
+    const signature = levelsSignature(this.hls.levels);
+    if (signature !== this._signature) {
+      if (!sharedContext) sharedContext = native.createContext(this._device);
+      if (this._map) native.destroyMap(this._map);
+      this._map = native.createMap(sharedContext, snapshotLevels(this.hls.levels));
+      this._signature = signature;
+    }
+    return this._map;
+  }
+
+  getSegmentTime(segmentView) {         // media-map.js:14-19
+    if (segmentView.time === undefined) throw new Error('getSegmentTime: segmentView.time is undefined');
+    return segmentView.time;
+  }
+
+  getSegmentList(trackView, beginTime, duration) {          // media-map.js:27-54
+    const levels = this.hls.levels;     // TypeError below if undefined, like the reference
+    if (!levels[trackView.level]) throw new Error("getSegmentList: level doesn't exist");
+    if (!levels[trackView.level].details) {
+      console.warn('getSegmentList: level not parsed yet');
+      return [];
+    }
+    const r = native.getSegmentList(this._deviceMap(), null, Int32Array.of(trackView.level),
+      Float64Array.of(beginTime), Float64Array.of(duration));
+    const out = new Array(r.totalHits);
+    for (let i = 0; i < r.totalHits; i++) out[i] = new SegmentView({ sn: r.sn[i], trackView, time: r.time[i] });
+    return out;
+  }
+
+  // Added entry point: typed arrays in, typed arrays out, no per-hit objects.
+  // queries = {playlist?: Int32Array, level: Int32Array, beginTime: Float64Array, duration: Float64Array}
+  // -> {offsets: Int32Array(Q+1), sn: Int32Array(H), time: Float64Array(H), status: Uint8Array(Q)}
+  getSegmentListBatch(queries, options) {
+    const r = native.getSegmentList(this._deviceMap(), queries.playlist || null, queries.level,
+      queries.beginTime, queries.duration);
+    if (!(options && options.strict === false)) {
+      if (r.nMissing > 0) throw new Error("getSegmentList: level doesn't exist");
+      if (r.nUnparsed > 0) console.warn('getSegmentList: level not parsed yet');
+    }
+    return r;
+  }
+
+  getTrackList() {                      // media-map.js:60-73
+    if (!this.hls.levels) return [];
+    const r = native.getTrackList(this._deviceMap(), 0);
+    return Array.from(r.level, (level, i) => new TrackView({ level, urlId: r.urlId[i] }));
+  }
+
+  getSegmentDuration(segmentView) {     // media-map.js:81-87
+    const level = this.hls.levels[segmentView.trackView.level];
+    void level.details.fragments;       // TypeError on a missing / unparsed level, like the reference
+    const r = native.getSegmentDuration(this._deviceMap(), null, Int32Array.of(segmentView.trackView.level));
+    if (r.status[0] === ST_EMPTY) throw new Error('All segments should have a duration');
+    return Number.isNaN(r.out[0]) ? undefined : r.out[0];
+  }
+}
+
+module.exports = { MediaMap, SegmentView, TrackView, native, ST_UNPARSED, ST_MISSING, ST_EMPTY };
