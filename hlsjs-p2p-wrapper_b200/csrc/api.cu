@@ -1060,4 +1060,151 @@ int hlsmap_view_format(hlsmap_ctx *ctx, int64_t n, const int32_t *level, const i
     return r;
 }
 
+
+// ---------------------------------------------------------------------------------------
+//  getSegmentList without any allocation
+// ---------------------------------------------------------------------------------------
+// Who this is for: code that must not touch the CUDA allocator while it runs -- a media
+// server's real-time thread with a no-malloc rule, a plugin running inside a host that owns
+// all device memory and forbids cudaMalloc from callbacks, or a caller whose own pool already
+// holds every byte of HBM.  hlsmap_get_segment_list_dev() grows the context's tile-status
+// scratch with cudaMalloc the first time a batch is larger than any before it; this variant
+// never does.  Its scratch is the fixed array below, which lives in every GPU context that
+// loads the library (about 0.5 MiB per GPU, until the process exits).
+//
+// Layout, in 8-byte words: [0,4) ScanCounters, [8,12) DeviceResult, [32, 32+kNoAllocMaxTiles)
+// one look-back status word per tile.
+namespace {
+constexpr long long kNoAllocMaxTiles = 65536;
+constexpr int kNoAllocHeaderWords = 32;
+constexpr int kNoAllocMaxDevices = 64;
+}  // namespace
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[kNoAllocHeaderWords + kNoAllocMaxTiles];
+
+namespace {
+// `g_noalloc_scratch` is only a stand-in name on the host; the device address has to be asked
+// for, once per GPU, with that GPU current.  Nothing here allocates.
+void *g_noalloc_ptr[kNoAllocMaxDevices] = {};
+
+int noalloc_scratch_for(hlsmap_ctx *ctx, unsigned long long **out)
+{
+    if (ctx->device < 0 || ctx->device >= kNoAllocMaxDevices)
+        return fail(HLSMAP_ERR_INVALID, "no-alloc entry point: device ordinal beyond its table");
+    if (!g_noalloc_ptr[ctx->device]) {
+        void *ptr = nullptr;
+        CK(cudaSetDevice(ctx->device));
+        cudaError_t e = cudaGetSymbolAddress((void **)&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess || !ptr) {
+            cudaGetLastError();
+            return fail(HLSMAP_ERR_CUDA, std::string("cudaGetSymbolAddress(no-alloc scratch): ") +
+                                             cudaGetErrorString(e));
+        }
+        g_noalloc_ptr[ctx->device] = ptr;
+    }
+    *out = static_cast<unsigned long long *>(g_noalloc_ptr[ctx->device]);
+    return HLSMAP_OK;
+}
+}  // namespace
+
+int hlsmap_get_segment_list_noalloc_dev(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
+                                        const int32_t *d_level, const double *d_begin,
+                                        const double *d_duration, int32_t *d_offsets,
+                                        int32_t *d_sn_out, double *d_time_out,
+                                        int64_t hit_capacity, uint8_t *d_status, void *stream,
+                                        hlsmap_result *result)
+{
+    if (!map) return fail(HLSMAP_ERR_INVALID, "null map");
+    hlsmap_ctx *ctx = map->ctx;
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (nq < 0 || !d_offsets || (nq > 0 && (!d_level || !d_begin || !d_duration)))
+        return fail(HLSMAP_ERR_INVALID, "get_segment_list_noalloc: null query/offset arrays");
+    if ((d_sn_out == nullptr) != (d_time_out == nullptr))
+        return fail(HLSMAP_ERR_INVALID, "get_segment_list_noalloc: sn_out and time_out go together");
+    if (hit_capacity < 0) return fail(HLSMAP_ERR_INVALID, "negative hit capacity");
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+
+    const int path = pick_path(map);
+    const int tile_q = path == HLSMAP_PATH_SEARCH ? resolve_search_tile(map->info.stage_all != 0, map->ipt)
+                                                  : kFilterTileQueries;
+    const int64_t n_tiles = (nq + tile_q - 1) / tile_q;
+    if (n_tiles > kNoAllocMaxTiles)
+        return fail(HLSMAP_ERR_INVALID,
+                    "get_segment_list_noalloc: batch of " + std::to_string(nq) +
+                        " queries needs " + std::to_string(n_tiles) + " tiles, the fixed scratch holds " +
+                        std::to_string(kNoAllocMaxTiles) + " (at most " +
+                        std::to_string(kNoAllocMaxTiles * tile_q) +
+                        " queries per call on this map): split the batch");
+
+    unsigned long long *scratch = nullptr;
+    r = noalloc_scratch_for(ctx, &scratch);   // first call on a GPU: looks the array up
+    if (r) return r;
+    ScanCounters *ctr = reinterpret_cast<ScanCounters *>(scratch);
+    DeviceResult *dres = reinterpret_cast<DeviceResult *>(scratch + 8);
+    unsigned long long *tile_status = scratch + kNoAllocHeaderWords;
+
+    // The array keeps whatever the previous call left: the header counters and the status
+    // words this batch will read must start at zero (stream-ordered, no allocation).
+    CK(cudaMemsetAsync(scratch, 0, (size_t)(kNoAllocHeaderWords + (n_tiles > 0 ? n_tiles : 0)) * 8, s));
+    if (nq == 0) {
+        CK(cudaMemsetAsync(d_offsets, 0, sizeof(int32_t), s));
+    } else {
+        ResolveParams p{};
+        p.desc = map->d_desc;
+        p.playlist_base = map->d_playlist_base;
+        p.n_playlists = map->n_playlists;
+        p.start = map->d_start;
+        p.sn = map->d_sn;
+        p.n_frag_padded = map->n_frag_padded;
+        p.nq = nq;
+        p.q_playlist = d_playlist;
+        p.q_level = d_level;
+        p.q_begin = d_begin;
+        p.q_duration = d_duration;
+        p.offsets = d_offsets;
+        p.sn_out = d_sn_out;
+        p.time_out = d_time_out;
+        p.capacity = d_sn_out ? hit_capacity : 0;
+        p.status = d_status;
+        p.tile_status = tile_status;
+        p.ctr = ctr;
+        p.result = dres;
+        p.epoch = 1;   // words were just zeroed, so any non-zero epoch marks "written by this call"
+        p.n_tiles = (int)n_tiles;
+        p.stage_elems = map->stage_elems;
+        p.stage_all = map->info.stage_all;
+        p.small = map->info.stage_all;
+        p.ipt = map->ipt;
+        p.hint = map->d_hint;
+        p.grid = map->d_grid;
+        p.grid_padded = map->grid_padded;
+        p.vec_ok = al16(d_level) && al16(d_begin) && al16(d_duration) && al16(d_offsets) &&
+                   (!d_playlist || al16(d_playlist)) &&
+                   (!d_status || (reinterpret_cast<uintptr_t>(d_status) & 3u) == 0);
+        if (path == HLSMAP_PATH_SEARCH) {
+            const int grid = (int)(n_tiles < map->grid_search ? n_tiles : map->grid_search);
+            CK(launch_resolve_search(p, grid, map->stage_smem, s));
+        } else {
+            const int grid = (int)(n_tiles < map->grid_filter ? n_tiles : map->grid_filter);
+            CK(launch_resolve_filter(p, grid, s));
+        }
+    }
+    if (!result) return HLSMAP_OK;
+
+    // h_result is the context's pinned 32-byte mailbox, allocated when the context was made
+    CK(cudaMemcpyAsync(ctx->h_result, dres, sizeof(DeviceResult), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    result->total_hits = ctx->h_result->total_hits;
+    result->n_unparsed = ctx->h_result->n_unparsed;
+    result->n_missing = ctx->h_result->n_missing;
+    result->kernel_launches = nq > 0 ? 1 : 0;
+    result->path = path;
+    if (ctx->h_result->overflow)
+        return fail(HLSMAP_ERR_OVERFLOW, "batch produced more than INT32_MAX hits; split it");
+    if (d_sn_out && result->total_hits > hit_capacity)
+        return fail(HLSMAP_ERR_CAPACITY, "hit buffers too small: need " +
+                                             std::to_string(result->total_hits) + " entries");
+    return HLSMAP_OK;
+}
+
 }  // extern "C"

@@ -240,6 +240,19 @@ class DeviceMap:
         N.check(code)
         return res
 
+    def get_segment_list_noalloc_dev(self, nq, d_playlist, d_level, d_begin, d_duration, d_offsets,
+                                     d_sn_out, d_time_out, capacity, d_status=0, stream=None,
+                                     sync=True):
+        """Same batch through the entry point that never allocates (for hosts that forbid
+        cudaMalloc while running): fixed in-library scratch, at most 65536 tiles per call, calls
+        must not overlap on the GPU.  Device pointers as ints."""
+        res = N.Result() if sync else None
+        N.check(self._lib.hlsmap_get_segment_list_noalloc_dev(
+            self._h, int(nq), d_playlist or None, d_level, d_begin, d_duration, d_offsets,
+            d_sn_out or None, d_time_out or None, int(capacity), d_status or None, _stream(stream),
+            ctypes.byref(res) if sync else None))
+        return res
+
     def last_result(self, stream=None):
         res = N.Result()
         N.check(self._lib.hlsmap_ctx_last_result(self.ctx._h, _stream(stream), ctypes.byref(res)))

@@ -140,6 +140,33 @@ int hlsmap_get_segment_list(hlsmap_map *map, int64_t nq, const int32_t *playlist
                             const int32_t *level, const double *begin, const double *duration,
                             int32_t *offsets, int32_t *sn_out, double *time_out,
                             int64_t hit_capacity, uint8_t *status, hlsmap_result *result);
+/* The same batch for callers that may not allocate.  (No counterpart in the reference: a
+ * JavaScript library never sees an allocator; this exists for native hosts of the engine.)
+ * Some callers cannot call cudaMalloc while they run: a real-time thread with a no-malloc
+ * rule, a plugin inside a host process that owns all device memory and forbids allocation
+ * from callbacks, a service whose own pool has already taken every byte of HBM.  The
+ * regular _dev entry point grows its look-back scratch with cudaMalloc when a batch is
+ * larger than any before it; this one never allocates or frees anything, on the device or
+ * the host.  Inputs and outputs are still the caller's device buffers; the scratch is a
+ * fixed array inside the library image (about 0.5 MiB held by every GPU that loads the
+ * library, until exit).
+ *   - Limit: 65536 tiles per call.  That is 33 554 432 queries on a map small enough to
+ *     live in shared memory (512-query tiles), 67 108 864 on larger sorted maps, 16 777 216
+ *     on the filter path.  Larger batches are refused with HLSMAP_ERR_INVALID and a message
+ *     that says how many queries fit on this map -- split the batch.
+ *   - The first call on each GPU looks up the array's device address; make that first
+ *     call before starting any stream capture.
+ *   - All calls share the one array: calls that overlap on the GPU (two streams, two
+ *     threads) corrupt each other's offsets.  Issue them in stream order or serialise.
+ *   - The array keeps the previous call's contents; every call zeroes the words it reads.
+ * result == NULL keeps the call asynchronous (the counters are then not retrievable: use
+ * the offsets[nq] entry for the hit total). */
+int hlsmap_get_segment_list_noalloc_dev(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
+                                        const int32_t *d_level, const double *d_begin,
+                                        const double *d_duration, int32_t *d_offsets,
+                                        int32_t *d_sn_out, double *d_time_out,
+                                        int64_t hit_capacity, uint8_t *d_status, void *stream,
+                                        hlsmap_result *result);
 /* Counters of the most recent batch issued through ctx (synchronises its stream). */
 int hlsmap_ctx_last_result(hlsmap_ctx *ctx, void *stream, hlsmap_result *result);
 
