@@ -67,6 +67,7 @@ struct hlsmap_map {
     TrackHint *d_hint = nullptr;        // SMALL maps: per-track hint-grid parameters
     unsigned short *d_grid = nullptr;   // SMALL maps: the hint grid itself
     int grid_padded = 0;
+    int n_tracks_padded = 1, n_base_padded = 4;
     std::vector<int32_t> h_playlist_base;
     std::vector<int32_t> h_url_count;
     std::vector<uint8_t> h_monotone;
@@ -158,6 +159,22 @@ int pick_path(const hlsmap_map *m)
 }
 
 inline bool al16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// Tiling of a batch: full tiles of the kernel's 256*ipt queries.  (Trimming the tile size so
+// that every CTA gets a whole number of tiles was measured on B200 and lost: 61 us vs 57 us on
+// the 10^6-query workload -- per-tile fixed costs outweigh the idle tail round.)
+void plan_tiles(const hlsmap_map *map, int path, int64_t nq, int *tile_q, int64_t *n_tiles)
+{
+    if (path != HLSMAP_PATH_SEARCH) {
+        *tile_q = kFilterTileQueries;
+        *n_tiles = (nq + kFilterTileQueries - 1) / kFilterTileQueries;
+        return;
+    }
+    const int tq = resolve_search_tile(map->info.stage_all != 0, map->ipt);
+    const int64_t tiles = (nq + tq - 1) / tq;
+    *tile_q = tq;
+    *n_tiles = tiles;
+}
 
 }  // namespace
 
@@ -321,7 +338,10 @@ int hlsmap_map_create(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *playl
 
     cudaStream_t s = ctx->stream;
     CKM(cudaMalloc(&m->d_desc, sizeof(TrackDesc) * (size_t)(n_tracks + 1)));
-    CKM(cudaMalloc(&m->d_playlist_base, sizeof(int) * (size_t)(n_playlists + 1)));
+    m->n_tracks_padded = n_tracks > 0 ? n_tracks : 1;
+    m->n_base_padded = (n_playlists + 1 + 3) & ~3;
+    CKM(cudaMalloc(&m->d_playlist_base, sizeof(int) * (size_t)m->n_base_padded));
+    CKM(cudaMemsetAsync(m->d_playlist_base, 0, sizeof(int) * (size_t)m->n_base_padded, ctx->stream));
     CKM(cudaMalloc(&m->d_start, sizeof(double) * (size_t)m->n_frag_padded));
     CKM(cudaMalloc(&m->d_sn, sizeof(int) * (size_t)m->n_frag_padded));
     CKM(cudaMalloc(&m->d_dur0, sizeof(double) * (size_t)(n_tracks + 1)));
@@ -388,7 +408,9 @@ int hlsmap_map_create(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *playl
         }
         grid_entries = (grid_entries + 7) & ~7ll;
         if (grid_entries < 8) grid_entries = 8;
-        if (m->n_frag_padded * 12 + grid_entries * 2 > small_limit) small = false;
+        if (m->n_frag_padded * 12 + grid_entries * 2 + (int64_t)m->n_tracks_padded * 48 +
+                (int64_t)m->n_base_padded * 4 > small_limit)
+            small = false;
     }
     if (small) {
         m->grid_padded = (int)grid_entries;
@@ -402,7 +424,8 @@ int hlsmap_map_create(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *playl
         CKM(cudaStreamSynchronize(s));
         m->info.stage_all = 1;
         m->stage_elems = (int)m->n_frag_padded;
-        m->stage_smem = (size_t)(m->n_frag_padded * 12 + grid_entries * 2);
+        m->stage_smem = (size_t)(m->n_frag_padded * 12 + grid_entries * 2 + (int64_t)m->n_tracks_padded * 48 +
+                                 (int64_t)m->n_base_padded * 4);
         m->info.device_bytes += (int64_t)(sizeof(TrackHint) * (size_t)(n_tracks + 1) + 2 * (size_t)grid_entries);
     } else {
         m->info.stage_all = 0;
@@ -496,9 +519,9 @@ int hlsmap_get_segment_list_dev(hlsmap_map *map, int64_t nq, const int32_t *d_pl
         return HLSMAP_OK;
     }
 
-    const int tile_q = path == HLSMAP_PATH_SEARCH ? resolve_search_tile(map->info.stage_all != 0, map->ipt)
-                                                  : kFilterTileQueries;
-    const int64_t n_tiles = (nq + tile_q - 1) / tile_q;
+    int tile_q = 0;
+    int64_t n_tiles = 0;
+    plan_tiles(map, path, nq, &tile_q, &n_tiles);
     if (n_tiles > 0x7fffffff) return fail(HLSMAP_ERR_INVALID, "batch too large: split it");
     r = prepare_scan(ctx, n_tiles, s);
     if (r) return r;
@@ -525,6 +548,7 @@ int hlsmap_get_segment_list_dev(hlsmap_map *map, int64_t nq, const int32_t *d_pl
     p.result = ctx->d_result;
     p.epoch = ctx->epoch;
     p.n_tiles = (int)n_tiles;
+    p.tile_q = tile_q;
     p.stage_elems = map->stage_elems;
     p.stage_all = map->info.stage_all;
     p.small = map->info.stage_all;
@@ -532,6 +556,8 @@ int hlsmap_get_segment_list_dev(hlsmap_map *map, int64_t nq, const int32_t *d_pl
     p.hint = map->d_hint;
     p.grid = map->d_grid;
     p.grid_padded = map->grid_padded;
+    p.n_tracks_padded = map->n_tracks_padded;
+    p.n_base_padded = map->n_base_padded;
     p.vec_ok = al16(d_level) && al16(d_begin) && al16(d_duration) && al16(d_offsets) &&
                (!d_playlist || al16(d_playlist)) &&
                (!d_status || (reinterpret_cast<uintptr_t>(d_status) & 3u) == 0);
@@ -539,8 +565,8 @@ int hlsmap_get_segment_list_dev(hlsmap_map *map, int64_t nq, const int32_t *d_pl
     unsigned long long *d_trace = nullptr;
     const char *trace_path = getenv("HLSMAP_TRACE");     // experiment: per-tile phase timestamps
     if (trace_path && path == HLSMAP_PATH_SEARCH) {
-        CK(cudaMalloc(&d_trace, (size_t)n_tiles * 64));
-        CK(cudaMemsetAsync(d_trace, 0, (size_t)n_tiles * 64, s));
+        CK(cudaMalloc(&d_trace, (size_t)n_tiles * 128));
+        CK(cudaMemsetAsync(d_trace, 0, (size_t)n_tiles * 128, s));
         p.trace = d_trace;
     }
     if (path == HLSMAP_PATH_SEARCH) {
@@ -556,8 +582,8 @@ int hlsmap_get_segment_list_dev(hlsmap_map *map, int64_t nq, const int32_t *d_pl
     }
     ctx->last_launches = 1;
     if (d_trace) {
-        std::vector<unsigned long long> h((size_t)n_tiles * 8);
-        CK(cudaMemcpyAsync(h.data(), d_trace, (size_t)n_tiles * 64, cudaMemcpyDeviceToHost, s));
+        std::vector<unsigned long long> h((size_t)n_tiles * 16);
+        CK(cudaMemcpyAsync(h.data(), d_trace, (size_t)n_tiles * 128, cudaMemcpyDeviceToHost, s));
         CK(cudaStreamSynchronize(s));
         if (FILE *f = fopen(trace_path, "wb")) {
             fwrite(h.data(), 8, h.size(), f);
@@ -1125,9 +1151,9 @@ int hlsmap_get_segment_list_noalloc_dev(hlsmap_map *map, int64_t nq, const int32
     cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
 
     const int path = pick_path(map);
-    const int tile_q = path == HLSMAP_PATH_SEARCH ? resolve_search_tile(map->info.stage_all != 0, map->ipt)
-                                                  : kFilterTileQueries;
-    const int64_t n_tiles = (nq + tile_q - 1) / tile_q;
+    int tile_q = 0;
+    int64_t n_tiles = 0;
+    plan_tiles(map, path, nq, &tile_q, &n_tiles);
     if (n_tiles > kNoAllocMaxTiles)
         return fail(HLSMAP_ERR_INVALID,
                     "get_segment_list_noalloc: batch of " + std::to_string(nq) +
@@ -1171,6 +1197,7 @@ int hlsmap_get_segment_list_noalloc_dev(hlsmap_map *map, int64_t nq, const int32
         p.result = dres;
         p.epoch = 1;   // words were just zeroed, so any non-zero epoch marks "written by this call"
         p.n_tiles = (int)n_tiles;
+        p.tile_q = tile_q;
         p.stage_elems = map->stage_elems;
         p.stage_all = map->info.stage_all;
         p.small = map->info.stage_all;
@@ -1178,6 +1205,8 @@ int hlsmap_get_segment_list_noalloc_dev(hlsmap_map *map, int64_t nq, const int32
         p.hint = map->d_hint;
         p.grid = map->d_grid;
         p.grid_padded = map->grid_padded;
+        p.n_tracks_padded = map->n_tracks_padded;
+        p.n_base_padded = map->n_base_padded;
         p.vec_ok = al16(d_level) && al16(d_begin) && al16(d_duration) && al16(d_offsets) &&
                    (!d_playlist || al16(d_playlist)) &&
                    (!d_status || (reinterpret_cast<uintptr_t>(d_status) & 3u) == 0);

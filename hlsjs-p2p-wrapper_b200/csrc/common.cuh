@@ -69,6 +69,8 @@ struct ResolveParams {
     const TrackHint *hint;        // SMALL maps only
     const unsigned short *grid;   // SMALL maps only
     int grid_padded;              // u16 entries in grid (multiple of 8)
+    int n_tracks_padded;          // SMALL: descriptors staged in shared memory (>= 1)
+    int n_base_padded;            // SMALL: playlist_base ints staged (multiple of 4)
     int small;                    // whole map staged in shared memory + hint grid
     int ipt;                      // queries per thread of the SMALL kernel (2 or 4)
     // queries
@@ -93,6 +95,7 @@ struct ResolveParams {
     int stage_elems;  // capacity of the shared-memory copy of start[], in doubles
     int stage_all;    // the whole column fits: stage once per CTA
     int vec_ok;       // query/offset pointers are 16-byte aligned
+    int tile_q;       // queries per tile (<= 256 * ipt, multiple of 4)
     unsigned long long *trace;  // diagnostics: per-tile phase timestamps (HLSMAP_TRACE=file); NULL normally
 };
 

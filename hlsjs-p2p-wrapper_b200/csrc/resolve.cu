@@ -79,6 +79,7 @@ struct SearchSmem {
     unsigned long long warp_cnt[kWarps];
     int warp_heads[kWarps];
     int tile_slot[2];              // next tile id, double buffered across iterations
+    int tile_peek;                 // the same, announced early for the L2 prefetch
     RecTable<SMALL, Shape<IPT>::kTile> rec;
     // per 32 output slots of the window: .x = bitmap of slots where a record starts,
     // .y = records that start before this word (tile-wide rank base).  Double buffered.
@@ -133,6 +134,8 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned pari
 }
 
 // ---- level lookup: media-map.js:28-37 --------------------------------------------------
+// IN_SMEM: the descriptor arrays were staged in shared memory (plain loads instead of __ldg).
+template <bool IN_SMEM = false>
 __device__ __forceinline__ int lookup_track(const TrackDesc *desc, const int *playlist_base,
                                             int n_playlists, int playlist, int level,
                                             long long &off, int &len, unsigned &flags,
@@ -143,10 +146,11 @@ __device__ __forceinline__ int lookup_track(const TrackDesc *desc, const int *pl
     flags = 0;
     if (track) *track = 0;
     if ((unsigned)playlist >= (unsigned)n_playlists) return HLSMAP_ST_MISSING;
-    const int b = __ldg(playlist_base + playlist);
-    const int e = __ldg(playlist_base + playlist + 1);
+    const int b = IN_SMEM ? playlist_base[playlist] : __ldg(playlist_base + playlist);
+    const int e = IN_SMEM ? playlist_base[playlist + 1] : __ldg(playlist_base + playlist + 1);
     if ((unsigned)level >= (unsigned)(e - b)) return HLSMAP_ST_MISSING;  // levels[level] undefined
-    const int4 raw = __ldg(reinterpret_cast<const int4 *>(desc + b + level));
+    const int4 raw = IN_SMEM ? *reinterpret_cast<const int4 *>(desc + b + level)
+                             : __ldg(reinterpret_cast<const int4 *>(desc + b + level));
     if (track) *track = b + level;
     flags = (unsigned)raw.w;
     const unsigned st = flags & kTrackStateMask;
@@ -250,12 +254,22 @@ __device__ __forceinline__ void trace_mark(const ResolveParams &p, int tile, int
     if (p.trace != nullptr && threadIdx.x == 0) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-        p.trace[(long long)tile * 8 + slot] = t;
+        p.trace[(long long)tile * 16 + slot] = t;
         if (slot == 0) {
             unsigned smid;
             asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-            p.trace[(long long)tile * 8 + 7] = smid;
+            p.trace[(long long)tile * 16 + 15] = smid;
         }
+    }
+}
+
+// Same, but issued only once `dep` has been produced (e.g. a loaded value).
+__device__ __forceinline__ void trace_mark_after(const ResolveParams &p, int tile, int slot, int dep)
+{
+    if (p.trace != nullptr && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t) : "r"(dep));
+        p.trace[(long long)tile * 16 + slot] = t;
     }
 }
 
@@ -275,17 +289,23 @@ __device__ __forceinline__ int hint_cell(double x, double t0, double inv, int nc
 //  aggregate is visible to later tiles before A's long emission starts.
 // =========================================================================================
 template <bool SMALL, int IPT>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, (SMALL && IPT == 2) ? 4 : (SMALL ? 3 : 2))
 resolve_search_kernel(const ResolveParams p)
 {
     using S = Shape<IPT>;
-    constexpr int kIpt = S::kIpt, kTile = S::kTile, kWindow = S::kWindow, kWords = S::kWords;
+    constexpr int kIpt = S::kIpt, kWindow = S::kWindow, kWords = S::kWords;
     extern __shared__ __align__(128) unsigned char dyn_smem[];
     __shared__ SearchSmem<SMALL, IPT> sm;
     double *s_start = reinterpret_cast<double *>(dyn_smem);
     const int *s_sn = reinterpret_cast<const int *>(dyn_smem + p.n_frag_padded * 8);
     const unsigned short *s_grid =
         reinterpret_cast<const unsigned short *>(dyn_smem + p.n_frag_padded * 12);
+    // SMALL: track descriptors, hints and the playlist index live in shared memory too (the
+    // carve-out leaves almost no L1, so global lookups would each cost an L2 round trip)
+    const unsigned char *s_meta = dyn_smem + p.n_frag_padded * 12 + (long long)p.grid_padded * 2;
+    const TrackDesc *s_desc = reinterpret_cast<const TrackDesc *>(s_meta);
+    const TrackHint *s_hint = reinterpret_cast<const TrackHint *>(s_meta + (long long)p.n_tracks_padded * 16);
+    const int *s_base = reinterpret_cast<const int *>(s_meta + (long long)p.n_tracks_padded * 48);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned lane_le = 0xffffffffu >> (31 - lane);
@@ -306,10 +326,17 @@ resolve_search_kernel(const ResolveParams p)
             const unsigned b_start = (unsigned)(p.n_frag_padded * 8);
             const unsigned b_sn = (unsigned)(p.n_frag_padded * 4);
             const unsigned b_grid = (unsigned)(p.grid_padded * 2);
-            mbar_expect_tx(&sm.mbar, b_start + b_sn + b_grid);
-            bulk_g2s_chunked(dyn_smem, p.start, b_start, &sm.mbar);
-            bulk_g2s_chunked(dyn_smem + b_start, p.sn, b_sn, &sm.mbar);
-            bulk_g2s_chunked(dyn_smem + b_start + b_sn, p.grid, b_grid, &sm.mbar);
+            const unsigned b_desc = (unsigned)(p.n_tracks_padded * 16);
+            const unsigned b_hint = (unsigned)(p.n_tracks_padded * 32);
+            const unsigned b_base = (unsigned)(p.n_base_padded * 4);
+            mbar_expect_tx(&sm.mbar, b_start + b_sn + b_grid + b_desc + b_hint + b_base);
+            unsigned char *d = dyn_smem;
+            bulk_g2s_chunked(d, p.start, b_start, &sm.mbar); d += b_start;
+            bulk_g2s_chunked(d, p.sn, b_sn, &sm.mbar); d += b_sn;
+            bulk_g2s_chunked(d, p.grid, b_grid, &sm.mbar); d += b_grid;
+            bulk_g2s_chunked(d, p.desc, b_desc, &sm.mbar); d += b_desc;
+            bulk_g2s_chunked(d, p.hint, b_hint, &sm.mbar); d += b_hint;
+            bulk_g2s_chunked(d, p.playlist_base, b_base, &sm.mbar);
         }
         stage_pending = true;
     }
@@ -333,6 +360,7 @@ resolve_search_kernel(const ResolveParams p)
 #pragma unroll
     for (int k = 0; k < kIpt; k++) { a_cnt[k] = 0; a_src[k] = 0; }
 
+    bool ticket_pending = false;         // thread 0: a ticket was requested for the next tile
     for (;;) {
         const bool haveB = tileB < p.n_tiles;
         if (!haveB && tileA < 0) break;
@@ -348,9 +376,16 @@ resolve_search_kernel(const ResolveParams p)
         for (int k = 0; k < kIpt; k++) { off[k] = 0; lo[k] = 0; cnt[k] = 0; }
 
         if (haveB) {
-            const long long q0 = (long long)tileB * kTile + (long long)tid * kIpt;
-            const bool full = p.vec_ok && q0 + kIpt <= p.nq;
+            // a tile holds p.tile_q <= 256*kIpt queries; threads past its end idle through the search
+            const int tq0 = tid * kIpt;
+            const long long q0 = (long long)tileB * p.tile_q + tq0;
+            const long long q_end = min(p.nq, (long long)(tileB + 1) * p.tile_q);
+            const bool full = p.vec_ok && q0 + kIpt <= q_end;
             trace_mark(p, tileB, 0);
+            if (tid == 0) {    // claim the next tile now: the atomic lands during the search
+                t_new = atomicAdd(&p.ctr->ticket[p.epoch & 1u], 1u);
+                ticket_pending = true;
+            }
 
             // ---- load this thread's consecutive queries -----------------------------------
             int pl[kIpt], lv[kIpt];
@@ -385,7 +420,7 @@ resolve_search_kernel(const ResolveParams p)
             } else {
 #pragma unroll
                 for (int k = 0; k < kIpt; k++) {
-                    const bool in = q0 + k < p.nq;
+                    const bool in = q0 + k < q_end;
                     lv[k] = in ? __ldcs(p.q_level + q0 + k) : -1;
                     pl[k] = (in && p.q_playlist) ? __ldcs(p.q_playlist + q0 + k) : 0;
                     bg[k] = in ? __ldcs(p.q_begin + q0 + k) : 0.0;
@@ -393,16 +428,22 @@ resolve_search_kernel(const ResolveParams p)
                 }
             }
 
+            trace_mark_after(p, tileB, 6, lv[0] ^ __double2loint(bg[kIpt - 1]) ^ __double2loint(du[kIpt - 1]));
             // ---- resolve (playlist, level) -> fragment table -----------------------------
+            if (SMALL && stage_pending) {      // first tile only: tables + metadata have landed
+                mbar_wait(&sm.mbar, mbar_phase);
+                mbar_phase ^= 1u;
+                stage_pending = false;
+            }
             int len[kIpt], st[kIpt], trk[kIpt];
             int n_unp = 0, n_mis = 0;
             long long mn = 0x7fffffffffffffffll, mx = -1;
 #pragma unroll
             for (int k = 0; k < kIpt; k++) {
                 unsigned fl;
-                st[k] = lookup_track(p.desc, p.playlist_base, p.n_playlists, pl[k], lv[k], off[k],
-                                     len[k], fl, &trk[k]);
-                const bool in = q0 + k < p.nq;
+                st[k] = lookup_track<SMALL>(SMALL ? s_desc : p.desc, SMALL ? s_base : p.playlist_base,
+                                            p.n_playlists, pl[k], lv[k], off[k], len[k], fl, &trk[k]);
+                const bool in = q0 + k < q_end;
                 n_unp += (in && st[k] == HLSMAP_ST_UNPARSED);
                 n_mis += (in && st[k] == HLSMAP_ST_MISSING);
                 if (!SMALL && st[k] == HLSMAP_ST_OK && len[k] > 0) {
@@ -418,7 +459,7 @@ resolve_search_kernel(const ResolveParams p)
                 } else {
 #pragma unroll
                     for (int k = 0; k < kIpt; k++)
-                        if (q0 + k < p.nq) p.status[q0 + k] = (unsigned char)st[k];
+                        if (q0 + k < q_end) p.status[q0 + k] = (unsigned char)st[k];
                 }
             }
 
@@ -432,8 +473,8 @@ resolve_search_kernel(const ResolveParams p)
                 for (int k = 0; k < kIpt; k++) {
                     // one fp64 add, round-to-nearest, never contracted: `beginTime + duration`
                     ub[k] = __dadd_rn(bg[k], du[k]);
-                    const int4 h0 = __ldg(reinterpret_cast<const int4 *>(p.hint + trk[k]));
-                    const int4 h1 = __ldg(reinterpret_cast<const int4 *>(p.hint + trk[k]) + 1);
+                    const int4 h0 = *reinterpret_cast<const int4 *>(s_hint + trk[k]);
+                    const int4 h1 = *(reinterpret_cast<const int4 *>(s_hint + trk[k]) + 1);
                     const double t0 = __hiloint2double(h0.y, h0.x);
                     const double inv = __hiloint2double(h0.w, h0.z);
                     const bool ok = st[k] == HLSMAP_ST_OK;
@@ -441,11 +482,7 @@ resolve_search_kernel(const ResolveParams p)
                     b0[k] = (ok ? h1.x : 0) + hint_cell(bg[k], t0, inv, ncell);   // grid index
                     u0[k] = (ok ? h1.x : 0) + hint_cell(ub[k], t0, inv, ncell);
                 }
-                if (stage_pending) {
-                    mbar_wait(&sm.mbar, mbar_phase);
-                    mbar_phase ^= 1u;
-                    stage_pending = false;
-                }
+                trace_mark_after(p, tileB, 7, b0[0] ^ u0[kIpt - 1]);
 #pragma unroll
                 for (int k = 0; k < kIpt; k++) {
                     const int gb0 = s_grid[b0[k]], gb1 = s_grid[b0[k] + 1];
@@ -531,7 +568,7 @@ resolve_search_kernel(const ResolveParams p)
                 }
             }
 
-            trace_mark(p, tileB, 1);
+            trace_mark_after(p, tileB, 1, cnt[0] ^ cnt[kIpt - 1]);
             // ---- fused scan of (hit count, non-empty flag): thread -> warp -> CTA ---------
             unsigned long long tval = 0;
 #pragma unroll
@@ -540,7 +577,23 @@ resolve_search_kernel(const ResolveParams p)
             unsigned long long wtot;
             const unsigned long long texcl = warp_excl_scan64(tval, wtot);
             if (lane == 0) sm.warp_cnt[warp] = wtot;
+            if (tid == 0) sm.tile_peek = (int)t_new;   // the tile searched next
             __syncthreads();     // also: everyone is past the previous emission of rec[]/hb[]
+            {   // pull the next tile's queries towards L2 while this one is emitted
+                const int tileC = sm.tile_peek;
+                if (tileC < p.n_tiles) {
+                    const long long c0 = (long long)tileC * p.tile_q;
+                    const long long cn = min((long long)p.tile_q, p.nq - c0);     // queries in that tile
+                    const int l64 = (int)((cn * 8 + 127) >> 7), l32 = (int)((cn * 4 + 127) >> 7);
+                    const char *a = nullptr;
+                    if (tid < l64) a = reinterpret_cast<const char *>(p.q_begin + c0) + tid * 128;
+                    else if (tid < 2 * l64) a = reinterpret_cast<const char *>(p.q_duration + c0) + (tid - l64) * 128;
+                    else if (tid < 2 * l64 + l32) a = reinterpret_cast<const char *>(p.q_level + c0) + (tid - 2 * l64) * 128;
+                    else if (tid < 2 * l64 + 2 * l32 && p.q_playlist)
+                        a = reinterpret_cast<const char *>(p.q_playlist + c0) + (tid - 2 * l64 - l32) * 128;
+                    if (a) asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
+                }
+            }
             unsigned long long wbase = 0, tile_tot = 0;
 #pragma unroll
             for (int w = 0; w < kWarps; w++) {
@@ -548,10 +601,10 @@ resolve_search_kernel(const ResolveParams p)
                 wbase += (w < warp) ? c : 0ull;
                 tile_tot += c;
             }
+            trace_mark_after(p, tileB, 8, (int)tile_tot);
             b_cnt_tile = tile_tot & kCntMask;
             Scan::publish_aggregate(p.tile_status, p.epoch, tileB, b_cnt_tile);
             trace_mark(p, tileB, 2);
-            if (tid == 0) t_new = atomicAdd(&p.ctr->ticket[p.epoch & 1u], 1u);   // lands during emit
             b_rel = (wbase + texcl) & kCntMask;
             b_rank = (int)((wbase + texcl) >> kCntBits);
             {   // rare: fold the unparsed / missing tallies (one atomic per warp when non-zero)
@@ -574,11 +627,12 @@ resolve_search_kernel(const ResolveParams p)
         //  EMIT tile A (searched one iteration ago): look-back, offsets, hits
         // =====================================================================================
         if (tileA >= 0) {
-            const long long q0 = (long long)tileA * kTile + (long long)tid * kIpt;
-            const bool full = p.vec_ok && q0 + kIpt <= p.nq;
+            const long long q0 = (long long)tileA * p.tile_q + tid * kIpt;
+            const long long q_end = min(p.nq, (long long)(tileA + 1) * p.tile_q);
+            const bool full = p.vec_ok && q0 + kIpt <= q_end;
             trace_mark(p, tileA, 3);
             const unsigned long long tile_base =
-                Scan::wait_prefix(sm.scan, p.tile_status, p.epoch, tileA, a_cnt_tile);
+                Scan::wait_prefix<4>(sm.scan, p.tile_status, p.epoch, tileA, a_cnt_tile);
             trace_mark(p, tileA, 4);
 
             // ---- offsets[q] --------------------------------------------------------------
@@ -597,7 +651,7 @@ resolve_search_kernel(const ResolveParams p)
                 } else {
 #pragma unroll
                     for (int k = 0; k < kIpt; k++)
-                        if (q0 + k < p.nq) p.offsets[q0 + k] = o[k];
+                        if (q0 + k < q_end) p.offsets[q0 + k] = o[k];
                 }
             }
             if (tileA == p.n_tiles - 1 && tid == kThreads - 1) {
@@ -716,7 +770,15 @@ resolve_search_kernel(const ResolveParams p)
         // ---- rotate the pipeline: B becomes the pending tile --------------------------------
         if (tileA >= 0) trace_mark(p, tileA, 5);
         slot ^= 1u;            // alternate slots: the one read last iteration is not rewritten
-        if (tid == 0) sm.tile_slot[slot] = haveB ? (int)t_new : p.n_tiles;
+        if (tid == 0) {
+            if (haveB) {
+                if (!ticket_pending) t_new = atomicAdd(&p.ctr->ticket[p.epoch & 1u], 1u);
+                sm.tile_slot[slot] = (int)t_new;
+                ticket_pending = false;
+            } else {
+                sm.tile_slot[slot] = p.n_tiles;
+            }
+        }
         __syncthreads();       // all global writes of tile A issued; next tile id visible
         if (tid == kThreads - 1 && tileA >= 0) {
             // completion count off the critical path: only this thread pays for the fence

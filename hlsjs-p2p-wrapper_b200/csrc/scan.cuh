@@ -79,6 +79,9 @@ struct TileScan {
 
     // Step 2: the sum of the aggregates of all earlier tiles.  Called by every thread of the
     // CTA after publish_aggregate(); work that does not need the prefix can sit in between.
+    // Every step inspects SLOTS * THREADS predecessors at once (independent loads in flight):
+    // the nearest tile that already knows its own prefix ends the walk.
+    template <int SLOTS = 1>
     __device__ static unsigned long long wait_prefix(Smem &s, unsigned long long *status,
                                                      unsigned epoch, int tile,
                                                      unsigned long long aggregate)
@@ -89,34 +92,49 @@ struct TileScan {
         unsigned long long running = 0;
         int top = tile - 1;
         for (;;) {
-            const int idx = top - tid;
-            unsigned long long val = 0;
-            bool is_prefix = true;  // idx < 0: the virtual tile -1 holds prefix 0
-            if (idx >= 0) {
-                unsigned long long w = ld_relaxed_u64(&status[idx]);
-                while ((unsigned)(w >> 42) != (epoch & kEpochMask)) {
-                    __nanosleep(256);   // do not flood the few L2 lines every CTA polls
-                    w = ld_relaxed_u64(&status[idx]);
-                }
-                val = w & ((1ull << kValueBits) - 1ull);
-                is_prefix = ((w >> kValueBits) & 3ull) == kStatePrefix;
+            unsigned long long w[SLOTS];
+#pragma unroll
+            for (int j = 0; j < SLOTS; j++) {      // distance d = tid + j*THREADS behind `top`
+                const int idx = top - (tid + j * THREADS);
+                w[j] = idx >= 0 ? ld_relaxed_u64(&status[idx]) : 0ull;
             }
-            const unsigned ball = __ballot_sync(0xffffffffu, is_prefix);
+            int my_first = 0x7fffffff;             // nearest distance holding a full prefix
+            unsigned long long val[SLOTS];
+#pragma unroll
+            for (int j = 0; j < SLOTS; j++) {
+                const int d = tid + j * THREADS;
+                const int idx = top - d;
+                bool is_prefix = true;             // idx < 0: the virtual tile -1 holds prefix 0
+                val[j] = 0;
+                if (idx >= 0) {
+                    while ((unsigned)(w[j] >> 42) != (epoch & kEpochMask)) {
+                        __nanosleep(128);          // not published yet: poll politely
+                        w[j] = ld_relaxed_u64(&status[idx]);
+                    }
+                    val[j] = w[j] & ((1ull << kValueBits) - 1ull);
+                    is_prefix = ((w[j] >> kValueBits) & 3ull) == kStatePrefix;
+                }
+                if (is_prefix) my_first = min(my_first, d);
+            }
+#pragma unroll
+            for (int dd = 16; dd > 0; dd >>= 1) my_first = min(my_first, __shfl_xor_sync(0xffffffffu, my_first, dd));
             __syncthreads();  // s.warp_first / s.warp_sum free for reuse
-            if (lane == 0) s.warp_first[warp] = ball ? warp * 32 + (__ffs(ball) - 1) : 0x7fffffff;
+            if (lane == 0) s.warp_first[warp] = my_first;
             __syncthreads();
             int first = 0x7fffffff;
 #pragma unroll
-            for (int w = 0; w < NW; w++) first = min(first, s.warp_first[w]);
-            unsigned long long c = (tid <= first) ? val : 0ull;
+            for (int ww = 0; ww < NW; ww++) first = min(first, s.warp_first[ww]);
+            unsigned long long c = 0;
 #pragma unroll
-            for (int d = 16; d > 0; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
+            for (int j = 0; j < SLOTS; j++) c += (tid + j * THREADS <= first) ? val[j] : 0ull;
+#pragma unroll
+            for (int dd = 16; dd > 0; dd >>= 1) c += __shfl_xor_sync(0xffffffffu, c, dd);
             if (lane == 0) s.warp_sum[warp] = c;
             __syncthreads();
 #pragma unroll
-            for (int w = 0; w < NW; w++) running += s.warp_sum[w];
+            for (int ww = 0; ww < NW; ww++) running += s.warp_sum[ww];
             if (first != 0x7fffffff) break;
-            top -= THREADS;
+            top -= SLOTS * THREADS;
         }
         running = running < kSat ? running : kSat;
         if (tid == 0)
