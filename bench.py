@@ -359,8 +359,8 @@ def run_ours(args):
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     e2e_value = sum_over_ranks(float(nq * args.e2e_steps)) / e2e_s
     assert int(pins["off"].array[-1]) == s0["hits"] == r.total_hits
-    h2d = 24 * nq
-    d2h = 4 * (nq + 1) + 12 * s0["hits"]
+    h2d = 24 * nq * world                               # all ranks, per step
+    d2h = (4 * (nq + 1) + 12 * s0["hits"]) * world
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -394,7 +394,7 @@ def run_ours(args):
                     "ms_per_step": 1e3 * e2e_s / args.e2e_steps,
                     "api": "hlsmap_get_segment_list (host pointers, pinned)",
                     "kernel_launches_per_step": e2e_launches},
-            "gpu_launches": args.steps, "clocks": clocks, "node": node_version(),
+            "gpu_launches": args.steps * world, "clocks": clocks, "node": node_version(),
         }
         print(json.dumps(line))
     for p in pins.values():

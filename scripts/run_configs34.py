@@ -1,0 +1,136 @@
+#!/usr/bin/env python
+"""BASELINE.json configs[2] (live sliding windows) and configs[3] (view round trips): parity
+against the oracle plus device-resident kernel timings (CUDA events, L2 flushed between runs).
+
+    python scripts/run_configs34.py --out gpurun_out/configs34.json
+"""
+import argparse
+import ctypes
+import json
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import oracle
+import hlsjs_p2p_wrapper_b200 as pk
+from hlsjs_p2p_wrapper_b200 import synth, _native as N
+
+PEAK = 6551.4
+
+
+def timed(fn, stream, flush, reps=20):
+    ms = []
+    for _ in range(reps):
+        flush.add_(1)                       # > 126 MB written: L2 holds none of the operands
+        torch.cuda.synchronize()
+        with torch.cuda.stream(stream):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+        torch.cuda.synchronize()
+        ms.append(a.elapsed_time(b))
+    return float(np.median(ms)), float(np.min(ms))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--out", default="gpurun_out/configs34.json")
+    args = ap.parse_args()
+    ctx = pk.Context(0)
+    lib = ctx._lib
+    dev = torch.device("cuda:0")
+    stream = torch.cuda.Stream(device=dev)
+    flush = torch.zeros(64 * 1024 * 1024, dtype=torch.int32, device=dev)   # 256 MB
+    out = {}
+    dv = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+
+    # ---- config 3: 10^5 players x 3 levels x 6-fragment window --------------------------------
+    t, q = synth.config3()
+    m = ctx.upload(t)
+    res = m.get_segment_list(q.playlist, q.level, q.begin, q.duration)
+    o_off, o_st, o_sn, o_tm = oracle.get_segment_list_batch(t.playlist_base, t.track_off, t.track_state,
+                                                            t.start, t.sn, q.playlist, q.level, q.begin,
+                                                            q.duration, threads=16)
+    ok = (np.array_equal(res.offsets.astype(np.int64), o_off) and np.array_equal(res.sn, o_sn)
+          and np.array_equal(res.time.view(np.uint64), o_tm.view(np.uint64)))
+    d_out, d_st = m.get_segment_duration(q.playlist, q.level)
+    e_out, e_st = oracle.get_segment_duration_batch(t.playlist_base, t.track_off, t.track_state, t.dur0(),
+                                                    q.playlist, q.level)
+    ok_d = np.array_equal(d_out, e_out) and np.array_equal(d_st, e_st)
+    nq, H = len(q), int(res.total_hits)
+    d = {k: dv(getattr(q, k)) for k in ("playlist", "level", "begin", "duration")}
+    off = torch.empty(nq + 1, dtype=torch.int32, device=dev)
+    sn = torch.empty(H, dtype=torch.int32, device=dev)
+    tm = torch.empty(H, dtype=torch.float64, device=dev)
+    durs = torch.empty(nq, dtype=torch.float64, device=dev)
+    dst = torch.empty(nq, dtype=torch.uint8, device=dev)
+    ms, mn = timed(lambda: m.get_segment_list_dev(nq, d["playlist"].data_ptr(), d["level"].data_ptr(),
+                                                  d["begin"].data_ptr(), d["duration"].data_ptr(),
+                                                  off.data_ptr(), sn.data_ptr(), tm.data_ptr(), H,
+                                                  stream=stream.cuda_stream), stream, flush)
+    bytes3 = 28.0 * nq + 12.0 * H + 12.0 * t.n_fragments
+    ms_d, _ = timed(lambda: N.check(lib.hlsmap_get_segment_duration_dev(
+        m._h, nq, ctypes.c_void_p(d["playlist"].data_ptr()), ctypes.c_void_p(d["level"].data_ptr()),
+        ctypes.c_void_p(durs.data_ptr()), ctypes.c_void_p(dst.data_ptr()),
+        ctypes.c_void_p(stream.cuda_stream))), stream, flush)
+    out["config3_live_windows"] = {
+        "players": 100000, "queries": nq, "hits": H, "fragments": t.n_fragments,
+        "parity_getSegmentList": bool(ok), "parity_getSegmentDuration": bool(ok_d),
+        "getSegmentList_ms_median": ms, "getSegmentList_ms_min": mn,
+        "getSegmentList_queries_per_s": nq / (ms * 1e-3),
+        "getSegmentList_GBs": bytes3 / (ms * 1e-3) / 1e9, "getSegmentList_frac_of_measured_peak": bytes3 / (ms * 1e-3) / 1e9 / PEAK,
+        "getSegmentDuration_ms_median": ms_d, "getSegmentDuration_queries_per_s": nq / (ms_d * 1e-3),
+        "note": "2e5 queries is a launch-latency-sized batch: ~10 us of fixed cost dominates"}
+    m.close()
+
+    # ---- config 4: 10^6 views, 8 levels x 10k fragments ------------------------------------------
+    t, v, o = synth.config4()
+    n = len(v["sn"])
+    wire, eq = ctx.view_roundtrip(v["level"], v["urlId"], v["sn"])
+    ewire, eeq = oracle.view_roundtrip(v["level"], v["urlId"], v["sn"])
+    lv, ui, s2 = ctx.view_unpack(wire)
+    same = ctx.view_is_equal(lv.astype(np.int32), ui.astype(np.int32), s2.astype(np.int32),
+                             o["level"], o["urlId"], o["sn"])
+    esame = oracle.view_is_equal(v["level"], v["urlId"], v["sn"], o["level"], o["urlId"], o["sn"])
+    ok4 = wire.tobytes() == ewire.tobytes() and np.array_equal(eq, eeq) and np.array_equal(same, esame)
+    L, U, S = dv(v["level"]), dv(v["urlId"]), dv(v["sn"])
+    L2, U2, S2 = dv(o["level"]), dv(o["urlId"]), dv(o["sn"])
+    W = torch.empty(3 * n, dtype=torch.int32, device=dev)
+    E = torch.empty(n, dtype=torch.uint8, device=dev)
+    PL, PU, PS = (torch.empty(n, dtype=torch.int32, device=dev) for _ in range(3))
+    p = lambda x: ctypes.c_void_p(x.data_ptr())
+    sp = ctypes.c_void_p(stream.cuda_stream)
+    kern = {
+        "roundtrip (pack+parse+isEqual fused, 25 B/view)": (lambda: N.check(lib.hlsmap_view_roundtrip_dev(ctx._h, n, p(L), p(U), p(S), p(W), p(E), sp)), 25.0),
+        "pack (24 B/view)": (lambda: N.check(lib.hlsmap_view_pack_dev(ctx._h, n, p(L), p(U), p(S), p(W), sp)), 24.0),
+        "unpack (24 B/view)": (lambda: N.check(lib.hlsmap_view_unpack_dev(ctx._h, n, p(W), p(PL), p(PU), p(PS), sp)), 24.0),
+        "isEqual (25 B/view)": (lambda: N.check(lib.hlsmap_view_is_equal_dev(ctx._h, n, p(L), p(U), p(S), p(L2), p(U2), p(S2), p(E), sp)), 25.0),
+    }
+    r4 = {"views": n, "parity": bool(ok4), "false_fraction": float((same == 0).mean())}
+    for name, (fn, bpv) in kern.items():
+        ms, mn = timed(fn, stream, flush)
+        r4[name] = {"ms_median": ms, "ms_min": mn, "views_per_s": n / (ms * 1e-3),
+                    "GBs": bpv * n / (ms * 1e-3) / 1e9, "frac_of_measured_peak": bpv * n / (ms * 1e-3) / 1e9 / PEAK}
+    # a batch big enough to leave launch latency behind
+    nb = 64 * n
+    Lb, Ub, Sb = L.repeat(64), U.repeat(64), S.repeat(64)
+    Wb = torch.empty(3 * nb, dtype=torch.int32, device=dev)
+    Eb = torch.empty(nb, dtype=torch.uint8, device=dev)
+    ms, mn = timed(lambda: N.check(lib.hlsmap_view_roundtrip_dev(ctx._h, nb, p(Lb), p(Ub), p(Sb), p(Wb), p(Eb), sp)),
+                   stream, flush, reps=10)
+    r4["roundtrip x64 (6.4e7 views)"] = {"ms_median": ms, "views_per_s": nb / (ms * 1e-3),
+                                         "GBs": 25.0 * nb / (ms * 1e-3) / 1e9,
+                                         "frac_of_measured_peak": 25.0 * nb / (ms * 1e-3) / 1e9 / PEAK}
+    out["config4_view_roundtrips"] = r4
+    os.makedirs(os.path.dirname(args.out) or ".", exist_ok=True)
+    json.dump(out, open(args.out, "w"), indent=1)
+    print(json.dumps(out, indent=1))
+    return 0 if ok and ok_d and ok4 else 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())
