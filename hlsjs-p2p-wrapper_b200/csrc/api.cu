@@ -570,11 +570,7 @@ int hlsmap_get_segment_list_dev(hlsmap_map *map, int64_t nq, const int32_t *d_pl
         p.trace = d_trace;
     }
     if (path == HLSMAP_PATH_SEARCH) {
-        int grid = (int)(n_tiles < map->grid_search ? n_tiles : map->grid_search);
-        if (const char *e = getenv("HLSMAP_GRID_PER_SM")) {   // experiment switch
-            const int g = atoi(e) * ctx->sm_count;
-            if (g > 0 && g < grid) grid = g;
-        }
+        const int grid = (int)(n_tiles < map->grid_search ? n_tiles : map->grid_search);
         CK(launch_resolve_search(p, grid, map->stage_smem, s));
     } else {
         const int grid = (int)(n_tiles < map->grid_filter ? n_tiles : map->grid_filter);

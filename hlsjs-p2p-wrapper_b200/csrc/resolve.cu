@@ -365,6 +365,10 @@ resolve_search_kernel(const ResolveParams p)
         const bool haveB = tileB < p.n_tiles;
         if (!haveB && tileA < 0) break;
 
+        // tile A's look-back window: load it now, use it after the search (hides the L2 trip)
+        unsigned long long pre[2] = {0ull, 0ull};
+        if (tileA > 0) Scan::template prefetch_window<2>(p.tile_status, tileA, pre);
+
         // =====================================================================================
         //  SEARCH tile B
         // =====================================================================================
@@ -632,7 +636,7 @@ resolve_search_kernel(const ResolveParams p)
             const bool full = p.vec_ok && q0 + kIpt <= q_end;
             trace_mark(p, tileA, 3);
             const unsigned long long tile_base =
-                Scan::wait_prefix<4>(sm.scan, p.tile_status, p.epoch, tileA, a_cnt_tile);
+                Scan::wait_prefix<2>(sm.scan, p.tile_status, p.epoch, tileA, a_cnt_tile, pre);
             trace_mark(p, tileA, 4);
 
             // ---- offsets[q] --------------------------------------------------------------

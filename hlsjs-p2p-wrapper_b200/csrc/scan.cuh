@@ -81,10 +81,24 @@ struct TileScan {
     // CTA after publish_aggregate(); work that does not need the prefix can sit in between.
     // Every step inspects SLOTS * THREADS predecessors at once (independent loads in flight):
     // the nearest tile that already knows its own prefix ends the walk.
+    // Issues the loads of the first look-back window of `tile` early (e.g. before a search
+    // phase) so their L2 round trip is hidden; hand `pre` to wait_prefix() later.
+    template <int SLOTS>
+    __device__ static void prefetch_window(const unsigned long long *status, int tile,
+                                           unsigned long long (&pre)[SLOTS])
+    {
+#pragma unroll
+        for (int j = 0; j < SLOTS; j++) {
+            const int idx = tile - 1 - ((int)threadIdx.x + j * THREADS);
+            pre[j] = idx >= 0 ? ld_relaxed_u64(&status[idx]) : 0ull;
+        }
+    }
+
     template <int SLOTS = 1>
     __device__ static unsigned long long wait_prefix(Smem &s, unsigned long long *status,
                                                      unsigned epoch, int tile,
-                                                     unsigned long long aggregate)
+                                                     unsigned long long aggregate,
+                                                     const unsigned long long *pre = nullptr)
     {
         const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
         if (tile == 0) return 0ull;
@@ -96,7 +110,8 @@ struct TileScan {
 #pragma unroll
             for (int j = 0; j < SLOTS; j++) {      // distance d = tid + j*THREADS behind `top`
                 const int idx = top - (tid + j * THREADS);
-                w[j] = idx >= 0 ? ld_relaxed_u64(&status[idx]) : 0ull;
+                if (pre != nullptr && top == tile - 1) w[j] = pre[j];   // loaded ahead of time
+                else w[j] = idx >= 0 ? ld_relaxed_u64(&status[idx]) : 0ull;
             }
             int my_first = 0x7fffffff;             // nearest distance holding a full prefix
             unsigned long long val[SLOTS];

@@ -150,10 +150,10 @@ int hlsmap_get_segment_list(hlsmap_map *map, int64_t nq, const int32_t *playlist
  * the host.  Inputs and outputs are still the caller's device buffers; the scratch is a
  * fixed array inside the library image (about 0.5 MiB held by every GPU that loads the
  * library, until exit).
- *   - Limit: 65536 tiles per call.  That is 33 554 432 queries on a map small enough to
- *     live in shared memory (512-query tiles), 67 108 864 on larger sorted maps, 16 777 216
- *     on the filter path.  Larger batches are refused with HLSMAP_ERR_INVALID and a message
- *     that says how many queries fit on this map -- split the batch.
+ *   - Limit: 65536 tiles per call.  A tile holds 256 to 4096 queries depending on the map
+ *     and the kernel that serves it (at least 16 777 216 queries per call, 33 554 432 or more
+ *     on sorted maps).  Larger batches are refused with HLSMAP_ERR_INVALID and a message that
+ *     says how many queries fit on this map -- split the batch.
  *   - The first call on each GPU looks up the array's device address; make that first
  *     call before starting any stream capture.
  *   - All calls share the one array: calls that overlap on the GPU (two streams, two

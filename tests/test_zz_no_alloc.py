@@ -92,7 +92,7 @@ def test_noalloc_refuses_batches_beyond_its_fixed_scratch():
     dev = torch.device("cuda:0")
     d, out = _device_batch(torch, dev, q, 16)
     o = out()
-    too_many = 65536 * 512 + 1              # one query more than 65536 tiles of 512
+    too_many = 65536 * 4096 + 1             # more than 65536 tiles whatever the tile size (<= 4096)
     with pytest.raises(N.HlsMapError) as e:
         # the size check comes before any pointer is touched, so small buffers are fine here
         m.get_segment_list_noalloc_dev(too_many, d["pl"].data_ptr(), d["lv"].data_ptr(),
