@@ -42,6 +42,9 @@ struct hlsmap_ctx {
     int sm_count = 0;
     int max_smem_optin = 0;
     cudaStream_t stream = nullptr;      // compute + copies of the host-pointer variants
+    cudaStream_t s_in = nullptr;        // host pipeline: query uploads
+    cudaStream_t s_out = nullptr;       // host pipeline: result downloads
+    cudaEvent_t ev_in[2] = {nullptr, nullptr};
     ScanCounters *ctr = nullptr;        // scan scratch header
     DeviceResult *d_result = nullptr;
     DeviceResult *h_result = nullptr;   // pinned
@@ -215,6 +218,10 @@ int hlsmap_ctx_create(int device, hlsmap_ctx **out)
     c->sm_count = prop.multiProcessorCount;
     c->max_smem_optin = (int)prop.sharedMemPerBlockOptin;
     CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&c->s_in, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&c->ev_in[0], cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&c->ev_in[1], cudaEventDisableTiming));
     CK(cudaMalloc(&c->ctr, sizeof(ScanCounters)));
     CK(cudaMalloc(&c->d_result, sizeof(DeviceResult)));
     CK(cudaMemset(c->ctr, 0, sizeof(ScanCounters)));
@@ -237,6 +244,10 @@ void hlsmap_ctx_destroy(hlsmap_ctx *c)
     if (c->d_result) cudaFree(c->d_result);
     if (c->h_result) cudaFreeHost(c->h_result);
     if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->s_in) cudaStreamDestroy(c->s_in);
+    if (c->s_out) cudaStreamDestroy(c->s_out);
+    if (c->ev_in[0]) cudaEventDestroy(c->ev_in[0]);
+    if (c->ev_in[1]) cudaEventDestroy(c->ev_in[1]);
     delete c;
 }
 
@@ -491,11 +502,13 @@ int hlsmap_map_set_path(hlsmap_map *map, int path)
 // ---------------------------------------------------------------------------------------
 //  getSegmentList
 // ---------------------------------------------------------------------------------------
-int hlsmap_get_segment_list_dev(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
-                                const int32_t *d_level, const double *d_begin,
-                                const double *d_duration, int32_t *d_offsets, int32_t *d_sn_out,
-                                double *d_time_out, int64_t hit_capacity, uint8_t *d_status,
-                                void *stream, hlsmap_result *result)
+// One batch on `stream`.  `base` = hits produced by earlier chunks of the same logical call:
+// offsets, hit positions and the reported total all include it.
+static int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
+                     const int32_t *d_level, const double *d_begin,
+                     const double *d_duration, int32_t *d_offsets, int32_t *d_sn_out,
+                     double *d_time_out, int64_t hit_capacity, uint8_t *d_status,
+                     void *stream, hlsmap_result *result, unsigned long long base)
 {
     if (!map) return fail(HLSMAP_ERR_INVALID, "null map");
     hlsmap_ctx *ctx = map->ctx;
@@ -549,6 +562,7 @@ int hlsmap_get_segment_list_dev(hlsmap_map *map, int64_t nq, const int32_t *d_pl
     p.epoch = ctx->epoch;
     p.n_tiles = (int)n_tiles;
     p.tile_q = tile_q;
+    p.base = base;
     p.stage_elems = map->stage_elems;
     p.stage_all = map->info.stage_all;
     p.small = map->info.stage_all;
@@ -598,6 +612,16 @@ int hlsmap_get_segment_list_dev(hlsmap_map *map, int64_t nq, const int32_t *d_pl
     return HLSMAP_OK;
 }
 
+int hlsmap_get_segment_list_dev(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
+                                const int32_t *d_level, const double *d_begin,
+                                const double *d_duration, int32_t *d_offsets, int32_t *d_sn_out,
+                                double *d_time_out, int64_t hit_capacity, uint8_t *d_status,
+                                void *stream, hlsmap_result *result)
+{
+    return list_core(map, nq, d_playlist, d_level, d_begin, d_duration, d_offsets, d_sn_out, d_time_out,
+                     hit_capacity, d_status, stream, result, 0ull);
+}
+
 int hlsmap_ctx_last_result(hlsmap_ctx *ctx, void *stream, hlsmap_result *result)
 {
     int r = use_ctx(ctx);
@@ -634,6 +658,69 @@ int hlsmap_get_segment_list(hlsmap_map *map, int64_t nq, const int32_t *playlist
     if ((r = ensure_slot(ctx, 3, n1 * 8, &v))) return r; d_du = (double *)v;
     if ((r = ensure_slot(ctx, 4, (n1 + 1) * 4, &v))) return r; d_off = (int *)v;
     if (status) { if ((r = ensure_slot(ctx, 5, n1, &v))) return r; d_st = (uint8_t *)v; }
+    // Large filling batches go through a chunked pipeline: while chunk c's hits travel to the
+    // host, chunk c+1's queries travel to the device (PCIe is full duplex) and its kernel runs.
+    constexpr int64_t kChunk = 131072;      // queries per chunk (multiple of 1024: aligned sections)
+    if (fill && nq >= 2 * kChunk && !getenv("HLSMAP_NO_PIPELINE")) {
+        int64_t dev_cap = ctx->slot_bytes[6] / 4 < ctx->slot_bytes[7] / 8 ? ctx->slot_bytes[6] / 4
+                                                                         : ctx->slot_bytes[7] / 8;
+        int64_t want = nq * 16 + 1024;
+        if (want > hit_capacity) want = hit_capacity;
+        if (dev_cap < want) dev_cap = want;
+        if (dev_cap > hit_capacity) dev_cap = hit_capacity;
+        if ((r = ensure_slot(ctx, 6, dev_cap * 4, &v))) return r; d_sn = (int *)v;
+        if ((r = ensure_slot(ctx, 7, dev_cap * 8, &v))) return r; d_tm = (double *)v;
+        auto upload = [&](int64_t c) -> int {
+            const int64_t q0 = c * kChunk, n = nq - q0 < kChunk ? nq - q0 : kChunk;
+            if (playlist) CK(cudaMemcpyAsync(d_pl + q0, playlist + q0, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->s_in));
+            CK(cudaMemcpyAsync(d_lv + q0, level + q0, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->s_in));
+            CK(cudaMemcpyAsync(d_bg + q0, begin + q0, (size_t)n * 8, cudaMemcpyHostToDevice, ctx->s_in));
+            CK(cudaMemcpyAsync(d_du + q0, duration + q0, (size_t)n * 8, cudaMemcpyHostToDevice, ctx->s_in));
+            CK(cudaEventRecord(ctx->ev_in[c & 1], ctx->s_in));
+            return HLSMAP_OK;
+        };
+        const int64_t n_chunks = (nq + kChunk - 1) / kChunk;
+        hlsmap_result acc{};
+        unsigned long long base = 0;
+        bool overflow_dev = false;
+        CK(cudaStreamSynchronize(ctx->s_out));          // earlier downloads are done with the slots
+        if ((r = upload(0))) return r;
+        for (int64_t c = 0; c < n_chunks; c++) {
+            const int64_t q0 = c * kChunk, n = nq - q0 < kChunk ? nq - q0 : kChunk;
+            CK(cudaStreamWaitEvent(s, ctx->ev_in[c & 1], 0));
+            if (c + 1 < n_chunks && (r = upload(c + 1))) return r;
+            hlsmap_result rc{};
+            r = list_core(map, n, playlist ? d_pl + q0 : nullptr, d_lv + q0, d_bg + q0, d_du + q0,
+                          d_off + q0, d_sn, d_tm, dev_cap, status ? d_st + q0 : nullptr, s, &rc, base);
+            acc.kernel_launches += 1;
+            acc.path = rc.path;
+            if (r == HLSMAP_ERR_CAPACITY) { overflow_dev = true; break; }   // device guess too small
+            if (r) return r;
+            const unsigned long long total_c = (unsigned long long)rc.total_hits - base;
+            acc.n_unparsed += rc.n_unparsed;
+            acc.n_missing += rc.n_missing;
+            CK(cudaMemcpyAsync(offsets + q0, d_off + q0, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->s_out));
+            if (status) CK(cudaMemcpyAsync(status + q0, d_st + q0, (size_t)n, cudaMemcpyDeviceToHost, ctx->s_out));
+            if (total_c > 0 && (int64_t)rc.total_hits <= hit_capacity) {
+                CK(cudaMemcpyAsync(sn_out + base, d_sn + base, (size_t)total_c * 4, cudaMemcpyDeviceToHost, ctx->s_out));
+                CK(cudaMemcpyAsync(time_out + base, d_tm + base, (size_t)total_c * 8, cudaMemcpyDeviceToHost, ctx->s_out));
+            }
+            base = (unsigned long long)rc.total_hits;
+        }
+        CK(cudaStreamSynchronize(ctx->s_in));
+        CK(cudaStreamSynchronize(ctx->s_out));
+        if (!overflow_dev) {
+            offsets[nq] = (int32_t)base;
+            acc.total_hits = (int64_t)base;
+            ctx->last_launches = acc.kernel_launches;
+            if (result) *result = acc;
+            if ((int64_t)base > hit_capacity)
+                return fail(HLSMAP_ERR_CAPACITY, "hit buffers too small: need " + std::to_string(base) + " entries");
+            return HLSMAP_OK;
+        }
+        // the device-side guess was too small: fall through to the one-shot path, which sizes
+        // the device buffers from the exact count
+    }
     if (nq) {
         if (playlist) CK(cudaMemcpyAsync(d_pl, playlist, (size_t)nq * 4, cudaMemcpyHostToDevice, s));
         CK(cudaMemcpyAsync(d_lv, level, (size_t)nq * 4, cudaMemcpyHostToDevice, s));

@@ -96,6 +96,7 @@ struct ResolveParams {
     int stage_all;    // the whole column fits: stage once per CTA
     int vec_ok;       // query/offset pointers are 16-byte aligned
     int tile_q;       // queries per tile (<= 256 * ipt, multiple of 4)
+    unsigned long long base;  // hits produced by earlier chunks of the same call (0 normally)
     unsigned long long *trace;  // diagnostics: per-tile phase timestamps (HLSMAP_TRACE=file); NULL normally
 };
 

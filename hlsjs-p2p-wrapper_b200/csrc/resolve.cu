@@ -607,7 +607,7 @@ resolve_search_kernel(const ResolveParams p)
             }
             trace_mark_after(p, tileB, 8, (int)tile_tot);
             b_cnt_tile = tile_tot & kCntMask;
-            Scan::publish_aggregate(p.tile_status, p.epoch, tileB, b_cnt_tile);
+            Scan::publish_aggregate(p.tile_status, p.epoch, tileB, b_cnt_tile, p.base);
             trace_mark(p, tileB, 2);
             b_rel = (wbase + texcl) & kCntMask;
             b_rank = (int)((wbase + texcl) >> kCntBits);
@@ -636,7 +636,7 @@ resolve_search_kernel(const ResolveParams p)
             const bool full = p.vec_ok && q0 + kIpt <= q_end;
             trace_mark(p, tileA, 3);
             const unsigned long long tile_base =
-                Scan::wait_prefix<2>(sm.scan, p.tile_status, p.epoch, tileA, a_cnt_tile, pre);
+                Scan::wait_prefix<2>(sm.scan, p.tile_status, p.epoch, tileA, a_cnt_tile, pre, p.base);
             trace_mark(p, tileA, 4);
 
             // ---- offsets[q] --------------------------------------------------------------
@@ -920,7 +920,7 @@ resolve_filter_kernel(const ResolveParams p)
             tile_total += c;
         }
         const unsigned long long tile_base =
-            FScan::exclusive_prefix(scan, p.tile_status, p.epoch, tile, tile_total);
+            FScan::exclusive_prefix(scan, p.tile_status, p.epoch, tile, tile_total, p.base);
         const unsigned long long my_base = tile_base + wbase + (unsigned long long)lexcl;
         if (in) p.offsets[q] = (int)my_base;
         if (tile == p.n_tiles - 1 && tid == kFThreads - 1) {

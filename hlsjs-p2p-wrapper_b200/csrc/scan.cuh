@@ -68,13 +68,17 @@ struct TileScan {
     static constexpr unsigned long long kSat = 1ull << 33;
 
     // Step 1: make this tile's aggregate visible to later tiles (tile 0 publishes a prefix).
+    // `base` = entries produced by earlier batches of the same logical call (chunked host
+    // pipeline): it is the prefix of the virtual tile before tile 0.
     __device__ static void publish_aggregate(unsigned long long *status, unsigned epoch, int tile,
-                                             unsigned long long aggregate)
+                                             unsigned long long aggregate,
+                                             unsigned long long base = 0)
     {
         aggregate = aggregate < kSat ? aggregate : kSat;
         if (threadIdx.x == 0)
             st_relaxed_u64(&status[tile],
-                           make_status(epoch, tile == 0 ? kStatePrefix : kStateAggregate, aggregate));
+                           tile == 0 ? make_status(epoch, kStatePrefix, base + aggregate)
+                                     : make_status(epoch, kStateAggregate, aggregate));
     }
 
     // Step 2: the sum of the aggregates of all earlier tiles.  Called by every thread of the
@@ -98,10 +102,11 @@ struct TileScan {
     __device__ static unsigned long long wait_prefix(Smem &s, unsigned long long *status,
                                                      unsigned epoch, int tile,
                                                      unsigned long long aggregate,
-                                                     const unsigned long long *pre = nullptr)
+                                                     const unsigned long long *pre = nullptr,
+                                                     unsigned long long base = 0)
     {
         const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-        if (tile == 0) return 0ull;
+        if (tile == 0) return base;
         aggregate = aggregate < kSat ? aggregate : kSat;
         unsigned long long running = 0;
         int top = tile - 1;
@@ -159,10 +164,11 @@ struct TileScan {
 
     __device__ static unsigned long long exclusive_prefix(Smem &s, unsigned long long *status,
                                                           unsigned epoch, int tile,
-                                                          unsigned long long aggregate)
+                                                          unsigned long long aggregate,
+                                                          unsigned long long base = 0)
     {
-        publish_aggregate(status, epoch, tile, aggregate);
-        return wait_prefix(s, status, epoch, tile, aggregate);
+        publish_aggregate(status, epoch, tile, aggregate, base);
+        return wait_prefix(s, status, epoch, tile, aggregate, nullptr, base);
     }
 
     // Ticket prefetch: thread 0 asks for the CTA's next tile while the current one is still

@@ -57,7 +57,7 @@ def test_config2_full_size_search(ctx):
     info = m.info()
     assert info["all_monotone"] == 1 and info["stage_all"] == 1
     res = m.get_segment_list(q.playlist, q.level, q.begin, q.duration)
-    assert res.path == N.PATH_SEARCH and res.kernel_launches in (1, 2)
+    assert res.path == N.PATH_SEARCH and res.kernel_launches >= 1
     assert_same(res, oracle_list(t, q))
     # range form agrees with the list form
     first, count, status = m.get_segment_range(q.playlist, q.level, q.begin, q.duration)
