@@ -1085,10 +1085,10 @@ static int max_grid_of(size_t smem)
 int resolve_search_max_grid(size_t smem, bool small, int ipt)
 {
     if (small) return ipt == 2 ? max_grid_of<true, 2>(smem) : max_grid_of<true, 4>(smem);
-    return max_grid_of<false, 4>(smem);
+    return ipt == 2 ? max_grid_of<false, 2>(smem) : max_grid_of<false, 4>(smem);
 }
 
-int resolve_search_tile(bool small, int ipt) { return kThreads * ((small && ipt == 2) ? 2 : 4); }
+int resolve_search_tile(bool small, int ipt) { (void)small; return kThreads * (ipt == 2 ? 2 : 4); }
 
 int resolve_filter_max_grid()
 {
@@ -1103,6 +1103,7 @@ cudaError_t launch_resolve_search(const ResolveParams &p, int grid, size_t smem,
 {
     if (p.small && p.ipt == 2) resolve_search_kernel<true, 2><<<grid, kThreads, smem, s>>>(p);
     else if (p.small) resolve_search_kernel<true, 4><<<grid, kThreads, smem, s>>>(p);
+    else if (p.ipt == 2) resolve_search_kernel<false, 2><<<grid, kThreads, smem, s>>>(p);
     else resolve_search_kernel<false, 4><<<grid, kThreads, smem, s>>>(p);
     return cudaGetLastError();
 }

@@ -6,7 +6,7 @@ import hlsjs_p2p_wrapper_b200 as pk
 from hlsjs_p2p_wrapper_b200 import synth
 out = sys.argv[1]
 ctx = pk.Context(0)
-t, q = synth.config2()
+t, q = synth.config5(n_playlists=20000) if os.environ.get('TRACE_WORKLOAD') == 'config5' else synth.config2()
 m = ctx.upload(t)
 dev = torch.device("cuda:0")
 d = {k: torch.from_numpy(getattr(q, k)).to(dev) for k in ("playlist", "level", "begin", "duration")}
