@@ -79,7 +79,6 @@ struct SearchSmem {
     unsigned long long warp_cnt[kWarps];
     int warp_heads[kWarps];
     int tile_slot[2];              // next tile id, double buffered across iterations
-    int tile_peek;                 // the same, announced early for the L2 prefetch
     RecTable<SMALL, Shape<IPT>::kTile> rec;
     // per 32 output slots of the window: .x = bitmap of slots where a record starts,
     // .y = records that start before this word (tile-wide rank base).  Double buffered.
@@ -249,9 +248,9 @@ __device__ __forceinline__ unsigned long long warp_excl_scan64(unsigned long lon
 // NaN-free column  cell(s) < cell(x) => s < x  and  cell(s) > cell(x) => s > x : a bound
 // always lies inside [grid[cell], grid[cell+1]] and is finished there with the filter's own
 // comparison.  The grid narrows the search; it never decides a comparison.
-__device__ __forceinline__ void trace_mark(const ResolveParams &p, int tile, int slot)
+__device__ __forceinline__ void trace_mark(const ResolveParams &p, int tile, int slot, int who = 0)
 {
-    if (p.trace != nullptr && threadIdx.x == 0) {
+    if (p.trace != nullptr && threadIdx.x == who) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         p.trace[(long long)tile * 16 + slot] = t;
@@ -264,9 +263,10 @@ __device__ __forceinline__ void trace_mark(const ResolveParams &p, int tile, int
 }
 
 // Same, but issued only once `dep` has been produced (e.g. a loaded value).
-__device__ __forceinline__ void trace_mark_after(const ResolveParams &p, int tile, int slot, int dep)
+__device__ __forceinline__ void trace_mark_after(const ResolveParams &p, int tile, int slot, int dep,
+                                                 int who = 0)
 {
-    if (p.trace != nullptr && threadIdx.x == 0) {
+    if (p.trace != nullptr && threadIdx.x == who) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t) : "r"(dep));
         p.trace[(long long)tile * 16 + slot] = t;
@@ -386,9 +386,22 @@ resolve_search_kernel(const ResolveParams p)
             const long long q_end = min(p.nq, (long long)(tileB + 1) * p.tile_q);
             const bool full = p.vec_ok && q0 + kIpt <= q_end;
             trace_mark(p, tileB, 0);
-            if (tid == 0) {    // claim the next tile now: the atomic lands during the search
-                t_new = atomicAdd(&p.ctr->ticket[p.epoch & 1u], 1u);
-                ticket_pending = true;
+            {   // Pull the queries of the tile one grid-width ahead towards L2.  Tiles are handed
+                // out in order, so every tile beyond the first wave is prefetched exactly once,
+                // about one round before whichever CTA claims it loads them.
+                const long long tileC = (long long)tileB + gridDim.x;
+                if (tileC < p.n_tiles) {
+                    const long long c0 = tileC * p.tile_q;
+                    const long long cn = min((long long)p.tile_q, p.nq - c0);
+                    const int l64 = (int)((cn * 8 + 127) >> 7), l32 = (int)((cn * 4 + 127) >> 7);
+                    const char *a = nullptr;
+                    if (tid < l64) a = reinterpret_cast<const char *>(p.q_begin + c0) + tid * 128;
+                    else if (tid < 2 * l64) a = reinterpret_cast<const char *>(p.q_duration + c0) + (tid - l64) * 128;
+                    else if (tid < 2 * l64 + l32) a = reinterpret_cast<const char *>(p.q_level + c0) + (tid - 2 * l64) * 128;
+                    else if (tid < 2 * l64 + 2 * l32 && p.q_playlist)
+                        a = reinterpret_cast<const char *>(p.q_playlist + c0) + (tid - 2 * l64 - l32) * 128;
+                    if (a) asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
+                }
             }
 
             // ---- load this thread's consecutive queries -----------------------------------
@@ -581,23 +594,7 @@ resolve_search_kernel(const ResolveParams p)
             unsigned long long wtot;
             const unsigned long long texcl = warp_excl_scan64(tval, wtot);
             if (lane == 0) sm.warp_cnt[warp] = wtot;
-            if (tid == 0) sm.tile_peek = (int)t_new;   // the tile searched next
             __syncthreads();     // also: everyone is past the previous emission of rec[]/hb[]
-            {   // pull the next tile's queries towards L2 while this one is emitted
-                const int tileC = sm.tile_peek;
-                if (tileC < p.n_tiles) {
-                    const long long c0 = (long long)tileC * p.tile_q;
-                    const long long cn = min((long long)p.tile_q, p.nq - c0);     // queries in that tile
-                    const int l64 = (int)((cn * 8 + 127) >> 7), l32 = (int)((cn * 4 + 127) >> 7);
-                    const char *a = nullptr;
-                    if (tid < l64) a = reinterpret_cast<const char *>(p.q_begin + c0) + tid * 128;
-                    else if (tid < 2 * l64) a = reinterpret_cast<const char *>(p.q_duration + c0) + (tid - l64) * 128;
-                    else if (tid < 2 * l64 + l32) a = reinterpret_cast<const char *>(p.q_level + c0) + (tid - 2 * l64) * 128;
-                    else if (tid < 2 * l64 + 2 * l32 && p.q_playlist)
-                        a = reinterpret_cast<const char *>(p.q_playlist + c0) + (tid - 2 * l64 - l32) * 128;
-                    if (a) asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
-                }
-            }
             unsigned long long wbase = 0, tile_tot = 0;
 #pragma unroll
             for (int w = 0; w < kWarps; w++) {
@@ -701,6 +698,13 @@ resolve_search_kernel(const ResolveParams p)
                 const bool all_fit = (long long)tile_base + total <= p.capacity;   // CTA-uniform
                 for (int w0 = 0; w0 < total; w0 += kWindow) {
                     uint2 *H = sm.hb[hbuf];
+                    if (tid == 0 && haveB && !ticket_pending && w0 + kWindow >= total) {
+                        // Claim the next tile as late as possible -- a claimed but unsearched
+                        // tile stalls the look-back of every later tile -- yet early enough
+                        // for the atomic's round trip to hide behind this last window.
+                        t_new = atomicAdd(&p.ctr->ticket[p.epoch & 1u], 1u);
+                        ticket_pending = true;
+                    }
                     {   // mark where this thread's records start inside the window, rank words
                         int r2 = (int)a_rel;
 #pragma unroll
