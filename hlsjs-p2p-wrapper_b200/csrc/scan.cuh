@@ -48,21 +48,6 @@ struct TileScan {
         return s.tile;
     }
 
-    // CTA-wide sum of a per-thread value; result valid in every thread.
-    __device__ static unsigned long long block_sum(Smem &s, unsigned long long v)
-    {
-        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
-        __syncthreads();
-        if (lane == 0) s.warp_sum[warp] = v;
-        __syncthreads();
-        unsigned long long t = 0;
-#pragma unroll
-        for (int w = 0; w < NW; w++) t += s.warp_sum[w];
-        return t;
-    }
-
     // A batch may not produce more than INT32_MAX entries (the host reports OVERFLOW), so
     // published values saturate far above that instead of wrapping the 40-bit field.
     static constexpr unsigned long long kSat = 1ull << 33;
@@ -169,40 +154,6 @@ struct TileScan {
     {
         publish_aggregate(status, epoch, tile, aggregate, base);
         return wait_prefix(s, status, epoch, tile, aggregate, nullptr, base);
-    }
-
-    // Ticket prefetch: thread 0 asks for the CTA's next tile while the current one is still
-    // being written, so the L2 round trip of the atomic is off the critical path.
-    __device__ static unsigned prefetch_ticket(ScanCounters *ctr, unsigned epoch)
-    {
-        return threadIdx.x == 0 ? atomicAdd(&ctr->ticket[epoch & 1u], 1u) : 0u;
-    }
-    __device__ static int next_tile_prefetched(Smem &s, unsigned ticket)
-    {
-        __syncthreads();  // previous tile fully consumed (shared buffers, s.tile)
-        if (threadIdx.x == 0) s.tile = (int)ticket;
-        __syncthreads();
-        return s.tile;
-    }
-
-    // Fire-and-forget completion count: no thread waits for the atomic's return value.
-    __device__ static void tile_done_async(ScanCounters *ctr)
-    {
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            __threadfence();
-            atomicAdd(&ctr->done, 1u);
-        }
-    }
-    // Called (by all threads) in the CTA that ran the batch's LAST tile, after its own
-    // tile_done_async(): thread 0 waits for every other tile, then publishes the result.
-    __device__ static void finish_when_all_done(ScanCounters *ctr, DeviceResult *result,
-                                                unsigned epoch, int n_tiles)
-    {
-        if (threadIdx.x != 0) return;
-        while (ld_relaxed_u32(&ctr->done) != (unsigned)n_tiles) { }
-        __threadfence();
-        finish_batch(ctr, result, epoch);
     }
 
     // Call once per finished tile, after its global writes.  Returns true in thread 0 of

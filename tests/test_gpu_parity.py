@@ -275,3 +275,40 @@ def test_device_pointer_variant_full_size_properties(ctx):
     assert np.array_equal(off, assert_same_dev[0]) and np.array_equal(sn, assert_same_dev[2])
     assert np.array_equal(tm.view(np.uint64), assert_same_dev[3].view(np.uint64))
     m.close()
+
+
+# ---- host-pointer pipeline (chunked H2D / kernel / D2H) ------------------------------------------
+def test_host_pipeline_many_hits_falls_back_and_stays_exact(ctx):
+    """> 16 hits per query on average: the pipeline's device-side guess overflows, the call falls
+    back to the exact-count path, and the result is still bit-exact."""
+    t, _ = synth.config2(n_queries=4)
+    nq = 300_000
+    rng = np.random.default_rng(8)
+    q = QueryBatch(np.zeros(nq, np.int32), rng.integers(0, 3, nq).astype(np.int32),
+                   rng.integers(0, 5000, nq).astype(np.float64), np.full(nq, 200.0))
+    m = ctx.upload(t)
+    ref = oracle_list(t, q)
+    assert ref[0][-1] > 16 * nq + 1024
+    res = m.get_segment_list(q.playlist, q.level, q.begin, q.duration, capacity=int(ref[0][-1]))
+    assert_same(res, ref)
+    m.close()
+
+
+def test_host_pipeline_capacity_and_statuses(ctx):
+    """Chunked path: caller capacity one short -> CAPACITY error with the needed total; statuses
+    and unparsed / missing tallies accumulate across chunks."""
+    t = synth.hls_mock_tables(3, 1, False)              # level 1 parsed, 0 and 2 unparsed
+    nq = 400_000
+    rng = np.random.default_rng(9)
+    q = QueryBatch(np.zeros(nq, np.int32), rng.integers(-1, 5, nq).astype(np.int32),
+                   rng.integers(0, 2500, nq).astype(np.float64), rng.integers(0, 60, nq).astype(np.float64))
+    m = ctx.upload(t)
+    ref = oracle_list(t, q)
+    total = int(ref[0][-1])
+    res = m.get_segment_list(q.playlist, q.level, q.begin, q.duration, capacity=total)
+    assert res.kernel_launches >= 2                      # it really went through the chunks
+    assert_same(res, ref)
+    with pytest.raises(N.HlsMapError) as e:
+        m.get_segment_list(q.playlist, q.level, q.begin, q.duration, capacity=total - 1)
+    assert e.value.code == N.ERR_CAPACITY and str(total) in e.value.message
+    m.close()
