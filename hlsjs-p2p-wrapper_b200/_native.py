@@ -43,6 +43,7 @@ SYMBOLS = {
     "hlsmap_ctx_create": (_INT, [_INT, _P]),
     "hlsmap_ctx_destroy": (None, [_P]),
     "hlsmap_ctx_device": (_INT, [_P]),
+    "hlsmap_ctx_set_batch_overlap": (_INT, [_P, _INT]),
     "hlsmap_ctx_synchronize": (_INT, [_P]),
     "hlsmap_host_alloc": (_INT, [_P, _I64, _P]),
     "hlsmap_host_free": (_INT, [_P, _P]),

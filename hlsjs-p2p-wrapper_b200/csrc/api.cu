@@ -45,10 +45,12 @@ struct hlsmap_ctx {
     cudaStream_t s_in = nullptr;        // host pipeline: query uploads
     cudaStream_t s_out = nullptr;       // host pipeline: result downloads
     cudaEvent_t ev_in[2] = {nullptr, nullptr};
-    ScanCounters *ctr = nullptr;        // scan scratch header
-    DeviceResult *d_result = nullptr;
+    ScanCounters *ctr = nullptr;        // scan scratch headers, one per scratch set (2)
+    DeviceResult *d_result = nullptr;   // results, one per scratch set (2)
+    bool overlap = false;               // consecutive search batches may overlap (PDL)
+    unsigned set_launches[2] = {0, 0};  // kernels launched on each scratch set (ticket slot parity)
     DeviceResult *h_result = nullptr;   // pinned
-    unsigned long long *tile_status = nullptr;
+    unsigned long long *tile_status = nullptr;   // 2 x tile_cap status words (set = epoch & 1)
     int64_t tile_cap = 0;
     unsigned epoch = 0;
     int last_launches = 0;
@@ -113,7 +115,8 @@ int ensure_slot(hlsmap_ctx *ctx, int i, int64_t bytes, void **out)
     return HLSMAP_OK;
 }
 
-// Scratch for a scan batch of n_tiles tiles; bumps the launch epoch.
+// Scratch for a scan batch of n_tiles tiles; bumps the launch epoch.  Launches alternate
+// between two scratch sets (epoch & 1) so that a batch may start while its predecessor drains.
 int prepare_scan(hlsmap_ctx *ctx, int64_t n_tiles, cudaStream_t s)
 {
     if (n_tiles > ctx->tile_cap) {
@@ -122,27 +125,36 @@ int prepare_scan(hlsmap_ctx *ctx, int64_t n_tiles, cudaStream_t s)
         if (ctx->tile_status) CK(cudaFree(ctx->tile_status));
         ctx->tile_status = nullptr;
         const int64_t cap = n_tiles + n_tiles / 2 + 1024;
-        cudaError_t e = cudaMalloc(&ctx->tile_status, (size_t)cap * 8);
+        cudaError_t e = cudaMalloc(&ctx->tile_status, (size_t)cap * 16);
         if (e != cudaSuccess) {
             cudaGetLastError();
             ctx->tile_cap = 0;
             return fail(HLSMAP_ERR_NOMEM, "cudaMalloc of tile status failed");
         }
         ctx->tile_cap = cap;
-        CK(cudaMemsetAsync(ctx->tile_status, 0, (size_t)cap * 8, s));
+        CK(cudaMemsetAsync(ctx->tile_status, 0, (size_t)cap * 16, s));
     }
     ctx->epoch++;
     if (ctx->epoch > kEpochMask) {  // epoch 0 means "never written": wipe and restart
-        CK(cudaMemsetAsync(ctx->tile_status, 0, (size_t)ctx->tile_cap * 8, s));
-        CK(cudaMemsetAsync(ctx->ctr, 0, sizeof(ScanCounters), s));
+        CK(cudaStreamSynchronize(s));
+        CK(cudaMemsetAsync(ctx->tile_status, 0, (size_t)ctx->tile_cap * 16, s));
+        CK(cudaMemsetAsync(ctx->ctr, 0, 2 * sizeof(ScanCounters), s));
+        ctx->set_launches[0] = ctx->set_launches[1] = 0;
         ctx->epoch = 1;
     }
     return HLSMAP_OK;
 }
 
+inline ScanCounters *ctr_of(hlsmap_ctx *ctx) { return ctx->ctr + (ctx->epoch & 1u); }
+inline DeviceResult *result_of(hlsmap_ctx *ctx) { return ctx->d_result + (ctx->epoch & 1u); }
+inline unsigned long long *status_of(hlsmap_ctx *ctx)
+{
+    return ctx->tile_status + (ctx->epoch & 1u) * ctx->tile_cap;
+}
+
 int fetch_result(hlsmap_ctx *ctx, cudaStream_t s, hlsmap_result *out)
 {
-    CK(cudaMemcpyAsync(ctx->h_result, ctx->d_result, sizeof(DeviceResult), cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(ctx->h_result, result_of(ctx), sizeof(DeviceResult), cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
     out->total_hits = ctx->h_result->total_hits;
     out->n_unparsed = ctx->h_result->n_unparsed;
@@ -222,10 +234,10 @@ int hlsmap_ctx_create(int device, hlsmap_ctx **out)
     CK(cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&c->ev_in[0], cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&c->ev_in[1], cudaEventDisableTiming));
-    CK(cudaMalloc(&c->ctr, sizeof(ScanCounters)));
-    CK(cudaMalloc(&c->d_result, sizeof(DeviceResult)));
-    CK(cudaMemset(c->ctr, 0, sizeof(ScanCounters)));
-    CK(cudaMemset(c->d_result, 0, sizeof(DeviceResult)));
+    CK(cudaMalloc(&c->ctr, 2 * sizeof(ScanCounters)));
+    CK(cudaMalloc(&c->d_result, 2 * sizeof(DeviceResult)));
+    CK(cudaMemset(c->ctr, 0, 2 * sizeof(ScanCounters)));
+    CK(cudaMemset(c->d_result, 0, 2 * sizeof(DeviceResult)));
     CK(cudaHostAlloc(&c->h_result, sizeof(DeviceResult), cudaHostAllocDefault));
     memset(c->h_result, 0, sizeof(DeviceResult));
     *out = c;
@@ -252,6 +264,13 @@ void hlsmap_ctx_destroy(hlsmap_ctx *c)
 }
 
 int hlsmap_ctx_device(const hlsmap_ctx *ctx) { return ctx ? ctx->device : -1; }
+
+int hlsmap_ctx_set_batch_overlap(hlsmap_ctx *ctx, int enable)
+{
+    if (!ctx) return fail(HLSMAP_ERR_INVALID, "null context");
+    ctx->overlap = enable != 0;
+    return HLSMAP_OK;
+}
 
 int hlsmap_ctx_synchronize(hlsmap_ctx *ctx)
 {
@@ -528,8 +547,10 @@ static int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
     ctx->have_last = true;
 
     if (nq == 0) {
+        r = prepare_scan(ctx, 0, s);        // moves to the other scratch set
+        if (r) return r;
         CK(cudaMemsetAsync(d_offsets, 0, sizeof(int32_t), s));
-        CK(cudaMemsetAsync(ctx->d_result, 0, sizeof(DeviceResult), s));
+        CK(cudaMemsetAsync(result_of(ctx), 0, sizeof(DeviceResult), s));
         if (result) return fetch_result(ctx, s, result);
         return HLSMAP_OK;
     }
@@ -558,10 +579,11 @@ static int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
     p.time_out = d_time_out;
     p.capacity = d_sn_out ? hit_capacity : 0;
     p.status = d_status;
-    p.tile_status = ctx->tile_status;
-    p.ctr = ctx->ctr;
-    p.result = ctx->d_result;
+    p.tile_status = status_of(ctx);
+    p.ctr = ctr_of(ctx);
+    p.result = result_of(ctx);
     p.epoch = ctx->epoch;
+    p.tslot = ctx->set_launches[ctx->epoch & 1u] & 1u;
     p.n_tiles = (int)n_tiles;
     p.tile_q = tile_q;
     p.base = base;
@@ -587,11 +609,12 @@ static int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
     }
     if (path == HLSMAP_PATH_SEARCH) {
         const int grid = (int)(n_tiles < map->grid_search ? n_tiles : map->grid_search);
-        CK(launch_resolve_search(p, grid, map->stage_smem, s));
+        CK(launch_resolve_search(p, grid, map->stage_smem, s, ctx->overlap && d_trace == nullptr));
     } else {
         const int grid = (int)(n_tiles < map->grid_filter ? n_tiles : map->grid_filter);
         CK(launch_resolve_filter(p, grid, s));
     }
+    ctx->set_launches[ctx->epoch & 1u]++;      // only after a successful launch
     ctx->last_launches = 1;
     if (d_trace) {
         std::vector<unsigned long long> h((size_t)n_tiles * 16);
@@ -1004,13 +1027,15 @@ int hlsmap_view_format_dev(hlsmap_ctx *ctx, int64_t n, const int32_t *d_level,
     p.offsets = d_offsets;
     p.chars = d_chars;
     p.capacity = capacity;
-    p.tile_status = ctx->tile_status;
-    p.ctr = ctx->ctr;
-    p.result = ctx->d_result;
+    p.tile_status = status_of(ctx);
+    p.ctr = ctr_of(ctx);
+    p.result = result_of(ctx);
     p.epoch = ctx->epoch;
+    p.tslot = ctx->set_launches[ctx->epoch & 1u] & 1u;
     p.n_tiles = (int)n_tiles;
     const int maxg = view_format_max_grid();
     CK(launch_view_format(p, (int)(n_tiles < maxg ? n_tiles : maxg), s));
+    ctx->set_launches[ctx->epoch & 1u]++;
     ctx->last_launches = 1;
     if (total_out) {
         hlsmap_result res{};
@@ -1281,6 +1306,7 @@ int hlsmap_get_segment_list_noalloc_dev(hlsmap_map *map, int64_t nq, const int32
         p.ctr = ctr;
         p.result = dres;
         p.epoch = 1;   // words were just zeroed, so any non-zero epoch marks "written by this call"
+        p.tslot = 0;
         p.n_tiles = (int)n_tiles;
         p.tile_q = tile_q;
         p.stage_elems = map->stage_elems;

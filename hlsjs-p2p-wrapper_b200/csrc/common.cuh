@@ -26,13 +26,16 @@ struct __align__(16) TrackHint {
 constexpr unsigned kTrackStateMask = 3u;
 constexpr unsigned kTrackMonotone = 4u;
 
-// Per-context scratch header for the single-pass scan kernels.  ticket[] is double
-// buffered by launch parity so that late ticket fetches of launch e never see the reset
-// done for launch e+1.
+// Per-context scratch header for the single-pass scan kernels.  A context owns TWO scratch
+// sets (header + status words + result) used by alternate launches (set = epoch & 1), so that
+// a batch may start while the previous one is still draining; `owner` is the epoch of the
+// launch currently using the set (0 = free), and ticket[] is double buffered: the host tells
+// each launch which of the two counters to use (they alternate per set), and a launch's last
+// tile zeroes the OTHER one, so late ticket fetches of a launch never see the next one's reset.
 struct ScanCounters {
     unsigned int ticket[2];
     unsigned int done;
-    unsigned int pad;
+    unsigned int owner;
     unsigned long long n_unparsed;
     unsigned long long n_missing;
 };
@@ -90,6 +93,7 @@ struct ResolveParams {
     ScanCounters *ctr;
     DeviceResult *result;
     unsigned epoch;
+    unsigned tslot;         // which ticket counter of the set this launch uses (0 / 1)
     int n_tiles;
     // staging
     int stage_elems;  // capacity of the shared-memory copy of start[], in doubles
@@ -116,7 +120,8 @@ struct RangeParams {
 };
 
 // launchers (resolve.cu)
-cudaError_t launch_resolve_search(const ResolveParams &p, int grid, size_t smem, cudaStream_t s);
+cudaError_t launch_resolve_search(const ResolveParams &p, int grid, size_t smem, cudaStream_t s,
+                                  bool overlap_next = false);
 cudaError_t launch_resolve_filter(const ResolveParams &p, int grid, cudaStream_t s);
 cudaError_t launch_range(const RangeParams &p, cudaStream_t s);
 cudaError_t launch_monotone_check(const double *start, TrackDesc *desc, int n_tracks,
@@ -144,6 +149,7 @@ struct FormatParams {
     ScanCounters *ctr;
     DeviceResult *result;
     unsigned epoch;
+    unsigned tslot;
     int n_tiles;
 };
 constexpr int kFormatTileViews = 1024;

@@ -346,7 +346,11 @@ resolve_search_kernel(const ResolveParams p)
     //      (No deeper look-ahead: a claimed tile is a tile no idle CTA can take.)
     unsigned t_new = 0;
     unsigned slot = 0;
-    if (tid == 0) sm.tile_slot[0] = (int)atomicAdd(&p.ctr->ticket[p.epoch & 1u], 1u);
+    // Programmatic dependent launch: let the next batch's CTAs take the slots this grid frees
+    // while it drains (only takes effect when the host launched with that attribute).
+    asm volatile("griddepcontrol.launch_dependents;");
+    Scan::acquire_set(p.ctr, p.epoch);
+    if (tid == 0) sm.tile_slot[0] = (int)atomicAdd(&p.ctr->ticket[p.tslot & 1u], 1u);
     __syncthreads();
     int tileB = sm.tile_slot[0];
 
@@ -702,7 +706,7 @@ resolve_search_kernel(const ResolveParams p)
                         // Claim the next tile as late as possible -- a claimed but unsearched
                         // tile stalls the look-back of every later tile -- yet early enough
                         // for the atomic's round trip to hide behind this last window.
-                        t_new = atomicAdd(&p.ctr->ticket[p.epoch & 1u], 1u);
+                        t_new = atomicAdd(&p.ctr->ticket[p.tslot & 1u], 1u);
                         ticket_pending = true;
                     }
                     {   // mark where this thread's records start inside the window, rank words
@@ -780,7 +784,7 @@ resolve_search_kernel(const ResolveParams p)
         slot ^= 1u;            // alternate slots: the one read last iteration is not rewritten
         if (tid == 0) {
             if (haveB) {
-                if (!ticket_pending) t_new = atomicAdd(&p.ctr->ticket[p.epoch & 1u], 1u);
+                if (!ticket_pending) t_new = atomicAdd(&p.ctr->ticket[p.tslot & 1u], 1u);
                 sm.tile_slot[slot] = (int)t_new;
                 ticket_pending = false;
             } else {
@@ -795,7 +799,7 @@ resolve_search_kernel(const ResolveParams p)
             if (tileA == p.n_tiles - 1) {                  // the batch's last tile: wrap up
                 while (ld_relaxed_u32(&p.ctr->done) != (unsigned)p.n_tiles) { }
                 __threadfence();
-                Scan::finish_batch(p.ctr, p.result, p.epoch);
+                Scan::finish_batch(p.ctr, p.result, p.tslot);
             }
         }
         tileA = haveB ? tileB : -1;
@@ -872,8 +876,9 @@ resolve_filter_kernel(const ResolveParams p)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned lane_lt = (1u << lane) - 1u;
 
+    FScan::acquire_set(p.ctr, p.epoch);
     for (;;) {
-        const int tile = FScan::next_tile(scan, p.ctr, p.epoch);
+        const int tile = FScan::next_tile(scan, p.ctr, p.tslot);
         if (tile >= p.n_tiles) break;
         const long long q = (long long)tile * kFThreads + tid;
         const bool in = q < p.nq;
@@ -965,7 +970,7 @@ resolve_filter_kernel(const ResolveParams p)
             }
         }
 
-        if (FScan::tile_done(p.ctr, p.n_tiles)) FScan::finish_batch(p.ctr, p.result, p.epoch);
+        if (FScan::tile_done(p.ctr, p.n_tiles)) FScan::finish_batch(p.ctr, p.result, p.tslot);
     }
 }
 
@@ -1103,13 +1108,33 @@ int resolve_filter_max_grid()
     return per_sm * sm_count();
 }
 
-cudaError_t launch_resolve_search(const ResolveParams &p, int grid, size_t smem, cudaStream_t s)
+template <bool SMALL, int IPT>
+static cudaError_t launch_search_variant(const ResolveParams &p, int grid, size_t smem,
+                                         cudaStream_t s, bool overlap_next)
 {
-    if (p.small && p.ipt == 2) resolve_search_kernel<true, 2><<<grid, kThreads, smem, s>>>(p);
-    else if (p.small) resolve_search_kernel<true, 4><<<grid, kThreads, smem, s>>>(p);
-    else if (p.ipt == 2) resolve_search_kernel<false, 2><<<grid, kThreads, smem, s>>>(p);
-    else resolve_search_kernel<false, 4><<<grid, kThreads, smem, s>>>(p);
-    return cudaGetLastError();
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = overlap_next ? 1 : 0;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, resolve_search_kernel<SMALL, IPT>, p);
+}
+
+// overlap_next: this batch may begin while the previous kernel on the stream is draining.
+cudaError_t launch_resolve_search(const ResolveParams &p, int grid, size_t smem, cudaStream_t s,
+                                  bool overlap_next)
+{
+    cudaError_t e;
+    if (p.small && p.ipt == 2) e = launch_search_variant<true, 2>(p, grid, smem, s, overlap_next);
+    else if (p.small) e = launch_search_variant<true, 4>(p, grid, smem, s, overlap_next);
+    else if (p.ipt == 2) e = launch_search_variant<false, 2>(p, grid, smem, s, overlap_next);
+    else e = launch_search_variant<false, 4>(p, grid, smem, s, overlap_next);
+    return e != cudaSuccess ? e : cudaGetLastError();
 }
 
 cudaError_t launch_resolve_filter(const ResolveParams &p, int grid, cudaStream_t s)

@@ -38,12 +38,27 @@ struct TileScan {
         unsigned long long warp_sum[NW];
     };
 
+    // Called by every CTA before its first ticket: waits until the previous user of this
+    // scratch set (two launches back) has wrapped up, then marks the set as this launch's.
+    __device__ static void acquire_set(ScanCounters *ctr, unsigned epoch)
+    {
+        if (threadIdx.x == 0) {
+            const unsigned e = epoch & kEpochMask;
+            for (;;) {
+                const unsigned o = atomicCAS(&ctr->owner, 0u, e);
+                if (o == 0u || o == e) break;
+                __nanosleep(256);
+            }
+        }
+        __syncthreads();
+    }
+
     // Tickets hand out tiles in order, so every predecessor of a tile is already owned
     // by a running CTA (forward progress of the look-back does not depend on blockIdx).
-    __device__ static int next_tile(Smem &s, ScanCounters *ctr, unsigned epoch)
+    __device__ static int next_tile(Smem &s, ScanCounters *ctr, unsigned tslot)
     {
         __syncthreads();  // previous tile fully consumed (shared buffers, s.tile)
-        if (threadIdx.x == 0) s.tile = (int)atomicAdd(&ctr->ticket[epoch & 1u], 1u);
+        if (threadIdx.x == 0) s.tile = (int)atomicAdd(&ctr->ticket[tslot & 1u], 1u);
         __syncthreads();
         return s.tile;
     }
@@ -171,15 +186,16 @@ struct TileScan {
 
     // Run by the thread tile_done() elected: hand the counters to the host-visible
     // result and re-arm the scratch header for the next launch.
-    __device__ static void finish_batch(ScanCounters *ctr, DeviceResult *result, unsigned epoch)
+    __device__ static void finish_batch(ScanCounters *ctr, DeviceResult *result, unsigned tslot)
     {
         result->n_unparsed = (long long)atomicAdd(&ctr->n_unparsed, 0ull);
         result->n_missing = (long long)atomicAdd(&ctr->n_missing, 0ull);
         ctr->n_unparsed = 0ull;
         ctr->n_missing = 0ull;
         ctr->done = 0u;
-        ctr->ticket[(epoch + 1u) & 1u] = 0u;  // untouched by this launch's late fetches
+        ctr->ticket[(tslot & 1u) ^ 1u] = 0u;       // untouched by this launch's late fetches
         __threadfence();
+        atomicExch(&ctr->owner, 0u);                // the set is free for the launch after next
     }
 };
 

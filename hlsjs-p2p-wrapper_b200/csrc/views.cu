@@ -220,8 +220,9 @@ view_format_kernel(const FormatParams p)
     __shared__ char buf[kFormatTileViews * kFmtMaxChars];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
+    FmtScan::acquire_set(p.ctr, p.epoch);
     for (;;) {
-        const int tile = FmtScan::next_tile(scan, p.ctr, p.epoch);
+        const int tile = FmtScan::next_tile(scan, p.ctr, p.tslot);
         if (tile >= p.n_tiles) break;
         const long long v0 = (long long)tile * kFormatTileViews + (long long)tid * kFmtIpt;
         int l[kFmtIpt], u[kFmtIpt], s[kFmtIpt], len[kFmtIpt];
@@ -284,7 +285,7 @@ view_format_kernel(const FormatParams p)
             const long long o = (long long)tile_base + i;
             if (o < p.capacity) p.chars[o] = buf[i];
         }
-        if (FmtScan::tile_done(p.ctr, p.n_tiles)) FmtScan::finish_batch(p.ctr, p.result, p.epoch);
+        if (FmtScan::tile_done(p.ctr, p.n_tiles)) FmtScan::finish_batch(p.ctr, p.result, p.tslot);
     }
 }
 

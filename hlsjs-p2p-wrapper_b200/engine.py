@@ -58,6 +58,11 @@ class Context:
         except Exception:
             pass
 
+    def set_batch_overlap(self, enable=True):
+        """Allow consecutive, independent device-pointer batches to overlap (the next one starts
+        while the previous one drains).  The caller guarantees they share no output buffers."""
+        N.check(self._lib.hlsmap_ctx_set_batch_overlap(self._h, int(bool(enable))))
+
     def synchronize(self):
         N.check(self._lib.hlsmap_ctx_synchronize(self._h))
 

@@ -87,6 +87,13 @@ int hlsmap_device_count(void);
 int hlsmap_ctx_create(int device, hlsmap_ctx **out);
 void hlsmap_ctx_destroy(hlsmap_ctx *ctx);
 int hlsmap_ctx_device(const hlsmap_ctx *ctx);
+/* Opt in to overlapping consecutive getSegmentList batches issued with the _dev entry point:
+ * with enable != 0 a batch may begin (programmatic dependent launch) while the previous batch
+ * on the same stream is still writing its last hits, which hides each batch's ramp-up behind
+ * its predecessor's tail.  ONLY legal when consecutive batches are independent: the next batch
+ * must not read, or write to, any buffer the previous one is still writing.  Off by default
+ * (plain stream order).  The library's own scratch is double-buffered for this. */
+int hlsmap_ctx_set_batch_overlap(hlsmap_ctx *ctx, int enable);
 /* Block until everything issued through the context's own stream has finished. */
 int hlsmap_ctx_synchronize(hlsmap_ctx *ctx);
 

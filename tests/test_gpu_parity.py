@@ -312,3 +312,45 @@ def test_host_pipeline_capacity_and_statuses(ctx):
         m.get_segment_list(q.playlist, q.level, q.begin, q.duration, capacity=total - 1)
     assert e.value.code == N.ERR_CAPACITY and str(total) in e.value.message
     m.close()
+
+
+def test_overlapping_batches_on_disjoint_buffers(ctx):
+    """hlsmap_ctx_set_batch_overlap: consecutive batches with their own buffers may overlap on
+    the GPU (the next starts while the previous drains); every batch must still be bit-exact,
+    and the library's double-buffered scratch must survive many launches in a row."""
+    import torch
+    dev = torch.device("cuda:0")
+    t, _ = synth.config2(n_queries=4)
+    m = ctx.upload(t)
+    stream = torch.cuda.Stream(device=dev)
+    sets = []
+    for i, nq in enumerate((200_000, 70_001, 333_333, 1_000, 150_000)):
+        _, q = synth.config2(seed=40 + i, n_queries=nq)
+        ref = oracle_list(t, q)
+        H = int(ref[0][-1])
+        sets.append({"q": q, "ref": ref, "H": H,
+                     "pl": torch.from_numpy(q.playlist).to(dev), "lv": torch.from_numpy(q.level).to(dev),
+                     "bg": torch.from_numpy(q.begin).to(dev), "du": torch.from_numpy(q.duration).to(dev),
+                     "off": torch.empty(nq + 1, dtype=torch.int32, device=dev),
+                     "sn": torch.empty(max(H, 1), dtype=torch.int32, device=dev),
+                     "tm": torch.empty(max(H, 1), dtype=torch.float64, device=dev)})
+    torch.cuda.synchronize()
+    ctx.set_batch_overlap(True)
+    try:
+        for rep in range(4):                       # 20 launches back to back, no host sync between
+            for s in sets:
+                s["off"].fill_(-1)
+                m.get_segment_list_dev(len(s["q"]), s["pl"].data_ptr(), s["lv"].data_ptr(),
+                                       s["bg"].data_ptr(), s["du"].data_ptr(), s["off"].data_ptr(),
+                                       s["sn"].data_ptr(), s["tm"].data_ptr(), s["H"],
+                                       stream=stream.cuda_stream)
+        last = m.last_result(stream.cuda_stream)
+        assert last.total_hits == sets[-1]["H"]
+        torch.cuda.synchronize()
+        for s in sets:
+            assert np.array_equal(s["off"].cpu().numpy().astype(np.int64), s["ref"][0])
+            assert np.array_equal(s["sn"][:s["H"]].cpu().numpy(), s["ref"][2])
+            assert np.array_equal(s["tm"][:s["H"]].cpu().numpy().view(np.uint64), s["ref"][3].view(np.uint64))
+    finally:
+        ctx.set_batch_overlap(False)
+    m.close()
