@@ -417,7 +417,7 @@ int hlsmap_map_create(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *playl
     // and a u16 hint grid of `cells` cells per fragment) fits next to the kernel's own
     // shared state, so it is staged once per CTA.  Otherwise the search kernel stages, per
     // tile, the window of the start column its queries touch.
-    int64_t small_limit = 100 * 1024, window = 96 * 1024, cells = 2;
+    int64_t small_limit = 100 * 1024, window = 64 * 1024, cells = 2;
     if (const char *e = getenv("HLSMAP_SMALL_KB")) small_limit = atoll(e) * 1024;
     if (const char *e = getenv("HLSMAP_STAGE_WINDOW_KB")) window = atoll(e) * 1024;
     if (const char *e = getenv("HLSMAP_HINT_CELLS")) cells = atoll(e) > 0 ? atoll(e) : 1;
@@ -463,7 +463,8 @@ int hlsmap_map_create(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *playl
         m->stage_smem = (size_t)m->stage_elems * 8;
     }
     // measured on B200: 512-query tiles win for both kernels (config 2: 4 CTAs/SM instead of 2-3;
-    // config 5: a tile's tracks then fit the 96 KB staging window, 37 % vs 27 % of the HBM roofline)
+    // config 5: a tile's tracks then fit the 64 KB staging window at 3 CTAs/SM, 40 % vs 27 % of
+    // the HBM roofline)
     m->ipt = 2;
     if (const char *e = getenv(small ? "HLSMAP_IPT" : "HLSMAP_IPT_GENERAL")) m->ipt = atoi(e) == 4 ? 4 : 2;
     m->grid_search = resolve_search_max_grid(m->stage_smem, small, m->ipt);

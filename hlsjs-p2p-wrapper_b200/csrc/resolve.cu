@@ -289,7 +289,7 @@ __device__ __forceinline__ int hint_cell(double x, double t0, double inv, int nc
 //  aggregate is visible to later tiles before A's long emission starts.
 // =========================================================================================
 template <bool SMALL, int IPT>
-__global__ void __launch_bounds__(kThreads, (SMALL && IPT == 2) ? 4 : (SMALL ? 3 : 2))
+__global__ void __launch_bounds__(kThreads, (SMALL && IPT == 2) ? 4 : ((SMALL || IPT == 2) ? 3 : 2))
 resolve_search_kernel(const ResolveParams p)
 {
     using S = Shape<IPT>;
