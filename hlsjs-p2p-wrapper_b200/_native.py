@@ -52,6 +52,7 @@ SYMBOLS = {
     "hlsmap_map_get_info": (_INT, [_P, _P]),
     "hlsmap_map_get_monotone": (_INT, [_P, _P]),
     "hlsmap_map_set_path": (_INT, [_P, _INT]),
+    "hlsmap_map_slide_tracks": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P]),
     "hlsmap_get_segment_list_dev": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P, _I64, _P, _P, _P]),
     "hlsmap_get_segment_list": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P, _I64, _P, _P]),
     "hlsmap_get_segment_list_noalloc_dev": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P, _I64, _P, _P, _P]),

@@ -76,6 +76,8 @@ struct hlsmap_map {
     std::vector<int32_t> h_playlist_base;
     std::vector<int32_t> h_url_count;
     std::vector<uint8_t> h_monotone;
+    std::vector<uint8_t> h_state;       // HLSMAP_TRACK_* per track
+    std::vector<int32_t> h_len, h_cap;  // current and reserved fragments per track (live updates)
     hlsmap_map_info info{};
     int path = HLSMAP_PATH_AUTO;
     int stage_elems = 0;
@@ -398,6 +400,10 @@ int hlsmap_map_create(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *playl
     CKM(cudaStreamSynchronize(s));
 
     m->h_monotone.resize(n_tracks);
+    m->h_state.assign(track_state, track_state + n_tracks);
+    m->h_len.resize(n_tracks);
+    for (int32_t t = 0; t < n_tracks; t++) m->h_len[t] = (int32_t)(track_offset[t + 1] - track_offset[t]);
+    m->h_cap = m->h_len;
     int mono = 0;
     for (int32_t t = 0; t < n_tracks; t++) {
         m->h_monotone[t] = (desc[t].flags & kTrackMonotone) ? 1 : 0;
@@ -518,6 +524,86 @@ int hlsmap_map_set_path(hlsmap_map *map, int path)
                     "search path refused: a start column is not sorted / NaN-free, only the "
                     "filter kernel is exact for this map");
     map->path = path;
+    return HLSMAP_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+//  live update: slide track windows in place
+// ---------------------------------------------------------------------------------------
+int hlsmap_map_slide_tracks(hlsmap_map *map, int64_t n, const int32_t *playlist, const int32_t *level,
+                            const int32_t *drop, const int64_t *append_offset, const double *new_start,
+                            const int32_t *new_sn, const double *new_dur0)
+{
+    if (!map) return fail(HLSMAP_ERR_INVALID, "null map");
+    hlsmap_ctx *ctx = map->ctx;
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (n < 0 || (n > 0 && (!level || !drop || !append_offset)))
+        return fail(HLSMAP_ERR_INVALID, "slide_tracks: null arrays");
+    if (n == 0) return HLSMAP_OK;
+    const int64_t n_new = append_offset[n] - append_offset[0];
+    if (append_offset[0] != 0 || n_new < 0 || (n_new > 0 && (!new_start || !new_sn)))
+        return fail(HLSMAP_ERR_INVALID, "slide_tracks: bad append_offset / null fragment arrays");
+    // resolve and validate on the host: a parsed track, at most once, within its reserved size
+    std::vector<int32_t> track((size_t)n);
+    std::vector<uint8_t> seen((size_t)map->n_tracks, 0);
+    for (int64_t i = 0; i < n; i++) {
+        const int32_t p = playlist ? playlist[i] : 0;
+        if (p < 0 || p >= map->n_playlists) return fail(HLSMAP_ERR_INVALID, "slide_tracks: playlist out of range");
+        const int32_t b = map->h_playlist_base[p], e = map->h_playlist_base[p + 1];
+        if (level[i] < 0 || level[i] >= e - b) return fail(HLSMAP_ERR_INVALID, "slide_tracks: level out of range");
+        const int32_t t = b + level[i];
+        if (map->h_state[t] != HLSMAP_TRACK_PARSED) return fail(HLSMAP_ERR_INVALID, "slide_tracks: level is not parsed");
+        if (seen[t]) return fail(HLSMAP_ERR_INVALID, "slide_tracks: a track appears twice in one call");
+        seen[t] = 1;
+        const int64_t add = append_offset[i + 1] - append_offset[i];
+        const int32_t k = drop[i] < 0 ? 0 : (drop[i] > map->h_len[t] ? map->h_len[t] : drop[i]);
+        if (add < 0 || (int64_t)map->h_len[t] - k + add > map->h_cap[t])
+            return fail(HLSMAP_ERR_CAPACITY, "slide_tracks: track would outgrow the " +
+                                                 std::to_string(map->h_cap[t]) + " fragments reserved at upload");
+        track[i] = t;
+    }
+    cudaStream_t s = ctx->stream;
+    void *v;
+    int *d_track, *d_drop, *d_nsn = nullptr;
+    long long *d_aoff;
+    double *d_nst = nullptr, *d_nd0 = nullptr;
+    if ((r = ensure_slot(ctx, 0, n * 4, &v))) return r; d_track = (int *)v;
+    if ((r = ensure_slot(ctx, 1, n * 4, &v))) return r; d_drop = (int *)v;
+    if ((r = ensure_slot(ctx, 2, (n + 1) * 8, &v))) return r; d_aoff = (long long *)v;
+    if ((r = ensure_slot(ctx, 3, (n_new > 0 ? n_new : 1) * 8, &v))) return r; d_nst = (double *)v;
+    if ((r = ensure_slot(ctx, 4, (n_new > 0 ? n_new : 1) * 4, &v))) return r; d_nsn = (int *)v;
+    if (new_dur0) { if ((r = ensure_slot(ctx, 6, n * 8, &v))) return r; d_nd0 = (double *)v; }
+    CK(cudaMemcpyAsync(d_track, track.data(), (size_t)n * 4, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d_drop, drop, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d_aoff, append_offset, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, s));
+    if (n_new > 0) {
+        CK(cudaMemcpyAsync(d_nst, new_start, (size_t)n_new * 8, cudaMemcpyHostToDevice, s));
+        CK(cudaMemcpyAsync(d_nsn, new_sn, (size_t)n_new * 4, cudaMemcpyHostToDevice, s));
+    }
+    if (new_dur0) CK(cudaMemcpyAsync(d_nd0, new_dur0, (size_t)n * 8, cudaMemcpyHostToDevice, s));
+    CK(launch_slide_tracks(map->d_start, map->d_sn, map->d_dur0, map->d_desc, n, d_track, d_drop, d_aoff,
+                           d_nst, d_nsn, d_nd0, s));
+    // shared-memory-resident maps: the hint grid follows the new columns
+    if (map->info.stage_all)
+        CK(launch_build_hint(map->d_start, map->d_desc, map->d_hint, map->d_grid, map->n_tracks, s));
+    // refresh the host's view of lengths and monotone flags (routes AUTO to search or filter)
+    std::vector<TrackDesc> desc((size_t)map->n_tracks);
+    CK(cudaMemcpyAsync(desc.data(), map->d_desc, sizeof(TrackDesc) * (size_t)map->n_tracks,
+                       cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    int mono = 0;
+    int64_t nf = 0;
+    for (int32_t t = 0; t < map->n_tracks; t++) {
+        map->h_len[t] = desc[t].len;
+        map->h_monotone[t] = (desc[t].flags & kTrackMonotone) ? 1 : 0;
+        mono += map->h_monotone[t];
+        nf += desc[t].len;
+    }
+    map->info.n_fragments = nf;
+    map->info.n_monotone_tracks = mono;
+    map->info.all_monotone = (mono == map->info.n_parsed_tracks) ? 1 : 0;
+    if (!map->info.all_monotone && map->path == HLSMAP_PATH_SEARCH) map->path = HLSMAP_PATH_AUTO;
     return HLSMAP_OK;
 }
 

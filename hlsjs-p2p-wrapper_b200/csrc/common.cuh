@@ -130,6 +130,10 @@ cudaError_t launch_segment_duration(const TrackDesc *desc, const int *playlist_b
                                     int n_playlists, const double *dur0, long long n,
                                     const int *q_playlist, const int *q_level, double *out,
                                     unsigned char *status, cudaStream_t s);
+cudaError_t launch_slide_tracks(double *start, int *sn, double *dur0, TrackDesc *desc, long long n,
+                                const int *track, const int *drop, const long long *append_off,
+                                const double *new_start, const int *new_sn, const double *new_dur0,
+                                cudaStream_t s);
 int resolve_search_max_grid(size_t smem, bool small, int ipt);
 int resolve_search_tile(bool small, int ipt);
 cudaError_t launch_build_hint(const double *start, const TrackDesc *desc, TrackHint *hint,

@@ -1039,6 +1039,66 @@ monotone_check_kernel(const double *__restrict__ start, TrackDesc *desc, int n_t
 }
 
 // =========================================================================================
+//  live playlists: slide the fragment windows of many tracks in place (one warp per track).
+//  The batch analogue of hls.js replacing level.details.fragments on a playlist reload, which
+//  the reference then reads live (media-map.js:28,41).
+// =========================================================================================
+__global__ void __launch_bounds__(256)
+slide_tracks_kernel(double *start, int *sn, double *dur0, TrackDesc *desc, long long n,
+                    const int *track, const int *drop, const long long *append_off,
+                    const double *new_start, const int *new_sn, const double *new_dur0)
+{
+    const int lane = threadIdx.x & 31;
+    const int wpb = blockDim.x >> 5;
+    for (long long e = (long long)blockIdx.x * wpb + (threadIdx.x >> 5); e < n;
+         e += (long long)gridDim.x * wpb) {
+        const int t = track[e];
+        TrackDesc d = desc[t];
+        const int k = min(max(drop[e], 0), d.len);          // fragments evicted at the front
+        const int keep = d.len - k;
+        const long long a0 = append_off[e];
+        const int add = (int)(append_off[e + 1] - a0);
+        // shift left by k: every chunk reads at or beyond everything written before it
+        for (int i0 = 0; i0 < keep; i0 += 32) {
+            const int i = i0 + lane;
+            double s = 0.0;
+            int q = 0;
+            if (i < keep) {
+                s = start[d.off + k + i];
+                q = sn[d.off + k + i];
+            }
+            __syncwarp();
+            if (i < keep && k > 0) {
+                start[d.off + i] = s;
+                sn[d.off + i] = q;
+            }
+            __syncwarp();
+        }
+        for (int j = lane; j < add; j += 32) {              // append the new fragments
+            start[d.off + keep + j] = new_start[a0 + j];
+            sn[d.off + keep + j] = new_sn[a0 + j];
+        }
+        __syncwarp();
+        const int len = keep + add;
+        // re-prove monotonicity of the whole column (the search kernel relies on the flag)
+        bool bad = false;
+        for (int i = lane; i < len; i += 32) {
+            const double s = start[d.off + i];
+            bad |= (s != s);
+            if (i > 0) bad |= (s < start[d.off + i - 1]);
+        }
+        const unsigned any_bad = __ballot_sync(0xffffffffu, bad);
+        if (lane == 0) {
+            unsigned fl = d.flags & ~kTrackMonotone;
+            if ((fl & kTrackStateMask) == HLSMAP_TRACK_PARSED && !any_bad) fl |= kTrackMonotone;
+            desc[t].len = len;
+            desc[t].flags = fl;
+            if (new_dur0) dur0[t] = new_dur0[e];
+        }
+    }
+}
+
+// =========================================================================================
 //  getSegmentDuration (media-map.js:81-87): first fragment's duration of the level
 // =========================================================================================
 __global__ void __launch_bounds__(256)
@@ -1172,6 +1232,20 @@ cudaError_t launch_build_hint(const double *start, const TrackDesc *desc, TrackH
     const long long cap = (long long)sm_count() * 8;
     if (blocks > cap) blocks = cap;
     build_hint_kernel<<<(int)blocks, 256, 0, s>>>(start, desc, hint, grid, n_tracks);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_slide_tracks(double *start, int *sn, double *dur0, TrackDesc *desc, long long n,
+                                const int *track, const int *drop, const long long *append_off,
+                                const double *new_start, const int *new_sn, const double *new_dur0,
+                                cudaStream_t s)
+{
+    if (n <= 0) return cudaSuccess;
+    long long blocks = (n + 7) / 8;
+    const long long cap = (long long)sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    slide_tracks_kernel<<<(int)blocks, 256, 0, s>>>(start, sn, dur0, desc, n, track, drop, append_off,
+                                                    new_start, new_sn, new_dur0);
     return cudaGetLastError();
 }
 

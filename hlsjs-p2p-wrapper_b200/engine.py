@@ -182,6 +182,18 @@ class DeviceMap:
     def set_path(self, path):
         N.check(self._lib.hlsmap_map_set_path(self._h, int(path)))
 
+    def slide_tracks(self, playlist, level, drop, append_offset, new_start, new_sn, new_dur0=None):
+        """Live update: per listed track evict `drop` fragments at the front and append the
+        fragments new_start/new_sn[append_offset[i]:append_offset[i+1]] (media-map.js:28,41 reads
+        hls.levels live; this keeps the HBM copy current without re-uploading the map)."""
+        playlist, level, drop = _arr(playlist, np.int32), _arr(level, np.int32), _arr(drop, np.int32)
+        append_offset = _arr(append_offset, np.int64)
+        new_start, new_sn = _arr(new_start, np.float64), _arr(new_sn, np.int32)
+        new_dur0 = _arr(new_dur0, np.float64)
+        N.check(self._lib.hlsmap_map_slide_tracks(self._h, len(level), _ptr(playlist), _ptr(level),
+                                                  _ptr(drop), _ptr(append_offset), _ptr(new_start),
+                                                  _ptr(new_sn), _ptr(new_dur0)))
+
     # ---- getSegmentList -------------------------------------------------------------------
     def get_segment_list(self, playlist, level, begin, duration, want_status=True,
                          capacity=None):

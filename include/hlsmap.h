@@ -126,6 +126,20 @@ int hlsmap_map_get_monotone(const hlsmap_map *map, uint8_t *flags);
 /* Force a kernel (tests, benchmarks).  SEARCH on a map that is not all-monotone fails. */
 int hlsmap_map_set_path(hlsmap_map *map, int path);
 
+/* ---- live playlists: slide fragment windows in place ------------------------------- */
+/* The reference holds a live reference to hls.levels (media-map.js:6-8) and reads
+ * level.details.fragments on every call (:28,41), so a playlist reload is seen at once.  The
+ * batch analogue: for each i, track (playlist[i], level[i]) evicts its first drop[i] fragments
+ * and appends new_start/new_sn[append_offset[i] .. append_offset[i+1]) (append_offset[0] = 0);
+ * new_dur0[i] (nullable array) becomes the duration of the track's new first fragment
+ * (getSegmentDuration).  A track may appear once per call and may not outgrow the fragment
+ * count it had at hlsmap_map_create (HLSMAP_ERR_CAPACITY).  Monotonicity is re-proven on the
+ * GPU for every touched track; a track that stops being sorted routes the map to the filter
+ * kernel.  Host pointers; blocks until the tables are updated. */
+int hlsmap_map_slide_tracks(hlsmap_map *map, int64_t n, const int32_t *playlist, const int32_t *level,
+                            const int32_t *drop, const int64_t *append_offset, const double *new_start,
+                            const int32_t *new_sn, const double *new_dur0);
+
 /* ---- getSegmentList (media-map.js:27-54), batched ---------------------------------- */
 /* Query q = (playlist[q], level[q], begin[q], duration[q]); playlist may be NULL (all 0).
  * `urlId` never takes part in the lookup (media-map.js:28) -- bindings echo it.

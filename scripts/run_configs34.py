@@ -85,6 +85,27 @@ def main():
         "getSegmentList_GBs": bytes3 / (ms * 1e-3) / 1e9, "getSegmentList_frac_of_measured_peak": bytes3 / (ms * 1e-3) / 1e9 / PEAK,
         "getSegmentDuration_ms_median": ms_d, "getSegmentDuration_queries_per_s": nq / (ms_d * 1e-3),
         "note": "2e5 queries is a launch-latency-sized batch: ~10 us of fixed cost dominates"}
+    # live update: every window slides by one fragment (evict the oldest, append one)
+    import time as _time
+    nt = t.n_tracks
+    pl_all = (np.arange(nt) // 3).astype(np.int32)
+    lv_all = (np.arange(nt) % 3).astype(np.int32)
+    last = t.start[t.track_off[1:] - 1]
+    m.slide_tracks(pl_all, lv_all, np.ones(nt, np.int32), np.arange(nt + 1, dtype=np.int64), last + 2.0,
+                   t.sn[t.track_off[1:] - 1] + 1, new_dur0=np.full(nt, 2.0))          # warm-up
+    t0 = _time.perf_counter()
+    reps = 5
+    for i in range(reps):
+        m.slide_tracks(pl_all, lv_all, np.ones(nt, np.int32), np.arange(nt + 1, dtype=np.int64),
+                       last + 2.0 * (i + 2), t.sn[t.track_off[1:] - 1] + 2 + i, new_dur0=np.full(nt, 2.0))
+    dt = (_time.perf_counter() - t0) / reps
+    out["config3_live_windows"]["slide_all_windows_ms"] = dt * 1e3
+    out["config3_live_windows"]["window_slides_per_s"] = nt / dt
+    out["config3_live_windows"]["slide_note"] = ("hlsmap_map_slide_tracks on all %d tracks, host pointers: upload of the "
+                                                 "update, in-place shift + append + monotonicity re-proof on the GPU, "
+                                                 "download of the track descriptors" % nt)
+    res2 = m.get_segment_list(q.playlist, q.level, q.begin + 2.0 * (reps + 1), q.duration)
+    out["config3_live_windows"]["hits_after_slides"] = int(res2.total_hits)
     m.close()
 
     # ---- config 4: 10^6 views, 8 levels x 10k fragments ------------------------------------------
