@@ -9,7 +9,7 @@ from . import build as _build
 c_i32p = ctypes.c_void_p
 OK = 0
 ERR_INVALID, ERR_CUDA, ERR_NOMEM, ERR_CAPACITY, ERR_OVERFLOW = -1, -2, -3, -4, -5
-ST_OK, ST_UNPARSED, ST_MISSING, ST_EMPTY, ST_SCATTERED = 0, 1, 2, 3, 4
+ST_OK, ST_UNPARSED, ST_MISSING, ST_EMPTY, ST_SCATTERED, ST_NO_FRAGMENT = 0, 1, 2, 3, 4, 5
 TRACK_MISSING, TRACK_UNPARSED, TRACK_PARSED = 0, 1, 2
 PATH_AUTO, PATH_SEARCH, PATH_FILTER = 0, 1, 2
 
@@ -61,6 +61,10 @@ SYMBOLS = {
     "hlsmap_get_segment_range": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P]),
     "hlsmap_get_segment_duration_dev": (_INT, [_P, _I64, _P, _P, _P, _P, _P]),
     "hlsmap_get_segment_duration": (_INT, [_P, _I64, _P, _P, _P, _P]),
+    "hlsmap_views_from_fragments_dev": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P]),
+    "hlsmap_views_from_fragments": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P]),
+    "hlsmap_get_next_segment_view_dev": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "hlsmap_get_next_segment_view": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P]),
     "hlsmap_get_track_list": (_INT, [_P, _I32, _P, _P, _I64, _P]),
     "hlsmap_view_pack_dev": (_INT, [_P, _I64, _P, _P, _P, _P, _P]),
     "hlsmap_view_pack": (_INT, [_P, _I64, _P, _P, _P, _P]),

@@ -1004,6 +1004,96 @@ int hlsmap_get_segment_duration(hlsmap_map *map, int64_t n, const int32_t *playl
     return HLSMAP_OK;
 }
 
+// ---- views from fragments / next segment view (extension) -----------------------------------
+int hlsmap_views_from_fragments_dev(hlsmap_map *map, int64_t n, const int32_t *d_playlist,
+                                    const int32_t *d_level, const int32_t *d_index, int32_t *d_sn_out,
+                                    double *d_time_out, uint8_t *d_status, void *stream)
+{
+    if (!map) return fail(HLSMAP_ERR_INVALID, "null map");
+    hlsmap_ctx *ctx = map->ctx;
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (n < 0 || (n > 0 && (!d_level || !d_index || !d_sn_out || !d_time_out)))
+        return fail(HLSMAP_ERR_INVALID, "views_from_fragments: null arrays");
+    if (n == 0) return HLSMAP_OK;
+    CK(launch_views_from_fragments(map->d_desc, map->d_playlist_base, map->n_playlists, map->d_start,
+                                   map->d_sn, n, d_playlist, d_level, d_index, d_sn_out, d_time_out,
+                                   d_status, stream ? (cudaStream_t)stream : ctx->stream));
+    ctx->last_launches = 1;
+    return HLSMAP_OK;
+}
+
+int hlsmap_get_next_segment_view_dev(hlsmap_map *map, int64_t n, const int32_t *d_playlist,
+                                     const int32_t *d_level, const int32_t *d_sn, int32_t *d_sn_out,
+                                     double *d_time_out, uint8_t *d_found, uint8_t *d_status,
+                                     void *stream)
+{
+    if (!map) return fail(HLSMAP_ERR_INVALID, "null map");
+    hlsmap_ctx *ctx = map->ctx;
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (n < 0 || (n > 0 && (!d_level || !d_sn || !d_sn_out || !d_time_out || !d_found)))
+        return fail(HLSMAP_ERR_INVALID, "get_next_segment_view: null arrays");
+    if (n == 0) return HLSMAP_OK;
+    CK(launch_next_segment_view(map->d_desc, map->d_playlist_base, map->n_playlists, map->d_start,
+                                map->d_sn, n, d_playlist, d_level, d_sn, d_sn_out, d_time_out, d_found,
+                                d_status, stream ? (cudaStream_t)stream : ctx->stream));
+    ctx->last_launches = 1;
+    return HLSMAP_OK;
+}
+
+// shared host-pointer wrapper: 3 int32 inputs, (sn, time[, found], status) outputs
+static int frag_host_call(hlsmap_map *map, int64_t n, const int32_t *playlist, const int32_t *level,
+                          const int32_t *third, int32_t *sn_out, double *time_out, uint8_t *found,
+                          uint8_t *status, bool next_view)
+{
+    if (!map) return fail(HLSMAP_ERR_INVALID, "null map");
+    hlsmap_ctx *ctx = map->ctx;
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (n < 0 || (n > 0 && (!level || !third || !sn_out || !time_out || (next_view && !found))))
+        return fail(HLSMAP_ERR_INVALID, "null arrays");
+    if (n == 0) return HLSMAP_OK;
+    cudaStream_t s = ctx->stream;
+    void *v;
+    int *d_pl = nullptr, *d_lv, *d_th, *d_sn;
+    double *d_tm;
+    uint8_t *d_st = nullptr, *d_fd = nullptr;
+    if (playlist) { if ((r = ensure_slot(ctx, 0, n * 4, &v))) return r; d_pl = (int *)v; }
+    if ((r = ensure_slot(ctx, 1, n * 4, &v))) return r; d_lv = (int *)v;
+    if ((r = ensure_slot(ctx, 4, n * 4, &v))) return r; d_th = (int *)v;
+    if ((r = ensure_slot(ctx, 6, n * 4, &v))) return r; d_sn = (int *)v;
+    if ((r = ensure_slot(ctx, 7, n * 8, &v))) return r; d_tm = (double *)v;
+    if (status) { if ((r = ensure_slot(ctx, 5, n, &v))) return r; d_st = (uint8_t *)v; }
+    if (next_view) { if ((r = ensure_slot(ctx, 8, n, &v))) return r; d_fd = (uint8_t *)v; }
+    if (playlist) CK(cudaMemcpyAsync(d_pl, playlist, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d_lv, level, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d_th, third, (size_t)n * 4, cudaMemcpyHostToDevice, s));
+    r = next_view ? hlsmap_get_next_segment_view_dev(map, n, d_pl, d_lv, d_th, d_sn, d_tm, d_fd, d_st, s)
+                  : hlsmap_views_from_fragments_dev(map, n, d_pl, d_lv, d_th, d_sn, d_tm, d_st, s);
+    if (r) return r;
+    CK(cudaMemcpyAsync(sn_out, d_sn, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(time_out, d_tm, (size_t)n * 8, cudaMemcpyDeviceToHost, s));
+    if (status) CK(cudaMemcpyAsync(status, d_st, (size_t)n, cudaMemcpyDeviceToHost, s));
+    if (next_view) CK(cudaMemcpyAsync(found, d_fd, (size_t)n, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return HLSMAP_OK;
+}
+
+int hlsmap_views_from_fragments(hlsmap_map *map, int64_t n, const int32_t *playlist,
+                                const int32_t *level, const int32_t *index, int32_t *sn_out,
+                                double *time_out, uint8_t *status)
+{
+    return frag_host_call(map, n, playlist, level, index, sn_out, time_out, nullptr, status, false);
+}
+
+int hlsmap_get_next_segment_view(hlsmap_map *map, int64_t n, const int32_t *playlist,
+                                 const int32_t *level, const int32_t *sn, int32_t *sn_out,
+                                 double *time_out, uint8_t *found, uint8_t *status)
+{
+    return frag_host_call(map, n, playlist, level, sn, sn_out, time_out, found, status, true);
+}
+
 int hlsmap_get_track_list(const hlsmap_map *map, int32_t playlist, int32_t *level_out,
                           int32_t *url_id_out, int64_t capacity, int64_t *n_out)
 {

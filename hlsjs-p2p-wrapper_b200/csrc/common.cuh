@@ -134,6 +134,16 @@ cudaError_t launch_slide_tracks(double *start, int *sn, double *dur0, TrackDesc 
                                 const int *track, const int *drop, const long long *append_off,
                                 const double *new_start, const int *new_sn, const double *new_dur0,
                                 cudaStream_t s);
+cudaError_t launch_views_from_fragments(const TrackDesc *desc, const int *playlist_base, int n_playlists,
+                                        const double *start, const int *sn, long long n,
+                                        const int *q_playlist, const int *q_level, const int *q_index,
+                                        int *out_sn, double *out_time, unsigned char *status,
+                                        cudaStream_t s);
+cudaError_t launch_next_segment_view(const TrackDesc *desc, const int *playlist_base, int n_playlists,
+                                     const double *start, const int *sn, long long n,
+                                     const int *q_playlist, const int *q_level, const int *q_sn,
+                                     int *out_sn, double *out_time, unsigned char *found,
+                                     unsigned char *status, cudaStream_t s);
 int resolve_search_max_grid(size_t smem, bool small, int ipt);
 int resolve_search_tile(bool small, int ipt);
 cudaError_t launch_build_hint(const double *start, const TrackDesc *desc, TrackHint *hint,

@@ -1125,6 +1125,79 @@ segment_duration_kernel(const TrackDesc *desc, const int *playlist_base, int n_p
 }
 
 // =========================================================================================
+//  view construction from fragments (p2p-loader-generator.js:145-147): per (playlist, level,
+//  fragment index) -> SegmentView{sn: frag.sn, trackView{level, urlId}, time: frag.start}
+// =========================================================================================
+__global__ void __launch_bounds__(256)
+views_from_fragments_kernel(const TrackDesc *desc, const int *playlist_base, int n_playlists,
+                            const double *start, const int *sn, long long n, const int *q_playlist,
+                            const int *q_level, const int *q_index, int *out_sn, double *out_time,
+                            unsigned char *status)
+{
+    for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < n;
+         q += (long long)gridDim.x * blockDim.x) {
+        long long off;
+        int len;
+        unsigned fl;
+        int st = lookup_track(desc, playlist_base, n_playlists, q_playlist ? q_playlist[q] : 0,
+                              q_level[q], off, len, fl);
+        int s = 0;
+        double t = __longlong_as_double(0x7ff8000000000000ll);
+        if (st == HLSMAP_ST_OK) {
+            const int i = q_index[q];
+            if ((unsigned)i >= (unsigned)len) st = HLSMAP_ST_NO_FRAGMENT;   // fragments[i] undefined
+            else {
+                s = __ldg(sn + off + i);
+                t = __ldg(start + off + i);
+            }
+        }
+        out_sn[q] = s;
+        out_time[q] = t;
+        if (status) status[q] = (unsigned char)st;
+    }
+}
+
+// =========================================================================================
+//  getNextSegmentView -- EXTENSION, no counterpart in this reference (the method was removed
+//  in 3.2.5, CHANGELOG.md:89).  Defined here as: the fragment that follows, in the same level,
+//  the first fragment whose sn equals the given sn; found = 0 when there is none.
+// =========================================================================================
+__global__ void __launch_bounds__(256)
+next_segment_view_kernel(const TrackDesc *desc, const int *playlist_base, int n_playlists,
+                         const double *start, const int *sn, long long n, const int *q_playlist,
+                         const int *q_level, const int *q_sn, int *out_sn, double *out_time,
+                         unsigned char *found, unsigned char *status)
+{
+    for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < n;
+         q += (long long)gridDim.x * blockDim.x) {
+        long long off;
+        int len;
+        unsigned fl;
+        const int st = lookup_track(desc, playlist_base, n_playlists, q_playlist ? q_playlist[q] : 0,
+                                    q_level[q], off, len, fl);
+        int s = 0, idx = -1;
+        double t = __longlong_as_double(0x7ff8000000000000ll);
+        if (st == HLSMAP_ST_OK && len > 0) {
+            const int want = q_sn[q];
+            // contiguous numbering (the HLS norm) puts it at want - sn[0]; verified, not assumed
+            const long long guess = (long long)want - (long long)__ldg(sn + off);
+            if (guess >= 0 && guess < len && __ldg(sn + off + guess) == want) idx = (int)guess;
+            for (int i = 0; i < len && (idx < 0 || i < idx); i++)      // first match wins
+                if (__ldg(sn + off + i) == want) { idx = i; break; }
+        }
+        const bool ok = idx >= 0 && idx + 1 < len;
+        if (ok) {
+            s = __ldg(sn + off + idx + 1);
+            t = __ldg(start + off + idx + 1);
+        }
+        out_sn[q] = s;
+        out_time[q] = t;
+        found[q] = ok ? 1 : 0;
+        if (status) status[q] = (unsigned char)st;
+    }
+}
+
+// =========================================================================================
 //  launchers
 // =========================================================================================
 static int g_sm_count = 0;
@@ -1260,6 +1333,38 @@ cudaError_t launch_segment_duration(const TrackDesc *desc, const int *playlist_b
     if (blocks < 1) blocks = 1;
     segment_duration_kernel<<<(int)blocks, 256, 0, s>>>(desc, playlist_base, n_playlists, dur0, n,
                                                         q_playlist, q_level, out, status);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_views_from_fragments(const TrackDesc *desc, const int *playlist_base, int n_playlists,
+                                        const double *start, const int *sn, long long n,
+                                        const int *q_playlist, const int *q_level, const int *q_index,
+                                        int *out_sn, double *out_time, unsigned char *status,
+                                        cudaStream_t s)
+{
+    long long blocks = (n + 255) / 256;
+    const long long cap = (long long)sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    views_from_fragments_kernel<<<(int)blocks, 256, 0, s>>>(desc, playlist_base, n_playlists, start, sn, n,
+                                                            q_playlist, q_level, q_index, out_sn,
+                                                            out_time, status);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_next_segment_view(const TrackDesc *desc, const int *playlist_base, int n_playlists,
+                                     const double *start, const int *sn, long long n,
+                                     const int *q_playlist, const int *q_level, const int *q_sn,
+                                     int *out_sn, double *out_time, unsigned char *found,
+                                     unsigned char *status, cudaStream_t s)
+{
+    long long blocks = (n + 255) / 256;
+    const long long cap = (long long)sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    next_segment_view_kernel<<<(int)blocks, 256, 0, s>>>(desc, playlist_base, n_playlists, start, sn, n,
+                                                         q_playlist, q_level, q_sn, out_sn, out_time,
+                                                         found, status);
     return cudaGetLastError();
 }
 

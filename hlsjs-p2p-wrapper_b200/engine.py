@@ -292,6 +292,27 @@ class DeviceMap:
                                                       _ptr(out), _ptr(status)))
         return out, status
 
+    def views_from_fragments(self, playlist, level, index):
+        """(sn, time, status) of fragment `index` of each (playlist, level): what the loader puts
+        into `new SegmentView({sn: frag.sn, trackView, time: frag.start})`."""
+        playlist, level, index = _arr(playlist, np.int32), _arr(level, np.int32), _arr(index, np.int32)
+        n = len(level)
+        sn, tm, st = np.empty(n, np.int32), np.empty(n, np.float64), np.empty(n, np.uint8)
+        N.check(self._lib.hlsmap_views_from_fragments(self._h, n, _ptr(playlist), _ptr(level), _ptr(index),
+                                                      _ptr(sn), _ptr(tm), _ptr(st)))
+        return sn, tm, st
+
+    def get_next_segment_view(self, playlist, level, sn):
+        """EXTENSION (not in the reference, see include/hlsmap.h): the fragment after the first
+        fragment whose sn matches -> (sn, time, found, status)."""
+        playlist, level, sn = _arr(playlist, np.int32), _arr(level, np.int32), _arr(sn, np.int32)
+        n = len(level)
+        osn, tm = np.empty(n, np.int32), np.empty(n, np.float64)
+        fd, st = np.empty(n, np.uint8), np.empty(n, np.uint8)
+        N.check(self._lib.hlsmap_get_next_segment_view(self._h, n, _ptr(playlist), _ptr(level), _ptr(sn),
+                                                       _ptr(osn), _ptr(tm), _ptr(fd), _ptr(st)))
+        return osn, tm, fd, st
+
     def get_track_list(self, playlist=0):
         n = ctypes.c_int64(0)
         N.check(self._lib.hlsmap_get_track_list(self._h, int(playlist), None, None, 0, ctypes.byref(n)))

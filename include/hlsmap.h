@@ -45,6 +45,7 @@ extern "C" {
 #define HLSMAP_ST_MISSING 2  /* no such level: the reference throws (media-map.js:30-32) */
 #define HLSMAP_ST_EMPTY 3    /* getSegmentDuration on an empty list (media-map.js:86) */
 #define HLSMAP_ST_SCATTERED 4 /* range form only: hits are not one contiguous run */
+#define HLSMAP_ST_NO_FRAGMENT 5 /* views_from_fragments: fragments[index] is undefined */
 
 /* track_state values for hlsmap_map_create */
 #define HLSMAP_TRACK_MISSING 0  /* hls.levels[i] is falsy */
@@ -209,6 +210,34 @@ int hlsmap_get_segment_duration_dev(hlsmap_map *map, int64_t n, const int32_t *d
                                     void *stream);
 int hlsmap_get_segment_duration(hlsmap_map *map, int64_t n, const int32_t *playlist,
                                 const int32_t *level, double *out, uint8_t *status);
+
+/* ---- SegmentView construction from fragments (the loader / track-change call sites) --- */
+/* `new SegmentView({sn: frag.sn, trackView: {level, urlId: level.urlId}, time: frag.start})`
+ * (p2p-loader-generator.js:145-147; TrackView on a level switch: player-interface.js:15-20).
+ * For fragment index[q] of (playlist[q], level[q]): sn_out[q] = fragment.sn, time_out[q] =
+ * fragment.start.  level and urlId are the caller's own columns (urlId is hls.js state the
+ * tables do not hold), so they are not copied.  status: MISSING / UNPARSED / NO_FRAGMENT. */
+int hlsmap_views_from_fragments_dev(hlsmap_map *map, int64_t n, const int32_t *d_playlist,
+                                    const int32_t *d_level, const int32_t *d_index, int32_t *d_sn_out,
+                                    double *d_time_out, uint8_t *d_status, void *stream);
+int hlsmap_views_from_fragments(hlsmap_map *map, int64_t n, const int32_t *playlist,
+                                const int32_t *level, const int32_t *index, int32_t *sn_out,
+                                double *time_out, uint8_t *status);
+
+/* ---- getNextSegmentView: EXTENSION -------------------------------------------------- */
+/* BASELINE.json configs[2] names getNextSegmentView, but this reference does not have it: it
+ * was removed in 3.2.5 (CHANGELOG.md:89) and no implementation or test survives, so there is
+ * nothing to be bit-exact with.  This entry point is the library's own, documented definition:
+ * in level (playlist[q], level[q]), take the first fragment whose sn equals sn[q]; if a
+ * fragment follows it, found[q] = 1 and sn_out/time_out[q] are that next fragment's sn and
+ * start; otherwise found[q] = 0.  Parity is claimed against oracle/ only. */
+int hlsmap_get_next_segment_view_dev(hlsmap_map *map, int64_t n, const int32_t *d_playlist,
+                                     const int32_t *d_level, const int32_t *d_sn, int32_t *d_sn_out,
+                                     double *d_time_out, uint8_t *d_found, uint8_t *d_status,
+                                     void *stream);
+int hlsmap_get_next_segment_view(hlsmap_map *map, int64_t n, const int32_t *playlist,
+                                 const int32_t *level, const int32_t *sn, int32_t *sn_out,
+                                 double *time_out, uint8_t *found, uint8_t *status);
 
 /* ---- getTrackList (media-map.js:60-73) --------------------------------------------- */
 /* Level-major, urlId-minor enumeration of one playlist's tracks.  Pass NULL outputs to

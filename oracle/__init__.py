@@ -182,3 +182,27 @@ def view_format(level, url_id, sn, with_sn=True):
 def is_monotone(start):
     start = _c(start, np.float64)
     return bool(lib().oracle_is_monotone(_p(start), ctypes.c_int64(len(start))))
+
+
+def views_from_fragments(playlist_base, track_off, track_state, start, sn, playlist, level, index):
+    pb, to, ts, st, s = _tables(playlist_base, track_off, track_state, start, sn)
+    playlist, level, index = _c(playlist, np.int32), _c(level, np.int32), _c(index, np.int32)
+    n = len(level)
+    osn, tm, status = np.empty(n, np.int32), np.empty(n, np.float64), np.empty(n, np.uint8)
+    lib().oracle_views_from_fragments(ctypes.c_int32(len(pb) - 1), _p(pb), _p(to), _p(ts), _p(st), _p(s),
+                                      ctypes.c_int64(n), _p(playlist), _p(level), _p(index), _p(osn),
+                                      _p(tm), _p(status))
+    return osn, tm, status
+
+
+def get_next_segment_view(playlist_base, track_off, track_state, start, sn, playlist, level, want):
+    """EXTENSION restated (no reference counterpart): -> (sn, time, found, status)."""
+    pb, to, ts, st, s = _tables(playlist_base, track_off, track_state, start, sn)
+    playlist, level, want = _c(playlist, np.int32), _c(level, np.int32), _c(want, np.int32)
+    n = len(level)
+    osn, tm = np.empty(n, np.int32), np.empty(n, np.float64)
+    found, status = np.empty(n, np.uint8), np.empty(n, np.uint8)
+    lib().oracle_get_next_segment_view(ctypes.c_int32(len(pb) - 1), _p(pb), _p(to), _p(ts), _p(st), _p(s),
+                                       ctypes.c_int64(n), _p(playlist), _p(level), _p(want), _p(osn),
+                                       _p(tm), _p(found), _p(status))
+    return osn, tm, found, status

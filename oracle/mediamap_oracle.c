@@ -384,3 +384,63 @@ int oracle_is_monotone(const double *start, int64_t n)
     }
     return 1;
 }
+
+/* ---- SegmentView construction at the loader (p2p-loader-generator.js:145-147) ---------- */
+/* new SegmentView({sn: frag.sn, trackView: {level, urlId: level.urlId}, time: frag.start}) for
+ * fragment `index` of the level; status 5 = fragments[index] is undefined. */
+#define ST_NO_FRAGMENT 5
+void oracle_views_from_fragments(int32_t n_playlists, const int32_t *playlist_base,
+                                 const int64_t *track_off, const uint8_t *track_state,
+                                 const double *start, const int32_t *sn, int64_t n,
+                                 const int32_t *playlist, const int32_t *level, const int32_t *index,
+                                 int32_t *sn_out, double *time_out, uint8_t *status)
+{
+    for (int64_t q = 0; q < n; q++) {
+        int32_t t = 0;
+        int st = resolve_track(n_playlists, playlist_base, track_state, playlist ? playlist[q] : 0,
+                               level[q], &t);
+        sn_out[q] = 0;
+        time_out[q] = NAN;
+        if (st == ST_OK) {
+            int64_t len = track_off[t + 1] - track_off[t];
+            if (index[q] < 0 || index[q] >= len) st = ST_NO_FRAGMENT;
+            else {
+                sn_out[q] = sn[track_off[t] + index[q]];
+                time_out[q] = start[track_off[t] + index[q]];
+            }
+        }
+        status[q] = (uint8_t)st;
+    }
+}
+
+/* ---- getNextSegmentView: EXTENSION, not in this reference (CHANGELOG.md:89) ------------ */
+/* The library's own definition, restated: the fragment following the first fragment of the
+ * level whose sn equals the given sn; found = 0 if there is none.  Parity unpinned. */
+void oracle_get_next_segment_view(int32_t n_playlists, const int32_t *playlist_base,
+                                  const int64_t *track_off, const uint8_t *track_state,
+                                  const double *start, const int32_t *sn, int64_t n,
+                                  const int32_t *playlist, const int32_t *level, const int32_t *want,
+                                  int32_t *sn_out, double *time_out, uint8_t *found, uint8_t *status)
+{
+    for (int64_t q = 0; q < n; q++) {
+        int32_t t = 0;
+        int st = resolve_track(n_playlists, playlist_base, track_state, playlist ? playlist[q] : 0,
+                               level[q], &t);
+        sn_out[q] = 0;
+        time_out[q] = NAN;
+        found[q] = 0;
+        status[q] = (uint8_t)st;
+        if (st != ST_OK) continue;
+        int64_t o = track_off[t], len = track_off[t + 1] - o;
+        for (int64_t i = 0; i < len; i++) {
+            if (sn[o + i] == want[q]) {
+                if (i + 1 < len) {
+                    sn_out[q] = sn[o + i + 1];
+                    time_out[q] = start[o + i + 1];
+                    found[q] = 1;
+                }
+                break;
+            }
+        }
+    }
+}
