@@ -8,7 +8,7 @@ from . import build as _build
 
 c_i32p = ctypes.c_void_p
 OK = 0
-ERR_INVALID, ERR_CUDA, ERR_NOMEM, ERR_CAPACITY, ERR_OVERFLOW = -1, -2, -3, -4, -5
+ERR_INVALID, ERR_CUDA, ERR_NOMEM, ERR_CAPACITY, ERR_OVERFLOW, ERR_UNSUPPORTED = -1, -2, -3, -4, -5, -6
 ST_OK, ST_UNPARSED, ST_MISSING, ST_EMPTY, ST_SCATTERED, ST_NO_FRAGMENT = 0, 1, 2, 3, 4, 5
 TRACK_MISSING, TRACK_UNPARSED, TRACK_PARSED = 0, 1, 2
 PATH_AUTO, PATH_SEARCH, PATH_FILTER = 0, 1, 2
@@ -25,6 +25,12 @@ class MapInfo(ctypes.Structure):
                 ("n_fragments", ctypes.c_int64), ("n_monotone_tracks", ctypes.c_int32),
                 ("n_parsed_tracks", ctypes.c_int32), ("all_monotone", ctypes.c_int32),
                 ("stage_all", ctypes.c_int32), ("device_bytes", ctypes.c_int64)]
+
+
+class IngestResult(ctypes.Structure):
+    _fields_ = [("n_fragments", ctypes.c_int64), ("n_sequence_tags", ctypes.c_int64),
+                ("n_unsupported", ctypes.c_int64), ("text_bytes", ctypes.c_int64),
+                ("kernel_launches", ctypes.c_int32), ("reserved", ctypes.c_int32)]
 
 
 class HlsMapError(RuntimeError):
@@ -65,6 +71,9 @@ SYMBOLS = {
     "hlsmap_views_from_fragments": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P]),
     "hlsmap_get_next_segment_view_dev": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P, _P]),
     "hlsmap_get_next_segment_view": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P]),
+    "hlsmap_parse_m3u8_dev": (_INT, [_P, _I32, _P, _P, _P, _I64, _P, _P, _P, _P, _P, _I64, _P, _P]),
+    "hlsmap_parse_m3u8": (_INT, [_P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _P]),
+    "hlsmap_map_create_from_m3u8": (_INT, [_P, _I32, _P, _I32, _P, _P, _P, _P, _P, _P]),
     "hlsmap_get_track_list": (_INT, [_P, _I32, _P, _P, _I64, _P]),
     "hlsmap_view_pack_dev": (_INT, [_P, _I64, _P, _P, _P, _P, _P]),
     "hlsmap_view_pack": (_INT, [_P, _I64, _P, _P, _P, _P]),

@@ -302,10 +302,13 @@ int hlsmap_host_free(hlsmap_ctx *ctx, void *p)
 // ---------------------------------------------------------------------------------------
 //  table upload
 // ---------------------------------------------------------------------------------------
-int hlsmap_map_create(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *playlist_track_base,
-                      int32_t n_tracks, const int64_t *track_offset, const uint8_t *track_state,
-                      const int32_t *url_count, const double *start, const int32_t *sn,
-                      const double *duration, hlsmap_map **out)
+// `start` / `sn` may live on the host or on the device (the copies below let the runtime tell);
+// `duration` is a host column or NULL; `dev_dur0`, when given, is a device array [n_tracks] that
+// already holds every track's first duration (tables parsed on the device).
+static int map_create_impl(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *playlist_track_base,
+                           int32_t n_tracks, const int64_t *track_offset, const uint8_t *track_state,
+                           const int32_t *url_count, const double *start, const int32_t *sn,
+                           const double *duration, const double *dev_dur0, hlsmap_map **out)
 {
     int r = use_ctx(ctx);
     if (r) return r;
@@ -383,14 +386,18 @@ int hlsmap_map_create(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *playl
     if (n_tracks) {
         CKM(cudaMemcpyAsync(m->d_desc, desc.data(), sizeof(TrackDesc) * (size_t)n_tracks,
                             cudaMemcpyHostToDevice, s));
-        CKM(cudaMemcpyAsync(m->d_dur0, dur0.data(), sizeof(double) * (size_t)n_tracks,
-                            cudaMemcpyHostToDevice, s));
+        if (dev_dur0)
+            CKM(cudaMemcpyAsync(m->d_dur0, dev_dur0, sizeof(double) * (size_t)n_tracks,
+                                cudaMemcpyDeviceToDevice, s));
+        else
+            CKM(cudaMemcpyAsync(m->d_dur0, dur0.data(), sizeof(double) * (size_t)n_tracks,
+                                cudaMemcpyHostToDevice, s));
     }
     CKM(cudaMemcpyAsync(m->d_playlist_base, playlist_track_base, sizeof(int) * (size_t)(n_playlists + 1),
                         cudaMemcpyHostToDevice, s));
     if (nf) {
-        CKM(cudaMemcpyAsync(m->d_start, start, sizeof(double) * (size_t)nf, cudaMemcpyHostToDevice, s));
-        CKM(cudaMemcpyAsync(m->d_sn, sn, sizeof(int) * (size_t)nf, cudaMemcpyHostToDevice, s));
+        CKM(cudaMemcpyAsync(m->d_start, start, sizeof(double) * (size_t)nf, cudaMemcpyDefault, s));
+        CKM(cudaMemcpyAsync(m->d_sn, sn, sizeof(int) * (size_t)nf, cudaMemcpyDefault, s));
     }
     // monotonicity of every start column, proven on the device (hard part 2)
     CKM(launch_monotone_check(m->d_start, m->d_desc, n_tracks, s));
@@ -481,6 +488,15 @@ int hlsmap_map_create(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *playl
 #undef CKM
     *out = m;
     return HLSMAP_OK;
+}
+
+int hlsmap_map_create(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *playlist_track_base,
+                      int32_t n_tracks, const int64_t *track_offset, const uint8_t *track_state,
+                      const int32_t *url_count, const double *start, const int32_t *sn,
+                      const double *duration, hlsmap_map **out)
+{
+    return map_create_impl(ctx, n_playlists, playlist_track_base, n_tracks, track_offset, track_state,
+                           url_count, start, sn, duration, nullptr, out);
 }
 
 void hlsmap_map_destroy(hlsmap_map *m)
@@ -1525,3 +1541,261 @@ int hlsmap_get_segment_list_noalloc_dev(hlsmap_map *map, int64_t nq, const int32
 }
 
 }  // extern "C"
+
+/* ---- media playlists (M3U8 text) -> fragment tables (ingest.cu) ------------- */
+namespace {
+
+struct DevBuf {   // frees on scope exit; the ingest entry points are set-up time, not hot
+    void *p = nullptr;
+    ~DevBuf()
+    {
+        if (p) cudaFree(p);
+    }
+    int alloc(size_t bytes)
+    {
+        if (p) {
+            cudaFree(p);
+            p = nullptr;
+        }
+        cudaError_t e = cudaMalloc(&p, bytes ? bytes : 16);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            p = nullptr;
+            return fail(HLSMAP_ERR_NOMEM, "cudaMalloc of " + std::to_string(bytes) + " bytes failed");
+        }
+        return HLSMAP_OK;
+    }
+};
+
+size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+// Everything on the device.  d_start / d_sn / d_dur may be NULL with capacity 0 (count only:
+// track_off, live and the totals are still produced).  d_dur0 may be NULL.
+int ingest_core(hlsmap_ctx *ctx, int32_t n_tracks, const uint8_t *d_state, const unsigned char *d_text,
+                const int64_t *d_text_off, int64_t n_bytes, int64_t *d_track_off, uint8_t *d_live,
+                double *d_start, int32_t *d_sn, double *d_dur, double *d_dur0, int64_t capacity,
+                cudaStream_t s, hlsmap_ingest_result *res)
+{
+    if (n_bytes > (int64_t)0x7fffffff * kIngestTileBytes / 2)
+        return fail(HLSMAP_ERR_INVALID, "parse_m3u8: text too large for one call");
+    const int n_tiles = (int)((n_bytes + kIngestTileBytes - 1) / kIngestTileBytes);
+    int64_t tag_cap = (int64_t)n_tracks * 2 + 1024;
+    IngestCounters h{};
+    int launches = 0;
+    DevBuf scratch;
+    const bool fill = d_start && d_sn && d_dur;
+    if (!fill) capacity = 0;
+    for (int attempt = 0; attempt < 2; attempt++) {
+        size_t o_tlo = 0, o_bf = align256(o_tlo + sizeof(int) * (size_t)(n_tiles + 1));
+        size_t o_sf = align256(o_bf + sizeof(int) * (size_t)(n_tiles + 1));
+        size_t o_st = align256(o_sf + 8 * (size_t)(n_tiles + 1));
+        size_t o_ctr = align256(o_st + 8 * (size_t)(n_tiles + 1));
+        size_t o_out = align256(o_ctr + sizeof(ScanCounters));
+        size_t o_tp = align256(o_out + sizeof(IngestCounters));
+        size_t o_tf = align256(o_tp + 8 * (size_t)tag_cap);
+        size_t o_tv = align256(o_tf + 8 * (size_t)tag_cap);
+        size_t o_d0 = align256(o_tv + 4 * (size_t)tag_cap);
+        size_t total = align256(o_d0 + 8 * (size_t)(n_tracks + 1));
+        int r = scratch.alloc(total);
+        if (r) return r;
+        char *b = (char *)scratch.p;
+        CK(cudaMemsetAsync(b, 0, o_tp, s));
+        if (n_tracks) CK(cudaMemsetAsync(d_live, 1, (size_t)n_tracks, s));
+        CK(cudaMemsetAsync(d_track_off, 0, 8 * (size_t)(n_tracks + 1), s));
+        IngestParams p{};
+        p.text = d_text;
+        p.n_bytes = n_bytes;
+        p.text_off = (const long long *)d_text_off;
+        p.n_tracks = n_tracks;
+        p.state = d_state;
+        p.tile_tlo = (int *)(b + o_tlo);
+        p.tile_bfirst = (int *)(b + o_bf);
+        p.dur = d_dur;
+        p.capacity = capacity;
+        p.track_off = (long long *)d_track_off;
+        p.live = d_live;
+        p.tag_pos = (long long *)(b + o_tp);
+        p.tag_frag = (long long *)(b + o_tf);
+        p.tag_val = (int *)(b + o_tv);
+        p.tag_capacity = tag_cap;
+        p.status_f = (unsigned long long *)(b + o_sf);
+        p.status_t = (unsigned long long *)(b + o_st);
+        p.ctr = (ScanCounters *)(b + o_ctr);
+        p.epoch = 1;
+        p.tslot = 0;
+        p.n_tiles = n_tiles;
+        p.vec_ok = ((uintptr_t)d_text & 15) == 0;
+        p.out = (IngestCounters *)(b + o_out);
+        if (n_tiles > 0 && n_tracks > 0) {
+            CK(launch_ingest_tile_index(p.text_off, n_tracks, n_tiles, (int *)(b + o_tlo), (int *)(b + o_bf), s));
+            CK(launch_ingest_scan(p, s));
+            launches += 2;
+        }
+        CK(cudaMemcpyAsync(&h, p.out, sizeof h, cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+        if ((int64_t)h.n_tags > tag_cap) {     // more sequence tags than tracks*2: size exactly, redo
+            tag_cap = (int64_t)h.n_tags;
+            continue;
+        }
+        if (fill && (int64_t)h.n_fragments <= capacity && n_tracks > 0) {
+            AssembleParams a{};
+            a.n_tracks = n_tracks;
+            a.state = d_state;
+            a.text_off = p.text_off;
+            a.track_off = p.track_off;
+            a.dur = d_dur;
+            a.tag_pos = p.tag_pos;
+            a.tag_frag = p.tag_frag;
+            a.tag_val = p.tag_val;
+            a.n_tags = (long long)h.n_tags;
+            a.start = d_start;
+            a.sn = d_sn;
+            a.dur0 = d_dur0 ? d_dur0 : (double *)(b + o_d0);
+            a.out = p.out;
+            CK(launch_ingest_assemble(a, (int64_t)h.n_fragments >= (int64_t)n_tracks * 24, s));
+            launches++;
+            CK(cudaMemcpyAsync(&h, p.out, sizeof h, cudaMemcpyDeviceToHost, s));
+            CK(cudaStreamSynchronize(s));
+        }
+        break;
+    }
+    if (res) {
+        res->n_fragments = (int64_t)h.n_fragments;
+        res->n_sequence_tags = (int64_t)h.n_tags;
+        res->n_unsupported = (int64_t)h.n_unsupported;
+        res->text_bytes = n_bytes;
+        res->kernel_launches = launches;
+        res->reserved = 0;
+    }
+    if (h.n_unsupported)
+        return fail(HLSMAP_ERR_UNSUPPORTED,
+                    "parse_m3u8: " + std::to_string(h.n_unsupported) +
+                        " number(s) outside what the parser converts exactly (more than 19 significant "
+                        "digits with an undecidable tail, or a sequence number beyond int32)");
+    if (fill && (int64_t)h.n_fragments > capacity)
+        return fail(HLSMAP_ERR_CAPACITY, "fragment buffers too small: need " + std::to_string(h.n_fragments) + " entries");
+    return HLSMAP_OK;
+}
+
+int check_text_offsets(int32_t n_tracks, const int64_t *text_offset)
+{
+    if (n_tracks < 0 || !text_offset) return fail(HLSMAP_ERR_INVALID, "parse_m3u8: missing text_offset");
+    if (text_offset[0] != 0) return fail(HLSMAP_ERR_INVALID, "parse_m3u8: text_offset[0] != 0");
+    for (int32_t t = 0; t < n_tracks; t++)
+        if (text_offset[t + 1] < text_offset[t]) return fail(HLSMAP_ERR_INVALID, "parse_m3u8: text_offset not monotone");
+    return HLSMAP_OK;
+}
+
+}  // namespace
+
+int hlsmap_parse_m3u8_dev(hlsmap_ctx *ctx, int32_t n_tracks, const uint8_t *track_state, const char *text,
+                          const int64_t *text_offset, int64_t text_bytes, int64_t *track_offset,
+                          uint8_t *track_live, double *start, int32_t *sn, double *duration,
+                          int64_t capacity, hlsmap_ingest_result *res, void *stream)
+{
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (n_tracks < 0 || text_bytes < 0 || !text_offset || !track_offset || (n_tracks > 0 && !track_live) ||
+        (text_bytes > 0 && !text))
+        return fail(HLSMAP_ERR_INVALID, "parse_m3u8_dev: missing arrays");
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    return ingest_core(ctx, n_tracks, track_state, (const unsigned char *)text, text_offset, text_bytes,
+                       track_offset, track_live, start, sn, duration, nullptr, capacity, s, res);
+}
+
+int hlsmap_parse_m3u8(hlsmap_ctx *ctx, int32_t n_tracks, const uint8_t *track_state, const char *text,
+                      const int64_t *text_offset, int64_t *track_offset, uint8_t *track_live, double *start,
+                      int32_t *sn, double *duration, int64_t capacity, hlsmap_ingest_result *res)
+{
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if ((r = check_text_offsets(n_tracks, text_offset))) return r;
+    if (!track_offset || (n_tracks > 0 && !track_live))
+        return fail(HLSMAP_ERR_INVALID, "parse_m3u8: missing output arrays");
+    const int64_t nb = text_offset[n_tracks];
+    if (nb > 0 && !text) return fail(HLSMAP_ERR_INVALID, "parse_m3u8: null text");
+    const bool fill = start && sn && duration && capacity > 0;
+    if (!fill) capacity = 0;
+    cudaStream_t s = ctx->stream;
+    DevBuf d_text, d_off, d_state, d_toff, d_live, d_start, d_sn, d_dur;
+    if ((r = d_text.alloc((size_t)nb + 16)) || (r = d_off.alloc(8 * (size_t)(n_tracks + 1))) ||
+        (r = d_state.alloc((size_t)n_tracks + 1)) || (r = d_toff.alloc(8 * (size_t)(n_tracks + 1))) ||
+        (r = d_live.alloc((size_t)n_tracks + 1)))
+        return r;
+    if (fill && ((r = d_start.alloc(8 * (size_t)capacity)) || (r = d_sn.alloc(4 * (size_t)capacity)) ||
+                 (r = d_dur.alloc(8 * (size_t)capacity))))
+        return r;
+    if (nb) CK(cudaMemcpyAsync(d_text.p, text, (size_t)nb, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d_off.p, text_offset, 8 * (size_t)(n_tracks + 1), cudaMemcpyHostToDevice, s));
+    if (track_state && n_tracks)
+        CK(cudaMemcpyAsync(d_state.p, track_state, (size_t)n_tracks, cudaMemcpyHostToDevice, s));
+    hlsmap_ingest_result local{};
+    r = ingest_core(ctx, n_tracks, track_state ? (const uint8_t *)d_state.p : nullptr,
+                    (const unsigned char *)d_text.p, (const int64_t *)d_off.p, nb, (int64_t *)d_toff.p,
+                    (uint8_t *)d_live.p, (double *)d_start.p, (int32_t *)d_sn.p, (double *)d_dur.p, nullptr,
+                    capacity, s, &local);
+    if (res) *res = local;
+    if (r != HLSMAP_OK && r != HLSMAP_ERR_CAPACITY) return r;
+    const std::string keep = g_err;
+    CK(cudaMemcpyAsync(track_offset, d_toff.p, 8 * (size_t)(n_tracks + 1), cudaMemcpyDeviceToHost, s));
+    if (n_tracks) CK(cudaMemcpyAsync(track_live, d_live.p, (size_t)n_tracks, cudaMemcpyDeviceToHost, s));
+    if (r == HLSMAP_OK && fill && local.n_fragments) {
+        const size_t nf = (size_t)local.n_fragments;
+        CK(cudaMemcpyAsync(start, d_start.p, 8 * nf, cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(sn, d_sn.p, 4 * nf, cudaMemcpyDeviceToHost, s));
+        CK(cudaMemcpyAsync(duration, d_dur.p, 8 * nf, cudaMemcpyDeviceToHost, s));
+    }
+    CK(cudaStreamSynchronize(s));
+    if (r) g_err = keep;
+    return r;
+}
+
+int hlsmap_map_create_from_m3u8(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *playlist_track_base,
+                                int32_t n_tracks, const uint8_t *track_state, const int32_t *url_count,
+                                const char *text, const int64_t *text_offset, hlsmap_ingest_result *res,
+                                hlsmap_map **out)
+{
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (!out) return fail(HLSMAP_ERR_INVALID, "null out pointer");
+    *out = nullptr;
+    if ((r = check_text_offsets(n_tracks, text_offset))) return r;
+    if (n_tracks > 0 && !track_state) return fail(HLSMAP_ERR_INVALID, "map_create_from_m3u8: null track_state");
+    const int64_t nb = text_offset[n_tracks];
+    if (nb > 0 && !text) return fail(HLSMAP_ERR_INVALID, "map_create_from_m3u8: null text");
+    cudaStream_t s = ctx->stream;
+    DevBuf d_text, d_off, d_state, d_toff, d_live, d_start, d_sn, d_dur, d_dur0;
+    if ((r = d_text.alloc((size_t)nb + 16)) || (r = d_off.alloc(8 * (size_t)(n_tracks + 1))) ||
+        (r = d_state.alloc((size_t)n_tracks + 1)) || (r = d_toff.alloc(8 * (size_t)(n_tracks + 1))) ||
+        (r = d_live.alloc((size_t)n_tracks + 1)) || (r = d_dur0.alloc(8 * (size_t)(n_tracks + 1))))
+        return r;
+    if (nb) CK(cudaMemcpyAsync(d_text.p, text, (size_t)nb, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(d_off.p, text_offset, 8 * (size_t)(n_tracks + 1), cudaMemcpyHostToDevice, s));
+    if (n_tracks) CK(cudaMemcpyAsync(d_state.p, track_state, (size_t)n_tracks, cudaMemcpyHostToDevice, s));
+    // pass 1 counts (the text is read once more, from L2 when it fits), so the columns are
+    // allocated at their exact size instead of the worst case of one fragment per 9 bytes
+    hlsmap_ingest_result local{};
+    r = ingest_core(ctx, n_tracks, (const uint8_t *)d_state.p, (const unsigned char *)d_text.p,
+                    (const int64_t *)d_off.p, nb, (int64_t *)d_toff.p, (uint8_t *)d_live.p, nullptr, nullptr,
+                    nullptr, nullptr, 0, s, &local);
+    if (res) *res = local;
+    if (r) return r;
+    const int64_t nf = local.n_fragments;
+    if ((r = d_start.alloc(8 * (size_t)nf + 16)) || (r = d_sn.alloc(4 * (size_t)nf + 16)) ||
+        (r = d_dur.alloc(8 * (size_t)nf + 16)))
+        return r;
+    const int first_launches = local.kernel_launches;
+    r = ingest_core(ctx, n_tracks, (const uint8_t *)d_state.p, (const unsigned char *)d_text.p,
+                    (const int64_t *)d_off.p, nb, (int64_t *)d_toff.p, (uint8_t *)d_live.p, (double *)d_start.p,
+                    (int32_t *)d_sn.p, (double *)d_dur.p, (double *)d_dur0.p, nf > 0 ? nf : 1, s, &local);
+    local.kernel_launches += first_launches;
+    if (res) *res = local;
+    if (r) return r;
+    std::vector<int64_t> h_off((size_t)n_tracks + 1, 0);
+    CK(cudaMemcpyAsync(h_off.data(), d_toff.p, 8 * (size_t)(n_tracks + 1), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    // tracks that are not parsed hold no fragments whatever their text said
+    return map_create_impl(ctx, n_playlists, playlist_track_base, n_tracks, h_off.data(), track_state, url_count,
+                           (const double *)d_start.p, (const int32_t *)d_sn.p, nullptr, (const double *)d_dur0.p,
+                           out);
+}

@@ -119,6 +119,55 @@ struct RangeParams {
     unsigned char *status;
 };
 
+// ---- playlist ingest (ingest.cu) -----------------------------------------------------------
+constexpr int kIngestTileBytes = 8192;
+struct IngestCounters {
+    unsigned long long n_fragments;
+    unsigned long long n_tags;
+    unsigned long long n_unsupported;
+};
+struct IngestParams {
+    const unsigned char *text;   // all playlists, concatenated
+    long long n_bytes;
+    const long long *text_off;   // [n_tracks + 1]
+    int n_tracks;
+    const unsigned char *state;  // nullable: every track is parsed
+    const int *tile_tlo;         // [n_tiles + 1] track holding the tile's first byte
+    const int *tile_bfirst;      // [n_tiles + 1] first track starting at/after the tile's first byte
+    double *dur;                 // durations in playlist order
+    long long capacity;
+    long long *track_off;        // [n_tracks + 1]
+    unsigned char *live;         // [n_tracks], preset to 1; ENDLIST clears it
+    long long *tag_pos;          // live #EXT-X-MEDIA-SEQUENCE tags: text position,
+    long long *tag_frag;         //   fragments before the tag,
+    int *tag_val;                //   and the number
+    long long tag_capacity;
+    unsigned long long *status_f, *status_t;   // look-back status words (zeroed; epoch 1)
+    ScanCounters *ctr;
+    unsigned epoch, tslot;
+    int n_tiles;
+    int vec_ok;                  // text is 16-byte aligned
+    IngestCounters *out;
+};
+struct AssembleParams {
+    int n_tracks;
+    const unsigned char *state;
+    const long long *text_off;
+    const long long *track_off;
+    const double *dur;
+    const long long *tag_pos, *tag_frag;
+    const int *tag_val;
+    long long n_tags;
+    double *start;
+    int *sn;
+    double *dur0;
+    IngestCounters *out;
+};
+cudaError_t launch_ingest_tile_index(const long long *text_off, int n_tracks, int n_tiles, int *tile_tlo,
+                                     int *tile_bfirst, cudaStream_t s);
+cudaError_t launch_ingest_scan(const IngestParams &p, cudaStream_t s);
+cudaError_t launch_ingest_assemble(const AssembleParams &p, bool warp_per_track, cudaStream_t s);
+
 // launchers (resolve.cu)
 cudaError_t launch_resolve_search(const ResolveParams &p, int grid, size_t smem, cudaStream_t s,
                                   bool overlap_next = false);

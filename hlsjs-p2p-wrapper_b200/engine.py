@@ -69,6 +69,37 @@ class Context:
     def upload(self, tables: FragmentTables):
         return DeviceMap(self, tables)
 
+    # ---- media playlists in text form (hlsmap_parse_m3u8) ----------------
+    @staticmethod
+    def _text_args(text, text_off):
+        if isinstance(text, (list, tuple)):          # one bytes object per track
+            text_off = np.concatenate([[0], np.cumsum([len(t) for t in text])]).astype(np.int64)
+            text = b"".join(text)
+        buf = np.frombuffer(text, np.uint8) if isinstance(text, (bytes, bytearray, memoryview)) else _arr(text, np.uint8)
+        return buf, _arr(text_off, np.int64)
+
+    def parse_m3u8(self, text, text_off=None, track_state=None):
+        """Level playlists (M3U8 text) -> SoA fragment columns, parsed on the GPU.  `text` is a list
+        of bytes (one per track) or one buffer with `text_off`.  -> dict(track_off, live, start, sn,
+        duration, result)"""
+        buf, off = self._text_args(text, text_off)
+        t = len(off) - 1
+        st = None if track_state is None else _arr(track_state, np.uint8)
+        track_off, live = np.zeros(t + 1, np.int64), np.ones(max(t, 1), np.uint8)
+        res = N.IngestResult()
+        args = [self._h, t, _ptr(st) if st is not None else None, _ptr(buf) if len(buf) else None, _ptr(off),
+                _ptr(track_off), _ptr(live)]
+        N.check(self._lib.hlsmap_parse_m3u8(*args, None, None, None, 0, ctypes.byref(res)))
+        n = int(res.n_fragments)
+        start, sn, dur = np.empty(n, np.float64), np.empty(n, np.int32), np.empty(n, np.float64)
+        if n:
+            N.check(self._lib.hlsmap_parse_m3u8(*args, _ptr(start), _ptr(sn), _ptr(dur), n, ctypes.byref(res)))
+        return dict(track_off=track_off, live=live[:t], start=start, sn=sn, duration=dur, result=res)
+
+    def upload_m3u8(self, playlist_base, track_state, text, text_off=None, url_count=None):
+        """`new MediaMap(hls)` for playlists still in text form: parsed on the GPU, columns stay there."""
+        return DeviceMap.from_m3u8(self, playlist_base, track_state, text, text_off, url_count)
+
     def pinned(self, shape, dtype):
         """numpy array over page-locked host memory (freed with the returned owner)."""
         dtype = np.dtype(dtype)
@@ -157,6 +188,21 @@ class DeviceMap:
                                             _ptr(ts), _ptr(uc), _ptr(st), _ptr(sn), _ptr(du),
                                             ctypes.byref(h)))
         self._h = h
+
+    @classmethod
+    def from_m3u8(cls, ctx, playlist_base, track_state, text, text_off=None, url_count=None):
+        buf, off = Context._text_args(text, text_off)
+        pb, ts = _arr(playlist_base, np.int32), _arr(track_state, np.uint8)
+        uc = None if url_count is None else _arr(url_count, np.int32)
+        self = object.__new__(cls)
+        self.ctx, self._lib, self.n_playlists = ctx, ctx._lib, len(pb) - 1
+        self.ingest = N.IngestResult()
+        h = ctypes.c_void_p()
+        N.check(self._lib.hlsmap_map_create_from_m3u8(
+            ctx._h, len(pb) - 1, _ptr(pb), len(ts), _ptr(ts), _ptr(uc) if uc is not None else None,
+            _ptr(buf) if len(buf) else None, _ptr(off), ctypes.byref(self.ingest), ctypes.byref(h)))
+        self._h = h
+        return self
 
     def close(self):
         if getattr(self, "_h", None) and self.ctx._h:

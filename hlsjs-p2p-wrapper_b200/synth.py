@@ -213,3 +213,82 @@ def hls_mock_tables(level_number=3, defined_level=1, live=False):
             lvl["details"] = {"live": live, "fragments": frags}
         levels.append(lvl)
     return FragmentTables.from_hls_levels([levels if level_number > 0 else None])
+
+
+# ---- media playlists in text form (input shape per a13) -------------------
+_NASTY = [
+    b"#EXTM3U\n#EXT-X-MEDIA-SEQUENCE:7\n#EXTINF:10,title #EXTINF:4,\r\nseg.ts\n#EXTINF:.5\n"
+    b"#EXT-X-KEY:METHOD=NONE#EXTINF:7,\n#EXTINF:.,\nx.ts\n#EXTINF:1.2.3,\n#EXTINF:abc,\n#EXT-X-ENDLIST",
+    b"#EXTINF:3#EXT-X-ENDLIST\n#EXT-X-ENDLISTING#EXTINF:2,\n#EXT-X-MEDIA-SEQUENCE:12#EXTINF:4,\n"
+    b"#EXT-X-MEDIA-SEQUENCE:x\n#EXTINF:5.,\n",
+    b"#EXT-X-PROGRAM-DATE-TIME:2016-01-01T00:00:00Z\xe2\x80\xa8#EXTINF:6,\n"
+    b"#EXT-X-KEY:URI=\"a#EXT-X-MEDIA-SEQUENCE:99\"\n#EXTINF:0.000,\nurl#EXTINF:8,\n#EXTINF:9.98458,|#EXTINF:3\n",
+    b"#EXT-X-MEDIA-SEQUENCE:2147483640\n#EXTINF:00010.500000000000000000000,\n#EXTINF:0.1234567890123456789,\n"
+    b"#EXTINF:123456789012345678,\n#EXTINF:0.30000000000000004,\n#EXTINF:9007199254740993,\n",
+    b"",
+    b"no tags here at all\n",
+    b"#EXT-X-MEDIA-SEQUENCE:5\n#EXTINF:2,\na\n#EXTINF:2,\nb\n#EXT-X-MEDIA-SEQUENCE:100\n#EXTINF:2,\nc\n"
+    b"#EXT-X-DISCONTINUITY\n#EXT-X-BYTERANGE:100@0\n#EXTINF:2,\nd\n#EXT-X-MEDIA-SEQUENCE:3\n",
+    b"#EXTINF:4,\n" * 3 + b"#EXT-X-MEDIA-SEQUENCE:",
+    b"#EXTINF:",
+    b"#" * 40 + b"#EXTINF:1," + b"#" * 9,
+]
+
+
+def m3u8_corpus(seed=8, n_playlists=200, n_levels=3, frags=(3, 12), nasty=True, unparsed_every=0):
+    """Level playlists as text -> (playlist_base int32[P+1], track_state uint8[T], texts list[bytes]).
+    Durations are printed in the formats segmenters use (integers, 3/5/6 decimals); every few
+    tracks use CRLF, drop the final newline, or carry no #EXT-X-MEDIA-SEQUENCE.  With `nasty`, hand
+    written tracks exercising the parser's corners are mixed in."""
+    rng = np.random.default_rng(seed)
+    nt = n_playlists * n_levels
+    lens = rng.integers(frags[0], frags[1] + 1, nt)
+    texts, state = [], np.full(nt, TRACK_PARSED, np.uint8)
+    fmts = ("%d", "%.3f", "%.5f", "%.6f")
+    for t in range(nt):
+        if unparsed_every and t % unparsed_every == unparsed_every - 1:
+            state[t] = t % 2                          # missing or unparsed: text must be ignored
+        if nasty and t % 11 == 5:
+            texts.append(_NASTY[(t // 11) % len(_NASTY)])
+            continue
+        nl = "\r\n" if t % 7 == 3 else "\n"
+        fmt = fmts[t % 4]
+        sn0 = int(rng.integers(0, 2_000_000_000))
+        d = rng.integers(2000, 10001, int(lens[t])) / 1000.0
+        head = ["#EXTM3U", "#EXT-X-VERSION:3", "#EXT-X-TARGETDURATION:10"]
+        if t % 13 != 12:
+            head.append("#EXT-X-MEDIA-SEQUENCE:%d" % sn0)
+        body = []
+        for i, x in enumerate(d):
+            body.append("#EXTINF:" + (fmt % (round(x) if fmt == "%d" else x)) + ",")
+            body.append("fileSequence%d.ts" % (sn0 + i))
+        if t % 5 == 0:
+            body.append("#EXT-X-ENDLIST")
+        s = nl.join(head + body) + ("" if t % 9 == 4 else nl)
+        texts.append(s.encode())
+    base = (np.arange(n_playlists + 1, dtype=np.int64) * n_levels).astype(np.int32)
+    return base, state, texts
+
+
+def m3u8_block(seed=9, n_tracks=1000, n_frag=800):
+    """A large, regular corpus built quickly (numpy): n_tracks VOD playlists of n_frag fragments with
+    5-decimal durations.  -> (text uint8[N], text_off int64[T+1])"""
+    rng = np.random.default_rng(seed)
+    nf = n_tracks * n_frag
+    ms = rng.integers(200000, 1000001, nf)            # 2.00000 .. 10.00000 s in 1e-5 steps
+    line = np.frombuffer(b"#EXTINF:0.00000,\nseg0000000.ts\n", np.uint8)
+    rows = np.tile(line, (nf, 1))
+    for k, col in enumerate((8, 10, 11, 12, 13, 14)):  # digits of d.ddddd
+        div = 10 ** (5 - k)
+        rows[:, col] = 48 + (ms // div) % 10
+    idx = np.arange(nf) % n_frag
+    for k in range(7):
+        rows[:, 20 + k] = 48 + (idx // 10 ** (6 - k)) % 10
+    head = b"#EXTM3U\n#EXT-X-TARGETDURATION:10\n#EXT-X-MEDIA-SEQUENCE:1000\n"
+    tail = b"#EXT-X-ENDLIST\n"
+    per = len(head) + n_frag * len(line) + len(tail)
+    out = np.empty((n_tracks, per), np.uint8)
+    out[:, :len(head)] = np.frombuffer(head, np.uint8)
+    out[:, len(head):len(head) + n_frag * len(line)] = rows.reshape(n_tracks, -1)
+    out[:, per - len(tail):] = np.frombuffer(tail, np.uint8)
+    return out.reshape(-1), np.arange(n_tracks + 1, dtype=np.int64) * per

@@ -38,6 +38,7 @@ extern "C" {
 #define HLSMAP_ERR_NOMEM (-3)
 #define HLSMAP_ERR_CAPACITY (-4)  /* hit buffers too small; result.total_hits = needed */
 #define HLSMAP_ERR_OVERFLOW (-5)  /* more than INT32_MAX hits in one batch: split it */
+#define HLSMAP_ERR_UNSUPPORTED (-6) /* parse_m3u8: a number the parser cannot convert exactly */
 
 /* per-query status */
 #define HLSMAP_ST_OK 0
@@ -238,6 +239,55 @@ int hlsmap_get_next_segment_view_dev(hlsmap_map *map, int64_t n, const int32_t *
 int hlsmap_get_next_segment_view(hlsmap_map *map, int64_t n, const int32_t *playlist,
                                  const int32_t *level, const int32_t *sn, int32_t *sn_out,
                                  double *time_out, uint8_t *found, uint8_t *status);
+
+/* ---- media playlists (M3U8 text) -> fragment tables --------------------- */
+/* The step BEFORE the mapping layer.  The reference never parses a playlist itself: hls.js does
+ * (package.json:34, "hls.js": "0.5.46", absent from the reference checkout), and media-map.js:28,
+ * 41-48 reads the `level.details.fragments` it leaves behind.  These entry points replace that
+ * hand-over for the batch case: the texts of many level playlists go to the GPU as bytes and come
+ * back as the SoA fragment tables hlsmap_map_create() takes -- or go straight into a map.
+ *
+ * What is restated of hls.js 0.5.46's parseLevelPlaylist (src/loader/playlist-loader.js), the
+ * part the mapping layer can observe: one global regular expression walks the text; of its
+ * alternatives `#EXT-X-MEDIA-SEQUENCE:(\d+)` sets the next sn (parseInt), `#EXTINF:([\d.]+)...`
+ * appends {sn: next sn++, start: running sum, duration: parseFloat(run)} unless that is NaN,
+ * `#EXT-X-ENDLIST` clears `live`, and the alternatives that swallow the rest of their line
+ * (EXTINF, `#EXT-X-KEY:(.*)`, `#EXT-X-PROGRAM-DATE-TIME:(.*)`) hide tags later on that line.
+ * `start` is summed in playlist order in fp64, so it carries the reference's bits.
+ * Parity: pinned only to the CPU restatement in oracle/ (glibc strtod as the independent decimal
+ * conversion) -- the parser's own source and tests are not in the reference checkout.
+ *
+ * text         all playlists' bytes, concatenated; track t owns [text_offset[t], text_offset[t+1])
+ * track_state  [n_tracks] HLSMAP_TRACK_*, or NULL (all parsed); the text of a track that is not
+ *              HLSMAP_TRACK_PARSED is ignored and the track gets no fragments
+ * track_offset [n_tracks + 1] out: first fragment of each track
+ * track_live   [n_tracks] out: 1 unless the playlist holds #EXT-X-ENDLIST
+ * start / sn / duration  [capacity] out, or all NULL with capacity 0 to only count
+ * Numbers the converter cannot round exactly (see csrc/decimal.cuh: more than 19 significant digits
+ * whose tail could change the rounding, or a sequence number beyond int32) are never guessed: the
+ * call fails with HLSMAP_ERR_UNSUPPORTED and res->n_unsupported says how many there were.
+ * HLSMAP_ERR_CAPACITY: res->n_fragments entries are needed; track_offset / track_live are valid. */
+typedef struct hlsmap_ingest_result {
+    int64_t n_fragments;
+    int64_t n_sequence_tags;
+    int64_t n_unsupported;
+    int64_t text_bytes;
+    int32_t kernel_launches;
+    int32_t reserved;
+} hlsmap_ingest_result;
+
+int hlsmap_parse_m3u8_dev(hlsmap_ctx *ctx, int32_t n_tracks, const uint8_t *d_track_state, const char *d_text,
+                          const int64_t *d_text_offset, int64_t text_bytes, int64_t *d_track_offset,
+                          uint8_t *d_track_live, double *d_start, int32_t *d_sn, double *d_duration,
+                          int64_t capacity, hlsmap_ingest_result *res, void *stream);
+int hlsmap_parse_m3u8(hlsmap_ctx *ctx, int32_t n_tracks, const uint8_t *track_state, const char *text,
+                      const int64_t *text_offset, int64_t *track_offset, uint8_t *track_live, double *start,
+                      int32_t *sn, double *duration, int64_t capacity, hlsmap_ingest_result *res);
+/* new MediaMap(hls) for playlists still in text form: parse on the device, keep the columns there. */
+int hlsmap_map_create_from_m3u8(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *playlist_track_base,
+                                int32_t n_tracks, const uint8_t *track_state, const int32_t *url_count,
+                                const char *text, const int64_t *text_offset, hlsmap_ingest_result *res,
+                                hlsmap_map **out);
 
 /* ---- getTrackList (media-map.js:60-73) --------------------------------------------- */
 /* Level-major, urlId-minor enumeration of one playlist's tracks.  Pass NULL outputs to

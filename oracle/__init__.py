@@ -206,3 +206,23 @@ def get_next_segment_view(playlist_base, track_off, track_state, start, sn, play
                                        ctypes.c_int64(n), _p(playlist), _p(level), _p(want), _p(osn),
                                        _p(tm), _p(found), _p(status))
     return osn, tm, found, status
+
+
+def parse_m3u8(text, text_off, track_state=None, threads=1):
+    """hls.js 0.5.46 parseLevelPlaylist, the part the mapping layer observes (restated; unpinned).
+    -> dict(track_off, live, start, sn, duration, bad)"""
+    text = np.frombuffer(bytes(text), np.uint8) if not isinstance(text, np.ndarray) else _c(text, np.uint8)
+    text_off = _c(text_off, np.int64)
+    state = _c(track_state, np.uint8)
+    t = len(text_off) - 1
+    track_off, live = np.zeros(t + 1, np.int64), np.ones(max(t, 1), np.uint8)
+    fn = lib().oracle_parse_m3u8
+    fn.restype = ctypes.c_int64
+    n = fn(ctypes.c_int32(t), _p(state), _p(text), _p(text_off), _p(track_off), _p(live), None, None, None,
+           ctypes.c_int(threads))
+    bad = n < 0
+    n = -1 - n if bad else n
+    sn, start, dur = np.empty(n, np.int32), np.empty(n, np.float64), np.empty(n, np.float64)
+    fn(ctypes.c_int32(t), _p(state), _p(text), _p(text_off), _p(track_off), _p(live), _p(sn), _p(start), _p(dur),
+       ctypes.c_int(threads))
+    return dict(track_off=track_off, live=live[:t], start=start, sn=sn, duration=dur, bad=bad)

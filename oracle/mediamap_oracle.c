@@ -444,3 +444,164 @@ void oracle_get_next_segment_view(int32_t n_playlists, const int32_t *playlist_b
         }
     }
 }
+
+/* ---- media playlist text -> fragments (the step before the path) ------- */
+/* hls.js 0.5.46 (package.json:34; the dependency is NOT in the reference checkout, so this is
+ * restated from that release's published src/loader/playlist-loader.js, parseLevelPlaylist, and
+ * the parity it gives is "unpinned": there is no golden vector of the parser to hold it to).
+ * One global regular expression is exec'd repeatedly; lastIndex moves past each match.  Only the
+ * alternatives that can change fragments[].{sn,start,duration}, `live`, or what a later match can
+ * see are restated; TARGETDURATION, DISCONTINUITY and BYTERANGE consume no '#' and set nothing the
+ * mapping layer reads, so skipping over them one byte at a time gives the same matches.
+ * Decimal conversion is glibc strtod (correctly rounded), the independent check of the device's
+ * integer-only converter.  Returns the fragment count; *bad is set when a sequence number leaves
+ * int32 (the tables hold sn as int32, media-map.js:46 only copies it). */
+static int has_lit(const unsigned char *s, int64_t n, int64_t i, const char *lit)
+{
+    int64_t k = (int64_t)strlen(lit);
+    return i + k <= n && memcmp(s + i, lit, (size_t)k) == 0;
+}
+
+static int64_t dot_star_end(const unsigned char *s, int64_t n, int64_t i)
+{   /* `.` stops at \n, \r, U+2028, U+2029 (UTF-8 E2 80 A8 / E2 80 A9) */
+    while (i < n) {
+        if (s[i] == '\n' || s[i] == '\r') break;
+        if (s[i] == 0xE2 && i + 2 < n && s[i + 1] == 0x80 && (s[i + 2] == 0xA8 || s[i + 2] == 0xA9)) break;
+        i++;
+    }
+    return i;
+}
+
+static int64_t m3u8_parse_one(const unsigned char *s, int64_t n, int32_t *sn_out, double *start_out,
+                              double *dur_out, uint8_t *live, int *bad)
+{
+    int64_t i = 0, count = 0;
+    double current_sn = 0.0; /* parseInt gives a Number */
+    volatile double total = 0.0;
+    *live = 1;
+    while (i < n) {
+        if (s[i] != '#') { i++; continue; }
+        if (has_lit(s, n, i, "#EXT-X-MEDIA-SEQUENCE:")) {
+            int64_t j = i + 22;
+            if (j < n && s[j] >= '0' && s[j] <= '9') {
+                double v = 0.0;
+                while (j < n && s[j] >= '0' && s[j] <= '9') { v = v * 10.0 + (s[j] - '0'); j++; }
+                if (v > 2147483647.0) { *bad = 1; v = 2147483647.0; }
+                current_sn = v;
+                i = j;
+                continue;
+            }
+        } else if (has_lit(s, n, i, "#EXT-X-KEY:")) {
+            i = dot_star_end(s, n, i + 11);
+            continue;
+        } else if (has_lit(s, n, i, "#EXT-X-PROGRAM-DATE-TIME:")) {
+            i = dot_star_end(s, n, i + 25);
+            continue;
+        } else if (has_lit(s, n, i, "#EXT-X-ENDLIST")) {
+            *live = 0;
+            i += 14;
+            continue;
+        } else if (has_lit(s, n, i, "#EXTINF:")) {
+            int64_t j = i + 8, r0 = j;
+            while (j < n && ((s[j] >= '0' && s[j] <= '9') || s[j] == '.')) j++;
+            if (j > r0) {
+                /* parseFloat of the captured run: the StrDecimalLiteral prefix, else NaN */
+                char stackbuf[64], *buf = stackbuf;
+                int64_t len = j - r0;
+                if (len + 1 > (int64_t)sizeof stackbuf) buf = (char *)malloc((size_t)len + 1);
+                memcpy(buf, s + r0, (size_t)len);
+                buf[len] = 0;
+                char *end = buf;
+                double d = strtod(buf, &end);
+                int is_nan = end == buf;
+                if (buf != stackbuf) free(buf);
+                while (j < n && s[j] != '\r' && s[j] != '\n') j++;          /* [^\r\n]* */
+                int64_t k = j;
+                while (k < n && (s[k] == '\r' || s[k] == '\n')) k++;        /* ([\r\n]+[^#|\r\n]+)? */
+                if (k > j) {
+                    int64_t u = k;
+                    while (u < n && s[u] != '#' && s[u] != '|' && s[u] != '\r' && s[u] != '\n') u++;
+                    if (u > k) j = u;
+                }
+                if (!is_nan) {
+                    if (current_sn > 2147483647.0) *bad = 1;
+                    if (sn_out) {
+                        sn_out[count] = (int32_t)(current_sn > 2147483647.0 ? 2147483647.0 : current_sn);
+                        start_out[count] = total;
+                        dur_out[count] = d;
+                    }
+                    current_sn += 1.0;
+                    total = total + d;
+                    count++;
+                }
+                i = j;
+                continue;
+            }
+        }
+        i++;
+    }
+    return count;
+}
+
+typedef struct {
+    int32_t t0, t1;
+    const uint8_t *state;
+    const unsigned char *text;
+    const int64_t *text_off;
+    int64_t *track_off; /* pass 1: counts at [t+1]; pass 2: offsets */
+    uint8_t *live;
+    int32_t *sn;
+    double *start, *dur;
+    int pass, bad;
+} m3u8_job_t;
+
+static void *m3u8_worker(void *arg)
+{
+    m3u8_job_t *j = (m3u8_job_t *)arg;
+    for (int32_t t = j->t0; t < j->t1; t++) {
+        const unsigned char *s = j->text + j->text_off[t];
+        int64_t n = j->text_off[t + 1] - j->text_off[t];
+        int parsed = !j->state || j->state[t] == 2;
+        if (j->pass == 1) {
+            j->live[t] = 1;
+            j->track_off[t + 1] = parsed ? m3u8_parse_one(s, n, NULL, NULL, NULL, &j->live[t], &j->bad) : 0;
+        } else if (parsed) {
+            int64_t o = j->track_off[t];
+            m3u8_parse_one(s, n, j->sn + o, j->start + o, j->dur + o, &j->live[t], &j->bad);
+        }
+    }
+    return NULL;
+}
+
+/* Returns the total fragment count, or -1 - count when a sequence number left int32.  Call with
+ * NULL sn/start/dur to size the columns (track_off and live are filled either way). */
+int64_t oracle_parse_m3u8(int32_t n_tracks, const uint8_t *state, const unsigned char *text,
+                          const int64_t *text_off, int64_t *track_off, uint8_t *live, int32_t *sn,
+                          double *start, double *dur, int threads)
+{
+    if (threads < 1) threads = 1;
+    if (threads > 256) threads = 256;
+    pthread_t tid[256];
+    m3u8_job_t jobs[256];
+    int bad = 0;
+    track_off[0] = 0;
+    for (int pass = 1; pass <= 2; pass++) {
+        if (pass == 2 && !(sn && start && dur)) break;
+        for (int i = 0; i < threads; i++) {
+            m3u8_job_t *j = &jobs[i];
+            j->t0 = (int32_t)((int64_t)n_tracks * i / threads);
+            j->t1 = (int32_t)((int64_t)n_tracks * (i + 1) / threads);
+            j->state = state; j->text = text; j->text_off = text_off; j->track_off = track_off;
+            j->live = live; j->sn = sn; j->start = start; j->dur = dur; j->pass = pass; j->bad = 0;
+            if (threads == 1) m3u8_worker(j);
+            else pthread_create(&tid[i], NULL, m3u8_worker, j);
+        }
+        for (int i = 0; i < threads; i++) {
+            if (threads > 1) pthread_join(tid[i], NULL);
+            bad |= jobs[i].bad;
+        }
+        if (pass == 1)
+            for (int32_t t = 0; t < n_tracks; t++) track_off[t + 1] += track_off[t];
+    }
+    return bad ? -1 - track_off[n_tracks] : track_off[n_tracks];
+}
