@@ -120,7 +120,8 @@ struct RangeParams {
 };
 
 // ---- playlist ingest (ingest.cu) -----------------------------------------------------------
-constexpr int kIngestTileBytes = 8192;
+constexpr int kIngestThreads = 128;
+constexpr int kIngestTileBytes = kIngestThreads * 128;
 struct IngestCounters {
     unsigned long long n_fragments;
     unsigned long long n_tags;

@@ -15,9 +15,9 @@
 //     #EXT-X-KEY:(.*)  #EXT-X-PROGRAM-DATE-TIME:(.*)     swallow the rest of their line
 //   matter here; a match that swallows the rest of its line hides any tag later on that line.
 //
-// Work split.  m3u8_scan_kernel is byte-parallel and single pass: 8 KB tiles handed out by
+// Work split.  m3u8_scan_kernel is byte-parallel and single pass: 32 KB tiles handed out by
 // ticket, every '#' of a tile becomes a candidate, candidates are classified with all lanes
-// busy, and two decoupled look-backs (fragments, sequence tags) give every fragment its global
+// busy, and a paired decoupled look-back (fragments, sequence tags) give every fragment its global
 // slot, so durations land in playlist order with the text read once.  What is inherently serial
 // -- `start` is a running fp64 sum, which must be added in the reference's order to give the
 // reference's bits -- is left to m3u8_assemble_kernel: one thread (short tracks) or one warp
@@ -29,10 +29,15 @@
 namespace hlsmap {
 namespace {
 
-constexpr int kThreads = 256;
+constexpr int kThreads = kIngestThreads;
 constexpr int kTile = kIngestTileBytes;       // bytes of text per tile
-constexpr int kBytesPerThread = kTile / kThreads;  // 32
-constexpr int kCap = 2048;                    // candidates classified per round
+constexpr int kBytesPerThread = kTile / kThreads;  // 128
+constexpr int kGroups = kBytesPerThread / 32;      // '#' masks per thread, one per 32 bytes
+constexpr int kCap = kThreads * 8;            // candidates classified per round
+constexpr int kRoundBytes = kCap;             // dense tiles: text bytes per round
+constexpr int kRounds = kTile / kRoundBytes;
+constexpr int kThreadsPerRound = kRoundBytes / kBytesPerThread;
+constexpr int kTrackStage = 260;              // text offsets staged per tile
 constexpr int kPerThread = kCap / kThreads;   // 8
 constexpr int kWarps = kThreads / 32;
 using Scan = TileScan<kThreads>;
@@ -112,6 +117,143 @@ __device__ __noinline__ Token classify_at(const TextView &v, long long p, long l
     return t;
 }
 
+// The same decision for the tags that produce something (EXTINF, MEDIA-SEQUENCE, ENDLIST), taken
+// from registers: up to 36 bytes at the '#' are fetched from the tile's shared-memory copy as
+// aligned words and shifted into place, literals are compared a word at a time, numbers are
+// walked with compile-time byte positions.  `limit` (<= 36) bytes are valid; `limit_is_end` says
+// the text ends there.  Returns false when the token does not resolve within those bytes (a number
+// longer than the window): the caller then takes classify_at().
+__constant__ double c_pow10[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
+                                   1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+
+__device__ __forceinline__ unsigned lit4(char a, char b, char c, char d)
+{
+    return (unsigned)(unsigned char)a | ((unsigned)(unsigned char)b << 8) | ((unsigned)(unsigned char)c << 16) |
+           ((unsigned)(unsigned char)d << 24);
+}
+
+__device__ __noinline__ bool decimal_slow(unsigned long long w, int exp10, bool sticky, double *out)
+{
+    DecimalScan d;
+    d.w = w;
+    d.exp10 = exp10;
+    d.sticky = sticky;
+    d.run = 1;
+    d.is_number = true;
+    return decimal_to_double(d, out);
+}
+
+__device__ __forceinline__ bool classify_fast(const unsigned char *stext, int pos_rel, int limit, bool limit_is_end,
+                                              Token &t)
+{
+    t.kind = kTokNone;
+    t.bits = 0;
+    t.unsupported = false;
+    if (limit < 9) return limit_is_end || limit >= 4;   // nothing that emits fits; "#EXT" test below needs 4
+    const unsigned *w32 = reinterpret_cast<const unsigned *>(stext + (pos_rel & ~3));
+    const unsigned sh = (unsigned)(pos_rel & 3) * 8u;
+    unsigned a[10];
+#pragma unroll
+    for (int j = 0; j < 7; j++) a[j] = w32[j];
+    const unsigned u0 = __funnelshift_r(a[0], a[1], sh), u1 = __funnelshift_r(a[1], a[2], sh);
+    if (u0 != lit4('#', 'E', 'X', 'T')) return true;
+    unsigned u[9];
+#pragma unroll
+    for (int j = 2; j < 6; j++) u[j] = __funnelshift_r(a[j], a[j + 1], sh);
+    if (u1 == lit4('I', 'N', 'F', ':')) {
+        // scan_decimal() on bytes 8..23
+        unsigned long long w = 0;
+        int ndig = 0, exp10 = 0, run = 0;
+        bool seen_dot = false, in_prefix = true, is_number = false, sticky = false, ended = false;
+#pragma unroll
+        for (int j = 8; j < 24; j++) {
+            if (ended) break;
+            if (j >= limit) {
+                if (!limit_is_end) return false;
+                ended = true;
+                break;
+            }
+            const int c = (int)((u[j >> 2] >> ((j & 3) * 8)) & 0xffu);
+            const bool digit = c >= '0' && c <= '9';
+            if (!digit && c != '.') {
+                ended = true;
+                break;
+            }
+            run++;
+            if (!in_prefix) continue;
+            if (c == '.') {
+                if (seen_dot) in_prefix = false;
+                else seen_dot = true;
+                continue;
+            }
+            is_number = true;
+            const int d = c - '0';
+            if (ndig == 0 && d == 0) {
+                if (seen_dot) exp10--;
+                continue;
+            }
+            w = w * 10ull + (unsigned long long)d;     // at most 16 digits here: no overflow
+            ndig++;
+            if (seen_dot) exp10--;
+        }
+        if (!ended) return false;                       // the run goes on past the window
+        if (run == 0) return true;
+        if (!is_number) {
+            t.kind = kTokInfNaN;
+            return true;
+        }
+        double x = 0.0;
+        if (w == 0) x = 0.0;
+        else if (w <= (1ull << 53)) x = __ddiv_rn((double)w, c_pow10[-exp10]);   // both exact: one IEEE division
+        else t.unsupported = !decimal_slow(w, exp10, sticky, &x);
+        t.kind = kTokFrag;
+        t.bits = __double_as_longlong(x);
+        return true;
+    }
+    if ((u1 & 0xffffffu) != (lit4('-', 'X', '-', 0) & 0xffffffu)) return true;
+    const unsigned c7 = u1 >> 24;
+    if (c7 == 'E') {
+        if (limit >= 14 && u[2] == lit4('N', 'D', 'L', 'I') && (u[3] & 0xffffu) == (lit4('S', 'T', 0, 0) & 0xffffu))
+            t.kind = kTokEnd;
+        return true;
+    }
+    if (c7 == 'M') {
+        if (limit < 23) return true;                    // "#EXT-X-MEDIA-SEQUENCE:" and one digit
+        if (u[2] != lit4('E', 'D', 'I', 'A') || u[3] != lit4('-', 'S', 'E', 'Q') || u[4] != lit4('U', 'E', 'N', 'C') ||
+            (u[5] & 0xffffu) != (lit4('E', ':', 0, 0) & 0xffffu))
+            return true;
+#pragma unroll
+        for (int j = 7; j < 10; j++) a[j] = w32[j];
+#pragma unroll
+        for (int j = 6; j < 9; j++) u[j] = __funnelshift_r(a[j], a[j + 1], sh);
+        long long val = 0;
+        int nd = 0;
+        bool ended = false;
+#pragma unroll
+        for (int j = 22; j < 36; j++) {
+            if (j >= limit) {
+                if (!limit_is_end) return false;
+                ended = true;
+                break;
+            }
+            const int c = (int)((u[j >> 2] >> ((j & 3) * 8)) & 0xffu);
+            if (c < '0' || c > '9') {
+                ended = true;
+                break;
+            }
+            nd++;
+            if (val <= 0x7fffffffll) val = val * 10 + (c - '0');
+        }
+        if (!ended) return false;
+        if (nd == 0) return true;
+        t.kind = kTokSeq;
+        t.unsupported = val > 0x7fffffffll;
+        t.bits = val > 0x7fffffffll ? 0x7fffffffll : val;
+        return true;
+    }
+    return true;   // KEY / PROGRAM-DATE-TIME and every other tag emit nothing themselves
+}
+
 // A '#' in the middle of a line is a match only if nothing before it on the line swallowed it:
 // replay the line from its first byte (global memory; this is the rare path).
 __device__ __noinline__ bool hidden_by_earlier_match(const unsigned char *text, long long track_lo, long long p,
@@ -147,20 +289,39 @@ __device__ __noinline__ bool hidden_by_earlier_match(const unsigned char *text, 
     return false;
 }
 
-__device__ __forceinline__ unsigned hash_mask4(unsigned w)
+// '#' bytes of 16 bytes of text as 16 bits in text order.  Per word: compare, keep one bit a byte,
+// and gather the four bits with one multiply (the partial products never collide below bit 28).
+__device__ __forceinline__ unsigned hash_nibble(unsigned w)
 {
-    const unsigned m = __vcmpeq4(w, 0x23232323u);   // 0xff per '#'
-    return ((m >> 7) & 1u) | ((m >> 14) & 2u) | ((m >> 21) & 4u) | ((m >> 28) & 8u);
+    return ((__vcmpeq4(w, 0x23232323u) & 0x01010101u) * 0x01020408u) >> 24;
 }
+__device__ __forceinline__ unsigned hash_mask16(const uint4 &w)
+{
+    return hash_nibble(w.x) | (hash_nibble(w.y) << 4) | (hash_nibble(w.z) << 8) | (hash_nibble(w.w) << 12);
+}
+
+// text_off[] of the tracks a tile touches, from shared memory when they were staged.
+struct TrackOffsets {
+    const long long *g;
+    const long long *s;
+    int lo, n;
+    __device__ __forceinline__ long long operator()(int t) const
+    {
+        const unsigned d = (unsigned)(t - lo);
+        return d < (unsigned)n ? s[d] : g[t];
+    }
+};
 
 struct Shared {
     Scan::Smem scan;
-    __align__(16) unsigned char text[kTile];
+    __align__(16) unsigned char text[kTile + 48];   // + room for the word fetches of classify_fast
     unsigned short cpos[kCap];          // tile-relative position of each candidate of the round
     unsigned short cfpre[kCap];         // fragments of the tile before that candidate
+    long long toff[kTrackStage];
+    unsigned short hpre[kThreads + 1];  // '#' bytes of the tile before each thread's span
     unsigned wtot[kPerThread * kWarps]; // per (slot, warp): fragments | tags << 16
     unsigned wpre[kPerThread * kWarps + 1];
-    int hash_warp[kWarps + 1];
+    int hash_warp[kWarps];
 };
 
 struct RoundRegs {
@@ -169,43 +330,37 @@ struct RoundRegs {
     unsigned char kind[kPerThread];
 };
 
-// Builds the candidate list of one round (the '#' bytes of threads [t0, t1)), classifies it and
-// scans the fragment / tag flags.  Returns the round's totals as fragments | tags << 16.
-__device__ unsigned classify_round(const IngestParams &p, Shared &sh, RoundRegs &rr, int tile, long long lo,
-                                   long long hi, unsigned my_mask, int my_first, int nc, unsigned running,
-                                   bool effects)
+// One candidate of the round's list: its track, what the expression matches there, whether an
+// earlier match on the line hides it.  Kept out of line: the caller's loop is unrolled so that its
+// results stay in registers, and eight inlined copies of this would not fit the instruction cache.
+__device__ __noinline__ int classify_candidate(const IngestParams &p, Shared &sh, const TrackOffsets &toff, int t_lo,
+                                               int t_hi, long long lo, long long hi, int i, bool effects,
+                                               long long &bits)
 {
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    // candidate list, in text order
-    if (my_first >= 0) {
-        unsigned m = my_mask;
-        int at = my_first;
-        while (m) {
-            const int b = __ffs(m) - 1;
-            m &= m - 1;
-            sh.cpos[at++] = (unsigned short)(tid * kBytesPerThread + b);
-        }
-    }
-    __syncthreads();
     const TextView v{p.text, sh.text, lo, hi};
-    const int t_lo = p.tile_tlo[tile], t_hi = p.tile_tlo[tile + 1];
-#pragma unroll
-    for (int k = 0; k < kPerThread; k++) {
-        const int i = tid + k * kThreads;
-        int kind = kTokNone;
-        long long bits = 0;
-        if (i < nc) {
+    int kind = kTokNone;
+    bits = 0;
+    {
             const long long pos = lo + sh.cpos[i];
             int a = t_lo, b = t_hi;               // last track whose text starts at or before pos
             while (a < b) {
                 const int mid = (a + b + 1) >> 1;
-                if (p.text_off[mid] <= pos) a = mid;
+                if (toff(mid) <= pos) a = mid;
                 else b = mid - 1;
             }
-            const long long tb = p.text_off[a], te = p.text_off[a + 1];
+            const long long tb = toff(a), te = toff(a + 1);
             const bool parsed = p.state == nullptr || p.state[a] == HLSMAP_TRACK_PARSED;
             if (parsed && pos < te) {
-                const Token t = classify_at(v, pos, te);
+                // bytes valid both in the tile's copy and in the track; a candidate in the tile's
+                // last bytes whose track runs on is left to the byte-wise classifier
+                const long long in_tile = hi - pos, in_track = te - pos;
+                Token t;
+                bool done = false;
+                if (in_track <= in_tile || in_tile >= 36) {
+                    const int limit = in_track < 36 ? (int)in_track : 36;
+                    done = classify_fast(sh.text, (int)sh.cpos[i], limit, limit == in_track, t);
+                }
+                if (!done) t = classify_at(v, pos, te);
                 bool live = t.kind != kTokNone;
                 if (live && pos > tb) {
                     const int prev = v(pos - 1);
@@ -218,7 +373,36 @@ __device__ unsigned classify_round(const IngestParams &p, Shared &sh, RoundRegs 
                     if (effects && kind == kTokEnd) p.live[a] = 0;
                 }
             }
+    }
+    return kind;
+}
+
+// Builds the candidate list of one round (this thread's '#' bytes go to cpos[my_first...] when
+// my_first >= 0), classifies it and scans the fragment / tag flags.  Returns the round's totals
+// as fragments | tags << 16.
+__device__ unsigned classify_round(const IngestParams &p, Shared &sh, RoundRegs &rr, const TrackOffsets &toff,
+                                   int t_lo, int t_hi, long long lo, long long hi, const unsigned (&mask)[kGroups],
+                                   int my_first, int nc, unsigned running, bool effects)
+{
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (my_first >= 0) {
+        int at = my_first;
+#pragma unroll
+        for (int g = 0; g < kGroups; g++) {
+            unsigned m = mask[g];
+            while (m) {
+                const int b = __ffs(m) - 1;
+                m &= m - 1;
+                sh.cpos[at++] = (unsigned short)(tid * kBytesPerThread + g * 32 + b);
+            }
         }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < kPerThread; k++) {
+        const int i = tid + k * kThreads;
+        long long bits = 0;
+        const int kind = i < nc ? classify_candidate(p, sh, toff, t_lo, t_hi, lo, hi, i, effects, bits) : kTokNone;
         rr.kind[k] = (unsigned char)kind;
         rr.bits[k] = bits;
         const unsigned fb = __ballot_sync(0xffffffffu, kind == kTokFrag);
@@ -228,16 +412,26 @@ __device__ unsigned classify_round(const IngestParams &p, Shared &sh, RoundRegs 
         if (lane == 0) sh.wtot[k * kWarps + warp] = (unsigned)__popc(fb) | ((unsigned)__popc(tb2) << 16);
     }
     __syncthreads();
-    if (warp == 0) {   // exclusive scan of the 64 (slot, warp) totals, slot-major = text order
-        const unsigned a = sh.wtot[2 * lane], b = sh.wtot[2 * lane + 1];
-        unsigned x = a + b;
+    if (warp == 0) {   // exclusive scan of the (slot, warp) totals, slot-major = text order
+        constexpr int E = kPerThread * kWarps / 32;
+        unsigned v[E], x = 0;
+#pragma unroll
+        for (int e = 0; e < E; e++) {
+            v[e] = sh.wtot[E * lane + e];
+            x += v[e];
+        }
+        const unsigned mine = x;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             const unsigned y = __shfl_up_sync(0xffffffffu, x, d);
             if (lane >= d) x += y;
         }
-        sh.wpre[2 * lane] = x - a - b;
-        sh.wpre[2 * lane + 1] = x - b;
+        unsigned run = x - mine;
+#pragma unroll
+        for (int e = 0; e < E; e++) {
+            sh.wpre[E * lane + e] = run;
+            run += v[e];
+        }
         if (lane == 31) sh.wpre[kPerThread * kWarps] = x;
     }
     __syncthreads();
@@ -254,9 +448,9 @@ __device__ unsigned classify_round(const IngestParams &p, Shared &sh, RoundRegs 
 
 // Writes what one classified round found: durations and sequence tags to their global slots,
 // and the fragment offset of every track whose text starts inside [b_lo, b_hi) of the tile.
-__device__ void emit_round(const IngestParams &p, Shared &sh, const RoundRegs &rr, int tile, long long lo,
-                           int nc, unsigned round_end, unsigned long long fbase, unsigned long long tbase,
-                           long long b_lo, long long b_hi)
+__device__ void emit_round(const IngestParams &p, Shared &sh, const RoundRegs &rr, const TrackOffsets &toff,
+                           int u0, int u1, long long lo, int nc, unsigned round_end, unsigned long long fbase,
+                           unsigned long long tbase, long long b_lo, long long b_hi)
 {
     const int tid = threadIdx.x;
 #pragma unroll
@@ -276,9 +470,8 @@ __device__ void emit_round(const IngestParams &p, Shared &sh, const RoundRegs &r
         }
     }
     // tracks starting in this byte range: fragments before the first candidate at/after the start
-    const int u0 = p.tile_bfirst[tile], u1 = p.tile_bfirst[tile + 1];
     for (int u = u0 + tid; u < u1; u += kThreads) {
-        const long long b = p.text_off[u];
+        const long long b = toff(u);
         if (b < b_lo || b >= b_hi) continue;
         const long long rel = b - lo;
         int a = 0, z = nc;                       // first candidate with cpos >= rel
@@ -294,7 +487,7 @@ __device__ void emit_round(const IngestParams &p, Shared &sh, const RoundRegs &r
 
 }  // namespace
 
-__global__ void __launch_bounds__(kThreads, 4)
+__global__ void __launch_bounds__(kThreads, 1024 / kThreads)
 m3u8_scan_kernel(const IngestParams p)
 {
     __shared__ Shared sh;
@@ -305,30 +498,41 @@ m3u8_scan_kernel(const IngestParams p)
         const long long lo = (long long)tile * kTile;
         const long long hi = lo + kTile < p.n_bytes ? lo + kTile : p.n_bytes;
         const bool last = tile == p.n_tiles - 1;
+        const long long open_end = 0x7fffffffffffffffll;
 
-        // stage the tile and find its '#' bytes
-        unsigned mask = 0;
-        {
-            const long long at = lo + (long long)tid * kBytesPerThread;
+        // stage the tile (coalesced 16-byte pieces) and the text offsets of the tracks it touches
 #pragma unroll
-            for (int g = 0; g < kBytesPerThread / 16; g++) {
-                const long long a = at + g * 16;
-                uint4 w = make_uint4(0, 0, 0, 0);
-                if (p.vec_ok && a + 16 <= p.n_bytes) {
-                    w = *reinterpret_cast<const uint4 *>(p.text + a);
-                } else {
-                    unsigned char tmp[16];
+        for (int j = 0; j < kBytesPerThread / 16; j++) {
+            const int piece = j * kThreads + tid;
+            const long long a = lo + (long long)piece * 16;
+            uint4 w = make_uint4(0, 0, 0, 0);
+            if (p.vec_ok && a + 16 <= p.n_bytes) {
+                w = __ldcs(reinterpret_cast<const uint4 *>(p.text + a));
+            } else if (a < p.n_bytes) {
+                unsigned char tmp[16];
 #pragma unroll
-                    for (int j = 0; j < 16; j++) tmp[j] = a + j < p.n_bytes ? p.text[a + j] : 0;
-                    memcpy(&w, tmp, 16);
-                }
-                *reinterpret_cast<uint4 *>(sh.text + tid * kBytesPerThread + g * 16) = w;
-                mask |= (hash_mask4(w.x) | (hash_mask4(w.y) << 4) | (hash_mask4(w.z) << 8) |
-                         (hash_mask4(w.w) << 12)) << (16 * g);
+                for (int q = 0; q < 16; q++) tmp[q] = a + q < p.n_bytes ? p.text[a + q] : 0;
+                memcpy(&w, tmp, 16);
             }
+            *reinterpret_cast<uint4 *>(sh.text + piece * 16) = w;
         }
-        // exclusive prefix of the per-thread '#' counts
-        const int cnt = __popc(mask);
+        const int t_lo = p.tile_tlo[tile], t_hi = p.tile_tlo[tile + 1];
+        const int u0 = p.tile_bfirst[tile], u1 = p.tile_bfirst[tile + 1];
+        const int n_staged = t_hi + 2 - t_lo < kTrackStage ? t_hi + 2 - t_lo : kTrackStage;
+        for (int i = tid; i < n_staged; i += kThreads) sh.toff[i] = p.text_off[t_lo + i];
+        const TrackOffsets toff{p.text_off, sh.toff, t_lo, n_staged};
+        __syncthreads();
+
+        // the '#' bytes of this thread's 128-byte span
+        unsigned mask[kGroups];
+        int cnt = 0;
+#pragma unroll
+        for (int g = 0; g < kGroups; g++) {
+            const unsigned char *at = sh.text + tid * kBytesPerThread + g * 32;
+            mask[g] = hash_mask16(*reinterpret_cast<const uint4 *>(at)) |
+                      (hash_mask16(*reinterpret_cast<const uint4 *>(at + 16)) << 16);
+            cnt += __popc(mask[g]);
+        }
         int x = cnt;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
@@ -338,51 +542,49 @@ m3u8_scan_kernel(const IngestParams p)
         if (lane == 31) sh.hash_warp[warp] = x;
         __syncthreads();
         int before = x - cnt, n_hash = 0;
-        int quarter_base[5];
 #pragma unroll
         for (int w = 0; w < kWarps; w++) {
             const int c = sh.hash_warp[w];
-            if ((w & 1) == 0) quarter_base[w >> 1] = n_hash;   // 2 warps = one quarter of the tile
             before += w < warp ? c : 0;
             n_hash += c;
         }
-        quarter_base[4] = n_hash;
 
         RoundRegs rr;
         unsigned long long fbase = 0, tbase = 0;
         unsigned totals = 0;
         if (n_hash <= kCap) {
             // the usual case: one round, classified once, results kept in registers
-            totals = classify_round(p, sh, rr, tile, lo, hi, mask, before, n_hash, 0u, true);
+            totals = classify_round(p, sh, rr, toff, t_lo, t_hi, lo, hi, mask, before, n_hash, 0u, true);
             Scan::publish_aggregate(p.status_f, p.epoch, tile, totals & 0xffffu);
             Scan::publish_aggregate(p.status_t, p.epoch, tile, totals >> 16);
-            fbase = Scan::wait_prefix(sh.scan, p.status_f, p.epoch, tile, totals & 0xffffu);
-            tbase = Scan::wait_prefix(sh.scan, p.status_t, p.epoch, tile, totals >> 16);
-            emit_round(p, sh, rr, tile, lo, n_hash, totals, fbase, tbase, lo,
-                       last ? 0x7fffffffffffffffll : hi);
+            Scan::wait_prefix_pair(sh.scan, p.status_f, p.status_t, p.epoch, tile, totals & 0xffffu, totals >> 16,
+                                   fbase, tbase);
+            emit_round(p, sh, rr, toff, u0, u1, lo, n_hash, totals, fbase, tbase, lo, last ? open_end : hi);
         } else {
-            // a tile dense with '#': four rounds of a quarter tile each, classified twice
-            // (count, then write) so that no round holds more than kCap candidates
-            for (int r = 0; r < 4; r++) {
-                const bool mine = (warp >> 1) == r;
-                totals += classify_round(p, sh, rr, tile, lo, hi, mine ? mask : 0u,
-                                         mine ? before - quarter_base[r] : -1,
-                                         quarter_base[r + 1] - quarter_base[r], 0u, false);
+            // a tile dense with '#': rounds of 2 KB of text (never more than kCap candidates),
+            // classified twice -- once to count, once more to write
+            sh.hpre[tid] = (unsigned short)before;
+            if (tid == 0) sh.hpre[kThreads] = (unsigned short)n_hash;
+            __syncthreads();
+            for (int r = 0; r < kRounds; r++) {
+                const bool mine = tid / kThreadsPerRound == r;
+                const int r0 = sh.hpre[r * kThreadsPerRound], r1 = sh.hpre[(r + 1) * kThreadsPerRound];
+                totals += classify_round(p, sh, rr, toff, t_lo, t_hi, lo, hi, mask, mine ? before - r0 : -1, r1 - r0,
+                                         0u, false);
             }
             Scan::publish_aggregate(p.status_f, p.epoch, tile, totals & 0xffffu);
             Scan::publish_aggregate(p.status_t, p.epoch, tile, totals >> 16);
-            fbase = Scan::wait_prefix(sh.scan, p.status_f, p.epoch, tile, totals & 0xffffu);
-            tbase = Scan::wait_prefix(sh.scan, p.status_t, p.epoch, tile, totals >> 16);
+            Scan::wait_prefix_pair(sh.scan, p.status_f, p.status_t, p.epoch, tile, totals & 0xffffu, totals >> 16,
+                                   fbase, tbase);
             unsigned running = 0;
-            for (int r = 0; r < 4; r++) {
-                const bool mine = (warp >> 1) == r;
-                const int nc = quarter_base[r + 1] - quarter_base[r];
-                const unsigned t = classify_round(p, sh, rr, tile, lo, hi, mine ? mask : 0u,
-                                                  mine ? before - quarter_base[r] : -1, nc, running, true);
-                running += t;
-                const long long b_lo = lo + (long long)r * (kTile / 4);
-                const long long b_hi = (r == 3) ? (last ? 0x7fffffffffffffffll : hi) : b_lo + kTile / 4;
-                emit_round(p, sh, rr, tile, lo, nc, running, fbase, tbase, b_lo, b_hi);
+            for (int r = 0; r < kRounds; r++) {
+                const bool mine = tid / kThreadsPerRound == r;
+                const int r0 = sh.hpre[r * kThreadsPerRound], r1 = sh.hpre[(r + 1) * kThreadsPerRound];
+                running += classify_round(p, sh, rr, toff, t_lo, t_hi, lo, hi, mask, mine ? before - r0 : -1, r1 - r0,
+                                          running, true);
+                const long long b_lo = lo + (long long)r * kRoundBytes;
+                const long long b_hi = r == kRounds - 1 ? (last ? open_end : hi) : b_lo + kRoundBytes;
+                emit_round(p, sh, rr, toff, u0, u1, lo, r1 - r0, running, fbase, tbase, b_lo, b_hi);
                 __syncthreads();
             }
         }
@@ -451,10 +653,11 @@ m3u8_assemble_kernel(const AssembleParams p)
     long long cur = 0;
     double total = 0.0;
     bool overflow = false;
+    const long long none = 0x7fffffffffffffffll;
+    long long next_tag = (e < p.n_tags && p.tag_pos[e] < te) ? p.tag_frag[e] : none;
     for (long long c = 0; c < len; c += LANES) {
         const long long i = c + lane;
         const double d = i < len ? p.dur[off + i] : 0.0;
-        const long long next_tag = (e < p.n_tags && p.tag_pos[e] < te) ? p.tag_frag[e] : 0x7fffffffffffffffll;
         const int n = len - c < LANES ? (int)(len - c) : LANES;
         long long my_sn = 0;
         double my_start = 0.0;
@@ -477,6 +680,7 @@ m3u8_assemble_kernel(const AssembleParams p)
                 total += dj;
                 cur++;
             }
+            next_tag = (e < p.n_tags && p.tag_pos[e] < te) ? p.tag_frag[e] : none;
         }
         if (i < len) {
             overflow |= my_sn > 0x7fffffffll;

@@ -57,9 +57,10 @@ def test_corpus_with_ignored_tracks(ctx):
 
 
 def test_tags_across_tile_borders(ctx):
-    """Every alignment of a playlist against the 8 KB tile border, including tags and numbers cut by it."""
+    """Every alignment of a playlist against a tile border (16 KB tiles; 32 KB is every second one),
+    including tags and numbers cut by it."""
     body = b"#EXT-X-MEDIA-SEQUENCE:41\n#EXTINF:9.98458,\nfileSequence41.ts\n#EXTINF:3.003,\nb.ts\n#EXT-X-ENDLIST\n"
-    for pad in list(range(8192 - len(body) - 2, 8192 + 2, 1)):
+    for pad in list(range(16384 - len(body) - 2, 16384 + 2)) + list(range(32768 - len(body) - 2, 32768 + 2, 3)):
         texts = [b"x" * pad, body, b"\n", body]
         got = ctx.parse_m3u8(texts)
         exp = oracle.parse_m3u8(b"".join(texts), _offsets(texts))
