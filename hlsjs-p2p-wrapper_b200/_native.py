@@ -12,6 +12,8 @@ ERR_INVALID, ERR_CUDA, ERR_NOMEM, ERR_CAPACITY, ERR_OVERFLOW, ERR_UNSUPPORTED = 
 ST_OK, ST_UNPARSED, ST_MISSING, ST_EMPTY, ST_SCATTERED, ST_NO_FRAGMENT = 0, 1, 2, 3, 4, 5
 TRACK_MISSING, TRACK_UNPARSED, TRACK_PARSED = 0, 1, 2
 PATH_AUTO, PATH_SEARCH, PATH_FILTER = 0, 1, 2
+JSON_OK, JSON_MALFORMED, JSON_UNSUPPORTED, JSON_NOT_INT32 = 0, 1, 2, 3
+JSON_HAS_SN, JSON_HAS_TRACKVIEW, JSON_HAS_LEVEL, JSON_HAS_URLID, JSON_HAS_TIME, JSON_TIME_NULL = 1, 2, 4, 8, 16, 32
 
 
 class Result(ctypes.Structure):
@@ -71,6 +73,10 @@ SYMBOLS = {
     "hlsmap_views_from_fragments": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P]),
     "hlsmap_get_next_segment_view_dev": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P, _P]),
     "hlsmap_get_next_segment_view": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P]),
+    "hlsmap_view_to_json_dev": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _I64, _P, _P]),
+    "hlsmap_view_to_json": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _I64, _P]),
+    "hlsmap_view_from_json_dev": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "hlsmap_view_from_json": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P, _P]),
     "hlsmap_parse_m3u8_dev": (_INT, [_P, _I32, _P, _P, _P, _I64, _P, _P, _P, _P, _P, _I64, _P, _P]),
     "hlsmap_parse_m3u8": (_INT, [_P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _P]),
     "hlsmap_map_create_from_m3u8": (_INT, [_P, _I32, _P, _I32, _P, _P, _P, _P, _P, _P]),

@@ -7,8 +7,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 LIB = os.path.join(CSRC, "libhlsmap.so")
-SOURCES = ["resolve.cu", "views.cu", "ingest.cu", "api.cu"]
-HEADERS = ["common.cuh", "scan.cuh", "decimal.cuh"]
+SOURCES = ["resolve.cu", "views.cu", "ingest.cu", "json.cu", "api.cu"]
+HEADERS = ["common.cuh", "scan.cuh", "decimal.cuh", "dtoa.cuh", "pow10_table.inc"]
 
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",

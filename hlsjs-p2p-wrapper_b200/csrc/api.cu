@@ -1542,6 +1542,146 @@ int hlsmap_get_segment_list_noalloc_dev(hlsmap_map *map, int64_t nq, const int32
 
 }  // extern "C"
 
+/* ---- JSON form of views (json.cu) ---------------------------------------- */
+int hlsmap_view_to_json_dev(hlsmap_ctx *ctx, int64_t n, const int32_t *d_level, const int32_t *d_url_id,
+                            const int32_t *d_sn, const double *d_time, int32_t *d_offsets, char *d_chars,
+                            int64_t capacity, void *stream, int64_t *total_out)
+{
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (n < 0 || !d_offsets || capacity < 0 ||
+        (n > 0 && (!d_level || !d_url_id || !d_sn || (capacity > 0 && !d_chars))))
+        return fail(HLSMAP_ERR_INVALID, "view_to_json: null arrays");
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    ctx->have_last = true;
+    ctx->last_path = 0;
+    ctx->last_launches = 0;
+    if (n == 0) {
+        CK(cudaMemsetAsync(d_offsets, 0, sizeof(int32_t), s));
+        if (total_out) *total_out = 0;
+        return HLSMAP_OK;
+    }
+    const int64_t n_tiles = (n + kJsonTileViews - 1) / kJsonTileViews;
+    if (n_tiles > 0x7fffffff) return fail(HLSMAP_ERR_INVALID, "batch too large: split it");
+    r = prepare_scan(ctx, n_tiles, s);
+    if (r) return r;
+    JsonWriteParams p{};
+    p.n = n;
+    p.level = d_level;
+    p.url_id = d_url_id;
+    p.sn = d_sn;
+    p.time = d_time;
+    p.offsets = d_offsets;
+    p.chars = d_chars;
+    p.capacity = capacity;
+    p.tile_status = status_of(ctx);
+    p.ctr = ctr_of(ctx);
+    p.result = result_of(ctx);
+    p.epoch = ctx->epoch;
+    p.tslot = ctx->set_launches[ctx->epoch & 1u] & 1u;
+    p.n_tiles = (int)n_tiles;
+    const int maxg = view_to_json_max_grid();
+    CK(launch_view_to_json(p, (int)(n_tiles < maxg ? n_tiles : maxg), s));
+    ctx->set_launches[ctx->epoch & 1u]++;
+    ctx->last_launches = 1;
+    if (total_out) {
+        hlsmap_result res{};
+        r = fetch_result(ctx, s, &res);
+        if (r) return r;
+        *total_out = res.total_hits;
+        if (res.total_hits > capacity)
+            return fail(HLSMAP_ERR_CAPACITY, "character buffer too small: need " +
+                                                 std::to_string(res.total_hits) + " bytes");
+    }
+    return HLSMAP_OK;
+}
+
+int hlsmap_view_to_json(hlsmap_ctx *ctx, int64_t n, const int32_t *level, const int32_t *url_id,
+                        const int32_t *sn, const double *time, int32_t *offsets, char *chars,
+                        int64_t capacity, int64_t *total_out)
+{
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (n < 0 || !offsets || capacity < 0 || (n > 0 && (!level || !url_id || !sn || (capacity > 0 && !chars))))
+        return fail(HLSMAP_ERR_INVALID, "view_to_json: null arrays");
+    const int64_t n1 = n > 0 ? n : 1;
+    Cols c[6] = {{level, n1 * 4, nullptr},  {url_id, n1 * 4, nullptr},       {sn, n1 * 4, nullptr},
+                 {time, n1 * 8, nullptr},   {nullptr, (n1 + 1) * 4, nullptr}, {nullptr, capacity > 0 ? capacity : 16, nullptr}};
+    if (n == 0) c[0].h = c[1].h = c[2].h = c[3].h = nullptr;
+    if ((r = stage_in(ctx, c, 6, 0))) return r;
+    int64_t total = 0;
+    r = hlsmap_view_to_json_dev(ctx, n, (int *)c[0].d, (int *)c[1].d, (int *)c[2].d, time ? (double *)c[3].d : nullptr,
+                                (int *)c[4].d, (char *)c[5].d, capacity, ctx->stream, &total);
+    if (total_out) *total_out = total;
+    if (r != HLSMAP_OK && r != HLSMAP_ERR_CAPACITY) return r;
+    const std::string keep = g_err;
+    CK(cudaMemcpyAsync(offsets, c[4].d, (size_t)(n + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (r == HLSMAP_OK && total > 0)
+        CK(cudaMemcpyAsync(chars, c[5].d, (size_t)total, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (r) g_err = keep;
+    return r;
+}
+
+int hlsmap_view_from_json_dev(hlsmap_ctx *ctx, int64_t n, const char *d_chars, const int32_t *d_offsets,
+                              int32_t *d_level, int32_t *d_url_id, int32_t *d_sn, double *d_time,
+                              uint8_t *d_flags, uint8_t *d_status, void *stream)
+{
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (n < 0 || (n > 0 && (!d_chars || !d_offsets || !d_level || !d_url_id || !d_sn || !d_time || !d_flags ||
+                            !d_status)))
+        return fail(HLSMAP_ERR_INVALID, "view_from_json: null arrays");
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    JsonReadParams p{};
+    p.n = n;
+    p.chars = d_chars;
+    p.offsets = d_offsets;
+    p.level = d_level;
+    p.url_id = d_url_id;
+    p.sn = d_sn;
+    p.time = d_time;
+    p.flags = d_flags;
+    p.status = d_status;
+    CK(launch_view_from_json(p, s));
+    ctx->have_last = true;
+    ctx->last_path = 0;
+    ctx->last_launches = n > 0 ? 1 : 0;
+    return HLSMAP_OK;
+}
+
+int hlsmap_view_from_json(hlsmap_ctx *ctx, int64_t n, const char *chars, const int32_t *offsets,
+                          int32_t *level, int32_t *url_id, int32_t *sn, double *time, uint8_t *flags,
+                          uint8_t *status)
+{
+    int r = use_ctx(ctx);
+    if (r) return r;
+    if (n < 0 || (n > 0 && (!chars || !offsets || !level || !url_id || !sn || !time || !flags || !status)))
+        return fail(HLSMAP_ERR_INVALID, "view_from_json: null arrays");
+    if (n == 0) return HLSMAP_OK;
+    if (offsets[0] != 0) return fail(HLSMAP_ERR_INVALID, "view_from_json: offsets[0] != 0");
+    for (int64_t i = 0; i < n; i++)
+        if (offsets[i + 1] < offsets[i]) return fail(HLSMAP_ERR_INVALID, "view_from_json: offsets not monotone");
+    const int64_t nc = offsets[n];
+    Cols c[8] = {{chars, nc > 0 ? nc : 16, nullptr}, {offsets, (n + 1) * 4, nullptr}, {nullptr, n * 4, nullptr},
+                 {nullptr, n * 4, nullptr},          {nullptr, n * 4, nullptr},       {nullptr, n * 8, nullptr},
+                 {nullptr, n, nullptr},              {nullptr, n, nullptr}};
+    if (nc == 0) c[0].h = nullptr;
+    if ((r = stage_in(ctx, c, 8, 0))) return r;
+    r = hlsmap_view_from_json_dev(ctx, n, (char *)c[0].d, (int *)c[1].d, (int *)c[2].d, (int *)c[3].d, (int *)c[4].d,
+                                  (double *)c[5].d, (uint8_t *)c[6].d, (uint8_t *)c[7].d, ctx->stream);
+    if (r) return r;
+    cudaStream_t s = ctx->stream;
+    CK(cudaMemcpyAsync(level, c[2].d, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(url_id, c[3].d, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(sn, c[4].d, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(time, c[5].d, (size_t)n * 8, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(flags, c[6].d, (size_t)n, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(status, c[7].d, (size_t)n, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return HLSMAP_OK;
+}
+
 /* ---- media playlists (M3U8 text) -> fragment tables (ingest.cu) ------------- */
 namespace {
 

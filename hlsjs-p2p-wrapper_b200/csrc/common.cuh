@@ -169,6 +169,33 @@ cudaError_t launch_ingest_tile_index(const long long *text_off, int n_tracks, in
 cudaError_t launch_ingest_scan(const IngestParams &p, cudaStream_t s);
 cudaError_t launch_ingest_assemble(const AssembleParams &p, bool warp_per_track, cudaStream_t s);
 
+// ---- JSON form of views (json.cu) -----------------------------------------------------------
+constexpr int kJsonTileViews = 256;
+struct JsonWriteParams {
+    long long n;
+    const int *level, *url_id, *sn;
+    const double *time;          // nullable: the property is undefined and left out
+    int *offsets;
+    char *chars;
+    long long capacity;
+    unsigned long long *tile_status;
+    ScanCounters *ctr;
+    DeviceResult *result;
+    unsigned epoch, tslot;
+    int n_tiles;
+};
+struct JsonReadParams {
+    long long n;
+    const char *chars;
+    const int *offsets;
+    int *level, *url_id, *sn;
+    double *time;
+    unsigned char *flags, *status;
+};
+int view_to_json_max_grid();
+cudaError_t launch_view_to_json(const JsonWriteParams &p, int grid, cudaStream_t s);
+cudaError_t launch_view_from_json(const JsonReadParams &p, cudaStream_t s);
+
 // launchers (resolve.cu)
 cudaError_t launch_resolve_search(const ResolveParams &p, int grid, size_t smem, cudaStream_t s,
                                   bool overlap_next = false);

@@ -144,4 +144,134 @@ HLSMAP_HD inline bool decimal_to_double(const DecimalScan &s, double *out)
 }
 #endif
 
+// ---- JSON numbers: -? int frac? exp?  (RFC 8259 / ECMA-404, what JSON.parse accepts) ---------
+struct JsonNumber {
+    unsigned long long w;  // first (up to 19) significant digits
+    int exp10;
+    int length;            // characters consumed; 0 = not a JSON number
+    bool sticky, negative;
+};
+
+template <class Get>
+HLSMAP_HD inline JsonNumber scan_json_number(const Get &get, long long p, long long lim)
+{
+    JsonNumber r;
+    r.w = 0;
+    r.exp10 = 0;
+    r.length = 0;
+    r.sticky = false;
+    r.negative = false;
+    long long q = p;
+    if (q < lim && get(q) == '-') {
+        r.negative = true;
+        q++;
+    }
+    int ndig = 0, int_digits = 0;
+    const long long int_start = q;
+    while (q < lim) {                       // int: "0" or [1-9][0-9]*
+        const int c = get(q);
+        if (c < '0' || c > '9') break;
+        if (int_digits == 1 && get(int_start) == '0') return r;   // leading zero
+        int_digits++;
+        const int d = c - '0';
+        if (ndig > 0 || d > 0) {
+            if (ndig < 19) {
+                r.w = r.w * 10ull + (unsigned long long)d;
+                ndig++;
+            } else {
+                if (d) r.sticky = true;
+                r.exp10++;
+            }
+        }
+        q++;
+    }
+    if (int_digits == 0) return r;
+    if (q < lim && get(q) == '.') {
+        q++;
+        int frac_digits = 0;
+        while (q < lim) {
+            const int c = get(q);
+            if (c < '0' || c > '9') break;
+            frac_digits++;
+            const int d = c - '0';
+            if (ndig > 0 || d > 0) {
+                if (ndig < 19) {
+                    r.w = r.w * 10ull + (unsigned long long)d;
+                    ndig++;
+                    r.exp10--;
+                } else if (d) {
+                    r.sticky = true;
+                }
+            } else {
+                r.exp10--;
+            }
+            q++;
+        }
+        if (frac_digits == 0) return r;
+    }
+    if (q < lim && (get(q) == 'e' || get(q) == 'E')) {
+        q++;
+        bool eneg = false;
+        if (q < lim && (get(q) == '+' || get(q) == '-')) {
+            eneg = get(q) == '-';
+            q++;
+        }
+        int e = 0, edigits = 0;
+        while (q < lim) {
+            const int c = get(q);
+            if (c < '0' || c > '9') break;
+            edigits++;
+            if (e < 100000) e = e * 10 + (c - '0');
+            q++;
+        }
+        if (edigits == 0) return r;
+        r.exp10 += eneg ? -e : e;
+    }
+    if (r.w == 0) r.exp10 = 0;
+    r.length = (int)(q - p);
+    return r;
+}
+
+#if defined(__CUDACC__) || defined(__SIZEOF_INT128__)
+// |value| = w * 10^exp10 (+ sticky) -> binary64, or false when outside what is answered exactly:
+// here exp10 may also be positive, up to 19 (w * 10^19 < 2^128).
+HLSMAP_HD inline bool json_number_to_double(const JsonNumber &n, double *out)
+{
+    double mag = 0.0;
+    if (n.w == 0 || n.exp10 <= 0) {
+        DecimalScan s;
+        s.w = n.w;
+        s.exp10 = n.exp10;
+        s.run = 1;
+        s.sticky = n.sticky;
+        s.is_number = true;
+        if (!decimal_to_double(s, &mag)) return false;
+    } else {
+        if (n.sticky || n.exp10 > 19) return false;
+        unsigned __int128 v = n.w;
+        for (int i = 0; i < n.exp10; i++) v *= 10u;
+        int top = 127;
+        while (!((v >> top) & 1)) top--;
+        if (top <= 52) {
+            mag = (double)(unsigned long long)v;
+        } else {
+            const int sh = top - 52;
+            unsigned long long m = (unsigned long long)(v >> sh);
+            const unsigned __int128 rest = v & ((((unsigned __int128)1) << sh) - 1);
+            const unsigned __int128 half = ((unsigned __int128)1) << (sh - 1);
+            int e = top;
+            if (rest > half || (rest == half && (m & 1ull))) m++;
+            if (m == (1ull << 53)) {
+                m >>= 1;
+                e++;
+            }
+            const unsigned long long bits = ((unsigned long long)(e + 1023) << 52) | (m & ((1ull << 52) - 1ull));
+            memcpy(&mag, &bits, sizeof mag);
+        }
+    }
+    *out = n.negative ? -mag : mag;
+    return true;
+}
+#endif
+
 }  // namespace hlsmap

@@ -1,0 +1,282 @@
+// json.cu -- JSON.stringify(segmentView) and new SegmentView(JSON.parse(text)), batched.
+//
+// SURVEY 8 row f3.  The reference serialises a view for transfer with JSON (test/segment-view.js:
+// 5-11); what JSON.stringify walks is the object the constructor built (segment-view.js:22-26:
+// `sn`, `trackView` -- a TrackView with `level`, `urlId`, track-view.js:6-9 -- then `time`), so the
+// text is   {"sn":25,"trackView":{"level":1,"urlId":0},"time":12.5}
+// with properties whose value is undefined left out, numbers printed by Number::toString and a
+// non-finite `time` printed as null.  Columns in, one string per view out -- and back.
+#include "common.cuh"
+#include "decimal.cuh"
+#include "dtoa.cuh"
+#include "scan.cuh"
+
+namespace hlsmap {
+
+__device__ const unsigned long long g_pow10_table[kPow10TableLen][2] = {
+#include "pow10_table.inc"
+};
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kMaxChars = 104;   // {"sn":-2147483648,"trackView":{"level":-2147483648,"urlId":-2147483648},"time":-1.2345678901234567e-308}
+using Scan = TileScan<kThreads>;
+static_assert(kThreads == kJsonTileViews, "one view per thread");
+
+__device__ __forceinline__ int int_len(int v)
+{
+    unsigned m = v < 0 ? 0u - (unsigned)v : (unsigned)v;
+    int d = 1;
+    while (m >= 10u) {
+        m /= 10u;
+        d++;
+    }
+    return d + (v < 0);
+}
+
+__device__ __forceinline__ int put_int(char *dst, int v)
+{
+    const int n = int_len(v);
+    unsigned m = v < 0 ? 0u - (unsigned)v : (unsigned)v;
+    for (int i = n - 1; i >= (v < 0); i--) {
+        dst[i] = (char)('0' + m % 10u);
+        m /= 10u;
+    }
+    if (v < 0) dst[0] = '-';
+    return n;
+}
+
+__device__ __forceinline__ int put_lit(char *dst, const char *lit, int n)
+{
+    for (int i = 0; i < n; i++) dst[i] = lit[i];
+    return n;
+}
+
+}  // namespace
+
+__global__ void __launch_bounds__(kThreads)
+view_to_json_kernel(const JsonWriteParams p)
+{
+    __shared__ Scan::Smem scan;
+    __shared__ unsigned long long warp_cnt[kThreads / 32];
+    __shared__ char buf[kThreads * kMaxChars];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    Scan::acquire_set(p.ctr, p.epoch);
+    for (;;) {
+        const int tile = Scan::next_tile(scan, p.ctr, p.tslot);
+        if (tile >= p.n_tiles) break;
+        const long long v = (long long)tile * kThreads + tid;
+        const bool in = v < p.n;
+        const int l = in ? p.level[v] : 0, u = in ? p.url_id[v] : 0, s = in ? p.sn[v] : 0;
+        // time: 0 = property absent, 1 = null (NaN, +-Infinity), 2 = a number
+        int tkind = 0, tlen = 0;
+        bool tneg = false;
+        Shortest sd;
+        sd.digits = 0;
+        sd.exp10 = 0;
+        sd.ndigits = 1;
+        if (in && p.time != nullptr) {
+            const unsigned long long bits = (unsigned long long)__double_as_longlong(p.time[v]);
+            const unsigned long long mag = bits & 0x7fffffffffffffffull;
+            if (mag >= 0x7ff0000000000000ull) {
+                tkind = 1;
+                tlen = 4;
+            } else {
+                tkind = 2;
+                if (mag == 0) {
+                    tlen = 1;                        // both zeros print as "0"
+                } else {
+                    tneg = (bits >> 63) != 0;
+                    sd = shortest_digits(mag, g_pow10_table);
+                    tlen = js_number_length(sd) + (tneg ? 1 : 0);
+                }
+            }
+        }
+        // {"sn":S,"trackView":{"level":L,"urlId":U}[,"time":T]}
+        const int len = in ? 6 + int_len(s) + 22 + int_len(l) + 9 + int_len(u) + 1 + (tkind ? 8 + tlen : 0) + 1 : 0;
+
+        int x = len;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int y = __shfl_up_sync(0xffffffffu, x, d);
+            if (lane >= d) x += y;
+        }
+        if (lane == 31) warp_cnt[warp] = (unsigned long long)x;
+        __syncthreads();
+        unsigned long long wbase = 0, tile_total = 0;
+#pragma unroll
+        for (int w = 0; w < kThreads / 32; w++) {
+            const unsigned long long c = warp_cnt[w];
+            wbase += (w < warp) ? c : 0ull;
+            tile_total += c;
+        }
+        const unsigned long long tile_base = Scan::exclusive_prefix(scan, p.tile_status, p.epoch, tile, tile_total);
+        const int at = (int)wbase + x - len;
+        if (in) {
+            p.offsets[v] = (int)(tile_base + (unsigned long long)at);
+            char *d = buf + at;
+            d += put_lit(d, "{\"sn\":", 6);
+            d += put_int(d, s);
+            d += put_lit(d, ",\"trackView\":{\"level\":", 22);
+            d += put_int(d, l);
+            d += put_lit(d, ",\"urlId\":", 9);
+            d += put_int(d, u);
+            *d++ = '}';
+            if (tkind) {
+                d += put_lit(d, ",\"time\":", 8);
+                if (tkind == 1) {
+                    d += put_lit(d, "null", 4);
+                } else if (sd.digits == 0) {
+                    *d++ = '0';
+                } else {
+                    if (tneg) *d++ = '-';
+                    d += js_number_write(sd, d);
+                }
+            }
+            *d++ = '}';
+        }
+        if (tile == p.n_tiles - 1 && tid == 0) {
+            const unsigned long long total = tile_base + tile_total;
+            p.offsets[p.n] = (int)total;
+            p.result->total_hits = (long long)total;
+            p.result->overflow = total > 0x7fffffffull ? 1 : 0;
+        }
+        __syncthreads();
+        for (int i = tid; i < (int)tile_total; i += kThreads) {   // coalesced copy of the tile's characters
+            const long long o = (long long)tile_base + i;
+            if (o < p.capacity) p.chars[o] = buf[i];
+        }
+        if (Scan::tile_done(p.ctr, p.n_tiles)) Scan::finish_batch(p.ctr, p.result, p.tslot);
+    }
+}
+
+// ---- parse: the text JSON.stringify(segmentView) produces -> columns ------------------------
+namespace {
+
+struct Text {
+    const char *s;
+    __device__ __forceinline__ int operator()(long long p) const { return (int)(unsigned char)s[p]; }
+};
+
+__device__ __forceinline__ bool eat(const Text &t, long long &q, long long lim, const char *lit, int n)
+{
+    if (q + n > lim) return false;
+    for (int i = 0; i < n; i++)
+        if (t(q + i) != (int)(unsigned char)lit[i]) return false;
+    q += n;
+    return true;
+}
+
+// A JSON number that must be an int32 (sn, level, urlId columns are int32).
+__device__ __forceinline__ int eat_int(const Text &t, long long &q, long long lim, int *out)
+{
+    const JsonNumber n = scan_json_number(t, q, lim);
+    if (n.length == 0) return HLSMAP_JSON_MALFORMED;
+    q += n.length;
+    double x = 0.0;
+    if (!json_number_to_double(n, &x)) return HLSMAP_JSON_UNSUPPORTED;
+    if (!(x >= -2147483648.0 && x <= 2147483647.0) || x != (double)(int)x) return HLSMAP_JSON_NOT_INT32;
+    *out = (int)x;
+    return HLSMAP_JSON_OK;
+}
+
+}  // namespace
+
+__global__ void __launch_bounds__(256)
+view_from_json_kernel(const JsonReadParams p)
+{
+    const long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= p.n) return;
+    const Text t{p.chars};
+    long long q = p.offsets[v];
+    const long long lim = p.offsets[v + 1];
+    int sn = 0, level = 0, url_id = 0, st = HLSMAP_JSON_OK;
+    unsigned flags = 0;
+    double time = __longlong_as_double(0x7ff8000000000000ll);
+    bool first = true;
+    do {
+        if (!eat(t, q, lim, "{", 1)) {
+            st = HLSMAP_JSON_MALFORMED;
+            break;
+        }
+        if (eat(t, q, lim, "\"sn\":", 5)) {
+            if ((st = eat_int(t, q, lim, &sn))) break;
+            flags |= HLSMAP_JSON_HAS_SN;
+            first = false;
+        }
+        if (eat(t, q, lim, first ? "\"trackView\":{" : ",\"trackView\":{", first ? 13 : 14)) {
+            flags |= HLSMAP_JSON_HAS_TRACKVIEW;
+            first = false;
+            bool inner_first = true;
+            if (eat(t, q, lim, "\"level\":", 8)) {
+                if ((st = eat_int(t, q, lim, &level))) break;
+                flags |= HLSMAP_JSON_HAS_LEVEL;
+                inner_first = false;
+            }
+            if (eat(t, q, lim, inner_first ? "\"urlId\":" : ",\"urlId\":", inner_first ? 8 : 9)) {
+                if ((st = eat_int(t, q, lim, &url_id))) break;
+                flags |= HLSMAP_JSON_HAS_URLID;
+            }
+            if (!eat(t, q, lim, "}", 1)) {
+                st = HLSMAP_JSON_MALFORMED;
+                break;
+            }
+        }
+        if (eat(t, q, lim, first ? "\"time\":" : ",\"time\":", first ? 7 : 8)) {
+            flags |= HLSMAP_JSON_HAS_TIME;
+            if (eat(t, q, lim, "null", 4)) {
+                flags |= HLSMAP_JSON_TIME_NULL;
+            } else {
+                const JsonNumber n = scan_json_number(t, q, lim);
+                if (n.length == 0) {
+                    st = HLSMAP_JSON_MALFORMED;
+                    break;
+                }
+                q += n.length;
+                if (!json_number_to_double(n, &time)) {
+                    st = HLSMAP_JSON_UNSUPPORTED;
+                    break;
+                }
+            }
+        }
+        if (!eat(t, q, lim, "}", 1) || q != lim) st = HLSMAP_JSON_MALFORMED;
+    } while (false);
+    p.sn[v] = sn;
+    p.level[v] = level;
+    p.url_id[v] = url_id;
+    p.time[v] = time;
+    p.flags[v] = (unsigned char)flags;
+    p.status[v] = (unsigned char)st;
+}
+
+int view_to_json_max_grid()
+{
+    static int grid = 0;
+    if (!grid) {
+        int dev = 0, sms = 0, per_sm = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, view_to_json_kernel, kThreads, 0) != cudaSuccess ||
+            per_sm < 1)
+            per_sm = 1;
+        grid = per_sm * (sms > 0 ? sms : 148);
+    }
+    return grid;
+}
+
+cudaError_t launch_view_to_json(const JsonWriteParams &p, int grid, cudaStream_t s)
+{
+    view_to_json_kernel<<<grid, kThreads, 0, s>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_view_from_json(const JsonReadParams &p, cudaStream_t s)
+{
+    if (p.n <= 0) return cudaSuccess;
+    view_from_json_kernel<<<(unsigned)((p.n + 255) / 256), 256, 0, s>>>(p);
+    return cudaGetLastError();
+}
+
+}  // namespace hlsmap

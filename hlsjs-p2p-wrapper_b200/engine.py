@@ -69,6 +69,31 @@ class Context:
     def upload(self, tables: FragmentTables):
         return DeviceMap(self, tables)
 
+    # ---- JSON form of views ---------------------------------------------
+    def view_to_json(self, level, url_id, sn, time=None):
+        """JSON.stringify of n SegmentViews -> (offsets int32[n+1], chars uint8[total])."""
+        level, url_id, sn = _arr(level, np.int32), _arr(url_id, np.int32), _arr(sn, np.int32)
+        time = None if time is None else _arr(time, np.float64)
+        n = len(sn)
+        offsets = np.zeros(n + 1, np.int32)
+        chars = np.empty(max(104 * n, 16), np.uint8)
+        total = ctypes.c_int64(0)
+        N.check(self._lib.hlsmap_view_to_json(self._h, n, _ptr(level), _ptr(url_id), _ptr(sn), _ptr(time),
+                                              _ptr(offsets), _ptr(chars), len(chars), ctypes.byref(total)))
+        return offsets, chars[:total.value].copy()
+
+    def view_from_json(self, chars, offsets):
+        """Texts in the shape JSON.stringify(segmentView) gives -> dict of columns, flags, status."""
+        chars = np.frombuffer(chars, np.uint8) if isinstance(chars, (bytes, bytearray)) else _arr(chars, np.uint8)
+        offsets = _arr(offsets, np.int32)
+        n = len(offsets) - 1
+        out = dict(level=np.empty(n, np.int32), url_id=np.empty(n, np.int32), sn=np.empty(n, np.int32),
+                   time=np.empty(n, np.float64), flags=np.empty(n, np.uint8), status=np.empty(n, np.uint8))
+        N.check(self._lib.hlsmap_view_from_json(self._h, n, _ptr(chars) if len(chars) else None, _ptr(offsets),
+                                                _ptr(out["level"]), _ptr(out["url_id"]), _ptr(out["sn"]),
+                                                _ptr(out["time"]), _ptr(out["flags"]), _ptr(out["status"])))
+        return out
+
     # ---- media playlists in text form (hlsmap_parse_m3u8; SURVEY 8 row f2) ----------------
     @staticmethod
     def _text_args(text, text_off):

@@ -292,3 +292,19 @@ def m3u8_block(seed=9, n_tracks=1000, n_frag=800):
     out[:, len(head):len(head) + n_frag * len(line)] = rows.reshape(n_tracks, -1)
     out[:, per - len(tail):] = np.frombuffer(tail, np.uint8)
     return out.reshape(-1), np.arange(n_tracks + 1, dtype=np.int64) * per
+
+
+def sample_doubles(n, seed):
+    """Finite doubles of every kind Number::toString lays out differently (any exponent, playlist
+    times, powers of two, subnormals, the classic hard cases), some negated."""
+    rng = np.random.default_rng(seed)
+    parts = [rng.integers(0, 2 ** 63, n // 4, dtype=np.int64).view(np.float64),          # any exponent
+             rng.integers(0, 10 ** 8, n // 4) / 1000.0,                                    # playlist times
+             rng.integers(0, 86400 * 1024, n // 4) / 1024.0 + rng.integers(0, 1000, n // 4) * 1e-7,
+             np.ldexp(1.0, rng.integers(-1074, 1024, n // 8)),                             # powers of two
+             rng.integers(0, 2 ** 52, n // 8, dtype=np.int64).view(np.float64),            # subnormals
+             np.asarray([0.1 + 0.2, 1e21, 1e-7, 123e-20, 2.0 ** -24, 5e-324, 1.7976931348623157e308, 1e20,
+                         1e-6, 999999999999999900000.0, 9007199254740993.0, 4.35, 0.000001, 1.5e300])]
+    x = np.concatenate(parts)
+    x = x[np.isfinite(x)]
+    return np.concatenate([x, -x[:1000]])

@@ -240,6 +240,44 @@ int hlsmap_get_next_segment_view(hlsmap_map *map, int64_t n, const int32_t *play
                                  const int32_t *level, const int32_t *sn, int32_t *sn_out,
                                  double *time_out, uint8_t *found, uint8_t *status);
 
+/* ---- JSON form of a SegmentView (test/segment-view.js:5-11) ------------------ */
+/* JSON.stringify(segmentView): the object the constructor built (segment-view.js:22-26 -- sn, then
+ * trackView = TrackView{level, urlId} (track-view.js:6-9), then time) walked in property order,
+ *     {"sn":25,"trackView":{"level":1,"urlId":0},"time":12.5}
+ * numbers printed by ECMAScript Number::toString (shortest digits that read back as the same
+ * double, four layouts by exponent), a NaN / +-Infinity time printed as null, and -- for a view
+ * with no time (time == NULL here), e.g. one made by fromArrayBuffer -- the property left out.
+ * offsets [n + 1] out; chars [capacity] out; *total = characters needed (HLSMAP_ERR_CAPACITY when
+ * capacity is smaller; offsets are valid then).  At most 104 characters per view. */
+int hlsmap_view_to_json_dev(hlsmap_ctx *ctx, int64_t n, const int32_t *d_level, const int32_t *d_url_id,
+                            const int32_t *d_sn, const double *d_time, int32_t *d_offsets, char *d_chars,
+                            int64_t capacity, void *stream, int64_t *total);
+int hlsmap_view_to_json(hlsmap_ctx *ctx, int64_t n, const int32_t *level, const int32_t *url_id,
+                        const int32_t *sn, const double *time, int32_t *offsets, char *chars,
+                        int64_t capacity, int64_t *total);
+
+/* new SegmentView(JSON.parse(text)) for texts of the shape JSON.stringify gives a SegmentView (keys
+ * in constructor order, each optional, no white space).  flags[i] says which properties were there;
+ * a missing one leaves 0 / NaN in its column, as `undefined` has no column value.  status[i]:
+ * OK, MALFORMED (not that shape), UNSUPPORTED (a number the exact converter does not cover: decimal
+ * exponent beyond +19 / -38 after 19 digits), NOT_INT32 (sn / level / urlId not an int32). */
+#define HLSMAP_JSON_OK 0
+#define HLSMAP_JSON_MALFORMED 1
+#define HLSMAP_JSON_UNSUPPORTED 2
+#define HLSMAP_JSON_NOT_INT32 3
+#define HLSMAP_JSON_HAS_SN 1
+#define HLSMAP_JSON_HAS_TRACKVIEW 2
+#define HLSMAP_JSON_HAS_LEVEL 4
+#define HLSMAP_JSON_HAS_URLID 8
+#define HLSMAP_JSON_HAS_TIME 16
+#define HLSMAP_JSON_TIME_NULL 32
+int hlsmap_view_from_json_dev(hlsmap_ctx *ctx, int64_t n, const char *d_chars, const int32_t *d_offsets,
+                              int32_t *d_level, int32_t *d_url_id, int32_t *d_sn, double *d_time,
+                              uint8_t *d_flags, uint8_t *d_status, void *stream);
+int hlsmap_view_from_json(hlsmap_ctx *ctx, int64_t n, const char *chars, const int32_t *offsets,
+                          int32_t *level, int32_t *url_id, int32_t *sn, double *time, uint8_t *flags,
+                          uint8_t *status);
+
 /* ---- media playlists (M3U8 text) -> fragment tables --------------------- */
 /* The step BEFORE the mapping layer.  The reference never parses a playlist itself: hls.js does
  * (package.json:34, "hls.js": "0.5.46", absent from the reference checkout), and media-map.js:28,

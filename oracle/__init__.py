@@ -226,3 +226,34 @@ def parse_m3u8(text, text_off, track_state=None, threads=1):
     fn(ctypes.c_int32(t), _p(state), _p(text), _p(text_off), _p(track_off), _p(live), _p(sn), _p(start), _p(dur),
        ctypes.c_int(threads))
     return dict(track_off=track_off, live=live[:t], start=start, sn=sn, duration=dur, bad=bad)
+
+
+def js_number_to_string(x):
+    """ECMAScript Number::toString (restated with glibc printf/strtod, see mediamap_oracle.c)."""
+    buf = ctypes.create_string_buffer(64)
+    n = lib().oracle_js_number_to_string(ctypes.c_double(float(x)), buf)
+    return buf.raw[:n].decode()
+
+
+def view_to_json(level, url_id, sn, time=None):
+    level, url_id, sn = _c(level, np.int32), _c(url_id, np.int32), _c(sn, np.int32)
+    time = _c(time, np.float64)
+    n = len(sn)
+    offsets = np.zeros(n + 1, np.int32)
+    fn = lib().oracle_view_to_json
+    fn.restype = ctypes.c_int64
+    total = fn(ctypes.c_int64(n), _p(level), _p(url_id), _p(sn), _p(time), _p(offsets), None)
+    chars = np.empty(total, np.uint8)
+    fn(ctypes.c_int64(n), _p(level), _p(url_id), _p(sn), _p(time), _p(offsets), _p(chars))
+    return offsets, chars
+
+
+def view_from_json(chars, offsets):
+    chars = np.frombuffer(bytes(chars), np.uint8) if isinstance(chars, (bytes, bytearray)) else _c(chars, np.uint8)
+    offsets = _c(offsets, np.int32)
+    n = len(offsets) - 1
+    out = dict(level=np.empty(n, np.int32), url_id=np.empty(n, np.int32), sn=np.empty(n, np.int32),
+               time=np.empty(n, np.float64), flags=np.empty(n, np.uint8), status=np.empty(n, np.uint8))
+    lib().oracle_view_from_json(ctypes.c_int64(n), _p(chars), _p(offsets), _p(out["level"]), _p(out["url_id"]),
+                                _p(out["sn"]), _p(out["time"]), _p(out["flags"]), _p(out["status"]))
+    return out

@@ -605,3 +605,193 @@ int64_t oracle_parse_m3u8(int32_t n_tracks, const uint8_t *state, const unsigned
     }
     return bad ? -1 - track_off[n_tracks] : track_off[n_tracks];
 }
+
+/* ---- JSON form of a SegmentView (test/segment-view.js:5-11) -------------- */
+/* JSON.stringify walks the object the constructor built (segment-view.js:22-26, track-view.js:6-9):
+ *   {"sn":S,"trackView":{"level":L,"urlId":U},"time":T}
+ * Number::toString (ECMA-262 7.1.12.1): the fewest digits k whose decimal still denotes the same
+ * Number, then a layout chosen by the exponent.  Digits here come from glibc -- for k = 1..17 print
+ * the correctly rounded k-digit decimal and read it back; at a power of two the interval is lopsided
+ * and the k-digit decimal one step up can read back when the rounded one does not -- which is
+ * independent of the device's table-driven digit generation.  tests/test_json_host.py holds this
+ * against CPython's repr (David Gay's shortest digits) as a third opinion. */
+static int js_digits(double x, char *dg, int *n_out)
+{   /* x finite, > 0.  digits without trailing zeros into dg; *n_out: value = 0.d1d2.. * 10^n */
+    char buf[64], alt[64];
+    int p;
+    for (p = 1; p <= 17; p++) {
+        snprintf(buf, sizeof buf, "%.*e", p - 1, x);
+        if (strtod(buf, NULL) == x) break;
+        char d2[32];
+        int k2 = 0;
+        char *e2 = strchr(buf, 'e');
+        for (char *c = buf; c < e2; c++) if (*c != '.') d2[k2++] = *c;
+        int ex2 = atoi(e2 + 1), i = k2 - 1;
+        while (i >= 0 && d2[i] == '9') d2[i--] = '0';
+        int at = 0;
+        if (i < 0) {
+            at = snprintf(alt, sizeof alt, "1e%d", ex2 + 1);
+        } else {
+            d2[i]++;
+            alt[at++] = d2[0];
+            alt[at++] = '.';
+            for (int j = 1; j < k2; j++) alt[at++] = d2[j];
+            if (k2 == 1) alt[at++] = '0';
+            at += snprintf(alt + at, sizeof alt - (size_t)at, "e%d", ex2);
+        }
+        if (strtod(alt, NULL) == x) { memcpy(buf, alt, sizeof buf); break; }
+    }
+    char *e = strchr(buf, 'e');
+    int k = 0;
+    for (char *c = buf; c < e; c++) if (*c != '.') dg[k++] = *c;
+    while (k > 1 && dg[k - 1] == '0') k--;
+    *n_out = atoi(e + 1) + 1;
+    return k;
+}
+
+/* Number::toString for any double; returns the length (no terminator written beyond it). */
+int oracle_js_number_to_string(double x, char *out)
+{
+    if (x != x) return (int)sprintf(out, "NaN");
+    if (x == 0) return (int)sprintf(out, "0");
+    int at = 0;
+    if (x < 0) { out[at++] = '-'; x = -x; }
+    if (x > 1.7976931348623157e308) return at + (int)sprintf(out + at, "Infinity");
+    char dg[32];
+    int n, k = js_digits(x, dg, &n);
+    if (k <= n && n <= 21) {
+        for (int i = 0; i < k; i++) out[at++] = dg[i];
+        for (int i = k; i < n; i++) out[at++] = '0';
+    } else if (0 < n && n <= 21) {
+        for (int i = 0; i < n; i++) out[at++] = dg[i];
+        out[at++] = '.';
+        for (int i = n; i < k; i++) out[at++] = dg[i];
+    } else if (-6 < n && n <= 0) {
+        out[at++] = '0';
+        out[at++] = '.';
+        for (int i = 0; i < -n; i++) out[at++] = '0';
+        for (int i = 0; i < k; i++) out[at++] = dg[i];
+    } else {
+        out[at++] = dg[0];
+        if (k > 1) {
+            out[at++] = '.';
+            for (int i = 1; i < k; i++) out[at++] = dg[i];
+        }
+        at += sprintf(out + at, "e%c%d", n - 1 < 0 ? '-' : '+', n - 1 < 0 ? 1 - n : n - 1);
+    }
+    out[at] = 0;
+    return at;
+}
+
+/* Batch JSON.stringify.  time may be NULL (property undefined -> omitted); a non-finite time prints
+ * as null.  Call with chars == NULL to size.  Returns the total character count. */
+int64_t oracle_view_to_json(int64_t n, const int32_t *level, const int32_t *url_id, const int32_t *sn,
+                            const double *time, int32_t *offsets, char *chars)
+{
+    int64_t at = 0;
+    char tmp[160], num[40];
+    for (int64_t i = 0; i < n; i++) {
+        int len = sprintf(tmp, "{\"sn\":%d,\"trackView\":{\"level\":%d,\"urlId\":%d}", sn[i], level[i], url_id[i]);
+        if (time) {
+            double t = time[i];
+            if (t != t || t - t != 0) len += sprintf(tmp + len, ",\"time\":null");
+            else { oracle_js_number_to_string(t, num); len += sprintf(tmp + len, ",\"time\":%s", num); }
+        }
+        tmp[len++] = '}';
+        offsets[i] = (int32_t)at;
+        if (chars) memcpy(chars + at, tmp, (size_t)len);
+        at += len;
+    }
+    offsets[n] = (int32_t)at;
+    return at;
+}
+
+/* new SegmentView(JSON.parse(text)) for texts in the shape above (keys in constructor order, each
+ * optional, no white space).  flags: 1 sn, 2 trackView, 4 level, 8 urlId, 16 time, 32 time is null.
+ * status: 0 ok, 1 malformed, 3 an int column that is not an int32.  (Status 2, "number outside the
+ * exact converter", is the device's own limit: strtod has none, so the tests keep such inputs apart.) */
+static int json_num(const char **pp, const char *end, double *out)
+{   /* RFC 8259 number at *pp; advances; 0 if not a number */
+    const char *p = *pp, *q = p;
+    if (q < end && *q == '-') q++;
+    if (q >= end || *q < '0' || *q > '9') return 0;
+    if (*q == '0') { q++; if (q < end && *q >= '0' && *q <= '9') return 0; }
+    else while (q < end && *q >= '0' && *q <= '9') q++;
+    if (q < end && *q == '.') {
+        q++;
+        if (q >= end || *q < '0' || *q > '9') return 0;
+        while (q < end && *q >= '0' && *q <= '9') q++;
+    }
+    if (q < end && (*q == 'e' || *q == 'E')) {
+        q++;
+        if (q < end && (*q == '+' || *q == '-')) q++;
+        if (q >= end || *q < '0' || *q > '9') return 0;
+        while (q < end && *q >= '0' && *q <= '9') q++;
+    }
+    char buf[400];
+    size_t len = (size_t)(q - p);
+    if (len >= sizeof buf) return 0;
+    memcpy(buf, p, len);
+    buf[len] = 0;
+    *out = strtod(buf, NULL);
+    *pp = q;
+    return 1;
+}
+
+static int json_lit(const char **pp, const char *end, const char *lit)
+{
+    size_t k = strlen(lit);
+    if ((size_t)(end - *pp) < k || memcmp(*pp, lit, k) != 0) return 0;
+    *pp += k;
+    return 1;
+}
+
+static int json_int(const char **pp, const char *end, int32_t *out)
+{
+    double x;
+    if (!json_num(pp, end, &x)) return 1;
+    if (!(x >= -2147483648.0 && x <= 2147483647.0) || x != (double)(int32_t)x) return 3;
+    *out = (int32_t)x;
+    return 0;
+}
+
+void oracle_view_from_json(int64_t n, const char *chars, const int32_t *offsets, int32_t *level,
+                           int32_t *url_id, int32_t *sn, double *time, uint8_t *flags, uint8_t *status)
+{
+    for (int64_t i = 0; i < n; i++) {
+        const char *p = chars + offsets[i], *end = chars + offsets[i + 1];
+        int st = 0, first = 1;
+        unsigned f = 0;
+        sn[i] = level[i] = url_id[i] = 0;
+        time[i] = NAN;
+        do {
+            if (!json_lit(&p, end, "{")) { st = 1; break; }
+            if (json_lit(&p, end, "\"sn\":")) {
+                if ((st = json_int(&p, end, &sn[i]))) break;
+                f |= 1; first = 0;
+            }
+            if (json_lit(&p, end, first ? "\"trackView\":{" : ",\"trackView\":{")) {
+                int inner_first = 1;
+                f |= 2; first = 0;
+                if (json_lit(&p, end, "\"level\":")) {
+                    if ((st = json_int(&p, end, &level[i]))) break;
+                    f |= 4; inner_first = 0;
+                }
+                if (json_lit(&p, end, inner_first ? "\"urlId\":" : ",\"urlId\":")) {
+                    if ((st = json_int(&p, end, &url_id[i]))) break;
+                    f |= 8;
+                }
+                if (!json_lit(&p, end, "}")) { st = 1; break; }
+            }
+            if (json_lit(&p, end, first ? "\"time\":" : ",\"time\":")) {
+                f |= 16;
+                if (json_lit(&p, end, "null")) f |= 32;
+                else if (!json_num(&p, end, &time[i])) { st = 1; break; }
+            }
+            if (!json_lit(&p, end, "}") || p != end) st = 1;
+        } while (0);
+        if (st) { /* columns of a rejected text hold what was read before the failure */ }
+        flags[i] = (uint8_t)f;
+        status[i] = (uint8_t)st;
+    }
+}
