@@ -323,13 +323,130 @@ static napi_value ViewFormat(napi_env env, napi_callback_info info)
     return out;
 }
 
+/* createMapFromM3u8(ctx, {playlistBase, trackState, urlCount|null, text: Uint8Array, textOffset: BigInt64Array})
+ *   -> external.  `new MediaMap(hls)` for playlists still in text form: the bytes hls.js 0.5.46 would
+ *   have parsed (package.json:34) go to the GPU and the fragment tables are built there. */
+static napi_value CreateMapFromM3u8(napi_env env, napi_callback_info info)
+{
+    size_t argc = 2, npb, nts, nuc, ntx, nto;
+    napi_value argv[2], out;
+    void *ctx, *pb, *ts, *uc, *tx, *to;
+    CHECK(env, napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+    CHECK(env, napi_get_value_external(env, argv[0], &ctx));
+    if (!typed(env, field(env, argv[1], "playlistBase"), napi_int32_array, &pb, &npb) ||
+        !typed(env, field(env, argv[1], "trackState"), napi_uint8_array, &ts, &nts) ||
+        !typed(env, field(env, argv[1], "urlCount"), napi_int32_array, &uc, &nuc) ||
+        !typed(env, field(env, argv[1], "text"), napi_uint8_array, &tx, &ntx) ||
+        !typed(env, field(env, argv[1], "textOffset"), napi_bigint64_array, &to, &nto) || npb < 1 || nto != nts + 1) {
+        napi_throw_type_error(env, NULL, "createMapFromM3u8: expected typed-array inputs");
+        return NULL;
+    }
+    hlsmap_map *map = NULL;
+    hlsmap_ingest_result res;
+    if (hlsmap_map_create_from_m3u8((hlsmap_ctx *)ctx, (int32_t)(npb - 1), (const int32_t *)pb, (int32_t)nts,
+                                    (const uint8_t *)ts, (const int32_t *)uc, (const char *)tx, (const int64_t *)to,
+                                    &res, &map) != HLSMAP_OK)
+        return fail_hlsmap(env);
+    CHECK(env, napi_create_external(env, map, NULL, NULL, &out));
+    return out;
+}
+
+/* viewsFromFragments(map, playlist|null, level, index) -> {sn, time, status}
+ * (`new SegmentView({sn: frag.sn, trackView, time: frag.start})`, p2p-loader-generator.js:145-147, batched) */
+static napi_value ViewsFromFragments(napi_env env, napi_callback_info info)
+{
+    size_t argc = 4, n, m;
+    napi_value argv[4], out;
+    void *map, *pl, *lv, *ix, *sn, *tm, *st;
+    CHECK(env, napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+    CHECK(env, napi_get_value_external(env, argv[0], &map));
+    if (!typed(env, argv[1], napi_int32_array, &pl, &m) || !typed(env, argv[2], napi_int32_array, &lv, &n) ||
+        !typed(env, argv[3], napi_int32_array, &ix, &m) || m != n) {
+        napi_throw_type_error(env, NULL, "viewsFromFragments: expected Int32Array columns");
+        return NULL;
+    }
+    napi_value a_sn = new_typed(env, napi_int32_array, 4, n, &sn);
+    napi_value a_tm = new_typed(env, napi_float64_array, 8, n, &tm);
+    napi_value a_st = new_typed(env, napi_uint8_array, 1, n, &st);
+    if (!a_sn || !a_tm || !a_st) return NULL;
+    if (hlsmap_views_from_fragments((hlsmap_map *)map, (int64_t)n, (const int32_t *)pl, (const int32_t *)lv,
+                                    (const int32_t *)ix, (int32_t *)sn, (double *)tm, (uint8_t *)st) != HLSMAP_OK)
+        return fail_hlsmap(env);
+    CHECK(env, napi_create_object(env, &out));
+    napi_set_named_property(env, out, "sn", a_sn);
+    napi_set_named_property(env, out, "time", a_tm);
+    napi_set_named_property(env, out, "status", a_st);
+    return out;
+}
+
+/* viewToJson(ctx, level, urlId, sn, time|null) -> {offsets: Int32Array(n+1), chars: Uint8Array}
+ * (JSON.stringify(segmentView), test/segment-view.js:5-11, batched) */
+static napi_value ViewToJson(napi_env env, napi_callback_info info)
+{
+    size_t argc = 5, n, m;
+    napi_value argv[5], out;
+    void *ctx, *lv, *ui, *sn, *tm, *off, *chars;
+    int64_t total = 0;
+    CHECK(env, napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+    CHECK(env, napi_get_value_external(env, argv[0], &ctx));
+    if (!typed(env, argv[1], napi_int32_array, &lv, &n) || !typed(env, argv[2], napi_int32_array, &ui, &m) ||
+        m != n || !typed(env, argv[3], napi_int32_array, &sn, &m) || m != n ||
+        !typed(env, argv[4], napi_float64_array, &tm, &m) || (tm && m != n)) {
+        napi_throw_type_error(env, NULL, "viewToJson: expected Int32Array columns and a Float64Array or null");
+        return NULL;
+    }
+    napi_value a_off = new_typed(env, napi_int32_array, 4, n + 1, &off);
+    napi_value a_ch = new_typed(env, napi_uint8_array, 1, 104 * n + 1, &chars);
+    if (!a_off || !a_ch) return NULL;
+    if (hlsmap_view_to_json((hlsmap_ctx *)ctx, (int64_t)n, (const int32_t *)lv, (const int32_t *)ui,
+                            (const int32_t *)sn, (const double *)tm, (int32_t *)off, (char *)chars,
+                            (int64_t)(104 * n + 1), &total) != HLSMAP_OK)
+        return fail_hlsmap(env);
+    CHECK(env, napi_create_object(env, &out));
+    napi_set_named_property(env, out, "offsets", a_off);
+    napi_set_named_property(env, out, "chars", a_ch);
+    return out;
+}
+
+/* viewFromJson(ctx, chars: Uint8Array, offsets: Int32Array) -> {level, urlId, sn, time, flags, status}
+ * (new SegmentView(JSON.parse(text)), batched) */
+static napi_value ViewFromJson(napi_env env, napi_callback_info info)
+{
+    size_t argc = 3, n, nc;
+    napi_value argv[3], out;
+    void *ctx, *ch, *off, *lv, *ui, *sn, *tm, *fl, *st;
+    CHECK(env, napi_get_cb_info(env, info, &argc, argv, NULL, NULL));
+    CHECK(env, napi_get_value_external(env, argv[0], &ctx));
+    if (!typed(env, argv[1], napi_uint8_array, &ch, &nc) || !typed(env, argv[2], napi_int32_array, &off, &n) || n < 1) {
+        napi_throw_type_error(env, NULL, "viewFromJson: expected a Uint8Array and an Int32Array of offsets");
+        return NULL;
+    }
+    n -= 1;
+    napi_value a_lv = new_typed(env, napi_int32_array, 4, n, &lv), a_ui = new_typed(env, napi_int32_array, 4, n, &ui);
+    napi_value a_sn = new_typed(env, napi_int32_array, 4, n, &sn), a_tm = new_typed(env, napi_float64_array, 8, n, &tm);
+    napi_value a_fl = new_typed(env, napi_uint8_array, 1, n, &fl), a_st = new_typed(env, napi_uint8_array, 1, n, &st);
+    if (!a_lv || !a_ui || !a_sn || !a_tm || !a_fl || !a_st) return NULL;
+    if (hlsmap_view_from_json((hlsmap_ctx *)ctx, (int64_t)n, (const char *)ch, (const int32_t *)off, (int32_t *)lv,
+                              (int32_t *)ui, (int32_t *)sn, (double *)tm, (uint8_t *)fl, (uint8_t *)st) != HLSMAP_OK)
+        return fail_hlsmap(env);
+    CHECK(env, napi_create_object(env, &out));
+    napi_set_named_property(env, out, "level", a_lv);
+    napi_set_named_property(env, out, "urlId", a_ui);
+    napi_set_named_property(env, out, "sn", a_sn);
+    napi_set_named_property(env, out, "time", a_tm);
+    napi_set_named_property(env, out, "flags", a_fl);
+    napi_set_named_property(env, out, "status", a_st);
+    return out;
+}
+
 static napi_value Init(napi_env env, napi_value exports)
 {
     static const struct { const char *name; napi_callback fn; } table[] = {
         {"createContext", CreateContext}, {"createMap", CreateMap}, {"destroyMap", DestroyMap},
         {"getSegmentList", GetSegmentList}, {"getSegmentDuration", GetSegmentDuration},
         {"getTrackList", GetTrackList}, {"viewPack", ViewPack}, {"viewUnpack", ViewUnpack},
-        {"viewIsEqual", ViewIsEqual}, {"viewFormat", ViewFormat},
+        {"viewIsEqual", ViewIsEqual}, {"viewFormat", ViewFormat}, {"createMapFromM3u8", CreateMapFromM3u8},
+        {"viewsFromFragments", ViewsFromFragments}, {"viewToJson", ViewToJson}, {"viewFromJson", ViewFromJson},
     };
     for (size_t i = 0; i < sizeof table / sizeof table[0]; i++) {
         napi_value fn;
