@@ -1636,6 +1636,7 @@ int hlsmap_view_from_json_dev(hlsmap_ctx *ctx, int64_t n, const char *d_chars, c
     JsonReadParams p{};
     p.n = n;
     p.chars = d_chars;
+    p.vec_ok = ((uintptr_t)d_chars & 15) == 0;
     p.offsets = d_offsets;
     p.level = d_level;
     p.url_id = d_url_id;

@@ -186,6 +186,7 @@ struct JsonWriteParams {
 };
 struct JsonReadParams {
     long long n;
+    int vec_ok;                  // chars is 16-byte aligned
     const char *chars;
     const int *offsets;
     int *level, *url_id, *sn;

@@ -29,17 +29,17 @@
 namespace hlsmap {
 namespace {
 
-constexpr int kThreads = kIngestThreads;
-constexpr int kTile = kIngestTileBytes;       // bytes of text per tile
-constexpr int kBytesPerThread = kTile / kThreads;  // 128
-constexpr int kGroups = kBytesPerThread / 32;      // '#' masks per thread, one per 32 bytes
-constexpr int kCap = kThreads * 8;            // candidates classified per round
-constexpr int kRoundBytes = kCap;             // dense tiles: text bytes per round
-constexpr int kRounds = kTile / kRoundBytes;
-constexpr int kThreadsPerRound = kRoundBytes / kBytesPerThread;
-constexpr int kTrackStage = 260;              // text offsets staged per tile
-constexpr int kPerThread = kCap / kThreads;   // 8
+constexpr int kThreads = kIngestThreads;          // 128: four warps
+constexpr int kTile = kIngestTileBytes;           // bytes of text per tile
 constexpr int kWarps = kThreads / 32;
+constexpr int kWarpBytes = kTile / kWarps;        // 4096: the span a warp owns
+constexpr int kLaneBytes = kWarpBytes / 32;       // 128
+constexpr int kGroups = kLaneBytes / 32;          // '#' masks per lane, one per 32 bytes
+constexpr int kWarpCap = 256;                     // candidates a warp classifies per round
+constexpr int kRoundBytes = kWarpCap;             // dense spans: text bytes per round
+constexpr int kRounds = kWarpBytes / kRoundBytes;
+constexpr int kLanesPerRound = kRoundBytes / kLaneBytes;
+constexpr int kTrackStage = 130;                  // text offsets staged per tile
 using Scan = TileScan<kThreads>;
 
 enum TokKind { kTokNone = 0, kTokFrag = 1, kTokSeq = 2, kTokEnd = 3, kTokLine = 4, kTokInfNaN = 5 };
@@ -312,79 +312,75 @@ struct TrackOffsets {
     }
 };
 
+// Shared state.  A tile is cut into one 4 KB span per warp; between the few CTA-wide barriers a
+// warp works on its own span with its own lists, so warps never wait for each other's parsing.
+struct WarpShared {
+    unsigned short cpos[kWarpCap];   // tile-relative position of each candidate of the round
+    unsigned cmeta[kWarpCap];        // kind | fragments of the warp before it << 3 | tags before it << 16
+    long long cbits[kWarpCap];       // duration bits / sequence number
+};
 struct Shared {
     Scan::Smem scan;
     __align__(16) unsigned char text[kTile + 48];   // + room for the word fetches of classify_fast
-    unsigned short cpos[kCap];          // tile-relative position of each candidate of the round
-    unsigned short cfpre[kCap];         // fragments of the tile before that candidate
     long long toff[kTrackStage];
-    unsigned short hpre[kThreads + 1];  // '#' bytes of the tile before each thread's span
-    unsigned wtot[kPerThread * kWarps]; // per (slot, warp): fragments | tags << 16
-    unsigned wpre[kPerThread * kWarps + 1];
-    int hash_warp[kWarps];
+    WarpShared w[kWarps];
+    unsigned wtot[kWarps];           // per warp: fragments | tags << 16
+    unsigned long long base[2];      // the tile's fragment / tag prefix, from the look-back
 };
 
-struct RoundRegs {
-    long long bits[kPerThread];
-    unsigned pre[kPerThread];   // exclusive (fragments | tags << 16) within the tile
-    unsigned char kind[kPerThread];
-};
-
-// One candidate of the round's list: its track, what the expression matches there, whether an
-// earlier match on the line hides it.  Kept out of line: the caller's loop is unrolled so that its
-// results stay in registers, and eight inlined copies of this would not fit the instruction cache.
-__device__ __noinline__ int classify_candidate(const IngestParams &p, Shared &sh, const TrackOffsets &toff, int t_lo,
-                                               int t_hi, long long lo, long long hi, int i, bool effects,
-                                               long long &bits)
+// One candidate: its track, what the expression matches there, whether an earlier match on the
+// line hides it.
+__device__ __forceinline__ int classify_candidate(const IngestParams &p, const Shared &sh, const TrackOffsets &toff,
+                                                  int t_lo, int t_hi, long long lo, long long hi, int pos_rel,
+                                                  bool effects, long long &bits)
 {
     const TextView v{p.text, sh.text, lo, hi};
     int kind = kTokNone;
     bits = 0;
-    {
-            const long long pos = lo + sh.cpos[i];
-            int a = t_lo, b = t_hi;               // last track whose text starts at or before pos
-            while (a < b) {
-                const int mid = (a + b + 1) >> 1;
-                if (toff(mid) <= pos) a = mid;
-                else b = mid - 1;
-            }
-            const long long tb = toff(a), te = toff(a + 1);
-            const bool parsed = p.state == nullptr || p.state[a] == HLSMAP_TRACK_PARSED;
-            if (parsed && pos < te) {
-                // bytes valid both in the tile's copy and in the track; a candidate in the tile's
-                // last bytes whose track runs on is left to the byte-wise classifier
-                const long long in_tile = hi - pos, in_track = te - pos;
-                Token t;
-                bool done = false;
-                if (in_track <= in_tile || in_tile >= 36) {
-                    const int limit = in_track < 36 ? (int)in_track : 36;
-                    done = classify_fast(sh.text, (int)sh.cpos[i], limit, limit == in_track, t);
-                }
-                if (!done) t = classify_at(v, pos, te);
-                bool live = t.kind != kTokNone;
-                if (live && pos > tb) {
-                    const int prev = v(pos - 1);
-                    if (prev != '\n' && prev != '\r') live = !hidden_by_earlier_match(p.text, tb, pos, te);
-                }
-                if (live) {
-                    kind = t.kind;
-                    bits = t.bits;
-                    if (effects && t.unsupported) atomicAdd(&p.out->n_unsupported, 1ull);
-                    if (effects && kind == kTokEnd) p.live[a] = 0;
-                }
-            }
+    const long long pos = lo + pos_rel;
+    int a = t_lo, b = t_hi;               // last track whose text starts at or before pos
+    while (a < b) {
+        const int mid = (a + b + 1) >> 1;
+        if (toff(mid) <= pos) a = mid;
+        else b = mid - 1;
+    }
+    const long long tb = toff(a), te = toff(a + 1);
+    const bool parsed = p.state == nullptr || p.state[a] == HLSMAP_TRACK_PARSED;
+    if (parsed && pos < te) {
+        // bytes valid both in the tile's copy and in the track; a candidate in the tile's last
+        // bytes whose track runs on is left to the byte-wise classifier
+        const long long in_tile = hi - pos, in_track = te - pos;
+        Token t;
+        bool done = false;
+        if (in_track <= in_tile || in_tile >= 36) {
+            const int limit = in_track < 36 ? (int)in_track : 36;
+            done = classify_fast(sh.text, pos_rel, limit, limit == in_track, t);
+        }
+        if (!done) t = classify_at(v, pos, te);
+        bool live = t.kind != kTokNone;
+        if (live && pos > tb) {
+            const int prev = v(pos - 1);
+            if (prev != '\n' && prev != '\r') live = !hidden_by_earlier_match(p.text, tb, pos, te);
+        }
+        if (live) {
+            kind = t.kind;
+            bits = t.bits;
+            if (effects && t.unsupported) atomicAdd(&p.out->n_unsupported, 1ull);
+            if (effects && kind == kTokEnd) p.live[a] = 0;
+        }
     }
     return kind;
 }
 
-// Builds the candidate list of one round (this thread's '#' bytes go to cpos[my_first...] when
-// my_first >= 0), classifies it and scans the fragment / tag flags.  Returns the round's totals
-// as fragments | tags << 16.
-__device__ unsigned classify_round(const IngestParams &p, Shared &sh, RoundRegs &rr, const TrackOffsets &toff,
-                                   int t_lo, int t_hi, long long lo, long long hi, const unsigned (&mask)[kGroups],
-                                   int my_first, int nc, unsigned running, bool effects)
+// Warp-wide: lists this warp's '#' bytes selected by `mine` lanes in text order, classifies them,
+// leaves kind / prefix / value per candidate in the warp's shared arrays.  Returns the round's
+// totals (fragments | tags << 16); `running` = the warp's totals of earlier rounds.
+__device__ __forceinline__ unsigned warp_classify(const IngestParams &p, Shared &sh, WarpShared &ws,
+                                                  const TrackOffsets &toff, int t_lo, int t_hi, long long lo,
+                                                  long long hi, const unsigned (&mask)[kGroups], int span_base,
+                                                  int my_first, int nc, unsigned running, bool effects)
 {
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int lane = threadIdx.x & 31;
     if (my_first >= 0) {
         int at = my_first;
 #pragma unroll
@@ -393,105 +389,148 @@ __device__ unsigned classify_round(const IngestParams &p, Shared &sh, RoundRegs 
             while (m) {
                 const int b = __ffs(m) - 1;
                 m &= m - 1;
-                sh.cpos[at++] = (unsigned short)(tid * kBytesPerThread + g * 32 + b);
+                ws.cpos[at++] = (unsigned short)(span_base + g * 32 + b);
             }
         }
     }
-    __syncthreads();
-#pragma unroll
-    for (int k = 0; k < kPerThread; k++) {
-        const int i = tid + k * kThreads;
+    __syncwarp();
+    unsigned run = 0;
+    const unsigned below = (1u << lane) - 1u;
+    for (int i0 = 0; i0 < nc; i0 += 32) {
+        const int i = i0 + lane;
         long long bits = 0;
-        const int kind = i < nc ? classify_candidate(p, sh, toff, t_lo, t_hi, lo, hi, i, effects, bits) : kTokNone;
-        rr.kind[k] = (unsigned char)kind;
-        rr.bits[k] = bits;
+        const int kind = i < nc ? classify_candidate(p, sh, toff, t_lo, t_hi, lo, hi, (int)ws.cpos[i], effects, bits)
+                                : kTokNone;
         const unsigned fb = __ballot_sync(0xffffffffu, kind == kTokFrag);
-        const unsigned tb2 = __ballot_sync(0xffffffffu, kind == kTokSeq);
-        const unsigned below = (1u << lane) - 1u;
-        rr.pre[k] = (unsigned)__popc(fb & below) | ((unsigned)__popc(tb2 & below) << 16);
-        if (lane == 0) sh.wtot[k * kWarps + warp] = (unsigned)__popc(fb) | ((unsigned)__popc(tb2) << 16);
-    }
-    __syncthreads();
-    if (warp == 0) {   // exclusive scan of the (slot, warp) totals, slot-major = text order
-        constexpr int E = kPerThread * kWarps / 32;
-        unsigned v[E], x = 0;
-#pragma unroll
-        for (int e = 0; e < E; e++) {
-            v[e] = sh.wtot[E * lane + e];
-            x += v[e];
+        const unsigned tb = __ballot_sync(0xffffffffu, kind == kTokSeq);
+        if (i < nc) {
+            const unsigned pre = running + run + ((unsigned)__popc(fb & below) | ((unsigned)__popc(tb & below) << 16));
+            ws.cmeta[i] = (unsigned)kind | ((pre & 0x1fffu) << 3) | (pre & 0xffff0000u);
+            ws.cbits[i] = bits;
         }
-        const unsigned mine = x;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const unsigned y = __shfl_up_sync(0xffffffffu, x, d);
-            if (lane >= d) x += y;
-        }
-        unsigned run = x - mine;
-#pragma unroll
-        for (int e = 0; e < E; e++) {
-            sh.wpre[E * lane + e] = run;
-            run += v[e];
-        }
-        if (lane == 31) sh.wpre[kPerThread * kWarps] = x;
+        run += (unsigned)__popc(fb) | ((unsigned)__popc(tb) << 16);
     }
-    __syncthreads();
-#pragma unroll
-    for (int k = 0; k < kPerThread; k++) {
-        const int i = tid + k * kThreads;
-        rr.pre[k] += sh.wpre[k * kWarps + warp] + running;
-        if (i < nc) sh.cfpre[i] = (unsigned short)(rr.pre[k] & 0xffffu);
-    }
-    const unsigned total = sh.wpre[kPerThread * kWarps];
-    __syncthreads();
-    return total;
+    __syncwarp();
+    return run;
 }
 
-// Writes what one classified round found: durations and sequence tags to their global slots,
-// and the fragment offset of every track whose text starts inside [b_lo, b_hi) of the tile.
-__device__ void emit_round(const IngestParams &p, Shared &sh, const RoundRegs &rr, const TrackOffsets &toff,
-                           int u0, int u1, long long lo, int nc, unsigned round_end, unsigned long long fbase,
-                           unsigned long long tbase, long long b_lo, long long b_hi)
+// Warp-wide: writes what warp_classify() left -- durations and sequence tags to their global slots,
+// and the fragment offset of every track whose text starts inside [b_lo, b_hi).
+__device__ __forceinline__ void warp_emit(const IngestParams &p, const WarpShared &ws, const TrackOffsets &toff,
+                                          int u0, int u1, long long lo, int nc, unsigned round_end,
+                                          unsigned long long fbase, unsigned long long tbase, long long b_lo,
+                                          long long b_hi)
 {
-    const int tid = threadIdx.x;
-#pragma unroll
-    for (int k = 0; k < kPerThread; k++) {
-        const int i = tid + k * kThreads;
-        if (i >= nc) continue;
-        const unsigned long long f = fbase + (rr.pre[k] & 0xffffu);
-        if (rr.kind[k] == kTokFrag) {
-            if ((long long)f < p.capacity) p.dur[f] = __longlong_as_double(rr.bits[k]);
-        } else if (rr.kind[k] == kTokSeq) {
-            const unsigned long long j = tbase + (rr.pre[k] >> 16);
+    const int lane = threadIdx.x & 31;
+    for (int i = lane; i < nc; i += 32) {
+        const unsigned meta = ws.cmeta[i];
+        const int kind = (int)(meta & 7u);
+        const unsigned long long f = fbase + ((meta >> 3) & 0x1fffu);
+        if (kind == kTokFrag) {
+            if ((long long)f < p.capacity) p.dur[f] = __longlong_as_double(ws.cbits[i]);
+        } else if (kind == kTokSeq) {
+            const unsigned long long j = tbase + (meta >> 16);
             if ((long long)j < p.tag_capacity) {
-                p.tag_pos[j] = lo + sh.cpos[i];
+                p.tag_pos[j] = lo + ws.cpos[i];
                 p.tag_frag[j] = (long long)f;
-                p.tag_val[j] = (int)rr.bits[k];
+                p.tag_val[j] = (int)ws.cbits[i];
             }
         }
     }
-    // tracks starting in this byte range: fragments before the first candidate at/after the start
-    for (int u = u0 + tid; u < u1; u += kThreads) {
+    for (int u = u0 + lane; u < u1; u += 32) {
         const long long b = toff(u);
         if (b < b_lo || b >= b_hi) continue;
         const long long rel = b - lo;
         int a = 0, z = nc;                       // first candidate with cpos >= rel
         while (a < z) {
             const int mid = (a + z) >> 1;
-            if ((long long)sh.cpos[mid] < rel) a = mid + 1;
+            if ((long long)ws.cpos[mid] < rel) a = mid + 1;
             else z = mid;
         }
-        const unsigned fp = a < nc ? (unsigned)sh.cfpre[a] : (round_end & 0xffffu);
+        const unsigned fp = a < nc ? ((ws.cmeta[a] >> 3) & 0x1fffu) : (round_end & 0xffffu);
         p.track_off[u] = (long long)(fbase + fp);
+    }
+}
+
+// Decoupled look-back over two status arrays at once, run by ONE warp (4 x 32 predecessors a
+// step, all eight loads in flight together) while the CTA's other warps wait at a barrier.
+__device__ void warp_lookback_pair(unsigned long long *status_f, unsigned long long *status_t, unsigned epoch, int tile,
+                                   unsigned long long agg_f, unsigned long long agg_t, unsigned long long &out_f,
+                                   unsigned long long &out_t)
+{
+    const int lane = threadIdx.x & 31;
+    constexpr int S = 4;
+    unsigned long long sum_f = 0, sum_t = 0;
+    if (tile > 0) {
+        int top_f = tile - 1, top_t = tile - 1;
+        bool done_f = false, done_t = false;
+        while (!(done_f && done_t)) {
+            unsigned long long wf[S], wt[S];
+#pragma unroll
+            for (int j = 0; j < S; j++) {
+                const int idf = top_f - (lane + 32 * j), idt = top_t - (lane + 32 * j);
+                wf[j] = (!done_f && idf >= 0) ? ld_relaxed_u64(&status_f[idf]) : 0ull;
+                wt[j] = (!done_t && idt >= 0) ? ld_relaxed_u64(&status_t[idt]) : 0ull;
+            }
+#pragma unroll
+            for (int a = 0; a < 2; a++) {
+                unsigned long long *status = a == 0 ? status_f : status_t;
+                const int top = a == 0 ? top_f : top_t;
+                if (a == 0 ? done_f : done_t) continue;
+                int my_first = 0x7fffffff;
+                unsigned long long val[S];
+#pragma unroll
+                for (int j = 0; j < S; j++) {
+                    const int d = lane + 32 * j, idx = top - d;
+                    unsigned long long w = a == 0 ? wf[j] : wt[j];
+                    bool is_prefix = true;         // idx < 0: the virtual tile -1 holds prefix 0
+                    val[j] = 0;
+                    if (idx >= 0) {
+                        while ((unsigned)(w >> 42) != (epoch & kEpochMask)) {
+                            __nanosleep(100);
+                            w = ld_relaxed_u64(&status[idx]);
+                        }
+                        val[j] = w & ((1ull << kValueBits) - 1ull);
+                        is_prefix = ((w >> kValueBits) & 3ull) == kStatePrefix;
+                    }
+                    if (is_prefix) my_first = min(my_first, d);
+                }
+                __syncwarp();
+#pragma unroll
+                for (int dd = 16; dd > 0; dd >>= 1) my_first = min(my_first, __shfl_xor_sync(0xffffffffu, my_first, dd));
+                unsigned long long c = 0;
+#pragma unroll
+                for (int j = 0; j < S; j++) c += (lane + 32 * j <= my_first) ? val[j] : 0ull;
+#pragma unroll
+                for (int dd = 16; dd > 0; dd >>= 1) c += __shfl_xor_sync(0xffffffffu, c, dd);
+                if (a == 0) {
+                    sum_f += c;
+                    done_f = my_first != 0x7fffffff;
+                    top_f -= 32 * S;
+                } else {
+                    sum_t += c;
+                    done_t = my_first != 0x7fffffff;
+                    top_t -= 32 * S;
+                }
+            }
+        }
+    }
+    out_f = sum_f;
+    out_t = sum_t;
+    if (lane == 0 && tile > 0) {
+        st_relaxed_u64(&status_f[tile], make_status(epoch, kStatePrefix, sum_f + agg_f));
+        st_relaxed_u64(&status_t[tile], make_status(epoch, kStatePrefix, sum_t + agg_t));
     }
 }
 
 }  // namespace
 
-__global__ void __launch_bounds__(kThreads, 1024 / kThreads)
+__global__ void __launch_bounds__(kThreads, 7)
 m3u8_scan_kernel(const IngestParams p)
 {
     __shared__ Shared sh;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    WarpShared &ws = sh.w[warp];
     for (;;) {
         const int tile = Scan::next_tile(sh.scan, p.ctr, p.tslot);
         if (tile >= p.n_tiles) break;
@@ -500,10 +539,11 @@ m3u8_scan_kernel(const IngestParams p)
         const bool last = tile == p.n_tiles - 1;
         const long long open_end = 0x7fffffffffffffffll;
 
-        // stage the tile (coalesced 16-byte pieces) and the text offsets of the tracks it touches
+        // stage the tile (each warp its own 4 KB span, coalesced 16-byte pieces) and the text
+        // offsets of the tracks the tile touches
 #pragma unroll
-        for (int j = 0; j < kBytesPerThread / 16; j++) {
-            const int piece = j * kThreads + tid;
+        for (int j = 0; j < kWarpBytes / 512; j++) {
+            const int piece = warp * (kWarpBytes / 16) + j * 32 + lane;
             const long long a = lo + (long long)piece * 16;
             uint4 w = make_uint4(0, 0, 0, 0);
             if (p.vec_ok && a + 16 <= p.n_bytes) {
@@ -521,14 +561,15 @@ m3u8_scan_kernel(const IngestParams p)
         const int n_staged = t_hi + 2 - t_lo < kTrackStage ? t_hi + 2 - t_lo : kTrackStage;
         for (int i = tid; i < n_staged; i += kThreads) sh.toff[i] = p.text_off[t_lo + i];
         const TrackOffsets toff{p.text_off, sh.toff, t_lo, n_staged};
-        __syncthreads();
+        __syncthreads();     // tokens may run from one warp's span into the next
 
-        // the '#' bytes of this thread's 128-byte span
+        // the '#' bytes of this lane's 128 bytes, and their rank within the warp's span
+        const int span_base = warp * kWarpBytes + lane * kLaneBytes;
         unsigned mask[kGroups];
         int cnt = 0;
 #pragma unroll
         for (int g = 0; g < kGroups; g++) {
-            const unsigned char *at = sh.text + tid * kBytesPerThread + g * 32;
+            const unsigned char *at = sh.text + span_base + g * 32;
             mask[g] = hash_mask16(*reinterpret_cast<const uint4 *>(at)) |
                       (hash_mask16(*reinterpret_cast<const uint4 *>(at + 16)) << 16);
             cnt += __popc(mask[g]);
@@ -539,58 +580,74 @@ m3u8_scan_kernel(const IngestParams p)
             const int y = __shfl_up_sync(0xffffffffu, x, d);
             if (lane >= d) x += y;
         }
-        if (lane == 31) sh.hash_warp[warp] = x;
+        const int before = x - cnt;
+        const int n_hash = __shfl_sync(0xffffffffu, x, 31);
+        const bool dense = n_hash > kWarpCap;      // warp-uniform
+
+        unsigned totals = 0;
+        if (!dense) {
+            totals = warp_classify(p, sh, ws, toff, t_lo, t_hi, lo, hi, mask, span_base, before, n_hash, 0u, true);
+        } else {
+            // a span dense with '#': rounds of 256 bytes (never more than kWarpCap candidates),
+            // classified twice -- now to count, after the look-back once more to write
+            for (int r = 0; r < kRounds; r++) {
+                const int r0 = __shfl_sync(0xffffffffu, before, r * kLanesPerRound);
+                const int r1n = __shfl_sync(0xffffffffu, before, ((r + 1) * kLanesPerRound) & 31);
+                const int r1 = r == kRounds - 1 ? n_hash : r1n;
+                const bool mine = lane / kLanesPerRound == r;
+                totals += warp_classify(p, sh, ws, toff, t_lo, t_hi, lo, hi, mask, span_base, mine ? before - r0 : -1,
+                                        r1 - r0, 0u, false);
+            }
+        }
+        if (lane == 0) sh.wtot[warp] = totals;
         __syncthreads();
-        int before = x - cnt, n_hash = 0;
+        unsigned tile_totals = 0, warp_before = 0;
 #pragma unroll
         for (int w = 0; w < kWarps; w++) {
-            const int c = sh.hash_warp[w];
-            before += w < warp ? c : 0;
-            n_hash += c;
+            const unsigned c = sh.wtot[w];
+            warp_before += w < warp ? c : 0u;
+            tile_totals += c;
         }
-
-        RoundRegs rr;
-        unsigned long long fbase = 0, tbase = 0;
-        unsigned totals = 0;
-        if (n_hash <= kCap) {
-            // the usual case: one round, classified once, results kept in registers
-            totals = classify_round(p, sh, rr, toff, t_lo, t_hi, lo, hi, mask, before, n_hash, 0u, true);
-            Scan::publish_aggregate(p.status_f, p.epoch, tile, totals & 0xffffu);
-            Scan::publish_aggregate(p.status_t, p.epoch, tile, totals >> 16);
-            Scan::wait_prefix_pair(sh.scan, p.status_f, p.status_t, p.epoch, tile, totals & 0xffffu, totals >> 16,
-                                   fbase, tbase);
-            emit_round(p, sh, rr, toff, u0, u1, lo, n_hash, totals, fbase, tbase, lo, last ? open_end : hi);
-        } else {
-            // a tile dense with '#': rounds of 2 KB of text (never more than kCap candidates),
-            // classified twice -- once to count, once more to write
-            sh.hpre[tid] = (unsigned short)before;
-            if (tid == 0) sh.hpre[kThreads] = (unsigned short)n_hash;
-            __syncthreads();
-            for (int r = 0; r < kRounds; r++) {
-                const bool mine = tid / kThreadsPerRound == r;
-                const int r0 = sh.hpre[r * kThreadsPerRound], r1 = sh.hpre[(r + 1) * kThreadsPerRound];
-                totals += classify_round(p, sh, rr, toff, t_lo, t_hi, lo, hi, mask, mine ? before - r0 : -1, r1 - r0,
-                                         0u, false);
+        if (warp == 0) {
+            if (lane == 0) {
+                const unsigned long long af = tile_totals & 0xffffu, at = tile_totals >> 16;
+                st_relaxed_u64(&p.status_f[tile], tile == 0 ? make_status(p.epoch, kStatePrefix, af)
+                                                            : make_status(p.epoch, kStateAggregate, af));
+                st_relaxed_u64(&p.status_t[tile], tile == 0 ? make_status(p.epoch, kStatePrefix, at)
+                                                            : make_status(p.epoch, kStateAggregate, at));
             }
-            Scan::publish_aggregate(p.status_f, p.epoch, tile, totals & 0xffffu);
-            Scan::publish_aggregate(p.status_t, p.epoch, tile, totals >> 16);
-            Scan::wait_prefix_pair(sh.scan, p.status_f, p.status_t, p.epoch, tile, totals & 0xffffu, totals >> 16,
-                                   fbase, tbase);
+            unsigned long long bf = 0, bt = 0;
+            warp_lookback_pair(p.status_f, p.status_t, p.epoch, tile, tile_totals & 0xffffu, tile_totals >> 16, bf, bt);
+            if (lane == 0) {
+                sh.base[0] = bf;
+                sh.base[1] = bt;
+                if (last) {
+                    p.out->n_fragments = bf + (tile_totals & 0xffffu);
+                    p.out->n_tags = bt + (tile_totals >> 16);
+                }
+            }
+        }
+        __syncthreads();
+        const unsigned long long fbase = sh.base[0] + (warp_before & 0xffffu);
+        const unsigned long long tbase = sh.base[1] + (warp_before >> 16);
+        const long long w_lo = lo + (long long)warp * kWarpBytes;
+        const long long w_hi = warp == kWarps - 1 ? (last ? open_end : lo + kTile) : w_lo + kWarpBytes;
+        if (!dense) {
+            warp_emit(p, ws, toff, u0, u1, lo, n_hash, totals, fbase, tbase, w_lo, w_hi);
+        } else {
             unsigned running = 0;
             for (int r = 0; r < kRounds; r++) {
-                const bool mine = tid / kThreadsPerRound == r;
-                const int r0 = sh.hpre[r * kThreadsPerRound], r1 = sh.hpre[(r + 1) * kThreadsPerRound];
-                running += classify_round(p, sh, rr, toff, t_lo, t_hi, lo, hi, mask, mine ? before - r0 : -1, r1 - r0,
-                                          running, true);
-                const long long b_lo = lo + (long long)r * kRoundBytes;
-                const long long b_hi = r == kRounds - 1 ? (last ? open_end : hi) : b_lo + kRoundBytes;
-                emit_round(p, sh, rr, toff, u0, u1, lo, r1 - r0, running, fbase, tbase, b_lo, b_hi);
-                __syncthreads();
+                const int r0 = __shfl_sync(0xffffffffu, before, r * kLanesPerRound);
+                const int r1n = __shfl_sync(0xffffffffu, before, ((r + 1) * kLanesPerRound) & 31);
+                const int r1 = r == kRounds - 1 ? n_hash : r1n;
+                const bool mine = lane / kLanesPerRound == r;
+                running += warp_classify(p, sh, ws, toff, t_lo, t_hi, lo, hi, mask, span_base, mine ? before - r0 : -1,
+                                         r1 - r0, running, true);
+                const long long b_lo = w_lo + (long long)r * kRoundBytes;
+                const long long b_hi = r == kRounds - 1 ? w_hi : b_lo + kRoundBytes;
+                warp_emit(p, ws, toff, u0, u1, lo, r1 - r0, running, fbase, tbase, b_lo, b_hi);
+                __syncwarp();
             }
-        }
-        if (last && tid == 0) {
-            p.out->n_fragments = fbase + (totals & 0xffffu);
-            p.out->n_tags = tbase + (totals >> 16);
         }
     }
 }

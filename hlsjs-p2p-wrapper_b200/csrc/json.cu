@@ -155,9 +155,16 @@ view_to_json_kernel(const JsonWriteParams p)
 // ---- parse: the text JSON.stringify(segmentView) produces -> columns ------------------------
 namespace {
 
+// The characters of a CTA's 256 texts: their shared-memory copy when it was staged (positions are
+// absolute offsets into the batch's character buffer), global memory otherwise.
 struct Text {
-    const char *s;
-    __device__ __forceinline__ int operator()(long long p) const { return (int)(unsigned char)s[p]; }
+    const char *g;
+    const char *s;      // shared copy of [lo, hi), or nullptr
+    long long lo;
+    __device__ __forceinline__ int operator()(long long p) const
+    {
+        return (int)(unsigned char)(s ? s[p - lo] : g[p]);
+    }
 };
 
 __device__ __forceinline__ bool eat(const Text &t, long long &q, long long lim, const char *lit, int n)
@@ -184,12 +191,34 @@ __device__ __forceinline__ int eat_int(const Text &t, long long &q, long long li
 
 }  // namespace
 
+constexpr int kParseStage = kThreads * kMaxChars;   // what 256 canonical texts can need
+
 __global__ void __launch_bounds__(256)
 view_from_json_kernel(const JsonReadParams p)
 {
-    const long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    __shared__ __align__(16) char stage[kParseStage + 16];
+    const long long v0 = (long long)blockIdx.x * blockDim.x, v = v0 + threadIdx.x;
+    // the CTA's texts are one contiguous run of characters: copy it in with coalesced loads
+    const long long v1 = v0 + blockDim.x < p.n ? v0 + blockDim.x : p.n;
+    const long long c_lo = p.offsets[v0], c_hi = p.offsets[v1];
+    const long long a_lo = c_lo & ~15ll;                 // aligned start; never before the buffer's own start
+    const bool staged = p.vec_ok && c_hi - a_lo <= kParseStage;
+    if (staged) {
+        for (long long o = a_lo + 16ll * threadIdx.x; o < c_hi; o += 16ll * blockDim.x) {
+            uint4 w;
+            if (o + 16 <= c_hi) {
+                w = *reinterpret_cast<const uint4 *>(p.chars + o);
+            } else {
+                char tmp[16];
+                for (int k = 0; k < 16; k++) tmp[k] = o + k < c_hi ? p.chars[o + k] : 0;
+                memcpy(&w, tmp, 16);
+            }
+            *reinterpret_cast<uint4 *>(stage + (o - a_lo)) = w;
+        }
+    }
+    __syncthreads();
     if (v >= p.n) return;
-    const Text t{p.chars};
+    const Text t{p.chars, staged ? stage : nullptr, a_lo};
     long long q = p.offsets[v];
     const long long lim = p.offsets[v + 1];
     int sn = 0, level = 0, url_id = 0, st = HLSMAP_JSON_OK;
