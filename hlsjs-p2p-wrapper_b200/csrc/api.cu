@@ -1723,7 +1723,6 @@ int ingest_core(hlsmap_ctx *ctx, int32_t n_tracks, const uint8_t *d_state, const
     int64_t tag_cap = (int64_t)n_tracks * 2 + 1024;
     IngestCounters h{};
     int launches = 0;
-    DevBuf scratch;
     const bool fill = d_start && d_sn && d_dur;
     if (!fill) capacity = 0;
     for (int attempt = 0; attempt < 2; attempt++) {
@@ -1737,9 +1736,10 @@ int ingest_core(hlsmap_ctx *ctx, int32_t n_tracks, const uint8_t *d_state, const
         size_t o_tv = align256(o_tf + 8 * (size_t)tag_cap);
         size_t o_d0 = align256(o_tv + 4 * (size_t)tag_cap);
         size_t total = align256(o_d0 + 8 * (size_t)(n_tracks + 1));
-        int r = scratch.alloc(total);
+        void *sp = nullptr;               // grow-only context scratch: no allocation after the first call
+        int r = ensure_slot(ctx, kSlots - 1, (int64_t)total, &sp);
         if (r) return r;
-        char *b = (char *)scratch.p;
+        char *b = (char *)sp;
         CK(cudaMemsetAsync(b, 0, o_tp, s));
         if (n_tracks) CK(cudaMemsetAsync(d_live, 1, (size_t)n_tracks, s));
         CK(cudaMemsetAsync(d_track_off, 0, 8 * (size_t)(n_tracks + 1), s));

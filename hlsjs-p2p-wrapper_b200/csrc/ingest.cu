@@ -721,7 +721,10 @@ m3u8_assemble_kernel(const AssembleParams p)
         if (next_tag > off + c + n - 1) {          // numbering runs straight through the chunk
             my_sn = cur + lane;
             cur += n;
-            for (int j = 0; j < n; j++) {
+            // lanes past the end hold 0.0, and total + 0.0 == total: the chain can always run its
+            // full, unrolled length
+#pragma unroll
+            for (int j = 0; j < LANES; j++) {
                 const double dj = LANES == 1 ? d : __shfl_sync(0xffffffffu, d, j);
                 if (j == lane) my_start = total;
                 total += dj;
