@@ -47,6 +47,8 @@ def parse_args():
     ap.add_argument("--queries", type=int, default=1_000_000)
     ap.add_argument("--e2e-steps", type=int, default=8)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-other-rows", action="store_true",
+                    help="skip the short timings of the rows either side of the path (ingest, JSON)")
     return ap.parse_args()
 
 
@@ -199,6 +201,74 @@ class ClockSampler:
 # ---------------------------------------------------------------------------------------------
 #  GPU arm
 # ---------------------------------------------------------------------------------------------
+def other_rows(ctx, torch, peak):
+    """Short device-timed runs of the SURVEY 8 'next' rows that sit either side of the path: playlist
+    text -> tables (f2) and views -> JSON -> views (f3).  Inputs resident in HBM; parity of both is the
+    business of tests/test_gpu_ingest.py and tests/test_gpu_json.py, not of this function."""
+    import ctypes
+    from hlsjs_p2p_wrapper_b200 import _native as N, synth
+    lib, dev = N.load(), torch.device("cuda", torch.cuda.current_device())
+    stream = torch.cuda.Stream()
+    sp = ctypes.c_void_p(stream.cuda_stream)
+    v = lambda x: ctypes.c_void_p(x.data_ptr())
+
+    def timed(fn, reps=5):
+        ts = []
+        for i in range(reps + 2):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            e0.record(stream)
+            fn()
+            e1.record(stream)
+            torch.cuda.synchronize()
+            if i >= 2:
+                ts.append(e0.elapsed_time(e1))
+        return float(np.median(ts))
+
+    out = {}
+    text, off = synth.m3u8_block(n_tracks=6000, n_frag=800)                  # 149 MB of M3U8: > L2
+    t, cap = len(off) - 1, 6000 * 800
+    d_text, d_off = torch.from_numpy(text).to(dev), torch.from_numpy(off).to(dev)
+    d_toff = torch.empty(t + 1, dtype=torch.int64, device=dev)
+    d_live = torch.empty(t, dtype=torch.uint8, device=dev)
+    d_start, d_dur = (torch.empty(cap, dtype=torch.float64, device=dev) for _ in range(2))
+    d_sn = torch.empty(cap, dtype=torch.int32, device=dev)
+    res = N.IngestResult()
+    ms = timed(lambda: N.check(lib.hlsmap_parse_m3u8_dev(ctx._h, t, None, v(d_text), v(d_off), len(text), v(d_toff),
+                                                         v(d_live), v(d_start), v(d_sn), v(d_dur), cap,
+                                                         ctypes.byref(res), sp)))
+    alg = len(text) + 28 * int(res.n_fragments)
+    out["ingest_m3u8"] = {"text_MB": len(text) / 1e6, "fragments": int(res.n_fragments), "ms_per_call": ms,
+                          "fragments_per_s": res.n_fragments / ms * 1e3, "text_GBps": len(text) / ms / 1e6,
+                          "roofline_frac": alg / ms / 1e6 / peak, "kernel_launches": int(res.kernel_launches)}
+    del d_text, d_start, d_dur, d_sn
+    n = 4_000_000
+    rng = np.random.default_rng(1)
+    cols = [torch.from_numpy(a).to(dev) for a in (rng.integers(0, 8, n).astype(np.int32),
+                                                  rng.integers(0, 2, n).astype(np.int32),
+                                                  rng.integers(0, 2 ** 31 - 1, n).astype(np.int32),
+                                                  np.cumsum(rng.integers(2000, 10001, n) / 1000.0) % 86400.0)]
+    d_o = torch.empty(n + 1, dtype=torch.int32, device=dev)
+    d_c = torch.empty(104 * n, dtype=torch.uint8, device=dev)
+    total = ctypes.c_int64(0)
+    ms_w = timed(lambda: N.check(lib.hlsmap_view_to_json_dev(ctx._h, n, v(cols[0]), v(cols[1]), v(cols[2]), v(cols[3]),
+                                                             v(d_o), v(d_c), 104 * n, sp, None)))
+    N.check(lib.hlsmap_view_to_json_dev(ctx._h, n, v(cols[0]), v(cols[1]), v(cols[2]), v(cols[3]), v(d_o), v(d_c),
+                                        104 * n, sp, ctypes.byref(total)))
+    back = [torch.empty(n, dtype=torch.int32, device=dev) for _ in range(3)]
+    b_t = torch.empty(n, dtype=torch.float64, device=dev)
+    b_f, b_s = (torch.empty(n, dtype=torch.uint8, device=dev) for _ in range(2))
+    ms_r = timed(lambda: N.check(lib.hlsmap_view_from_json_dev(ctx._h, n, v(d_c), v(d_o), v(back[0]), v(back[1]),
+                                                               v(back[2]), v(b_t), v(b_f), v(b_s), sp)))
+    exact = bool(torch.equal(back[2], cols[2]) and torch.equal(b_t, cols[3]) and int(b_s.sum()) == 0)
+    alg = 24 * n + total.value
+    out["views_json"] = {"views": n, "chars_per_view": total.value / n, "stringify_ms": ms_w,
+                         "stringify_views_per_s": n / ms_w * 1e3, "stringify_roofline_frac": alg / ms_w / 1e6 / peak,
+                         "parse_ms": ms_r, "parse_views_per_s": n / ms_r * 1e3, "round_trip_bit_exact": exact}
+    return out
+
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -387,6 +457,13 @@ def run_ours(args):
                          "media-map.js:42-51 with %d pthreads; node on this box: %s"
                          % (reps, nq, dt, threads, node_version() or "absent")}
 
+    rows = None
+    if rank == 0 and world == 1 and not args.no_other_rows:
+        try:
+            rows = other_rows(ctx, torch, peak)
+        except Exception as e:                      # never let the extra rows cost the headline line
+            rows = {"error": "%s: %s" % (type(e).__name__, e)}
+
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -416,6 +493,7 @@ def run_ours(args):
                     "api": "hlsmap_get_segment_list (host pointers, pinned)",
                     "kernel_launches_per_step": e2e_launches},
             "gpu_launches": args.steps * world, "clocks": clocks, "node": node_version(),
+            "other_rows": rows,
         }
         print(json.dumps(line))
     for p in pins.values():
