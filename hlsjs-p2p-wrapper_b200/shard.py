@@ -52,6 +52,23 @@ def split(tables: FragmentTables, queries: QueryBatch, bounds):
     return shards, order
 
 
+def split_texts(playlist_base, track_state, text, text_off, bounds):
+    """Playlists still in text form, cut on the same playlist boundaries: shard i gets
+    (playlist_base_i int32, track_state_i uint8, text_i uint8 view, text_off_i int64), ready for
+    `Context.upload_m3u8`.  The text of a shard is one contiguous slice: nothing is copied."""
+    playlist_base = np.asarray(playlist_base, np.int64)
+    text_off = np.asarray(text_off, np.int64)
+    text = np.frombuffer(text, np.uint8) if isinstance(text, (bytes, bytearray, memoryview)) else np.asarray(text, np.uint8)
+    out = []
+    for i in range(len(bounds) - 1):
+        p0, p1 = int(bounds[i]), int(bounds[i + 1])
+        t0, t1 = int(playlist_base[p0]), int(playlist_base[p1])
+        b0, b1 = int(text_off[t0]), int(text_off[t1])
+        out.append(((playlist_base[p0:p1 + 1] - t0).astype(np.int32), np.asarray(track_state[t0:t1], np.uint8),
+                    text[b0:b1], text_off[t0:t1 + 1] - b0))
+    return out
+
+
 def merge(results, order):
     """Host-side gather: per-shard list-form results (offsets, status, sn, time) back into
     the original query order."""
@@ -81,6 +98,23 @@ class ShardedMap:
         self.tables = tables
         self.maps = [c.upload(tables.slice_playlists(int(self.bounds[i]), int(self.bounds[i + 1])))
                      for i, c in enumerate(self.contexts)]
+
+    @classmethod
+    def from_m3u8(cls, contexts, playlist_base, track_state, text, text_off):
+        """Each GPU parses its own playlists' text; bounds split the text evenly by bytes (queries
+        are routed by playlist id alone, so the host never needs the parsed tables)."""
+        self = object.__new__(cls)
+        self.contexts = list(contexts)
+        pb, to = np.asarray(playlist_base, np.int64), np.asarray(text_off, np.int64)
+        c = to[pb].astype(np.float64)                       # text bytes before each playlist
+        cuts = np.searchsorted(c, c[-1] * np.arange(1, len(self.contexts)) / len(self.contexts), side="left")
+        self.bounds = np.maximum.accumulate(np.concatenate([[0], cuts, [len(pb) - 1]]).astype(np.int64))
+        nt = len(to) - 1
+        self.tables = FragmentTables(pb.astype(np.int32), np.zeros(nt + 1, np.int64), np.asarray(track_state, np.uint8),
+                                     np.ones(nt, np.int32), np.zeros(0), np.zeros(0, np.int32), np.zeros(0))
+        parts = split_texts(pb, track_state, text, to, self.bounds)
+        self.maps = [c.upload_m3u8(b, st, tx, off) for c, (b, st, tx, off) in zip(self.contexts, parts)]
+        return self
 
     def get_segment_list(self, queries: QueryBatch):
         shards, order = split(self.tables, queries, self.bounds)

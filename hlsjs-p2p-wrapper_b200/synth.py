@@ -308,3 +308,12 @@ def sample_doubles(n, seed):
     x = np.concatenate(parts)
     x = x[np.isfinite(x)]
     return np.concatenate([x, -x[:1000]])
+
+
+def m3u8_token_soup(rng):
+    """Text glued from the tokens the expression cares about, with no regard for the HLS grammar."""
+    tokens = ["#EXTINF:", "#EXT-X-MEDIA-SEQUENCE:", "#EXT-X-ENDLIST", "#EXT-X-KEY:", "#EXT-X-PROGRAM-DATE-TIME:",
+              "#EXT-X-TARGETDURATION:", "#EXT-X-DISCONTINUITY", "#EXT-X-BYTERANGE:", "#EXTM3U", "#EXT", "#", "\n", "\n",
+              "\r\n", "\r", ",", ".", "|", "@", "seg.ts", "9.98458", "10", "0.5", ".5", "5.", "1.2.3", "007", " ", "x",
+              " ", "12345678901234567", "0.1234567", "2147483640", "#EXT-X-", ":"]
+    return "".join(tokens[i] for i in rng.integers(0, len(tokens), int(rng.integers(1, 60))))

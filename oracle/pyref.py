@@ -256,3 +256,43 @@ class HlsMock:
     @property
     def levels(self):
         return self._levels
+
+
+# ---- hls.js 0.5.46 parseLevelPlaylist, the part the mapping layer observes ----
+# The dependency is not in the reference checkout (package.json:34), so this is the published
+# expression as restated for this build, run by a real regular-expression engine: an independent
+# formulation of what oracle_parse_m3u8 (mediamap_oracle.c) emulates by hand.  Parity unpinned.
+import re as _re
+
+_JS_DOT = "[^\\n\\r\\u2028\\u2029]"          # JavaScript's `.`; Python's would also take \r
+LEVEL_PLAYLIST_RE = _re.compile(
+    "(?:#EXT-X-(MEDIA-SEQUENCE):(\\d+))|(?:#EXT-X-(TARGETDURATION):(\\d+))|(?:#EXT-X-(KEY):(" + _JS_DOT + "*))"
+    "|(?:#EXT(INF):([\\d\\.]+)[^\\r\\n]*([\\r\\n]+[^#|\\r\\n]+)?)"
+    "|(?:#EXT-X-(BYTERANGE):([\\d]+[@\\[\\d]*)\\]*[\\r\\n]+([^#|\\r\\n]+)?|(?:#EXT-X-(ENDLIST))|(?:#EXT-X-(DIS)CONTINUITY))"
+    "|(?:#EXT-X-(PROGRAM-DATE-TIME):(" + _JS_DOT + "*))", _re.ASCII)
+_STR_DECIMAL = _re.compile(r"(?:\d+\.?\d*|\.\d+)", _re.ASCII)
+
+
+def js_parse_float_of_run(run):
+    """parseFloat on a [0-9.]+ run: the longest StrDecimalLiteral prefix, else NaN."""
+    m = _STR_DECIMAL.match(run)
+    return float(m.group(0)) if m else float("nan")
+
+
+def parse_level_playlist(text):
+    """-> (fragments [{sn, start, duration}], live).  `text` is a str (one level playlist)."""
+    current_sn, total, live, frags = 0, 0.0, True, []
+    for m in LEVEL_PLAYLIST_RE.finditer(text):
+        result = [g for g in m.groups() if g is not None]       # result.shift(); filter(undefined)
+        tag = result[0]
+        if tag == "MEDIA-SEQUENCE":
+            current_sn = int(result[1])
+        elif tag == "ENDLIST":
+            live = False
+        elif tag == "INF":
+            duration = js_parse_float_of_run(result[1])
+            if duration == duration:
+                frags.append({"sn": current_sn, "start": total, "duration": duration})
+                current_sn += 1
+                total += duration
+    return frags, live

@@ -195,3 +195,41 @@ def test_device_pointer_entry(ctx):
     got = dict(track_off=d_toff.cpu().numpy(), live=d_live.cpu().numpy(), start=d_start.cpu().numpy(),
                sn=d_sn.cpu().numpy(), duration=d_dur.cpu().numpy())
     _same(got, exp)
+
+
+def test_token_soup(ctx):
+    """Text glued at random from the tokens the expression cares about (the same soup the CPU suite
+    feeds to a real regex engine, tests/test_ingest_host.py)."""
+    rng = np.random.default_rng(11)
+    texts = [synth.m3u8_token_soup(rng).encode() for _ in range(20000)]
+    got = ctx.parse_m3u8(texts)
+    exp = oracle.parse_m3u8(b"".join(texts), _offsets(texts))
+    assert not exp["bad"]
+    _same(got, exp)
+    assert got["result"].n_fragments > 2000
+
+
+def test_sharded_map_from_text(ctx):
+    """Two shards (two contexts on this GPU), each parsing its own playlists; answers must be those
+    of the single map."""
+    from hlsjs_p2p_wrapper_b200 import shard
+    from hlsjs_p2p_wrapper_b200.engine import Context
+    from hlsjs_p2p_wrapper_b200.tables import QueryBatch
+    base, state, texts = synth.m3u8_corpus(n_playlists=120, unparsed_every=23)
+    off = _offsets(texts)
+    text = b"".join(texts)
+    other = Context(0)
+    sm = shard.ShardedMap.from_m3u8([ctx, other], base, state, text, off)
+    one = ctx.upload_m3u8(base, state, texts)
+    rng = np.random.default_rng(4)
+    n = 8000
+    q = QueryBatch(rng.integers(-1, 121, n).astype(np.int32), rng.integers(0, 4, n).astype(np.int32),
+                   rng.uniform(-5, 80, n), rng.uniform(0, 40, n))
+    o, st, sn, tm = sm.get_segment_list(q)
+    r = one.get_segment_list(q.playlist, q.level, q.begin, q.duration)
+    assert np.array_equal(o, r.offsets.astype(np.int64)) and np.array_equal(st, r.status)
+    assert np.array_equal(sn, r.sn) and np.array_equal(tm, r.time)
+    assert 0 < sm.bounds[1] < 120 and len(sn) > 1000
+    sm.close()
+    one.close()
+    other.close()

@@ -9,6 +9,7 @@ import numpy as np
 import pytest
 
 import oracle
+from oracle import pyref
 from hlsjs_p2p_wrapper_b200 import synth
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -128,3 +129,50 @@ def test_decimal_converter_matches_strtod_and_python(tmp_path):
     assert unsupported < len(cases) // 100      # only >19-digit inputs with an undecidable tail
     assert lines[cases.index("9007199254740994.99999999")].startswith("unsupported")
     assert lines[cases.index("12345678901234567890")].startswith("unsupported")   # 20 integer digits
+
+
+_random_playlist = synth.m3u8_token_soup
+
+
+def test_hand_emulation_agrees_with_a_regex_engine():
+    """oracle_parse_m3u8 walks the text by hand; oracle.pyref runs the same expression through
+    Python's `re`.  Random token soup (hidden tags, cut tags, odd numbers, U+2028) must agree."""
+    rng = np.random.default_rng(11)
+    texts = [_random_playlist(rng) for _ in range(6000)] + [t.decode() for t in synth._NASTY]
+    raw = [t.encode("utf-8") for t in texts]
+    off = np.concatenate([[0], np.cumsum([len(b) for b in raw])])
+    r = oracle.parse_m3u8(b"".join(raw), off)
+    total = 0
+    for i, t in enumerate(texts):
+        frags, live = pyref.parse_level_playlist(t)
+        a, b = int(r["track_off"][i]), int(r["track_off"][i + 1])
+        if any(f["sn"] > 2 ** 31 - 1 for f in frags):
+            continue                                   # beyond int32: the C side only flags these
+        assert b - a == len(frags), repr(t)
+        assert [f["sn"] for f in frags] == list(r["sn"][a:b]), repr(t)
+        assert [f["duration"] for f in frags] == list(r["duration"][a:b]), repr(t)
+        assert [f["start"] for f in frags] == list(r["start"][a:b]), repr(t)
+        assert int(live) == r["live"][i], repr(t)
+        total += len(frags)
+    assert total > 800
+
+
+def test_text_shards_parse_to_the_slices_of_the_whole():
+    from hlsjs_p2p_wrapper_b200 import shard
+    base, state, texts = synth.m3u8_corpus(n_playlists=90, unparsed_every=13)
+    off = np.concatenate([[0], np.cumsum([len(t) for t in texts])]).astype(np.int64)
+    text = b"".join(texts)
+    whole = oracle.parse_m3u8(text, off, state)
+    bounds = np.asarray([0, 17, 17, 60, 90])                     # one empty shard on purpose
+    parts = shard.split_texts(base, state, text, off, bounds)
+    f0 = 0
+    for (b, st, tx, to), p0, p1 in zip(parts, bounds[:-1], bounds[1:]):
+        assert b[0] == 0 and b[-1] == len(st) == len(to) - 1 and to[0] == 0 and to[-1] == len(tx)
+        r = oracle.parse_m3u8(tx, to, st)
+        n = int(r["track_off"][-1])
+        assert np.array_equal(r["sn"], whole["sn"][f0:f0 + n])
+        assert np.array_equal(r["start"], whole["start"][f0:f0 + n])
+        t0, t1 = base[p0], base[p1]
+        assert np.array_equal(r["track_off"], whole["track_off"][t0:t1 + 1] - whole["track_off"][t0])
+        f0 += n
+    assert f0 == whole["track_off"][-1]
