@@ -176,9 +176,32 @@ __device__ __forceinline__ bool eat(const Text &t, long long &q, long long lim, 
     return true;
 }
 
-// A JSON number that must be an int32 (sn, level, urlId columns are int32).
+// A JSON number that must be an int32 (sn, level, urlId columns are int32).  What JSON.stringify
+// prints for an int32 -- an optional '-' and up to ten digits -- is read directly; anything else
+// (a fraction, an exponent, more digits) goes through the general number scanner.
 __device__ __forceinline__ int eat_int(const Text &t, long long &q, long long lim, int *out)
 {
+    {
+        long long r = q;
+        const bool neg = r < lim && t(r) == '-';
+        if (neg) r++;
+        const long long d0 = r;
+        long long val = 0;
+        while (r < lim && r - d0 < 10) {
+            const int c = t(r);
+            if (c < '0' || c > '9') break;
+            val = val * 10 + (c - '0');
+            r++;
+        }
+        const int nd = (int)(r - d0);
+        const int nx = r < lim ? t(r) : 0;
+        const bool more = (nx >= '0' && nx <= '9') || nx == '.' || nx == 'e' || nx == 'E';
+        if (nd > 0 && !more && !(nd > 1 && t(d0) == '0') && val <= (neg ? 2147483648ll : 2147483647ll)) {
+            *out = (int)(neg ? -val : val);
+            q = r;
+            return HLSMAP_JSON_OK;
+        }
+    }
     const JsonNumber n = scan_json_number(t, q, lim);
     if (n.length == 0) return HLSMAP_JSON_MALFORMED;
     q += n.length;
@@ -187,6 +210,51 @@ __device__ __forceinline__ int eat_int(const Text &t, long long &q, long long li
     if (!(x >= -2147483648.0 && x <= 2147483647.0) || x != (double)(int)x) return HLSMAP_JSON_NOT_INT32;
     *out = (int)x;
     return HLSMAP_JSON_OK;
+}
+
+__constant__ double c_json_pow10[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
+                                        1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+
+// `time`: digits [. digits] with at most 15 significant digits and no exponent is one exact IEEE
+// division (both operands are exact doubles); the rest takes the general path.  Returns 0 when the
+// general path has to decide.
+__device__ __forceinline__ int eat_plain_decimal(const Text &t, long long &q, long long lim, double *out)
+{
+    long long r = q;
+    const bool neg = r < lim && t(r) == '-';
+    if (neg) r++;
+    const long long d0 = r;
+    unsigned long long w = 0;
+    int nsig = 0, frac = 0;
+    while (r < lim) {
+        const int c = t(r);
+        if (c < '0' || c > '9') break;
+        if (nsig > 0 || c != '0') nsig++;
+        w = w * 10ull + (unsigned long long)(c - '0');
+        r++;
+        if (nsig > 15) return 0;
+    }
+    const int ni = (int)(r - d0);
+    if (ni == 0 || (ni > 1 && t(d0) == '0')) return 0;
+    if (r < lim && t(r) == '.') {
+        r++;
+        const long long f0 = r;
+        while (r < lim) {
+            const int c = t(r);
+            if (c < '0' || c > '9') break;
+            if (nsig > 0 || c != '0') nsig++;
+            w = w * 10ull + (unsigned long long)(c - '0');
+            r++;
+            if (nsig > 15 || r - f0 > 22) return 0;
+        }
+        frac = (int)(r - f0);
+        if (frac == 0) return 0;
+    }
+    if (r < lim && (t(r) == 'e' || t(r) == 'E')) return 0;
+    const double mag = frac ? __ddiv_rn((double)w, c_json_pow10[frac]) : (double)w;
+    *out = neg ? -mag : mag;
+    q = r;
+    return 1;
 }
 
 }  // namespace
@@ -258,15 +326,17 @@ view_from_json_kernel(const JsonReadParams p)
             if (eat(t, q, lim, "null", 4)) {
                 flags |= HLSMAP_JSON_TIME_NULL;
             } else {
-                const JsonNumber n = scan_json_number(t, q, lim);
-                if (n.length == 0) {
-                    st = HLSMAP_JSON_MALFORMED;
-                    break;
-                }
-                q += n.length;
-                if (!json_number_to_double(n, &time)) {
-                    st = HLSMAP_JSON_UNSUPPORTED;
-                    break;
+                if (!eat_plain_decimal(t, q, lim, &time)) {
+                    const JsonNumber n = scan_json_number(t, q, lim);
+                    if (n.length == 0) {
+                        st = HLSMAP_JSON_MALFORMED;
+                        break;
+                    }
+                    q += n.length;
+                    if (!json_number_to_double(n, &time)) {
+                        st = HLSMAP_JSON_UNSUPPORTED;
+                        break;
+                    }
                 }
             }
         }
