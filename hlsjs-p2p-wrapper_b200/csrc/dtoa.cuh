@@ -163,51 +163,54 @@ HLSMAP_HD inline int js_number_length(const Shortest &s)
 }
 
 // Writes Number::toString of the digits at dst (no sign, no terminator); returns the length.
+// Digits are peeled off the low end and stored straight at their final position (no staging
+// array), in two 32-bit halves so that the divisions are 32-bit ones.
 HLSMAP_HD inline int js_number_write(const Shortest &s, char *dst)
 {
     const int k = s.ndigits, n = s.exp10 + k;
-    char d[20];
-    unsigned long long v = s.digits;
-    for (int i = k - 1; i >= 0; i--) {
-        d[i] = (char)('0' + (int)(v % 10ull));
-        v /= 10ull;
-    }
-    int at = 0;
+    // layout: where digit i (0 = most significant) goes, and what surrounds the digits
+    int shift_from = k, lead = 0, len;       // digit i lands at lead + i + (i >= shift_from)
     if (k <= n && n <= 21) {
-        for (int i = 0; i < k; i++) dst[at++] = d[i];
-        for (int i = k; i < n; i++) dst[at++] = '0';
-        return at;
+        for (int i = k; i < n; i++) dst[i] = '0';
+        len = n;
+    } else if (0 < n && n <= 21) {
+        shift_from = n;
+        dst[n] = '.';
+        len = k + 1;
+    } else if (-6 < n && n <= 0) {
+        dst[0] = '0';
+        dst[1] = '.';
+        for (int i = 0; i < -n; i++) dst[2 + i] = '0';
+        lead = 2 - n;
+        len = lead + k;
+    } else {
+        int at = k;
+        if (k > 1) {
+            shift_from = 1;
+            dst[1] = '.';
+            at = k + 1;
+        }
+        dst[at++] = 'e';
+        int ee = n - 1;
+        dst[at++] = ee < 0 ? '-' : '+';
+        if (ee < 0) ee = -ee;
+        if (ee >= 100) dst[at++] = (char)('0' + ee / 100);
+        if (ee >= 10) dst[at++] = (char)('0' + (ee / 10) % 10);
+        dst[at++] = (char)('0' + ee % 10);
+        len = at;
     }
-    if (0 < n && n <= 21) {
-        for (int i = 0; i < n; i++) dst[at++] = d[i];
-        dst[at++] = '.';
-        for (int i = n; i < k; i++) dst[at++] = d[i];
-        return at;
+    unsigned lo = (unsigned)(s.digits % 1000000000ull);
+    unsigned long long hi = s.digits / 1000000000ull;      // < 10^11: at most two more 9-digit groups
+    int i = k - 1;
+    for (int g = 0; g < 3 && i >= 0; g++) {
+        for (int j = 0; j < 9 && i >= 0; j++, i--) {
+            dst[lead + i + (i >= shift_from ? 1 : 0)] = (char)('0' + lo % 10u);
+            lo /= 10u;
+        }
+        lo = (unsigned)(hi % 1000000000ull);
+        hi /= 1000000000ull;
     }
-    if (-6 < n && n <= 0) {
-        dst[at++] = '0';
-        dst[at++] = '.';
-        for (int i = 0; i < -n; i++) dst[at++] = '0';
-        for (int i = 0; i < k; i++) dst[at++] = d[i];
-        return at;
-    }
-    dst[at++] = d[0];
-    if (k > 1) {
-        dst[at++] = '.';
-        for (int i = 1; i < k; i++) dst[at++] = d[i];
-    }
-    dst[at++] = 'e';
-    int ee = n - 1;
-    dst[at++] = ee < 0 ? '-' : '+';
-    if (ee < 0) ee = -ee;
-    char x[4];
-    int xl = 0;
-    do {
-        x[xl++] = (char)('0' + ee % 10);
-        ee /= 10;
-    } while (ee);
-    while (xl) dst[at++] = x[--xl];
-    return at;
+    return len;
 }
 
 }  // namespace hlsmap

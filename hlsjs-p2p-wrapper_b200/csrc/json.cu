@@ -60,7 +60,7 @@ view_to_json_kernel(const JsonWriteParams p)
 {
     __shared__ Scan::Smem scan;
     __shared__ unsigned long long warp_cnt[kThreads / 32];
-    __shared__ char buf[kThreads * kMaxChars];
+    __shared__ __align__(16) char buf[kThreads * kMaxChars + 16];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     Scan::acquire_set(p.ctr, p.epoch);
@@ -114,9 +114,12 @@ view_to_json_kernel(const JsonWriteParams p)
         }
         const unsigned long long tile_base = Scan::exclusive_prefix(scan, p.tile_status, p.epoch, tile, tile_total);
         const int at = (int)wbase + x - len;
+        // the tile's characters sit in shared memory at the same offset modulo 16 as their place in
+        // global memory, so the copy out below can move 16 bytes per thread with aligned accesses
+        const int pad = (int)((reinterpret_cast<unsigned long long>(p.chars) + tile_base) & 15ull);
         if (in) {
             p.offsets[v] = (int)(tile_base + (unsigned long long)at);
-            char *d = buf + at;
+            char *d = buf + pad + at;
             d += put_lit(d, "{\"sn\":", 6);
             d += put_int(d, s);
             d += put_lit(d, ",\"trackView\":{\"level\":", 22);
@@ -144,9 +147,24 @@ view_to_json_kernel(const JsonWriteParams p)
             p.result->overflow = total > 0x7fffffffull ? 1 : 0;
         }
         __syncthreads();
-        for (int i = tid; i < (int)tile_total; i += kThreads) {   // coalesced copy of the tile's characters
-            const long long o = (long long)tile_base + i;
-            if (o < p.capacity) p.chars[o] = buf[i];
+        {   // coalesced copy of the tile's characters: bytes up to the first 16-byte boundary, whole
+            // 16-byte pieces, bytes after the last boundary
+            const int total = (int)tile_total;
+            char *g = p.chars + (long long)tile_base - pad;          // 16-byte aligned
+            if ((long long)tile_base + total <= p.capacity) {
+                const int first = pad ? 16 : 0, last = (pad + total) & ~15;
+                if (last > first) {
+                    for (int i = first + 16 * tid; i < last; i += 16 * kThreads)
+                        *reinterpret_cast<uint4 *>(g + i) = *reinterpret_cast<const uint4 *>(buf + i);
+                    if (tid < 16 && pad && pad + tid < 16) g[pad + tid] = buf[pad + tid];
+                    if (tid >= 32 && tid < 48 && last + (tid - 32) < pad + total) g[last + tid - 32] = buf[last + tid - 32];
+                } else {
+                    for (int i = pad + tid; i < pad + total; i += kThreads) g[i] = buf[i];
+                }
+            } else {
+                for (int i = tid; i < total; i += kThreads)
+                    if ((long long)tile_base + i < p.capacity) g[pad + i] = buf[pad + i];
+            }
         }
         if (Scan::tile_done(p.ctr, p.n_tiles)) Scan::finish_batch(p.ctr, p.result, p.tslot);
     }
