@@ -217,7 +217,7 @@ view_format_kernel(const FormatParams p)
 {
     __shared__ FmtScan::Smem scan;
     __shared__ unsigned long long warp_cnt[kFmtThreads / 32];
-    __shared__ char buf[kFormatTileViews * kFmtMaxChars];
+    __shared__ __align__(16) char buf[kFormatTileViews * kFmtMaxChars + 16];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     FmtScan::acquire_set(p.ctr, p.epoch);
@@ -256,12 +256,15 @@ view_format_kernel(const FormatParams p)
         const unsigned long long tile_base =
             FmtScan::exclusive_prefix(scan, p.tile_status, p.epoch, tile, tile_total);
 
+        // the tile's characters sit in shared memory at the same offset modulo 16 as their place in
+        // global memory, so the copy out below moves 16 bytes per thread with aligned accesses
+        const int pad = (int)((reinterpret_cast<unsigned long long>(p.chars) + tile_base) & 15ull);
         int at = (int)wbase + texcl;  // tile-relative byte offset of this thread's first view
 #pragma unroll
         for (int k = 0; k < kFmtIpt; k++) {
             if (v0 + k < p.n) {
                 p.offsets[v0 + k] = (int)(tile_base + (unsigned long long)at);
-                char *d = buf + at;
+                char *d = buf + pad + at;
                 *d++ = 'L';
                 d += put_dec(d, l[k]);
                 *d++ = 'U';
@@ -280,10 +283,24 @@ view_format_kernel(const FormatParams p)
             p.result->overflow = total > 0x7fffffffull ? 1 : 0;
         }
         __syncthreads();
-        // coalesced copy of the tile's characters
-        for (int i = tid; i < (int)tile_total; i += kFmtThreads) {
-            const long long o = (long long)tile_base + i;
-            if (o < p.capacity) p.chars[o] = buf[i];
+        {   // coalesced copy of the tile's characters: bytes up to the first 16-byte boundary, whole
+            // 16-byte pieces, bytes after the last boundary
+            const int total = (int)tile_total;
+            char *g = p.chars + (long long)tile_base - pad;          // 16-byte aligned
+            if ((long long)tile_base + total <= p.capacity) {
+                const int first = pad ? 16 : 0, last = (pad + total) & ~15;
+                if (last > first) {
+                    for (int i = first + 16 * tid; i < last; i += 16 * kFmtThreads)
+                        *reinterpret_cast<uint4 *>(g + i) = *reinterpret_cast<const uint4 *>(buf + i);
+                    if (tid < 16 && pad && pad + tid < 16) g[pad + tid] = buf[pad + tid];
+                    if (tid >= 32 && tid < 48 && last + (tid - 32) < pad + total) g[last + tid - 32] = buf[last + tid - 32];
+                } else {
+                    for (int i = pad + tid; i < pad + total; i += kFmtThreads) g[i] = buf[i];
+                }
+            } else {
+                for (int i = tid; i < total; i += kFmtThreads)
+                    if ((long long)tile_base + i < p.capacity) g[pad + i] = buf[pad + i];
+            }
         }
         if (FmtScan::tile_done(p.ctr, p.n_tiles)) FmtScan::finish_batch(p.ctr, p.result, p.tslot);
     }
