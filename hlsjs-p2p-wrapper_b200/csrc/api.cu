@@ -1767,11 +1767,18 @@ int ingest_core(hlsmap_ctx *ctx, int32_t n_tracks, const uint8_t *d_state, const
         p.n_tiles = n_tiles;
         p.vec_ok = ((uintptr_t)d_text & 15) == 0;
         p.out = (IngestCounters *)(b + o_out);
+        static const bool timing = getenv("HLSMAP_INGEST_TIMING") != nullptr;     // diagnostics
+        cudaEvent_t ev[4] = {};
+        if (timing)
+            for (auto &e : ev) cudaEventCreate(&e);
+        if (timing) cudaEventRecord(ev[0], s);
         if (n_tiles > 0 && n_tracks > 0) {
             CK(launch_ingest_tile_index(p.text_off, n_tracks, n_tiles, (int *)(b + o_tlo), (int *)(b + o_bf), s));
+            if (timing) cudaEventRecord(ev[1], s);
             CK(launch_ingest_scan(p, s));
             launches += 2;
         }
+        if (timing) cudaEventRecord(ev[2], s);
         CK(cudaMemcpyAsync(&h, p.out, sizeof h, cudaMemcpyDeviceToHost, s));
         CK(cudaStreamSynchronize(s));
         if ((int64_t)h.n_tags > tag_cap) {     // more sequence tags than tracks*2: size exactly, redo
@@ -1795,9 +1802,20 @@ int ingest_core(hlsmap_ctx *ctx, int32_t n_tracks, const uint8_t *d_state, const
             a.out = p.out;
             CK(launch_ingest_assemble(a, (int64_t)h.n_fragments >= (int64_t)n_tracks * 24, s));
             launches++;
+            if (timing) cudaEventRecord(ev[3], s);
             CK(cudaMemcpyAsync(&h, p.out, sizeof h, cudaMemcpyDeviceToHost, s));
             CK(cudaStreamSynchronize(s));
+            if (timing && n_tiles > 0) {
+                float t_idx = 0, t_scan = 0, t_asm = 0;
+                cudaEventElapsedTime(&t_idx, ev[0], ev[1]);
+                cudaEventElapsedTime(&t_scan, ev[1], ev[2]);
+                cudaEventElapsedTime(&t_asm, ev[2], ev[3]);
+                fprintf(stderr, "[hlsmap ingest] tile index %.1f us, scan %.1f us, counters+assemble %.1f us\n",
+                        1e3 * t_idx, 1e3 * t_scan, 1e3 * t_asm);
+            }
         }
+        if (timing)
+            for (auto &e : ev) cudaEventDestroy(e);
         break;
     }
     if (res) {

@@ -144,6 +144,74 @@ HLSMAP_HD inline bool decimal_to_double(const DecimalScan &s, double *out)
 }
 #endif
 
+// ---- the same scan on 16 bytes held in two registers (SWAR) -------------------------------------
+// x0 holds text bytes 0..7, x1 bytes 8..15, first byte lowest; bytes past the end of the text
+// must be zero.  Answers what scan_decimal() answers when the [0-9.]+ run ends inside the 16
+// bytes and neither side of the '.' has more than 8 digits; returns false otherwise (the caller
+// then walks the bytes).  run = characters of the run; value = w * 10^-nf.
+HLSMAP_HD inline unsigned long long swar_nondigit(unsigned long long x)
+{
+    const unsigned long long t = x ^ 0x3030303030303030ull;
+    return (((t & 0x7f7f7f7f7f7f7f7full) + 0x7676767676767676ull) | t) & 0x8080808080808080ull;
+}
+HLSMAP_HD inline unsigned long long swar_is_byte(unsigned long long x, unsigned char c)
+{
+    const unsigned long long y = x ^ (0x0101010101010101ull * c);
+    return ((((y & 0x7f7f7f7f7f7f7f7full) + 0x7f7f7f7f7f7f7f7full) | y) & 0x8080808080808080ull) ^ 0x8080808080808080ull;
+}
+HLSMAP_HD inline int swar_first(unsigned long long m0, unsigned long long m1)   // first flagged byte, 16 if none
+{
+#ifdef __CUDA_ARCH__
+    if (m0) return (__ffsll((long long)m0) - 1) >> 3;
+    if (m1) return 8 + ((__ffsll((long long)m1) - 1) >> 3);
+#else
+    if (m0) return __builtin_ctzll(m0) >> 3;
+    if (m1) return 8 + (__builtin_ctzll(m1) >> 3);
+#endif
+    return 16;
+}
+HLSMAP_HD inline unsigned swar_parse8(unsigned long long v)   // eight ASCII digits (or zero bytes), first lowest
+{
+    v = ((v & 0x0f0f0f0f0f0f0f0full) * 2561ull) >> 8;
+    v = ((v & 0x00ff00ff00ff00ffull) * 6553601ull) >> 16;
+    return (unsigned)(((v & 0x0000ffff0000ffffull) * 42949672960001ull) >> 32);
+}
+HLSMAP_HD inline unsigned long long swar_bytes_from(unsigned long long x0, unsigned long long x1, int at)
+{   // the eight bytes starting at byte `at` (0..16) of the 16
+    if (at == 0) return x0;
+    if (at < 8) return (x0 >> (8 * at)) | (x1 << (64 - 8 * at));
+    if (at == 8) return x1;
+    if (at < 16) return x1 >> (8 * (at - 8));
+    return 0ull;
+}
+HLSMAP_HD inline bool swar_scan_decimal16(unsigned long long x0, unsigned long long x1, int *run, unsigned long long *w,
+                                          int *nf, bool *is_number)
+{
+    const unsigned long long d0 = swar_is_byte(x0, '.'), d1 = swar_is_byte(x1, '.');
+    const int pe = swar_first(swar_nondigit(x0) & ~d0, swar_nondigit(x1) & ~d1);
+    if (pe == 16) return false;                        // the run goes on past the window
+    *run = pe;
+    int pd = swar_first(d0, d1);                       // first '.', if inside the run
+    int ni = pe, nfrac = 0;
+    if (pd < pe) {
+        const unsigned long long e0 = d0 & (d0 - 1), e1 = d0 ? d1 : (d1 & (d1 - 1));   // dots after the first
+        int le = swar_first(e0, e1);
+        if (le > pe) le = pe;
+        ni = pd;
+        nfrac = le - pd - 1;
+    }
+    *is_number = ni + nfrac > 0;
+    if (ni > 8 || nfrac > 8) return false;
+    const unsigned ip = ni ? swar_parse8(x0 << (8 * (8 - ni))) : 0u;
+    unsigned fp = 0;
+    if (nfrac) fp = swar_parse8(swar_bytes_from(x0, x1, pd + 1) << (8 * (8 - nfrac)));
+    unsigned long long p10 = 1;
+    for (int i = 0; i < nfrac; i++) p10 *= 10ull;
+    *w = (unsigned long long)ip * p10 + fp;
+    *nf = nfrac;
+    return true;
+}
+
 // ---- JSON numbers: -? int frac? exp?  (RFC 8259 / ECMA-404, what JSON.parse accepts) ---------
 struct JsonNumber {
     unsigned long long w;  // first (up to 19) significant digits

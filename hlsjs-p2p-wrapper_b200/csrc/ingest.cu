@@ -161,42 +161,23 @@ __device__ __forceinline__ bool classify_fast(const unsigned char *stext, int po
 #pragma unroll
     for (int j = 2; j < 6; j++) u[j] = __funnelshift_r(a[j], a[j + 1], sh);
     if (u1 == lit4('I', 'N', 'F', ':')) {
-        // scan_decimal() on bytes 8..23
-        unsigned long long w = 0;
-        int ndig = 0, exp10 = 0, run = 0;
-        bool seen_dot = false, in_prefix = true, is_number = false, sticky = false, ended = false;
-#pragma unroll
-        for (int j = 8; j < 24; j++) {
-            if (ended) break;
-            if (j >= limit) {
-                if (!limit_is_end) return false;
-                ended = true;
-                break;
-            }
-            const int c = (int)((u[j >> 2] >> ((j & 3) * 8)) & 0xffu);
-            const bool digit = c >= '0' && c <= '9';
-            if (!digit && c != '.') {
-                ended = true;
-                break;
-            }
-            run++;
-            if (!in_prefix) continue;
-            if (c == '.') {
-                if (seen_dot) in_prefix = false;
-                else seen_dot = true;
-                continue;
-            }
-            is_number = true;
-            const int d = c - '0';
-            if (ndig == 0 && d == 0) {
-                if (seen_dot) exp10--;
-                continue;
-            }
-            w = w * 10ull + (unsigned long long)d;     // at most 16 digits here: no overflow
-            ndig++;
-            if (seen_dot) exp10--;
+        // scan_decimal() on bytes 8..23, sixteen bytes at a time in two registers (decimal.cuh);
+        // bytes past `limit` read as zero, and a window cut short is always cut by the text's end
+        unsigned long long x0 = (unsigned long long)u[2] | ((unsigned long long)u[3] << 32);
+        unsigned long long x1 = (unsigned long long)u[4] | ((unsigned long long)u[5] << 32);
+        const int nv = limit - 8;
+        if (nv < 8) {
+            x0 &= (1ull << (8 * nv)) - 1ull;
+            x1 = 0ull;
+        } else if (nv < 16) {
+            x1 &= nv == 8 ? 0ull : (1ull << (8 * (nv - 8))) - 1ull;
         }
-        if (!ended) return false;                       // the run goes on past the window
+        unsigned long long w = 0;
+        int run = 0, nfrac = 0;
+        bool is_number = false;
+        const bool sticky = false;
+        if (!swar_scan_decimal16(x0, x1, &run, &w, &nfrac, &is_number)) return false;
+        const int exp10 = -nfrac;
         if (run == 0) return true;
         if (!is_number) {
             t.kind = kTokInfNaN;
