@@ -1717,7 +1717,7 @@ int ingest_core(hlsmap_ctx *ctx, int32_t n_tracks, const uint8_t *d_state, const
                 double *d_start, int32_t *d_sn, double *d_dur, double *d_dur0, int64_t capacity,
                 cudaStream_t s, hlsmap_ingest_result *res)
 {
-    if (n_bytes > (int64_t)0x7fffffff * kIngestTileBytes / 2)
+    if (n_bytes > (int64_t)0x7fffffff * (kIngestSpanBytes / 2))
         return fail(HLSMAP_ERR_INVALID, "parse_m3u8: text too large for one call");
     const int n_tiles = (int)((n_bytes + kIngestTileBytes - 1) / kIngestTileBytes);
     int64_t tag_cap = (int64_t)n_tracks * 2 + 1024;
@@ -1726,21 +1726,27 @@ int ingest_core(hlsmap_ctx *ctx, int32_t n_tracks, const uint8_t *d_state, const
     const bool fill = d_start && d_sn && d_dur;
     if (!fill) capacity = 0;
     for (int attempt = 0; attempt < 2; attempt++) {
-        size_t o_tlo = 0, o_bf = align256(o_tlo + sizeof(int) * (size_t)(n_tiles + 1));
-        size_t o_sf = align256(o_bf + sizeof(int) * (size_t)(n_tiles + 1));
-        size_t o_st = align256(o_sf + 8 * (size_t)(n_tiles + 1));
-        size_t o_ctr = align256(o_st + 8 * (size_t)(n_tiles + 1));
-        size_t o_out = align256(o_ctr + sizeof(ScanCounters));
-        size_t o_tp = align256(o_out + sizeof(IngestCounters));
+        // zeroed head (block sums, counters), then everything the kernels fully overwrite
+        const int64_t n_spans = (int64_t)n_tiles * (kIngestTileBytes / kIngestSpanBytes);
+        const int64_t n_blocks = (n_spans + kIngestScanBlock - 1) / kIngestScanBlock;
+        size_t o_bs = 0, o_out = align256(o_bs + 16 * (size_t)(n_blocks + 1));
+        size_t o_zero_end = align256(o_out + sizeof(IngestCounters));
+        size_t o_tlo = o_zero_end, o_bf = align256(o_tlo + sizeof(int) * (size_t)(n_tiles + 1));
+        size_t o_sc = align256(o_bf + sizeof(int) * (size_t)(n_tiles + 1));
+        size_t o_bb = align256(o_sc + 4 * (size_t)(n_spans + 1));
+        size_t o_sb = align256(o_bb + 16 * (size_t)(n_blocks + 1));
+        size_t o_tp = align256(o_sb + 16 * (size_t)(n_spans + 1));
         size_t o_tf = align256(o_tp + 8 * (size_t)tag_cap);
         size_t o_tv = align256(o_tf + 8 * (size_t)tag_cap);
         size_t o_d0 = align256(o_tv + 4 * (size_t)tag_cap);
-        size_t total = align256(o_d0 + 8 * (size_t)(n_tracks + 1));
+        size_t o_sd = align256(o_d0 + 8 * (size_t)(n_tracks + 1));
+        size_t o_sg = align256(o_sd + (fill ? 8 * (size_t)kIngestSpanFrags * (size_t)n_spans : 0));
+        size_t total = align256(o_sg + (fill ? 8 * (size_t)kIngestSpanTags * (size_t)n_spans : 0));
         void *sp = nullptr;               // grow-only context scratch: no allocation after the first call
         int r = ensure_slot(ctx, kSlots - 1, (int64_t)total, &sp);
         if (r) return r;
         char *b = (char *)sp;
-        CK(cudaMemsetAsync(b, 0, o_tp, s));
+        CK(cudaMemsetAsync(b, 0, o_zero_end, s));
         if (n_tracks) CK(cudaMemsetAsync(d_live, 1, (size_t)n_tracks, s));
         CK(cudaMemsetAsync(d_track_off, 0, 8 * (size_t)(n_tracks + 1), s));
         IngestParams p{};
@@ -1759,11 +1765,14 @@ int ingest_core(hlsmap_ctx *ctx, int32_t n_tracks, const uint8_t *d_state, const
         p.tag_frag = (long long *)(b + o_tf);
         p.tag_val = (int *)(b + o_tv);
         p.tag_capacity = tag_cap;
-        p.status_f = (unsigned long long *)(b + o_sf);
-        p.status_t = (unsigned long long *)(b + o_st);
-        p.ctr = (ScanCounters *)(b + o_ctr);
-        p.epoch = 1;
-        p.tslot = 0;
+        p.stage_dur = fill ? (double *)(b + o_sd) : nullptr;
+        p.stage_tag = fill ? (unsigned long long *)(b + o_sg) : nullptr;
+        p.span_cnt = (unsigned *)(b + o_sc);
+        p.block_sum = (unsigned long long *)(b + o_bs);
+        p.block_base = (unsigned long long *)(b + o_bb);
+        p.span_base = (unsigned long long *)(b + o_sb);
+        p.n_spans = (int)n_spans;
+        p.n_blocks = (int)n_blocks;
         p.n_tiles = n_tiles;
         p.vec_ok = ((uintptr_t)d_text & 15) == 0;
         p.out = (IngestCounters *)(b + o_out);
@@ -1776,7 +1785,8 @@ int ingest_core(hlsmap_ctx *ctx, int32_t n_tracks, const uint8_t *d_state, const
             CK(launch_ingest_tile_index(p.text_off, n_tracks, n_tiles, (int *)(b + o_tlo), (int *)(b + o_bf), s));
             if (timing) cudaEventRecord(ev[1], s);
             CK(launch_ingest_scan(p, s));
-            launches += 2;
+            CK(launch_ingest_compact(p, s));
+            launches += fill ? 6 : 5;
         }
         if (timing) cudaEventRecord(ev[2], s);
         CK(cudaMemcpyAsync(&h, p.out, sizeof h, cudaMemcpyDeviceToHost, s));

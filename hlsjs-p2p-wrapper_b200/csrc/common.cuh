@@ -143,13 +143,22 @@ struct IngestParams {
     long long *tag_frag;         //   fragments before the tag,
     int *tag_val;                //   and the number
     long long tag_capacity;
-    unsigned long long *status_f, *status_t;   // look-back status words (zeroed; epoch 1)
-    ScanCounters *ctr;
-    unsigned epoch, tslot;
-    int n_tiles;
+    // No scan inside the parse: every 4 KB span of text leaves its fragments and tags in a slot
+    // of fixed size and its two counts; m3u8_compact_kernel moves them to their final places.
+    double *stage_dur;           // [n_spans * kIngestSpanFrags]; nullptr = count only
+    unsigned long long *stage_tag;   // [n_spans * kIngestSpanTags]: value | fragments before << 32 | position in span << 48
+    unsigned *span_cnt;          // [n_spans]: fragments | tags << 16
+    unsigned long long *block_sum;   // [n_blocks]: per kIngestScanBlock spans, fragments | tags << 40 (zeroed)
+    unsigned long long *block_base;  // [n_blocks + 1]: exclusive scan of block_sum
+    unsigned long long *span_base;   // [n_spans]: fragments | tags << 40 before each span
+    int n_tiles, n_spans, n_blocks;
     int vec_ok;                  // text is 16-byte aligned
     IngestCounters *out;
 };
+constexpr int kIngestSpanBytes = 4096;
+constexpr int kIngestSpanFrags = 456;   // a fragment takes at least "#EXTINF:0" and a line break
+constexpr int kIngestSpanTags = 180;    // "#EXT-X-MEDIA-SEQUENCE:0" is 23 bytes
+constexpr int kIngestScanBlock = 1024;  // spans per block of the two-level scan
 struct AssembleParams {
     int n_tracks;
     const unsigned char *state;
@@ -167,6 +176,7 @@ struct AssembleParams {
 cudaError_t launch_ingest_tile_index(const long long *text_off, int n_tracks, int n_tiles, int *tile_tlo,
                                      int *tile_bfirst, cudaStream_t s);
 cudaError_t launch_ingest_scan(const IngestParams &p, cudaStream_t s);
+cudaError_t launch_ingest_compact(const IngestParams &p, cudaStream_t s);   // block scan, compaction, track offsets
 cudaError_t launch_ingest_assemble(const AssembleParams &p, bool warp_per_track, cudaStream_t s);
 
 // ---- JSON form of views (json.cu) -----------------------------------------------------------

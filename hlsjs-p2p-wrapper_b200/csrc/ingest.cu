@@ -293,20 +293,17 @@ struct TrackOffsets {
     }
 };
 
-// Shared state.  A tile is cut into one 4 KB span per warp; between the few CTA-wide barriers a
-// warp works on its own span with its own lists, so warps never wait for each other's parsing.
+// Shared state.  A tile is cut into one 4 KB span per warp; after the one barrier that makes the
+// whole tile's text visible (tokens may run from one span into the next) a warp works alone on its
+// span, with its own lists, and nothing in this kernel waits for another tile.
 struct WarpShared {
     unsigned short cpos[kWarpCap];   // tile-relative position of each candidate of the round
-    unsigned cmeta[kWarpCap];        // kind | fragments of the warp before it << 3 | tags before it << 16
-    long long cbits[kWarpCap];       // duration bits / sequence number
+    unsigned short cfpre[kWarpCap];  // fragments of the span before that candidate
 };
 struct Shared {
-    Scan::Smem scan;
     __align__(16) unsigned char text[kTile + 48];   // + room for the word fetches of classify_fast
     long long toff[kTrackStage];
     WarpShared w[kWarps];
-    unsigned wtot[kWarps];           // per warp: fragments | tags << 16
-    unsigned long long base[2];      // the tile's fragment / tag prefix, from the look-back
 };
 
 // One candidate: its track, what the expression matches there, whether an earlier match on the
@@ -353,15 +350,16 @@ __device__ __forceinline__ int classify_candidate(const IngestParams &p, const S
     return kind;
 }
 
-// Warp-wide: lists this warp's '#' bytes selected by `mine` lanes in text order, classifies them,
-// leaves kind / prefix / value per candidate in the warp's shared arrays.  Returns the round's
-// totals (fragments | tags << 16); `running` = the warp's totals of earlier rounds.
+// Warp-wide: lists this warp's '#' bytes (those of the lanes with my_first >= 0) in text order,
+// classifies them 32 at a time and leaves every fragment's duration and every sequence tag in
+// the span's staging slot, at its rank within the span.  Returns the round's totals (fragments |
+// tags << 16); `running` = the span's totals from earlier rounds.
 __device__ __forceinline__ unsigned warp_classify(const IngestParams &p, Shared &sh, WarpShared &ws,
                                                   const TrackOffsets &toff, int t_lo, int t_hi, long long lo,
-                                                  long long hi, const unsigned (&mask)[kGroups], int span_base,
-                                                  int my_first, int nc, unsigned running, bool effects)
+                                                  long long hi, const unsigned (&mask)[kGroups], int lane_base,
+                                                  int my_first, int nc, unsigned running, long long span)
 {
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (my_first >= 0) {
         int at = my_first;
 #pragma unroll
@@ -370,7 +368,7 @@ __device__ __forceinline__ unsigned warp_classify(const IngestParams &p, Shared 
             while (m) {
                 const int b = __ffs(m) - 1;
                 m &= m - 1;
-                ws.cpos[at++] = (unsigned short)(span_base + g * 32 + b);
+                ws.cpos[at++] = (unsigned short)(lane_base + g * 32 + b);
             }
         }
     }
@@ -380,14 +378,20 @@ __device__ __forceinline__ unsigned warp_classify(const IngestParams &p, Shared 
     for (int i0 = 0; i0 < nc; i0 += 32) {
         const int i = i0 + lane;
         long long bits = 0;
-        const int kind = i < nc ? classify_candidate(p, sh, toff, t_lo, t_hi, lo, hi, (int)ws.cpos[i], effects, bits)
-                                : kTokNone;
+        const int pos_rel = i < nc ? (int)ws.cpos[i] : 0;
+        const int kind = i < nc ? classify_candidate(p, sh, toff, t_lo, t_hi, lo, hi, pos_rel, true, bits) : kTokNone;
         const unsigned fb = __ballot_sync(0xffffffffu, kind == kTokFrag);
         const unsigned tb = __ballot_sync(0xffffffffu, kind == kTokSeq);
         if (i < nc) {
             const unsigned pre = running + run + ((unsigned)__popc(fb & below) | ((unsigned)__popc(tb & below) << 16));
-            ws.cmeta[i] = (unsigned)kind | ((pre & 0x1fffu) << 3) | (pre & 0xffff0000u);
-            ws.cbits[i] = bits;
+            const unsigned fpre = pre & 0xffffu, tpre = pre >> 16;
+            ws.cfpre[i] = (unsigned short)fpre;
+            if (kind == kTokFrag && p.stage_dur != nullptr && fpre < (unsigned)kIngestSpanFrags)
+                p.stage_dur[span * kIngestSpanFrags + fpre] = __longlong_as_double(bits);
+            if (kind == kTokSeq && p.stage_tag != nullptr && tpre < (unsigned)kIngestSpanTags)
+                p.stage_tag[span * kIngestSpanTags + tpre] =
+                    (unsigned long long)(unsigned)bits | ((unsigned long long)fpre << 32) |
+                    ((unsigned long long)(unsigned)(pos_rel - warp * kWarpBytes) << 48);
         }
         run += (unsigned)__popc(fb) | ((unsigned)__popc(tb) << 16);
     }
@@ -395,29 +399,14 @@ __device__ __forceinline__ unsigned warp_classify(const IngestParams &p, Shared 
     return run;
 }
 
-// Warp-wide: writes what warp_classify() left -- durations and sequence tags to their global slots,
-// and the fragment offset of every track whose text starts inside [b_lo, b_hi).
-__device__ __forceinline__ void warp_emit(const IngestParams &p, const WarpShared &ws, const TrackOffsets &toff,
-                                          int u0, int u1, long long lo, int nc, unsigned round_end,
-                                          unsigned long long fbase, unsigned long long tbase, long long b_lo,
-                                          long long b_hi)
+// Warp-wide: the fragment offset, relative to the span, of every track whose text starts inside
+// [b_lo, b_hi) -- the fragments before the first candidate at or after the track's first byte.
+// m3u8_track_offsets_kernel adds the span's base afterwards.
+__device__ __forceinline__ void warp_bounds(const IngestParams &p, const WarpShared &ws, const TrackOffsets &toff,
+                                            int u0, int u1, long long lo, int nc, unsigned round_end, long long b_lo,
+                                            long long b_hi)
 {
     const int lane = threadIdx.x & 31;
-    for (int i = lane; i < nc; i += 32) {
-        const unsigned meta = ws.cmeta[i];
-        const int kind = (int)(meta & 7u);
-        const unsigned long long f = fbase + ((meta >> 3) & 0x1fffu);
-        if (kind == kTokFrag) {
-            if ((long long)f < p.capacity) p.dur[f] = __longlong_as_double(ws.cbits[i]);
-        } else if (kind == kTokSeq) {
-            const unsigned long long j = tbase + (meta >> 16);
-            if ((long long)j < p.tag_capacity) {
-                p.tag_pos[j] = lo + ws.cpos[i];
-                p.tag_frag[j] = (long long)f;
-                p.tag_val[j] = (int)ws.cbits[i];
-            }
-        }
-    }
     for (int u = u0 + lane; u < u1; u += 32) {
         const long long b = toff(u);
         if (b < b_lo || b >= b_hi) continue;
@@ -428,97 +417,24 @@ __device__ __forceinline__ void warp_emit(const IngestParams &p, const WarpShare
             if ((long long)ws.cpos[mid] < rel) a = mid + 1;
             else z = mid;
         }
-        const unsigned fp = a < nc ? ((ws.cmeta[a] >> 3) & 0x1fffu) : (round_end & 0xffffu);
-        p.track_off[u] = (long long)(fbase + fp);
-    }
-}
-
-// Decoupled look-back over two status arrays at once, run by ONE warp (4 x 32 predecessors a
-// step, all eight loads in flight together) while the CTA's other warps wait at a barrier.
-__device__ void warp_lookback_pair(unsigned long long *status_f, unsigned long long *status_t, unsigned epoch, int tile,
-                                   unsigned long long agg_f, unsigned long long agg_t, unsigned long long &out_f,
-                                   unsigned long long &out_t)
-{
-    const int lane = threadIdx.x & 31;
-    constexpr int S = 4;
-    unsigned long long sum_f = 0, sum_t = 0;
-    if (tile > 0) {
-        int top_f = tile - 1, top_t = tile - 1;
-        bool done_f = false, done_t = false;
-        while (!(done_f && done_t)) {
-            unsigned long long wf[S], wt[S];
-#pragma unroll
-            for (int j = 0; j < S; j++) {
-                const int idf = top_f - (lane + 32 * j), idt = top_t - (lane + 32 * j);
-                wf[j] = (!done_f && idf >= 0) ? ld_relaxed_u64(&status_f[idf]) : 0ull;
-                wt[j] = (!done_t && idt >= 0) ? ld_relaxed_u64(&status_t[idt]) : 0ull;
-            }
-#pragma unroll
-            for (int a = 0; a < 2; a++) {
-                unsigned long long *status = a == 0 ? status_f : status_t;
-                const int top = a == 0 ? top_f : top_t;
-                if (a == 0 ? done_f : done_t) continue;
-                int my_first = 0x7fffffff;
-                unsigned long long val[S];
-#pragma unroll
-                for (int j = 0; j < S; j++) {
-                    const int d = lane + 32 * j, idx = top - d;
-                    unsigned long long w = a == 0 ? wf[j] : wt[j];
-                    bool is_prefix = true;         // idx < 0: the virtual tile -1 holds prefix 0
-                    val[j] = 0;
-                    if (idx >= 0) {
-                        while ((unsigned)(w >> 42) != (epoch & kEpochMask)) {
-                            __nanosleep(100);
-                            w = ld_relaxed_u64(&status[idx]);
-                        }
-                        val[j] = w & ((1ull << kValueBits) - 1ull);
-                        is_prefix = ((w >> kValueBits) & 3ull) == kStatePrefix;
-                    }
-                    if (is_prefix) my_first = min(my_first, d);
-                }
-                __syncwarp();
-#pragma unroll
-                for (int dd = 16; dd > 0; dd >>= 1) my_first = min(my_first, __shfl_xor_sync(0xffffffffu, my_first, dd));
-                unsigned long long c = 0;
-#pragma unroll
-                for (int j = 0; j < S; j++) c += (lane + 32 * j <= my_first) ? val[j] : 0ull;
-#pragma unroll
-                for (int dd = 16; dd > 0; dd >>= 1) c += __shfl_xor_sync(0xffffffffu, c, dd);
-                if (a == 0) {
-                    sum_f += c;
-                    done_f = my_first != 0x7fffffff;
-                    top_f -= 32 * S;
-                } else {
-                    sum_t += c;
-                    done_t = my_first != 0x7fffffff;
-                    top_t -= 32 * S;
-                }
-            }
-        }
-    }
-    out_f = sum_f;
-    out_t = sum_t;
-    if (lane == 0 && tile > 0) {
-        st_relaxed_u64(&status_f[tile], make_status(epoch, kStatePrefix, sum_f + agg_f));
-        st_relaxed_u64(&status_t[tile], make_status(epoch, kStatePrefix, sum_t + agg_t));
+        p.track_off[u] = (long long)(a < nc ? (unsigned)ws.cfpre[a] : (round_end & 0xffffu));
     }
 }
 
 }  // namespace
 
-__global__ void __launch_bounds__(kThreads, 7)
+__global__ void __launch_bounds__(kThreads, 8)
 m3u8_scan_kernel(const IngestParams p)
 {
     __shared__ Shared sh;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     WarpShared &ws = sh.w[warp];
-    for (;;) {
-        const int tile = Scan::next_tile(sh.scan, p.ctr, p.tslot);
-        if (tile >= p.n_tiles) break;
+    const long long open_end = 0x7fffffffffffffffll;
+    for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
         const long long lo = (long long)tile * kTile;
         const long long hi = lo + kTile < p.n_bytes ? lo + kTile : p.n_bytes;
         const bool last = tile == p.n_tiles - 1;
-        const long long open_end = 0x7fffffffffffffffll;
+        __syncthreads();     // the previous tile's text is no longer read by anyone
 
         // stage the tile (each warp its own 4 KB span, coalesced 16-byte pieces) and the text
         // offsets of the tracks the tile touches
@@ -545,12 +461,12 @@ m3u8_scan_kernel(const IngestParams p)
         __syncthreads();     // tokens may run from one warp's span into the next
 
         // the '#' bytes of this lane's 128 bytes, and their rank within the warp's span
-        const int span_base = warp * kWarpBytes + lane * kLaneBytes;
+        const int lane_base = warp * kWarpBytes + lane * kLaneBytes;
         unsigned mask[kGroups];
         int cnt = 0;
 #pragma unroll
         for (int g = 0; g < kGroups; g++) {
-            const unsigned char *at = sh.text + span_base + g * 32;
+            const unsigned char *at = sh.text + lane_base + g * 32;
             mask[g] = hash_mask16(*reinterpret_cast<const uint4 *>(at)) |
                       (hash_mask16(*reinterpret_cast<const uint4 *>(at + 16)) << 16);
             cnt += __popc(mask[g]);
@@ -563,74 +479,163 @@ m3u8_scan_kernel(const IngestParams p)
         }
         const int before = x - cnt;
         const int n_hash = __shfl_sync(0xffffffffu, x, 31);
-        const bool dense = n_hash > kWarpCap;      // warp-uniform
-
-        unsigned totals = 0;
-        if (!dense) {
-            totals = warp_classify(p, sh, ws, toff, t_lo, t_hi, lo, hi, mask, span_base, before, n_hash, 0u, true);
-        } else {
-            // a span dense with '#': rounds of 256 bytes (never more than kWarpCap candidates),
-            // classified twice -- now to count, after the look-back once more to write
-            for (int r = 0; r < kRounds; r++) {
-                const int r0 = __shfl_sync(0xffffffffu, before, r * kLanesPerRound);
-                const int r1n = __shfl_sync(0xffffffffu, before, ((r + 1) * kLanesPerRound) & 31);
-                const int r1 = r == kRounds - 1 ? n_hash : r1n;
-                const bool mine = lane / kLanesPerRound == r;
-                totals += warp_classify(p, sh, ws, toff, t_lo, t_hi, lo, hi, mask, span_base, mine ? before - r0 : -1,
-                                        r1 - r0, 0u, false);
-            }
-        }
-        if (lane == 0) sh.wtot[warp] = totals;
-        __syncthreads();
-        unsigned tile_totals = 0, warp_before = 0;
-#pragma unroll
-        for (int w = 0; w < kWarps; w++) {
-            const unsigned c = sh.wtot[w];
-            warp_before += w < warp ? c : 0u;
-            tile_totals += c;
-        }
-        if (warp == 0) {
-            if (lane == 0) {
-                const unsigned long long af = tile_totals & 0xffffu, at = tile_totals >> 16;
-                st_relaxed_u64(&p.status_f[tile], tile == 0 ? make_status(p.epoch, kStatePrefix, af)
-                                                            : make_status(p.epoch, kStateAggregate, af));
-                st_relaxed_u64(&p.status_t[tile], tile == 0 ? make_status(p.epoch, kStatePrefix, at)
-                                                            : make_status(p.epoch, kStateAggregate, at));
-            }
-            unsigned long long bf = 0, bt = 0;
-            warp_lookback_pair(p.status_f, p.status_t, p.epoch, tile, tile_totals & 0xffffu, tile_totals >> 16, bf, bt);
-            if (lane == 0) {
-                sh.base[0] = bf;
-                sh.base[1] = bt;
-                if (last) {
-                    p.out->n_fragments = bf + (tile_totals & 0xffffu);
-                    p.out->n_tags = bt + (tile_totals >> 16);
-                }
-            }
-        }
-        __syncthreads();
-        const unsigned long long fbase = sh.base[0] + (warp_before & 0xffffu);
-        const unsigned long long tbase = sh.base[1] + (warp_before >> 16);
+        const long long span = (long long)tile * kWarps + warp;
         const long long w_lo = lo + (long long)warp * kWarpBytes;
         const long long w_hi = warp == kWarps - 1 ? (last ? open_end : lo + kTile) : w_lo + kWarpBytes;
-        if (!dense) {
-            warp_emit(p, ws, toff, u0, u1, lo, n_hash, totals, fbase, tbase, w_lo, w_hi);
+
+        unsigned totals = 0;
+        if (n_hash <= kWarpCap) {
+            totals = warp_classify(p, sh, ws, toff, t_lo, t_hi, lo, hi, mask, lane_base, before, n_hash, 0u, span);
+            warp_bounds(p, ws, toff, u0, u1, lo, n_hash, totals, w_lo, w_hi);
         } else {
-            unsigned running = 0;
+            // a span dense with '#': rounds of 256 bytes, never more than kWarpCap candidates each
             for (int r = 0; r < kRounds; r++) {
                 const int r0 = __shfl_sync(0xffffffffu, before, r * kLanesPerRound);
                 const int r1n = __shfl_sync(0xffffffffu, before, ((r + 1) * kLanesPerRound) & 31);
                 const int r1 = r == kRounds - 1 ? n_hash : r1n;
                 const bool mine = lane / kLanesPerRound == r;
-                running += warp_classify(p, sh, ws, toff, t_lo, t_hi, lo, hi, mask, span_base, mine ? before - r0 : -1,
-                                         r1 - r0, running, true);
+                totals += warp_classify(p, sh, ws, toff, t_lo, t_hi, lo, hi, mask, lane_base, mine ? before - r0 : -1,
+                                        r1 - r0, totals, span);
                 const long long b_lo = w_lo + (long long)r * kRoundBytes;
                 const long long b_hi = r == kRounds - 1 ? w_hi : b_lo + kRoundBytes;
-                warp_emit(p, ws, toff, u0, u1, lo, r1 - r0, running, fbase, tbase, b_lo, b_hi);
+                warp_bounds(p, ws, toff, u0, u1, lo, r1 - r0, totals, b_lo, b_hi);
                 __syncwarp();
             }
         }
+        if (lane == 0) {
+            p.span_cnt[span] = totals;
+            const long long blk = span / kIngestScanBlock;
+            if (totals & 0xffffu) atomicAdd(&p.block_sum[2 * blk], (unsigned long long)(totals & 0xffffu));
+            if (totals >> 16) atomicAdd(&p.block_sum[2 * blk + 1], (unsigned long long)(totals >> 16));
+        }
     }
+}
+
+// ---- from per-span slots to the final columns ----------------------------------------------
+// Two-level exclusive scan of the span counts: m3u8_scan_kernel already summed them per block of
+// 1024 spans (atomics); one CTA scans the block sums, then every block rescans its own spans.
+__global__ void __launch_bounds__(1024)
+m3u8_block_scan_kernel(const IngestParams p)
+{
+    __shared__ unsigned long long wsum[2][32];
+    __shared__ unsigned long long carry[2];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid < 2) carry[tid] = 0;
+    __syncthreads();
+    for (int b0 = 0; b0 < p.n_blocks; b0 += 1024) {
+        const int b = b0 + tid;
+        unsigned long long v[2], x[2];
+#pragma unroll
+        for (int a = 0; a < 2; a++) {
+            v[a] = b < p.n_blocks ? p.block_sum[2 * b + a] : 0ull;
+            x[a] = v[a];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const unsigned long long y = __shfl_up_sync(0xffffffffu, x[a], d);
+                if (lane >= d) x[a] += y;
+            }
+            if (lane == 31) wsum[a][warp] = x[a];
+        }
+        __syncthreads();
+#pragma unroll
+        for (int a = 0; a < 2; a++) {
+            unsigned long long before = carry[a], all = 0;
+            for (int w = 0; w < 32; w++) {
+                const unsigned long long c = wsum[a][w];
+                before += w < warp ? c : 0ull;
+                all += c;
+            }
+            if (b < p.n_blocks) p.block_base[2 * b + a] = before + x[a] - v[a];
+            __syncthreads();
+            if (tid == 0) carry[a] += all;
+        }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        p.block_base[2 * p.n_blocks] = carry[0];
+        p.block_base[2 * p.n_blocks + 1] = carry[1];
+        p.out->n_fragments = carry[0];
+        p.out->n_tags = carry[1];
+    }
+}
+
+// One CTA per block of 1024 spans: scan the block's span counts on top of the block's base.
+__global__ void __launch_bounds__(256)
+m3u8_span_base_kernel(const IngestParams p)
+{
+    __shared__ unsigned wsum[2][8];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const long long s0 = (long long)blockIdx.x * kIngestScanBlock;
+    unsigned c[4], f[4], t[4], fs = 0, ts = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const long long s = s0 + tid * 4 + k;
+        c[k] = s < p.n_spans ? p.span_cnt[s] : 0u;
+        f[k] = fs;
+        t[k] = ts;
+        fs += c[k] & 0xffffu;
+        ts += c[k] >> 16;
+    }
+    unsigned xf = fs, xt = ts;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const unsigned yf = __shfl_up_sync(0xffffffffu, xf, d), yt = __shfl_up_sync(0xffffffffu, xt, d);
+        if (lane >= d) {
+            xf += yf;
+            xt += yt;
+        }
+    }
+    if (lane == 31) {
+        wsum[0][warp] = xf;
+        wsum[1][warp] = xt;
+    }
+    __syncthreads();
+    unsigned bf = xf - fs, bt = xt - ts;
+    for (int w = 0; w < warp; w++) {
+        bf += wsum[0][w];
+        bt += wsum[1][w];
+    }
+    const unsigned long long base_f = p.block_base[2 * blockIdx.x], base_t = p.block_base[2 * blockIdx.x + 1];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const long long s = s0 + tid * 4 + k;
+        if (s < p.n_spans) {
+            p.span_base[2 * s] = base_f + bf + f[k];
+            p.span_base[2 * s + 1] = base_t + bt + t[k];
+        }
+    }
+}
+
+// A warp per span: the span's staged durations and tags go to their final, compact places
+// (coalesced both ways).
+__global__ void __launch_bounds__(256)
+m3u8_copy_kernel(const IngestParams p)
+{
+    const int lane = threadIdx.x & 31;
+    const long long s = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (s >= p.n_spans) return;
+    const unsigned cnt = p.span_cnt[s];
+    const int nf = (int)(cnt & 0xffffu), nt = (int)(cnt >> 16);
+    const unsigned long long f0 = p.span_base[2 * s], t0 = p.span_base[2 * s + 1];
+    for (int j = lane; j < nf; j += 32)
+        if ((long long)(f0 + j) < p.capacity) p.dur[f0 + j] = p.stage_dur[s * kIngestSpanFrags + j];
+    for (int j = lane; j < nt; j += 32) {
+        if ((long long)(t0 + j) >= p.tag_capacity) continue;
+        const unsigned long long e = p.stage_tag[s * kIngestSpanTags + j];
+        p.tag_val[t0 + j] = (int)(unsigned)e;
+        p.tag_frag[t0 + j] = (long long)(f0 + ((e >> 32) & 0xffffull));
+        p.tag_pos[t0 + j] = s * kIngestSpanBytes + (long long)(e >> 48);
+    }
+}
+
+// track_off[u] holds the fragments of u's span that come before u's first byte: add the span's base.
+__global__ void m3u8_track_offsets_kernel(const IngestParams p)
+{
+    const long long u = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (u > p.n_tracks) return;
+    long long s = p.text_off[u] / kIngestSpanBytes;
+    if (s > p.n_spans - 1) s = p.n_spans - 1;
+    p.track_off[u] += (long long)p.span_base[2 * s];
 }
 
 // First track of every tile, so that a candidate finds its track in a few steps.
@@ -762,6 +767,16 @@ cudaError_t launch_ingest_scan(const IngestParams &p, cudaStream_t s)
     if (grid > p.n_tiles) grid = p.n_tiles;
     if (grid < 1) return cudaSuccess;
     m3u8_scan_kernel<<<grid, kThreads, 0, s>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_ingest_compact(const IngestParams &p, cudaStream_t s)
+{
+    if (p.n_spans < 1) return cudaSuccess;
+    m3u8_block_scan_kernel<<<1, 1024, 0, s>>>(p);
+    m3u8_span_base_kernel<<<p.n_blocks, 256, 0, s>>>(p);
+    if (p.stage_dur != nullptr) m3u8_copy_kernel<<<(unsigned)((p.n_spans + 7) / 8), 256, 0, s>>>(p);
+    m3u8_track_offsets_kernel<<<(unsigned)((p.n_tracks + 1 + 255) / 256), 256, 0, s>>>(p);
     return cudaGetLastError();
 }
 
