@@ -1789,13 +1789,9 @@ int ingest_core(hlsmap_ctx *ctx, int32_t n_tracks, const uint8_t *d_state, const
             launches += fill ? 6 : 5;
         }
         if (timing) cudaEventRecord(ev[2], s);
-        CK(cudaMemcpyAsync(&h, p.out, sizeof h, cudaMemcpyDeviceToHost, s));
-        CK(cudaStreamSynchronize(s));
-        if ((int64_t)h.n_tags > tag_cap) {     // more sequence tags than tracks*2: size exactly, redo
-            tag_cap = (int64_t)h.n_tags;
-            continue;
-        }
-        if (fill && (int64_t)h.n_fragments <= capacity && n_tracks > 0) {
+        // the per-track assembly follows without a host round trip: it reads the counters itself
+        // and steps aside when the columns or the tag list are too small
+        if (fill && n_tracks > 0) {
             AssembleParams a{};
             a.n_tracks = n_tracks;
             a.state = d_state;
@@ -1805,24 +1801,31 @@ int ingest_core(hlsmap_ctx *ctx, int32_t n_tracks, const uint8_t *d_state, const
             a.tag_pos = p.tag_pos;
             a.tag_frag = p.tag_frag;
             a.tag_val = p.tag_val;
-            a.n_tags = (long long)h.n_tags;
+            a.capacity = capacity;
+            a.tag_capacity = tag_cap;
             a.start = d_start;
             a.sn = d_sn;
             a.dur0 = d_dur0 ? d_dur0 : (double *)(b + o_d0);
             a.out = p.out;
-            CK(launch_ingest_assemble(a, (int64_t)h.n_fragments >= (int64_t)n_tracks * 24, s));
+            CK(launch_ingest_assemble(a, n_bytes >= (int64_t)n_tracks * 768, s));   // long tracks: a warp each
             launches++;
-            if (timing) cudaEventRecord(ev[3], s);
-            CK(cudaMemcpyAsync(&h, p.out, sizeof h, cudaMemcpyDeviceToHost, s));
-            CK(cudaStreamSynchronize(s));
-            if (timing && n_tiles > 0) {
-                float t_idx = 0, t_scan = 0, t_asm = 0;
-                cudaEventElapsedTime(&t_idx, ev[0], ev[1]);
-                cudaEventElapsedTime(&t_scan, ev[1], ev[2]);
-                cudaEventElapsedTime(&t_asm, ev[2], ev[3]);
-                fprintf(stderr, "[hlsmap ingest] tile index %.1f us, scan %.1f us, counters+assemble %.1f us\n",
-                        1e3 * t_idx, 1e3 * t_scan, 1e3 * t_asm);
-            }
+        }
+        if (timing) cudaEventRecord(ev[3], s);
+        CK(cudaMemcpyAsync(&h, p.out, sizeof h, cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+        if (timing && n_tiles > 0) {
+            float t_idx = 0, t_scan = 0, t_asm = 0;
+            cudaEventElapsedTime(&t_idx, ev[0], ev[1]);
+            cudaEventElapsedTime(&t_scan, ev[1], ev[2]);
+            cudaEventElapsedTime(&t_asm, ev[2], ev[3]);
+            fprintf(stderr, "[hlsmap ingest] tile index %.1f us, scan+compact %.1f us, assemble %.1f us\n", 1e3 * t_idx,
+                    1e3 * t_scan, 1e3 * t_asm);
+        }
+        if ((int64_t)h.n_tags > tag_cap) {     // more sequence tags than tracks*2: size exactly, redo
+            tag_cap = (int64_t)h.n_tags;
+            if (timing)
+                for (auto &e : ev) cudaEventDestroy(e);
+            continue;
         }
         if (timing)
             for (auto &e : ev) cudaEventDestroy(e);

@@ -167,7 +167,7 @@ struct AssembleParams {
     const double *dur;
     const long long *tag_pos, *tag_frag;
     const int *tag_val;
-    long long n_tags;
+    long long capacity, tag_capacity;   // of the start/sn/dur columns and of the tag list
     double *start;
     int *sn;
     double *dur0;

@@ -677,47 +677,95 @@ template <int LANES>
 __global__ void __launch_bounds__(256)
 m3u8_assemble_kernel(const AssembleParams p)
 {
+    __shared__ __align__(16) double chunk[LANES == 1 ? 1 : 8][32];
     const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const long long t = gid / LANES;
     const int lane = (int)(gid % LANES);
     if (t >= p.n_tracks) return;
+    // launched without a host round trip after the scan: step aside if the caller's columns or the
+    // tag list turned out too small (the host sees the same counters and reports / retries)
+    const long long n_tags_seen = (long long)p.out->n_tags;
+    if ((long long)p.out->n_fragments > p.capacity || n_tags_seen > p.tag_capacity) return;
     const bool parsed = p.state == nullptr || p.state[t] == HLSMAP_TRACK_PARSED;
     const long long off = p.track_off[t], len = p.track_off[t + 1] - off;
     if (lane == 0) p.dur0[t] = (parsed && len > 0) ? p.dur[off] : __longlong_as_double(0x7ff8000000000000ll);
     if (!parsed || len == 0) return;
     // sequence tags of this track: those whose position lies in its text
     const long long tb = p.text_off[t], te = p.text_off[t + 1];
-    long long e = 0, z = p.n_tags;
-    while (e < z) {
-        const long long mid = (e + z) >> 1;
-        if (p.tag_pos[mid] < tb) e = mid + 1;
-        else z = mid;
+    // (first tag at or after the track's first byte; with one tag per playlist, as usual, that is
+    // tag number t, which two independent loads confirm -- else the binary search)
+    long long e = 0, z = n_tags_seen;
+    if (t < n_tags_seen && p.tag_pos[t] >= tb && (t == 0 || p.tag_pos[t - 1] < tb)) {
+        e = t;
+    } else {
+        while (e < z) {
+            const long long mid = (e + z) >> 1;
+            if (p.tag_pos[mid] < tb) e = mid + 1;
+            else z = mid;
+        }
     }
     long long cur = 0;
     double total = 0.0;
     bool overflow = false;
     const long long none = 0x7fffffffffffffffll;
-    long long next_tag = (e < p.n_tags && p.tag_pos[e] < te) ? p.tag_frag[e] : none;
+    long long next_tag = (e < n_tags_seen && p.tag_pos[e] < te) ? p.tag_frag[e] : none;
+    constexpr int kAhead = 4;                  // chunks whose loads are in flight together
+    double ahead[kAhead];
+#pragma unroll
+    for (int k = 0; k < kAhead; k++) ahead[k] = lane + k * LANES < len ? p.dur[off + lane + k * LANES] : 0.0;
     for (long long c = 0; c < len; c += LANES) {
         const long long i = c + lane;
-        const double d = i < len ? p.dur[off + i] : 0.0;
+        const int slot = (int)((c / LANES) % kAhead);
+        double d = 0.0;
+#pragma unroll
+        for (int k = 0; k < kAhead; k++) d = slot == k ? ahead[k] : d;
+        if (slot == kAhead - 1) {              // the window is used up: fetch the next kAhead chunks at once
+#pragma unroll
+            for (int k = 0; k < kAhead; k++) {
+                const long long ii = i + (long long)(k + 1) * LANES;
+                ahead[k] = ii < len ? p.dur[off + ii] : 0.0;
+            }
+        }
         const int n = len - c < LANES ? (int)(len - c) : LANES;
+        // tags sitting right at the chunk's first fragment (the usual one: the playlist's header)
+        while (next_tag <= off + c) {
+            cur = p.tag_val[e++];
+            next_tag = (e < n_tags_seen && p.tag_pos[e] < te) ? p.tag_frag[e] : none;
+        }
         long long my_sn = 0;
         double my_start = 0.0;
         if (next_tag > off + c + n - 1) {          // numbering runs straight through the chunk
             my_sn = cur + lane;
             cur += n;
-            // lanes past the end hold 0.0, and total + 0.0 == total: the chain can always run its
-            // full, unrolled length
+            if (LANES == 1) {
+                my_start = total;
+                total += d;
+            } else {
+                // Lane L needs total + d0 + ... + d(L-1), added in that order.  The 32 durations go
+                // through shared memory (one broadcast 16-byte load brings two of them to every
+                // lane) and each lane adds only the ones before its own: 2.5 instructions per
+                // fragment instead of shuffling every value to a chain every lane replays in full.
+                // Lanes past the end hold 0.0, and x + 0.0 == x, so the loop has a fixed length.
+                double *mine = chunk[threadIdx.x >> 5];
+                __syncwarp();
+                mine[lane] = d;
+                __syncwarp();
+                double acc = total;
 #pragma unroll
-            for (int j = 0; j < LANES; j++) {
-                const double dj = LANES == 1 ? d : __shfl_sync(0xffffffffu, d, j);
-                if (j == lane) my_start = total;
-                total += dj;
+                for (int j = 0; j < LANES; j += 2) {
+                    const double2 dd = *reinterpret_cast<const double2 *>(mine + j);
+                    if (j < lane) acc += dd.x;
+                    if (j + 1 < lane) acc += dd.y;
+                }
+                my_start = acc;
+                total = __shfl_sync(0xffffffffu, acc + d, LANES - 1);
             }
-        } else {
+        } else {                                   // a tag in the middle of the chunk
             for (int j = 0; j < n; j++) {
-                while (e < p.n_tags && p.tag_pos[e] < te && p.tag_frag[e] <= off + c + j) cur = p.tag_val[e++];
+                while (next_tag <= off + c + j) {
+                    cur = p.tag_val[e++];
+                    next_tag = (e < n_tags_seen && p.tag_pos[e] < te) ? p.tag_frag[e] : none;
+                }
                 const double dj = LANES == 1 ? d : __shfl_sync(0xffffffffu, d, j);
                 if (j == lane) {
                     my_start = total;
@@ -726,7 +774,6 @@ m3u8_assemble_kernel(const AssembleParams p)
                 total += dj;
                 cur++;
             }
-            next_tag = (e < p.n_tags && p.tag_pos[e] < te) ? p.tag_frag[e] : none;
         }
         if (i < len) {
             overflow |= my_sn > 0x7fffffffll;
