@@ -205,8 +205,11 @@ HLSMAP_HD inline bool swar_scan_decimal16(unsigned long long x0, unsigned long l
     const unsigned ip = ni ? swar_parse8(x0 << (8 * (8 - ni))) : 0u;
     unsigned fp = 0;
     if (nfrac) fp = swar_parse8(swar_bytes_from(x0, x1, pd + 1) << (8 * (8 - nfrac)));
-    unsigned long long p10 = 1;
-    for (int i = 0; i < nfrac; i++) p10 *= 10ull;
+    unsigned p10 = 1u;                                  // 10^nfrac, nfrac <= 8, without a loop
+    if (nfrac & 1) p10 *= 10u;
+    if (nfrac & 2) p10 *= 100u;
+    if (nfrac & 4) p10 *= 10000u;
+    if (nfrac & 8) p10 *= 100000000u;
     *w = (unsigned long long)ip * p10 + fp;
     *nf = nfrac;
     return true;

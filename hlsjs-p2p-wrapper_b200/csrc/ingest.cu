@@ -453,6 +453,10 @@ m3u8_scan_kernel(const IngestParams p)
             }
             *reinterpret_cast<uint4 *>(sh.text + piece * 16) = w;
         }
+        {   // the tile this CTA takes next: one 128-byte line per thread on its way to L2
+            const long long nx = lo + (long long)gridDim.x * kTile + (long long)tid * 128;
+            if (nx < p.n_bytes) asm volatile("prefetch.global.L2 [%0];" ::"l"(p.text + nx));
+        }
         const int t_lo = p.tile_tlo[tile], t_hi = p.tile_tlo[tile + 1];
         const int u0 = p.tile_bfirst[tile], u1 = p.tile_bfirst[tile + 1];
         const int n_staged = t_hi + 2 - t_lo < kTrackStage ? t_hi + 2 - t_lo : kTrackStage;
