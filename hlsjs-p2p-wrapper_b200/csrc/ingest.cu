@@ -22,6 +22,8 @@
 // -- `start` is a running fp64 sum, which must be added in the reference's order to give the
 // reference's bits -- is left to m3u8_assemble_kernel: one thread (short tracks) or one warp
 // (long tracks) per track walks its durations once.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "decimal.cuh"
 #include "scan.cuh"
@@ -788,6 +790,135 @@ m3u8_assemble_kernel(const AssembleParams p)
     if (overflow) atomicAdd(&p.out->n_unsupported, 1ull);
 }
 
+// ---- long tracks: 32 tracks per CTA, a lane per track ------------------------------------------
+// The running sum of a track is a chain nobody can shorten, but 32 lanes can each walk their own
+// track's chain at once instead of all replaying one.  Durations travel through a shared-memory
+// tile [track][32 fragments]: filled with coalesced asynchronous copies one round ahead (a row per
+// track, the rows shared out over the CTA's four warps), walked along the rows by warp 0 (lane =
+// track), written back out along the columns by all four warps again.
+constexpr int kAsmWarps = 8;
+__global__ void __launch_bounds__(32 * kAsmWarps)
+m3u8_assemble_tracks_kernel(const AssembleParams p)
+{
+    __shared__ __align__(16) double tile[2][32][33];      // [buffer][track][fragment], padded rows
+    __shared__ int sn_tile[32][33];
+    __shared__ __align__(16) longlong2 span_of[32];       // per track: {first fragment, fragments}
+    __shared__ long long maxlen_s;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long long n_tags_seen = (long long)p.out->n_tags;
+    if ((long long)p.out->n_fragments > p.capacity || n_tags_seen > p.tag_capacity) return;
+    // per-track state lives in warp 0: lane = track
+    const long long t = (long long)blockIdx.x * 32 + lane;
+    const long long none = 0x7fffffffffffffffll;
+    long long off = 0, len = 0, e = 0, te = 0, next_tag = none, cur = 0;
+    double total = 0.0;
+    bool overflow = false;
+    if (warp == 0) {
+        const bool valid = t < p.n_tracks;
+        const bool parsed = valid && (p.state == nullptr || p.state[t] == HLSMAP_TRACK_PARSED);
+        off = valid ? p.track_off[t] : 0;
+        len = parsed ? p.track_off[t + 1] - off : 0;
+        if (valid) p.dur0[t] = len > 0 ? p.dur[off] : __longlong_as_double(0x7ff8000000000000ll);
+        if (len > 0) {          // sequence tags of this lane's track (see m3u8_assemble_kernel)
+            const long long tb = p.text_off[t];
+            te = p.text_off[t + 1];
+            long long z = n_tags_seen;
+            if (t < n_tags_seen && p.tag_pos[t] >= tb && (t == 0 || p.tag_pos[t - 1] < tb)) {
+                e = t;
+            } else {
+                while (e < z) {
+                    const long long mid = (e + z) >> 1;
+                    if (p.tag_pos[mid] < tb) e = mid + 1;
+                    else z = mid;
+                }
+            }
+            next_tag = (e < n_tags_seen && p.tag_pos[e] < te) ? p.tag_frag[e] : none;
+        }
+        long long m = len;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            const long long o = __shfl_xor_sync(0xffffffffu, m, d);
+            m = o > m ? o : m;
+        }
+        span_of[lane] = make_longlong2(off, len);
+        if (lane == 0) maxlen_s = m;
+    }
+    __syncthreads();
+    const long long maxlen = maxlen_s;
+
+    // fills buffer b with fragments [c, c + 32) of the 32 tracks: warp w takes rows 8w .. 8w+7
+    auto fill = [&](int b, long long c) {
+#pragma unroll
+        for (int kk = 0; kk < 32 / kAsmWarps; kk++) {
+            const int k = warp * (32 / kAsmWarps) + kk;
+            const longlong2 sk = span_of[k];
+            double *dst = &tile[b][k][lane];
+            if (c + lane < sk.y) {
+                const unsigned sa = (unsigned)__cvta_generic_to_shared(dst);
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"(p.dur + sk.x + c + lane) : "memory");
+            } else {
+                *dst = 0.0;
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+
+    int buf = 0;
+    if (maxlen > 0) fill(0, 0);
+    for (long long c = 0; c < maxlen; c += 32) {
+        if (c + 32 < maxlen) {
+            fill(buf ^ 1, c + 32);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+        __syncthreads();
+        if (warp == 0) {        // lane = track: walk the row in order
+            const int n = len - c >= 32 ? 32 : (len > c ? (int)(len - c) : 0);
+            double *row = tile[buf][lane];
+            int *snrow = sn_tile[lane];
+            if (next_tag > off + c + n - 1) {          // no tag inside: numbering runs straight through
+#pragma unroll
+                for (int j = 0; j < 32; j++) {
+                    const double d = row[j];           // 0.0 past the end: total + 0.0 == total
+                    row[j] = total;
+                    total += d;
+                    snrow[j] = (int)(cur + j);
+                }
+                overflow |= n > 0 && cur + n - 1 > 0x7fffffffll;
+                cur += n;
+            } else {
+                for (int j = 0; j < n; j++) {
+                    while (next_tag <= off + c + j) {
+                        cur = p.tag_val[e++];
+                        next_tag = (e < n_tags_seen && p.tag_pos[e] < te) ? p.tag_frag[e] : none;
+                    }
+                    const double d = row[j];
+                    row[j] = total;
+                    total += d;
+                    overflow |= cur > 0x7fffffffll;
+                    snrow[j] = (int)cur;
+                    cur++;
+                }
+            }
+        }
+        __syncthreads();
+        // lane = fragment: write the columns out, a track at a time
+#pragma unroll
+        for (int kk = 0; kk < 32 / kAsmWarps; kk++) {
+            const int k = warp * (32 / kAsmWarps) + kk;
+            const longlong2 sk = span_of[k];
+            if (c + lane < sk.y) {
+                p.start[sk.x + c + lane] = tile[buf][k][lane];
+                p.sn[sk.x + c + lane] = sn_tile[k][lane];
+            }
+        }
+        __syncthreads();
+        buf ^= 1;
+    }
+    if (overflow) atomicAdd(&p.out->n_unsupported, 1ull);
+}
+
 // ---- launchers ---------------------------------------------------------------------------
 int ingest_scan_max_grid()
 {
@@ -834,9 +965,12 @@ cudaError_t launch_ingest_compact(const IngestParams &p, cudaStream_t s)
 cudaError_t launch_ingest_assemble(const AssembleParams &p, bool warp_per_track, cudaStream_t s)
 {
     if (p.n_tracks <= 0) return cudaSuccess;
-    if (warp_per_track) {
+    static const bool old_warp = getenv("HLSMAP_ASSEMBLE_WARP") != nullptr;     // diagnostics: the warp-per-track form
+    if (warp_per_track && old_warp) {
         const long long threads = (long long)p.n_tracks * 32;
         m3u8_assemble_kernel<32><<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(p);
+    } else if (warp_per_track) {
+        m3u8_assemble_tracks_kernel<<<(unsigned)((p.n_tracks + 31) / 32), 32 * kAsmWarps, 0, s>>>(p);
     } else {
         m3u8_assemble_kernel<1><<<(unsigned)((p.n_tracks + 255) / 256), 256, 0, s>>>(p);
     }
