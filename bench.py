@@ -448,6 +448,32 @@ def run_ours(args):
     h2d = 24 * nq * world                               # all ranks, per step
     d2h = (4 * (nq + 1) + 12 * s0["hits"]) * world
 
+    # the same queries through the range form (first index + count per query: 9 B back instead of
+    # 12 B per hit) -- what a PCIe-bound deployment would call; reported beside e2e, not instead of it
+    e2e_range = None
+    if rank == 0 and world == 1:
+        import ctypes
+        from hlsjs_p2p_wrapper_b200 import _native as N
+        rp = {k: ctx.pinned(nq, dt) for k, dt in (("first", np.int32), ("count", np.int32), ("st", np.uint8))}
+        pv = lambda a: ctypes.c_void_p(a.ctypes.data)
+
+        def range_step():
+            N.check(N.load().hlsmap_get_segment_range(dmap._h, nq, pv(pins["pl"].array), pv(pins["lv"].array),
+                                                      pv(pins["bg"].array), pv(pins["du"].array),
+                                                      pv(rp["first"].array), pv(rp["count"].array), pv(rp["st"].array)))
+        for _ in range(3):
+            range_step()
+        t0 = time.perf_counter()
+        for _ in range(args.e2e_steps):
+            range_step()
+        dt_r = time.perf_counter() - t0
+        assert int(rp["count"].array.astype(np.int64).sum()) == s0["hits"]
+        e2e_range = {"value": nq * args.e2e_steps / dt_r, "unit": UNIT, "ms_per_step": 1e3 * dt_r / args.e2e_steps,
+                     "h2d_bytes_per_step": 24 * nq, "d2h_bytes_per_step": 9 * nq,
+                     "api": "hlsmap_get_segment_range (host pointers, pinned)"}
+        for v in rp.values():
+            v.free()
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         threads = host_threads()
@@ -493,7 +519,7 @@ def run_ours(args):
                     "api": "hlsmap_get_segment_list (host pointers, pinned)",
                     "kernel_launches_per_step": e2e_launches},
             "gpu_launches": args.steps * world, "clocks": clocks, "node": node_version(),
-            "other_rows": rows,
+            "other_rows": rows, "e2e_range_form": e2e_range,
         }
         print(json.dumps(line))
     for p in pins.values():
