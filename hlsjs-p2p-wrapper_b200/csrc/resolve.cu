@@ -863,6 +863,7 @@ build_hint_kernel(const double *__restrict__ start, const TrackDesc *__restrict_
 // =========================================================================================
 namespace {
 constexpr int kFThreads = 256;
+constexpr int kFMaskWords = 32;
 constexpr int kFWarps = kFThreads / 32;
 using FScan = TileScan<kFThreads>;
 static_assert(kFThreads == kFilterTileQueries, "filter tile = one query per thread");
@@ -873,6 +874,9 @@ resolve_filter_kernel(const ResolveParams p)
 {
     __shared__ FScan::Smem scan;
     __shared__ unsigned long long warp_cnt[kFWarps];
+    // which fragments pass 1 kept, 32 per word, for tracks of up to 32 * kFMaskWords fragments: pass 2
+    // then visits only the words that hold a hit instead of comparing the whole track again
+    __shared__ unsigned kept[kFWarps][32][kFMaskWords];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned lane_lt = (1u << lane) - 1u;
 
@@ -905,14 +909,21 @@ resolve_filter_kernel(const ResolveParams p)
             const double jbg = __shfl_sync(0xffffffffu, bg, j);
             const double jub = __shfl_sync(0xffffffffu, ub, j);
             int c = 0;
-            for (int i0 = 0; i0 < jlen; i0 += 32) {
-                const int i = i0 + lane;
-                bool keep = false;
-                if (i < jlen) {
-                    const double s = __ldg(p.start + joff + i);
-                    keep = (jbg <= s) && (s <= jub);
+            for (int i0 = 0; i0 < jlen; i0 += 128) {       // four words of 32 fragments, loads in flight together
+                double s[4];
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const int i = i0 + 32 * k + lane;
+                    s[k] = i < jlen ? __ldg(p.start + joff + i) : __longlong_as_double(0x7ff8000000000000ll);
                 }
-                c += __popc(__ballot_sync(0xffffffffu, keep));
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const bool keep = (jbg <= s[k]) && (s[k] <= jub);      // NaN past the end: never kept
+                    const unsigned ball = __ballot_sync(0xffffffffu, keep);
+                    const int w = (i0 >> 5) + k;
+                    if (lane == 0 && w < kFMaskWords) kept[warp][j][w] = ball;
+                    c += __popc(ball);
+                }
             }
             if (lane == j) mycnt = c;
         }
@@ -949,15 +960,24 @@ resolve_filter_kernel(const ResolveParams p)
                 const double jbg = __shfl_sync(0xffffffffu, bg, j);
                 const double jub = __shfl_sync(0xffffffffu, ub, j);
                 long long out = (long long)__shfl_sync(0xffffffffu, my_base, j);
+                __syncwarp();
                 for (int i0 = 0; i0 < jlen; i0 += 32) {
                     const int i = i0 + lane;
                     bool keep = false;
                     double s = 0.0;
-                    if (i < jlen) {
-                        s = __ldg(p.start + joff + i);
-                        keep = (jbg <= s) && (s <= jub);
+                    unsigned ball;
+                    if (i0 < 32 * kFMaskWords) {           // remembered from pass 1
+                        ball = kept[warp][j][i0 >> 5];
+                        if (ball == 0u) continue;          // warp-uniform: nothing kept in these 32
+                        keep = (ball >> lane) & 1u;
+                        if (keep) s = __ldg(p.start + joff + i);
+                    } else {
+                        if (i < jlen) {
+                            s = __ldg(p.start + joff + i);
+                            keep = (jbg <= s) && (s <= jub);
+                        }
+                        ball = __ballot_sync(0xffffffffu, keep);
                     }
-                    const unsigned ball = __ballot_sync(0xffffffffu, keep);
                     if (keep) {
                         const long long o = out + __popc(ball & lane_lt);
                         if (o < p.capacity) {
