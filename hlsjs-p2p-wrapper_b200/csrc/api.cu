@@ -1563,8 +1563,10 @@ int hlsmap_view_to_json_dev(hlsmap_ctx *ctx, int64_t n, const int32_t *d_level, 
     }
     const int64_t n_tiles = (n + kJsonTileViews - 1) / kJsonTileViews;
     if (n_tiles > 0x7fffffff) return fail(HLSMAP_ERR_INVALID, "batch too large: split it");
-    r = prepare_scan(ctx, n_tiles, s);
-    if (r) return r;
+    void *st_d = nullptr, *st_m = nullptr, *st_b = nullptr;      // grow-only context scratch
+    if ((r = ensure_slot(ctx, 8, n * 8, &st_d)) || (r = ensure_slot(ctx, 9, n * 4, &st_m)) ||
+        (r = ensure_slot(ctx, 10, (n_tiles + 1) * 16, &st_b)))
+        return r;
     JsonWriteParams p{};
     p.n = n;
     p.level = d_level;
@@ -1574,16 +1576,15 @@ int hlsmap_view_to_json_dev(hlsmap_ctx *ctx, int64_t n, const int32_t *d_level, 
     p.offsets = d_offsets;
     p.chars = d_chars;
     p.capacity = capacity;
-    p.tile_status = status_of(ctx);
-    p.ctr = ctr_of(ctx);
+    p.stage_digits = (unsigned long long *)st_d;
+    p.stage_meta = (unsigned *)st_m;
+    p.block_sum = (unsigned long long *)st_b;
+    p.block_base = (unsigned long long *)st_b + n_tiles + 1;
     p.result = result_of(ctx);
-    p.epoch = ctx->epoch;
-    p.tslot = ctx->set_launches[ctx->epoch & 1u] & 1u;
     p.n_tiles = (int)n_tiles;
     const int maxg = view_to_json_max_grid();
     CK(launch_view_to_json(p, (int)(n_tiles < maxg ? n_tiles : maxg), s));
-    ctx->set_launches[ctx->epoch & 1u]++;
-    ctx->last_launches = 1;
+    ctx->last_launches = 3;
     if (total_out) {
         hlsmap_result res{};
         r = fetch_result(ctx, s, &res);

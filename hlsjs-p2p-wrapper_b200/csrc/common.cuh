@@ -188,10 +188,11 @@ struct JsonWriteParams {
     int *offsets;
     char *chars;
     long long capacity;
-    unsigned long long *tile_status;
-    ScanCounters *ctr;
+    unsigned long long *stage_digits;   // [n] shortest digits of time
+    unsigned *stage_meta;               // [n] exp10 | ndigits << 16 | kind << 21 | negative << 23 | length << 24
+    unsigned long long *block_sum;      // [n_tiles] characters per 256-view tile
+    unsigned long long *block_base;     // [n_tiles] characters before each tile
     DeviceResult *result;
-    unsigned epoch, tslot;
     int n_tiles;
 };
 struct JsonReadParams {

@@ -55,21 +55,20 @@ __device__ __forceinline__ int put_lit(char *dst, const char *lit, int n)
 
 }  // namespace
 
+// Three launches, none of which waits for another CTA: (1) measure -- the digits of `time` and the
+// length of every view's text, 12 bytes a view of staging and one sum per 256-view tile; (2) one
+// CTA scans the tile sums; (3) render -- every tile knows where its characters start.  (An earlier
+// single-pass build resolved the offsets with a decoupled look-back inside the kernel that also
+// generates the digits; a third of its time went to waiting for the slowest tile ahead.)
 __global__ void __launch_bounds__(kThreads)
-view_to_json_kernel(const JsonWriteParams p)
+view_json_measure_kernel(const JsonWriteParams p)
 {
-    __shared__ Scan::Smem scan;
-    __shared__ unsigned long long warp_cnt[kThreads / 32];
-    __shared__ __align__(16) char buf[kThreads * kMaxChars + 16];
+    __shared__ unsigned warp_sum[kThreads / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-
-    Scan::acquire_set(p.ctr, p.epoch);
-    for (;;) {
-        const int tile = Scan::next_tile(scan, p.ctr, p.tslot);
-        if (tile >= p.n_tiles) break;
-        const long long v = (long long)tile * kThreads + tid;
-        const bool in = v < p.n;
-        const int l = in ? p.level[v] : 0, u = in ? p.url_id[v] : 0, s = in ? p.sn[v] : 0;
+    const long long v = (long long)blockIdx.x * kThreads + tid;
+    const bool in = v < p.n;
+    int len = 0;
+    if (in) {
         // time: 0 = property absent, 1 = null (NaN, +-Infinity), 2 = a number
         int tkind = 0, tlen = 0;
         bool tneg = false;
@@ -77,7 +76,7 @@ view_to_json_kernel(const JsonWriteParams p)
         sd.digits = 0;
         sd.exp10 = 0;
         sd.ndigits = 1;
-        if (in && p.time != nullptr) {
+        if (p.time != nullptr) {
             const unsigned long long bits = (unsigned long long)__double_as_longlong(p.time[v]);
             const unsigned long long mag = bits & 0x7fffffffffffffffull;
             if (mag >= 0x7ff0000000000000ull) {
@@ -95,78 +94,141 @@ view_to_json_kernel(const JsonWriteParams p)
             }
         }
         // {"sn":S,"trackView":{"level":L,"urlId":U}[,"time":T]}
-        const int len = in ? 6 + int_len(s) + 22 + int_len(l) + 9 + int_len(u) + 1 + (tkind ? 8 + tlen : 0) + 1 : 0;
+        len = 6 + int_len(p.sn[v]) + 22 + int_len(p.level[v]) + 9 + int_len(p.url_id[v]) + 1 + (tkind ? 8 + tlen : 0) + 1;
+        p.stage_digits[v] = sd.digits;
+        p.stage_meta[v] = ((unsigned)sd.exp10 & 0xffffu) | ((unsigned)sd.ndigits << 16) | ((unsigned)tkind << 21) |
+                          ((unsigned)tneg << 23) | ((unsigned)len << 24);
+    }
+    int x = len;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) x += __shfl_xor_sync(0xffffffffu, x, d);
+    if (lane == 0) warp_sum[warp] = (unsigned)x;
+    __syncthreads();
+    if (tid == 0) {
+        unsigned t = 0;
+#pragma unroll
+        for (int w = 0; w < kThreads / 32; w++) t += warp_sum[w];
+        p.block_sum[blockIdx.x] = t;
+    }
+}
 
-        int x = len;
+__global__ void __launch_bounds__(1024)
+view_json_scan_kernel(const JsonWriteParams p)
+{
+    __shared__ unsigned long long wsum[32];
+    __shared__ unsigned long long carry;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) carry = 0;
+    __syncthreads();
+    for (int b0 = 0; b0 < p.n_tiles; b0 += 1024) {
+        const int b = b0 + tid;
+        const unsigned long long v = b < p.n_tiles ? p.block_sum[b] : 0ull;
+        unsigned long long x = v;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
-            const int y = __shfl_up_sync(0xffffffffu, x, d);
+            const unsigned long long y = __shfl_up_sync(0xffffffffu, x, d);
             if (lane >= d) x += y;
         }
-        if (lane == 31) warp_cnt[warp] = (unsigned long long)x;
+        if (lane == 31) wsum[warp] = x;
         __syncthreads();
-        unsigned long long wbase = 0, tile_total = 0;
+        unsigned long long before = carry, all = 0;
+        for (int w = 0; w < 32; w++) {
+            const unsigned long long c = wsum[w];
+            before += w < warp ? c : 0ull;
+            all += c;
+        }
+        if (b < p.n_tiles) p.block_base[b] = before + x - v;
+        __syncthreads();
+        if (tid == 0) carry += all;
+        __syncthreads();
+    }
+    if (tid == 0) {
+        const unsigned long long total = carry;
+        p.offsets[p.n] = (int)total;
+        p.result->total_hits = (long long)total;
+        p.result->n_unparsed = 0;
+        p.result->n_missing = 0;
+        p.result->overflow = total > 0x7fffffffull ? 1 : 0;
+    }
+}
+
+__global__ void __launch_bounds__(kThreads)
+view_json_render_kernel(const JsonWriteParams p)
+{
+    __shared__ unsigned warp_cnt[kThreads / 32];
+    __shared__ __align__(16) char buf[kThreads * kMaxChars + 16];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const long long v = (long long)blockIdx.x * kThreads + tid;
+    const bool in = v < p.n;
+    const unsigned meta = in ? p.stage_meta[v] : 0u;
+    const int len = (int)(meta >> 24);
+    int x = len;
 #pragma unroll
-        for (int w = 0; w < kThreads / 32; w++) {
-            const unsigned long long c = warp_cnt[w];
-            wbase += (w < warp) ? c : 0ull;
-            tile_total += c;
-        }
-        const unsigned long long tile_base = Scan::exclusive_prefix(scan, p.tile_status, p.epoch, tile, tile_total);
-        const int at = (int)wbase + x - len;
-        // the tile's characters sit in shared memory at the same offset modulo 16 as their place in
-        // global memory, so the copy out below can move 16 bytes per thread with aligned accesses
-        const int pad = (int)((reinterpret_cast<unsigned long long>(p.chars) + tile_base) & 15ull);
-        if (in) {
-            p.offsets[v] = (int)(tile_base + (unsigned long long)at);
-            char *d = buf + pad + at;
-            d += put_lit(d, "{\"sn\":", 6);
-            d += put_int(d, s);
-            d += put_lit(d, ",\"trackView\":{\"level\":", 22);
-            d += put_int(d, l);
-            d += put_lit(d, ",\"urlId\":", 9);
-            d += put_int(d, u);
-            *d++ = '}';
-            if (tkind) {
-                d += put_lit(d, ",\"time\":", 8);
-                if (tkind == 1) {
-                    d += put_lit(d, "null", 4);
-                } else if (sd.digits == 0) {
-                    *d++ = '0';
-                } else {
-                    if (tneg) *d++ = '-';
-                    d += js_number_write(sd, d);
-                }
-            }
-            *d++ = '}';
-        }
-        if (tile == p.n_tiles - 1 && tid == 0) {
-            const unsigned long long total = tile_base + tile_total;
-            p.offsets[p.n] = (int)total;
-            p.result->total_hits = (long long)total;
-            p.result->overflow = total > 0x7fffffffull ? 1 : 0;
-        }
-        __syncthreads();
-        {   // coalesced copy of the tile's characters: bytes up to the first 16-byte boundary, whole
-            // 16-byte pieces, bytes after the last boundary
-            const int total = (int)tile_total;
-            char *g = p.chars + (long long)tile_base - pad;          // 16-byte aligned
-            if ((long long)tile_base + total <= p.capacity) {
-                const int first = pad ? 16 : 0, last = (pad + total) & ~15;
-                if (last > first) {
-                    for (int i = first + 16 * tid; i < last; i += 16 * kThreads)
-                        *reinterpret_cast<uint4 *>(g + i) = *reinterpret_cast<const uint4 *>(buf + i);
-                    if (tid < 16 && pad && pad + tid < 16) g[pad + tid] = buf[pad + tid];
-                    if (tid >= 32 && tid < 48 && last + (tid - 32) < pad + total) g[last + tid - 32] = buf[last + tid - 32];
-                } else {
-                    for (int i = pad + tid; i < pad + total; i += kThreads) g[i] = buf[i];
-                }
+    for (int d = 1; d < 32; d <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, x, d);
+        if (lane >= d) x += y;
+    }
+    if (lane == 31) warp_cnt[warp] = (unsigned)x;
+    __syncthreads();
+    unsigned wbase = 0, tile_total = 0;
+#pragma unroll
+    for (int w = 0; w < kThreads / 32; w++) {
+        const unsigned c = warp_cnt[w];
+        wbase += (w < warp) ? c : 0u;
+        tile_total += c;
+    }
+    const unsigned long long tile_base = p.block_base[blockIdx.x];
+    const int at = (int)wbase + x - len;
+    // the tile's characters sit in shared memory at the same offset modulo 16 as their place in
+    // global memory, so the copy out below can move 16 bytes per thread with aligned accesses
+    const int pad = (int)((reinterpret_cast<unsigned long long>(p.chars) + tile_base) & 15ull);
+    if (in) {
+        p.offsets[v] = (int)(tile_base + (unsigned long long)at);
+        const int tkind = (int)((meta >> 21) & 3u);
+        char *d = buf + pad + at;
+        d += put_lit(d, "{\"sn\":", 6);
+        d += put_int(d, p.sn[v]);
+        d += put_lit(d, ",\"trackView\":{\"level\":", 22);
+        d += put_int(d, p.level[v]);
+        d += put_lit(d, ",\"urlId\":", 9);
+        d += put_int(d, p.url_id[v]);
+        *d++ = '}';
+        if (tkind) {
+            d += put_lit(d, ",\"time\":", 8);
+            Shortest sd;
+            sd.digits = p.stage_digits[v];
+            sd.exp10 = (int)(short)(meta & 0xffffu);
+            sd.ndigits = (int)((meta >> 16) & 31u);
+            if (tkind == 1) {
+                d += put_lit(d, "null", 4);
+            } else if (sd.digits == 0) {
+                *d++ = '0';
             } else {
-                for (int i = tid; i < total; i += kThreads)
-                    if ((long long)tile_base + i < p.capacity) g[pad + i] = buf[pad + i];
+                if ((meta >> 23) & 1u) *d++ = '-';
+                d += js_number_write(sd, d);
             }
         }
-        if (Scan::tile_done(p.ctr, p.n_tiles)) Scan::finish_batch(p.ctr, p.result, p.tslot);
+        *d++ = '}';
+    }
+    __syncthreads();
+    {   // coalesced copy of the tile's characters: bytes up to the first 16-byte boundary, whole
+        // 16-byte pieces, bytes after the last boundary
+        const int total = (int)tile_total;
+        char *g = p.chars + (long long)tile_base - pad;          // 16-byte aligned
+        if ((long long)tile_base + total <= p.capacity) {
+            const int first = pad ? 16 : 0, last = (pad + total) & ~15;
+            if (last > first) {
+                for (int i = first + 16 * tid; i < last; i += 16 * kThreads)
+                    *reinterpret_cast<uint4 *>(g + i) = *reinterpret_cast<const uint4 *>(buf + i);
+                if (tid < 16 && pad && pad + tid < 16) g[pad + tid] = buf[pad + tid];
+                if (tid >= 32 && tid < 48 && last + (tid - 32) < pad + total) g[last + tid - 32] = buf[last + tid - 32];
+            } else {
+                for (int i = pad + tid; i < pad + total; i += kThreads) g[i] = buf[i];
+            }
+        } else {
+            for (int i = tid; i < total; i += kThreads)
+                if ((long long)tile_base + i < p.capacity) g[pad + i] = buf[pad + i];
+        }
     }
 }
 
@@ -368,24 +430,14 @@ view_from_json_kernel(const JsonReadParams p)
     p.status[v] = (unsigned char)st;
 }
 
-int view_to_json_max_grid()
-{
-    static int grid = 0;
-    if (!grid) {
-        int dev = 0, sms = 0, per_sm = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, view_to_json_kernel, kThreads, 0) != cudaSuccess ||
-            per_sm < 1)
-            per_sm = 1;
-        grid = per_sm * (sms > 0 ? sms : 148);
-    }
-    return grid;
-}
+int view_to_json_max_grid() { return 0x7fffffff; }   // one CTA per 256-view tile: no persistent grid any more
 
-cudaError_t launch_view_to_json(const JsonWriteParams &p, int grid, cudaStream_t s)
+cudaError_t launch_view_to_json(const JsonWriteParams &p, int, cudaStream_t s)
 {
-    view_to_json_kernel<<<grid, kThreads, 0, s>>>(p);
+    if (p.n_tiles < 1) return cudaSuccess;
+    view_json_measure_kernel<<<p.n_tiles, kThreads, 0, s>>>(p);
+    view_json_scan_kernel<<<1, 1024, 0, s>>>(p);
+    view_json_render_kernel<<<p.n_tiles, kThreads, 0, s>>>(p);
     return cudaGetLastError();
 }
 
