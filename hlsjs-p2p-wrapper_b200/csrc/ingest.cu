@@ -15,18 +15,19 @@
 //     #EXT-X-KEY:(.*)  #EXT-X-PROGRAM-DATE-TIME:(.*)     swallow the rest of their line
 //   matter here; a match that swallows the rest of its line hides any tag later on that line.
 //
-// Work split.  m3u8_scan_kernel is byte-parallel and single pass: 32 KB tiles handed out by
-// ticket, every '#' of a tile becomes a candidate, candidates are classified with all lanes
-// busy, and a paired decoupled look-back (fragments, sequence tags) give every fragment its global
-// slot, so durations land in playlist order with the text read once.  What is inherently serial
-// -- `start` is a running fp64 sum, which must be added in the reference's order to give the
-// reference's bits -- is left to m3u8_assemble_kernel: one thread (short tracks) or one warp
-// (long tracks) per track walks its durations once.
+// Work split.  m3u8_scan_kernel is byte-parallel and knows no dependency between tiles: 16 KB
+// tiles, a 4 KB span per warp, every '#' of a span becomes a candidate, candidates are classified
+// with all lanes busy, and each fragment's duration and each sequence tag is left in the span's
+// fixed-size staging slot, with two counts per span.  A two-level scan of the counts and a
+// warp-per-span copy put them at their final places (m3u8_block_scan / span_base / copy /
+// track_offsets kernels), so the text is read once and nothing in the heavy kernel ever waits
+// for another CTA.  What is inherently serial -- `start` is a running fp64 sum, which must be
+// added in the reference's order to give the reference's bits -- is left to the assembly: a lane
+// per track (m3u8_assemble_kernel<1> for short tracks, m3u8_assemble_tracks_kernel for long ones).
 #include <cstdlib>
 
 #include "common.cuh"
 #include "decimal.cuh"
-#include "scan.cuh"
 
 namespace hlsmap {
 namespace {
@@ -42,7 +43,6 @@ constexpr int kRoundBytes = kWarpCap;             // dense spans: text bytes per
 constexpr int kRounds = kWarpBytes / kRoundBytes;
 constexpr int kLanesPerRound = kRoundBytes / kLaneBytes;
 constexpr int kTrackStage = 130;                  // text offsets staged per tile
-using Scan = TileScan<kThreads>;
 
 enum TokKind { kTokNone = 0, kTokFrag = 1, kTokSeq = 2, kTokEnd = 3, kTokLine = 4, kTokInfNaN = 5 };
 

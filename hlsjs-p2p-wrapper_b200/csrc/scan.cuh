@@ -162,83 +162,6 @@ struct TileScan {
         return running;
     }
 
-    // One look-back window of THREADS predecessors ending at `top`, its words already loaded
-    // (w = this thread's, distance tid behind top).  Returns the sum of the aggregates up to and
-    // including the nearest full prefix; found = whether the window held one.
-    __device__ static unsigned long long window_step(Smem &s, const unsigned long long *status,
-                                                     unsigned epoch, int top, unsigned long long w,
-                                                     bool &found)
-    {
-        const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-        const int idx = top - tid;
-        bool is_prefix = true;                 // idx < 0: the virtual tile -1 holds prefix 0
-        unsigned long long val = 0;
-        if (idx >= 0) {
-            while ((unsigned)(w >> 42) != (epoch & kEpochMask)) {
-                __nanosleep(128);
-                w = ld_relaxed_u64(&status[idx]);
-            }
-            val = w & ((1ull << kValueBits) - 1ull);
-            is_prefix = ((w >> kValueBits) & 3ull) == kStatePrefix;
-        }
-        int my_first = is_prefix ? tid : 0x7fffffff;
-#pragma unroll
-        for (int dd = 16; dd > 0; dd >>= 1) my_first = min(my_first, __shfl_xor_sync(0xffffffffu, my_first, dd));
-        __syncthreads();
-        if (lane == 0) s.warp_first[warp] = my_first;
-        __syncthreads();
-        int first = 0x7fffffff;
-#pragma unroll
-        for (int ww = 0; ww < NW; ww++) first = min(first, s.warp_first[ww]);
-        unsigned long long c = tid <= first ? val : 0ull;
-#pragma unroll
-        for (int dd = 16; dd > 0; dd >>= 1) c += __shfl_xor_sync(0xffffffffu, c, dd);
-        if (lane == 0) s.warp_sum[warp] = c;
-        __syncthreads();
-        unsigned long long sum = 0;
-#pragma unroll
-        for (int ww = 0; ww < NW; ww++) sum += s.warp_sum[ww];
-        found = first != 0x7fffffff;
-        return sum;
-    }
-
-    // Two scans over the same tiles (two status arrays) resolved in one walk: the windows of both
-    // are loaded together, so the pair costs one chain of L2 round trips, not two.  Both
-    // aggregates must already be published.
-    __device__ static void wait_prefix_pair(Smem &s, unsigned long long *status_a,
-                                            unsigned long long *status_b, unsigned epoch, int tile,
-                                            unsigned long long agg_a, unsigned long long agg_b,
-                                            unsigned long long &out_a, unsigned long long &out_b)
-    {
-        out_a = 0;
-        out_b = 0;
-        if (tile == 0) return;
-        const int tid = threadIdx.x;
-        int top_a = tile - 1, top_b = tile - 1;
-        bool done_a = false, done_b = false;
-        while (!(done_a && done_b)) {
-            unsigned long long wa = 0, wb = 0;
-            if (!done_a && top_a - tid >= 0) wa = ld_relaxed_u64(&status_a[top_a - tid]);
-            if (!done_b && top_b - tid >= 0) wb = ld_relaxed_u64(&status_b[top_b - tid]);
-            if (!done_a) {
-                out_a += window_step(s, status_a, epoch, top_a, wa, done_a);
-                top_a -= THREADS;
-            }
-            if (!done_b) {
-                out_b += window_step(s, status_b, epoch, top_b, wb, done_b);
-                top_b -= THREADS;
-            }
-        }
-        out_a = out_a < kSat ? out_a : kSat;
-        out_b = out_b < kSat ? out_b : kSat;
-        agg_a = agg_a < kSat ? agg_a : kSat;
-        agg_b = agg_b < kSat ? agg_b : kSat;
-        if (tid == 0) {
-            st_relaxed_u64(&status_a[tile], make_status(epoch, kStatePrefix, out_a + agg_a));
-            st_relaxed_u64(&status_b[tile], make_status(epoch, kStatePrefix, out_b + agg_b));
-        }
-    }
-
     __device__ static unsigned long long exclusive_prefix(Smem &s, unsigned long long *status,
                                                           unsigned epoch, int tile,
                                                           unsigned long long aggregate,
