@@ -161,4 +161,29 @@ class MediaMap {
   }
 }
 
-module.exports = { MediaMap, SegmentView, TrackView, native, ST_UNPARSED, ST_MISSING, ST_EMPTY };
+// ---- batch forms either side of the path (no counterpart in the reference's classes) ----------
+// The level playlists of many players, still as M3U8 text (what hls.js 0.5.46 would have parsed,
+// package.json:34), parsed on the GPU straight into a map.  tables = {playlistBase: Int32Array(P+1),
+// trackState: Uint8Array(T), urlCount: Int32Array(T)|null, text: Uint8Array, textOffset: BigInt64Array(T+1)}
+function createMapFromM3u8(tables, device) {
+  if (!sharedContext) sharedContext = native.createContext(device === undefined ? 0 : device);
+  return native.createMapFromM3u8(sharedContext, tables);
+}
+
+// JSON.stringify of many SegmentViews at once (test/segment-view.js:5-11, batched): columns in,
+// {offsets: Int32Array(n+1), chars: Uint8Array} out; texts[i] = chars.subarray(offsets[i], offsets[i+1]).
+function segmentViewsToJSON(columns) {
+  if (!sharedContext) sharedContext = native.createContext(0);
+  return native.viewToJson(sharedContext, columns.level, columns.urlId, columns.sn, columns.time || null);
+}
+
+// ... and back: {level, urlId, sn, time, flags, status} typed arrays, one entry per text.
+function segmentViewsFromJSON(chars, offsets) {
+  if (!sharedContext) sharedContext = native.createContext(0);
+  return native.viewFromJson(sharedContext, chars, offsets);
+}
+
+module.exports = {
+  MediaMap, SegmentView, TrackView, native, ST_UNPARSED, ST_MISSING, ST_EMPTY,
+  createMapFromM3u8, segmentViewsToJSON, segmentViewsFromJSON,
+};
