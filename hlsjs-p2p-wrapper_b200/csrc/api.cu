@@ -95,11 +95,14 @@ int use_ctx(hlsmap_ctx *ctx)
     return HLSMAP_OK;
 }
 
-int ensure_slot(hlsmap_ctx *ctx, int i, int64_t bytes, void **out)
+// `user` = the stream of a device-pointer call: work queued there by an earlier asynchronous call
+// may still be using the slot that is about to be replaced.
+int ensure_slot(hlsmap_ctx *ctx, int i, int64_t bytes, void **out, cudaStream_t user = nullptr)
 {
     if (bytes < 16) bytes = 16;
     if (ctx->slot_bytes[i] < bytes) {
         if (ctx->slot[i]) {
+            if (user && user != ctx->stream) CK(cudaStreamSynchronize(user));
             CK(cudaStreamSynchronize(ctx->stream));
             CK(cudaFree(ctx->slot[i]));
             ctx->slot[i] = nullptr;
@@ -1564,8 +1567,8 @@ int hlsmap_view_to_json_dev(hlsmap_ctx *ctx, int64_t n, const int32_t *d_level, 
     const int64_t n_tiles = (n + kJsonTileViews - 1) / kJsonTileViews;
     if (n_tiles > 0x7fffffff) return fail(HLSMAP_ERR_INVALID, "batch too large: split it");
     void *st_d = nullptr, *st_m = nullptr, *st_b = nullptr;      // grow-only context scratch
-    if ((r = ensure_slot(ctx, 8, n * 8, &st_d)) || (r = ensure_slot(ctx, 9, n * 4, &st_m)) ||
-        (r = ensure_slot(ctx, 10, (n_tiles + 1) * 16, &st_b)))
+    if ((r = ensure_slot(ctx, 8, n * 8, &st_d, s)) || (r = ensure_slot(ctx, 9, n * 4, &st_m, s)) ||
+        (r = ensure_slot(ctx, 10, (n_tiles + 1) * 16, &st_b, s)))
         return r;
     JsonWriteParams p{};
     p.n = n;
@@ -1744,7 +1747,7 @@ int ingest_core(hlsmap_ctx *ctx, int32_t n_tracks, const uint8_t *d_state, const
         size_t o_sg = align256(o_sd + (fill ? 8 * (size_t)kIngestSpanFrags * (size_t)n_spans : 0));
         size_t total = align256(o_sg + (fill ? 8 * (size_t)kIngestSpanTags * (size_t)n_spans : 0));
         void *sp = nullptr;               // grow-only context scratch: no allocation after the first call
-        int r = ensure_slot(ctx, kSlots - 1, (int64_t)total, &sp);
+        int r = ensure_slot(ctx, kSlots - 1, (int64_t)total, &sp, s);
         if (r) return r;
         char *b = (char *)sp;
         CK(cudaMemsetAsync(b, 0, o_zero_end, s));

@@ -102,3 +102,32 @@ def test_capacity_and_empty(ctx):
     p = lambda a: ctypes.c_void_p(a.ctypes.data)
     rc = N.load().hlsmap_view_to_json(ctx._h, 10, p(lv), p(ui), p(sn), None, p(offsets), p(buf), 20, ctypes.byref(total))
     assert rc == N.ERR_CAPACITY and total.value == offsets[10] > 20
+
+
+def test_async_calls_of_growing_size_on_a_caller_stream(ctx):
+    """Two device-pointer calls queued back to back on the caller's stream, the second needing larger
+    scratch than the first: replacing the scratch must not pull it from under the first call."""
+    import ctypes
+    import torch
+    lib, dev = N.load(), torch.device("cuda", 0)
+    stream = torch.cuda.Stream()
+    v = lambda x: ctypes.c_void_p(x.data_ptr())
+    outs = []
+    torch.cuda.synchronize()
+    for n in (300_000, 3_000_000):
+        lv, ui, sn = _views(n, n)
+        tm = np.resize(_doubles(50000, 9), n).copy()
+        d = [torch.from_numpy(a).to(dev) for a in (lv, ui, sn, tm)]
+        d_off = torch.empty(n + 1, dtype=torch.int32, device=dev)
+        d_ch = torch.empty(104 * n, dtype=torch.uint8, device=dev)
+        torch.cuda.synchronize()
+        outs.append((lv, ui, sn, tm, d, d_off, d_ch))
+    for lv, ui, sn, tm, d, d_off, d_ch in outs:                      # both queued before either is awaited
+        N.check(lib.hlsmap_view_to_json_dev(ctx._h, len(sn), v(d[0]), v(d[1]), v(d[2]), v(d[3]), v(d_off), v(d_ch),
+                                            104 * len(sn), ctypes.c_void_p(stream.cuda_stream), None))
+    torch.cuda.synchronize()
+    for lv, ui, sn, tm, d, d_off, d_ch in outs:
+        eoff, echars = oracle.view_to_json(lv[:20000], ui[:20000], sn[:20000], tm[:20000])
+        off = d_off.cpu().numpy()
+        assert np.array_equal(off[:20001], eoff)
+        assert np.array_equal(d_ch[:off[20000]].cpu().numpy(), echars)
