@@ -80,6 +80,7 @@ SYMBOLS = {
     "hlsmap_parse_m3u8_dev": (_INT, [_P, _I32, _P, _P, _P, _I64, _P, _P, _P, _P, _P, _I64, _P, _P]),
     "hlsmap_parse_m3u8": (_INT, [_P, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _I64, _P]),
     "hlsmap_map_create_from_m3u8": (_INT, [_P, _I32, _P, _I32, _P, _P, _P, _P, _P, _P]),
+    "hlsmap_map_create_from_m3u8_dev": (_INT, [_P, _I32, _P, _I32, _P, _P, _P, _P, _I64, _P, _P]),
     "hlsmap_get_track_list": (_INT, [_P, _I32, _P, _P, _I64, _P]),
     "hlsmap_view_pack_dev": (_INT, [_P, _I64, _P, _P, _P, _P, _P]),
     "hlsmap_view_pack": (_INT, [_P, _I64, _P, _P, _P, _P]),

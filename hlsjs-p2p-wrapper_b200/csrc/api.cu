@@ -1926,6 +1926,46 @@ int hlsmap_parse_m3u8(hlsmap_ctx *ctx, int32_t n_tracks, const uint8_t *track_st
     return r;
 }
 
+// Parse text that is already on the device (d_text, d_off) and build the map from the columns.
+static int map_from_device_text(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *playlist_track_base,
+                                int32_t n_tracks, const uint8_t *track_state, const int32_t *url_count,
+                                const unsigned char *d_text, const int64_t *d_off, int64_t nb,
+                                hlsmap_ingest_result *res, hlsmap_map **out)
+{
+    int r;
+    cudaStream_t s = ctx->stream;
+    DevBuf d_state, d_toff, d_live, d_start, d_sn, d_dur, d_dur0;
+    if ((r = d_state.alloc((size_t)n_tracks + 1)) || (r = d_toff.alloc(8 * (size_t)(n_tracks + 1))) ||
+        (r = d_live.alloc((size_t)n_tracks + 1)) || (r = d_dur0.alloc(8 * (size_t)(n_tracks + 1))))
+        return r;
+    if (n_tracks) CK(cudaMemcpyAsync(d_state.p, track_state, (size_t)n_tracks, cudaMemcpyHostToDevice, s));
+    // pass 1 counts (the text is read once more, from L2 when it fits), so the columns are
+    // allocated at their exact size instead of the worst case of one fragment per 9 bytes
+    hlsmap_ingest_result local{};
+    r = ingest_core(ctx, n_tracks, (const uint8_t *)d_state.p, d_text, d_off, nb, (int64_t *)d_toff.p,
+                    (uint8_t *)d_live.p, nullptr, nullptr, nullptr, nullptr, 0, s, &local);
+    if (res) *res = local;
+    if (r) return r;
+    const int64_t nf = local.n_fragments;
+    if ((r = d_start.alloc(8 * (size_t)nf + 16)) || (r = d_sn.alloc(4 * (size_t)nf + 16)) ||
+        (r = d_dur.alloc(8 * (size_t)nf + 16)))
+        return r;
+    const int first_launches = local.kernel_launches;
+    r = ingest_core(ctx, n_tracks, (const uint8_t *)d_state.p, d_text, d_off, nb, (int64_t *)d_toff.p,
+                    (uint8_t *)d_live.p, (double *)d_start.p, (int32_t *)d_sn.p, (double *)d_dur.p,
+                    (double *)d_dur0.p, nf > 0 ? nf : 1, s, &local);
+    local.kernel_launches += first_launches;
+    if (res) *res = local;
+    if (r) return r;
+    std::vector<int64_t> h_off((size_t)n_tracks + 1, 0);
+    CK(cudaMemcpyAsync(h_off.data(), d_toff.p, 8 * (size_t)(n_tracks + 1), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    // tracks that are not parsed hold no fragments whatever their text said
+    return map_create_impl(ctx, n_playlists, playlist_track_base, n_tracks, h_off.data(), track_state, url_count,
+                           (const double *)d_start.p, (const int32_t *)d_sn.p, nullptr, (const double *)d_dur0.p,
+                           out);
+}
+
 int hlsmap_map_create_from_m3u8(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *playlist_track_base,
                                 int32_t n_tracks, const uint8_t *track_state, const int32_t *url_count,
                                 const char *text, const int64_t *text_offset, hlsmap_ingest_result *res,
@@ -1940,38 +1980,26 @@ int hlsmap_map_create_from_m3u8(hlsmap_ctx *ctx, int32_t n_playlists, const int3
     const int64_t nb = text_offset[n_tracks];
     if (nb > 0 && !text) return fail(HLSMAP_ERR_INVALID, "map_create_from_m3u8: null text");
     cudaStream_t s = ctx->stream;
-    DevBuf d_text, d_off, d_state, d_toff, d_live, d_start, d_sn, d_dur, d_dur0;
-    if ((r = d_text.alloc((size_t)nb + 16)) || (r = d_off.alloc(8 * (size_t)(n_tracks + 1))) ||
-        (r = d_state.alloc((size_t)n_tracks + 1)) || (r = d_toff.alloc(8 * (size_t)(n_tracks + 1))) ||
-        (r = d_live.alloc((size_t)n_tracks + 1)) || (r = d_dur0.alloc(8 * (size_t)(n_tracks + 1))))
-        return r;
+    DevBuf d_text, d_off;
+    if ((r = d_text.alloc((size_t)nb + 16)) || (r = d_off.alloc(8 * (size_t)(n_tracks + 1)))) return r;
     if (nb) CK(cudaMemcpyAsync(d_text.p, text, (size_t)nb, cudaMemcpyHostToDevice, s));
     CK(cudaMemcpyAsync(d_off.p, text_offset, 8 * (size_t)(n_tracks + 1), cudaMemcpyHostToDevice, s));
-    if (n_tracks) CK(cudaMemcpyAsync(d_state.p, track_state, (size_t)n_tracks, cudaMemcpyHostToDevice, s));
-    // pass 1 counts (the text is read once more, from L2 when it fits), so the columns are
-    // allocated at their exact size instead of the worst case of one fragment per 9 bytes
-    hlsmap_ingest_result local{};
-    r = ingest_core(ctx, n_tracks, (const uint8_t *)d_state.p, (const unsigned char *)d_text.p,
-                    (const int64_t *)d_off.p, nb, (int64_t *)d_toff.p, (uint8_t *)d_live.p, nullptr, nullptr,
-                    nullptr, nullptr, 0, s, &local);
-    if (res) *res = local;
+    return map_from_device_text(ctx, n_playlists, playlist_track_base, n_tracks, track_state, url_count,
+                                (const unsigned char *)d_text.p, (const int64_t *)d_off.p, nb, res, out);
+}
+
+int hlsmap_map_create_from_m3u8_dev(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *playlist_track_base,
+                                    int32_t n_tracks, const uint8_t *track_state, const int32_t *url_count,
+                                    const char *d_text, const int64_t *d_text_offset, int64_t text_bytes,
+                                    hlsmap_ingest_result *res, hlsmap_map **out)
+{
+    int r = use_ctx(ctx);
     if (r) return r;
-    const int64_t nf = local.n_fragments;
-    if ((r = d_start.alloc(8 * (size_t)nf + 16)) || (r = d_sn.alloc(4 * (size_t)nf + 16)) ||
-        (r = d_dur.alloc(8 * (size_t)nf + 16)))
-        return r;
-    const int first_launches = local.kernel_launches;
-    r = ingest_core(ctx, n_tracks, (const uint8_t *)d_state.p, (const unsigned char *)d_text.p,
-                    (const int64_t *)d_off.p, nb, (int64_t *)d_toff.p, (uint8_t *)d_live.p, (double *)d_start.p,
-                    (int32_t *)d_sn.p, (double *)d_dur.p, (double *)d_dur0.p, nf > 0 ? nf : 1, s, &local);
-    local.kernel_launches += first_launches;
-    if (res) *res = local;
-    if (r) return r;
-    std::vector<int64_t> h_off((size_t)n_tracks + 1, 0);
-    CK(cudaMemcpyAsync(h_off.data(), d_toff.p, 8 * (size_t)(n_tracks + 1), cudaMemcpyDeviceToHost, s));
-    CK(cudaStreamSynchronize(s));
-    // tracks that are not parsed hold no fragments whatever their text said
-    return map_create_impl(ctx, n_playlists, playlist_track_base, n_tracks, h_off.data(), track_state, url_count,
-                           (const double *)d_start.p, (const int32_t *)d_sn.p, nullptr, (const double *)d_dur0.p,
-                           out);
+    if (!out) return fail(HLSMAP_ERR_INVALID, "null out pointer");
+    *out = nullptr;
+    if (n_tracks < 0 || text_bytes < 0 || !d_text_offset || (text_bytes > 0 && !d_text) || (n_tracks > 0 && !track_state))
+        return fail(HLSMAP_ERR_INVALID, "map_create_from_m3u8_dev: missing arrays");
+    CK(cudaStreamSynchronize(ctx->stream));
+    return map_from_device_text(ctx, n_playlists, playlist_track_base, n_tracks, track_state, url_count,
+                                (const unsigned char *)d_text, d_text_offset, text_bytes, res, out);
 }

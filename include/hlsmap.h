@@ -326,6 +326,13 @@ int hlsmap_map_create_from_m3u8(hlsmap_ctx *ctx, int32_t n_playlists, const int3
                                 int32_t n_tracks, const uint8_t *track_state, const int32_t *url_count,
                                 const char *text, const int64_t *text_offset, hlsmap_ingest_result *res,
                                 hlsmap_map **out);
+/* The same with the text and its offsets already in device memory (text_offset must start at 0, be
+ * monotone and end at text_bytes: it is not checked on the host); the small per-track metadata stays
+ * on the host.  Work is issued on the context's stream; the call returns when the map is ready. */
+int hlsmap_map_create_from_m3u8_dev(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *playlist_track_base,
+                                    int32_t n_tracks, const uint8_t *track_state, const int32_t *url_count,
+                                    const char *d_text, const int64_t *d_text_offset, int64_t text_bytes,
+                                    hlsmap_ingest_result *res, hlsmap_map **out);
 
 /* ---- getTrackList (media-map.js:60-73) --------------------------------------------- */
 /* Level-major, urlId-minor enumeration of one playlist's tracks.  Pass NULL outputs to

@@ -238,3 +238,33 @@ def test_sharded_map_from_text(ctx):
     sm.close()
     one.close()
     other.close()
+
+
+def test_map_from_text_already_on_the_device(ctx):
+    import ctypes
+    import torch
+    from hlsjs_p2p_wrapper_b200.engine import DeviceMap
+    base, state, texts = synth.m3u8_corpus(n_playlists=150, unparsed_every=29)
+    off = _offsets(texts)
+    text = np.frombuffer(b"".join(texts), np.uint8)
+    dev = torch.device("cuda", 0)
+    d_text, d_off = torch.from_numpy(text.copy()).to(dev), torch.from_numpy(off).to(dev)
+    torch.cuda.synchronize()
+    m = object.__new__(DeviceMap)
+    m.ctx, m._lib, m.n_playlists = ctx, ctx._lib, len(base) - 1
+    h, res = ctypes.c_void_p(), N.IngestResult()
+    p = lambda a: ctypes.c_void_p(a.ctypes.data)
+    N.check(N.load().hlsmap_map_create_from_m3u8_dev(ctx._h, len(base) - 1, p(base), len(state), p(state), None,
+                                                     ctypes.c_void_p(d_text.data_ptr()), ctypes.c_void_p(d_off.data_ptr()),
+                                                     len(text), ctypes.byref(res), ctypes.byref(h)))
+    m._h = h
+    one = ctx.upload_m3u8(base, state, texts)
+    assert res.n_fragments == one.ingest.n_fragments > 1000
+    rng = np.random.default_rng(8)
+    n = 10000
+    pl, lv = rng.integers(0, 150, n).astype(np.int32), rng.integers(0, 3, n).astype(np.int32)
+    bg, du = rng.uniform(-5, 80, n), rng.uniform(0, 40, n)
+    a, b = m.get_segment_list(pl, lv, bg, du), one.get_segment_list(pl, lv, bg, du)
+    assert np.array_equal(a.offsets, b.offsets) and np.array_equal(a.sn, b.sn) and np.array_equal(a.time, b.time)
+    m.close()
+    one.close()
