@@ -1212,7 +1212,10 @@ int hlsmap_view_format_dev(hlsmap_ctx *ctx, int64_t n, const int32_t *d_level,
     }
     const int64_t n_tiles = (n + kFormatTileViews - 1) / kFormatTileViews;
     if (n_tiles > 0x7fffffff) return fail(HLSMAP_ERR_INVALID, "batch too large: split it");
-    r = prepare_scan(ctx, n_tiles, s);
+    static const bool single_pass = getenv("HLSMAP_FORMAT_SINGLE_PASS") != nullptr;   // diagnostics: the look-back form
+    void *st_b = nullptr;
+    if (single_pass) r = prepare_scan(ctx, n_tiles, s);
+    else r = ensure_slot(ctx, 10, (n_tiles + 1) * 16, &st_b, s);
     if (r) return r;
     FormatParams p{};
     p.n = n;
@@ -1229,10 +1232,17 @@ int hlsmap_view_format_dev(hlsmap_ctx *ctx, int64_t n, const int32_t *d_level,
     p.epoch = ctx->epoch;
     p.tslot = ctx->set_launches[ctx->epoch & 1u] & 1u;
     p.n_tiles = (int)n_tiles;
-    const int maxg = view_format_max_grid();
-    CK(launch_view_format(p, (int)(n_tiles < maxg ? n_tiles : maxg), s));
-    ctx->set_launches[ctx->epoch & 1u]++;
-    ctx->last_launches = 1;
+    if (single_pass) {
+        const int maxg = view_format_max_grid();
+        CK(launch_view_format(p, (int)(n_tiles < maxg ? n_tiles : maxg), s));
+        ctx->set_launches[ctx->epoch & 1u]++;
+        ctx->last_launches = 1;
+    } else {
+        p.block_sum = (unsigned long long *)st_b;
+        p.block_base = (unsigned long long *)st_b + n_tiles + 1;
+        CK(launch_view_format_split(p, s));
+        ctx->last_launches = 3;
+    }
     if (total_out) {
         hlsmap_result res{};
         r = fetch_result(ctx, s, &res);

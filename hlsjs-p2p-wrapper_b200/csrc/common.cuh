@@ -254,6 +254,7 @@ struct FormatParams {
     unsigned epoch;
     unsigned tslot;
     int n_tiles;
+    unsigned long long *block_sum, *block_base;   // [n_tiles] each: the three-launch form
 };
 constexpr int kFormatTileViews = 1024;
 cudaError_t launch_view_pack(long long n, const int *level, const int *url_id, const int *sn,
@@ -268,6 +269,7 @@ cudaError_t launch_view_is_in_track(long long n, const int *al, const int *au, c
 cudaError_t launch_view_roundtrip(long long n, const int *level, const int *url_id, const int *sn,
                                   unsigned *wire, unsigned char *equal, cudaStream_t s);
 cudaError_t launch_view_format(const FormatParams &p, int grid, cudaStream_t s);
+cudaError_t launch_view_format_split(const FormatParams &p, cudaStream_t s);
 int view_format_max_grid();
 
 }  // namespace hlsmap

@@ -306,6 +306,154 @@ view_format_kernel(const FormatParams p)
     }
 }
 
+// ---- the same in three launches, none of which waits for another CTA -----------------------
+// (1) characters per 1024-view tile, (2) one CTA scans the tile sums, (3) render with known bases.
+// The columns are read twice (12 B a view more); in exchange no tile waits in a look-back for the
+// slowest tile ahead of it.
+__global__ void __launch_bounds__(kFmtThreads)
+view_format_measure_kernel(const FormatParams p)
+{
+    __shared__ unsigned warp_sum[kFmtThreads / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const long long v0 = (long long)blockIdx.x * kFormatTileViews + (long long)tid * kFmtIpt;
+    int x = 0;
+#pragma unroll
+    for (int k = 0; k < kFmtIpt; k++)
+        if (v0 + k < p.n)
+            x += 2 + dec_len(p.level[v0 + k]) + dec_len(p.url_id[v0 + k]) + (p.with_sn ? 1 + dec_len(p.sn[v0 + k]) : 0);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) x += __shfl_xor_sync(0xffffffffu, x, d);
+    if (lane == 0) warp_sum[warp] = (unsigned)x;
+    __syncthreads();
+    if (tid == 0) {
+        unsigned t = 0;
+#pragma unroll
+        for (int w = 0; w < kFmtThreads / 32; w++) t += warp_sum[w];
+        p.block_sum[blockIdx.x] = t;
+    }
+}
+
+__global__ void __launch_bounds__(1024)
+tile_sum_scan_kernel(const unsigned long long *sum, unsigned long long *base, int n_tiles, int *offsets_end,
+                     DeviceResult *result)
+{
+    __shared__ unsigned long long wsum[32];
+    __shared__ unsigned long long carry;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) carry = 0;
+    __syncthreads();
+    for (int b0 = 0; b0 < n_tiles; b0 += 1024) {
+        const int b = b0 + tid;
+        const unsigned long long v = b < n_tiles ? sum[b] : 0ull;
+        unsigned long long x = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned long long y = __shfl_up_sync(0xffffffffu, x, d);
+            if (lane >= d) x += y;
+        }
+        if (lane == 31) wsum[warp] = x;
+        __syncthreads();
+        unsigned long long before = carry, all = 0;
+        for (int w = 0; w < 32; w++) {
+            const unsigned long long c = wsum[w];
+            before += w < warp ? c : 0ull;
+            all += c;
+        }
+        if (b < n_tiles) base[b] = before + x - v;
+        __syncthreads();
+        if (tid == 0) carry += all;
+        __syncthreads();
+    }
+    if (tid == 0) {
+        const unsigned long long total = carry;
+        *offsets_end = (int)total;
+        result->total_hits = (long long)total;
+        result->n_unparsed = 0;
+        result->n_missing = 0;
+        result->overflow = total > 0x7fffffffull ? 1 : 0;
+    }
+}
+
+__global__ void __launch_bounds__(kFmtThreads)
+view_format_render_kernel(const FormatParams p)
+{
+    __shared__ unsigned warp_cnt[kFmtThreads / 32];
+    __shared__ __align__(16) char buf[kFormatTileViews * kFmtMaxChars + 16];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const long long v0 = (long long)blockIdx.x * kFormatTileViews + (long long)tid * kFmtIpt;
+    int l[kFmtIpt], u[kFmtIpt], s[kFmtIpt], len[kFmtIpt];
+    int tsum = 0;
+#pragma unroll
+    for (int k = 0; k < kFmtIpt; k++) {
+        const bool in = v0 + k < p.n;
+        l[k] = in ? p.level[v0 + k] : 0;
+        u[k] = in ? p.url_id[v0 + k] : 0;
+        s[k] = (in && p.with_sn) ? p.sn[v0 + k] : 0;
+        len[k] = in ? 2 + dec_len(l[k]) + dec_len(u[k]) + (p.with_sn ? 1 + dec_len(s[k]) : 0) : 0;
+        tsum += len[k];
+    }
+    int x = tsum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, x, d);
+        if (lane >= d) x += y;
+    }
+    if (lane == 31) warp_cnt[warp] = (unsigned)x;
+    __syncthreads();
+    unsigned wbase = 0, tile_total = 0;
+#pragma unroll
+    for (int w = 0; w < kFmtThreads / 32; w++) {
+        const unsigned c = warp_cnt[w];
+        wbase += (w < warp) ? c : 0u;
+        tile_total += c;
+    }
+    const unsigned long long tile_base = p.block_base[blockIdx.x];
+    const int pad = (int)((reinterpret_cast<unsigned long long>(p.chars) + tile_base) & 15ull);
+    int at = (int)wbase + x - tsum;
+#pragma unroll
+    for (int k = 0; k < kFmtIpt; k++) {
+        if (v0 + k < p.n) {
+            p.offsets[v0 + k] = (int)(tile_base + (unsigned long long)at);
+            char *d = buf + pad + at;
+            *d++ = 'L';
+            d += put_dec(d, l[k]);
+            *d++ = 'U';
+            d += put_dec(d, u[k]);
+            if (p.with_sn) {
+                *d++ = 'S';
+                d += put_dec(d, s[k]);
+            }
+            at += len[k];
+        }
+    }
+    __syncthreads();
+    const int total = (int)tile_total;
+    char *g = p.chars + (long long)tile_base - pad;          // 16-byte aligned
+    if ((long long)tile_base + total <= p.capacity) {
+        const int first = pad ? 16 : 0, last = (pad + total) & ~15;
+        if (last > first) {
+            for (int i = first + 16 * tid; i < last; i += 16 * kFmtThreads)
+                *reinterpret_cast<uint4 *>(g + i) = *reinterpret_cast<const uint4 *>(buf + i);
+            if (tid < 16 && pad && pad + tid < 16) g[pad + tid] = buf[pad + tid];
+            if (tid >= 32 && tid < 48 && last + (tid - 32) < pad + total) g[last + tid - 32] = buf[last + tid - 32];
+        } else {
+            for (int i = pad + tid; i < pad + total; i += kFmtThreads) g[i] = buf[i];
+        }
+    } else {
+        for (int i = tid; i < total; i += kFmtThreads)
+            if ((long long)tile_base + i < p.capacity) g[pad + i] = buf[pad + i];
+    }
+}
+
+cudaError_t launch_view_format_split(const FormatParams &p, cudaStream_t s)
+{
+    if (p.n_tiles < 1) return cudaSuccess;
+    view_format_measure_kernel<<<p.n_tiles, kFmtThreads, 0, s>>>(p);
+    tile_sum_scan_kernel<<<1, 1024, 0, s>>>(p.block_sum, p.block_base, p.n_tiles, p.offsets + p.n, p.result);
+    view_format_render_kernel<<<p.n_tiles, kFmtThreads, 0, s>>>(p);
+    return cudaGetLastError();
+}
+
 // ---- launchers ---------------------------------------------------------------------------
 static int views_sm_count()
 {
