@@ -301,6 +301,7 @@ struct TrackOffsets {
 struct WarpShared {
     unsigned short cpos[kWarpCap];   // tile-relative position of each candidate of the round
     unsigned short cfpre[kWarpCap];  // fragments of the span before that candidate
+    unsigned short ctrk[kWarpCap];   // track of the owning lane's first byte, relative to the tile's first track
 };
 struct Shared {
     __align__(16) unsigned char text[kTile + 48];   // + room for the word fetches of classify_fast
@@ -318,12 +319,8 @@ __device__ __forceinline__ int classify_candidate(const IngestParams &p, const S
     int kind = kTokNone;
     bits = 0;
     const long long pos = lo + pos_rel;
-    int a = t_lo, b = t_hi;               // last track whose text starts at or before pos
-    while (a < b) {
-        const int mid = (a + b + 1) >> 1;
-        if (toff(mid) <= pos) a = mid;
-        else b = mid - 1;
-    }
+    int a = t_lo;                         // t_lo: a track at or before the one holding pos (the owner lane's
+    while (a < t_hi && toff(a + 1) <= pos) a++;   // hint); the last track starting at or before pos is a few steps on
     const long long tb = toff(a), te = toff(a + 1);
     const bool parsed = p.state == nullptr || p.state[a] == HLSMAP_TRACK_PARSED;
     if (parsed && pos < te) {
@@ -363,6 +360,15 @@ __device__ __forceinline__ unsigned warp_classify(const IngestParams &p, Shared 
 {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (my_first >= 0) {
+        // the track holding this lane's first byte, searched once: its candidates start from there
+        int a = t_lo, b2 = t_hi;
+        const long long first_byte = lo + lane_base;
+        while (a < b2) {
+            const int mid = (a + b2 + 1) >> 1;
+            if (toff(mid) <= first_byte) a = mid;
+            else b2 = mid - 1;
+        }
+        const unsigned short hint = (unsigned short)(a - t_lo < 0xffff ? a - t_lo : 0xffff);
         int at = my_first;
 #pragma unroll
         for (int g = 0; g < kGroups; g++) {
@@ -370,6 +376,7 @@ __device__ __forceinline__ unsigned warp_classify(const IngestParams &p, Shared 
             while (m) {
                 const int b = __ffs(m) - 1;
                 m &= m - 1;
+                ws.ctrk[at] = hint;
                 ws.cpos[at++] = (unsigned short)(lane_base + g * 32 + b);
             }
         }
@@ -381,7 +388,9 @@ __device__ __forceinline__ unsigned warp_classify(const IngestParams &p, Shared 
         const int i = i0 + lane;
         long long bits = 0;
         const int pos_rel = i < nc ? (int)ws.cpos[i] : 0;
-        const int kind = i < nc ? classify_candidate(p, sh, toff, t_lo, t_hi, lo, hi, pos_rel, true, bits) : kTokNone;
+        const int kind = i < nc ? classify_candidate(p, sh, toff, t_lo + (int)ws.ctrk[i < nc ? i : 0], t_hi, lo, hi,
+                                                     pos_rel, true, bits)
+                                : kTokNone;
         const unsigned fb = __ballot_sync(0xffffffffu, kind == kTokFrag);
         const unsigned tb = __ballot_sync(0xffffffffu, kind == kTokSeq);
         if (i < nc) {
