@@ -799,6 +799,79 @@ m3u8_assemble_kernel(const AssembleParams p)
     if (overflow) atomicAdd(&p.out->n_unsupported, 1ull);
 }
 
+// ---- short tracks: a lane per track, 32 consecutive tracks per warp ---------------------------
+// Consecutive tracks own consecutive fragments, so the fragments of a warp's 32 tracks are one
+// contiguous run: when it is short enough (live windows: 6 fragments a track) it is loaded into
+// shared memory with coalesced reads, each lane walks its own track there, and start / sn leave
+// with coalesced writes.  A longer run is walked in global memory, a track per lane, as before.
+constexpr int kShortWarps = 4, kShortCap = 512;
+__global__ void __launch_bounds__(32 * kShortWarps)
+m3u8_assemble_short_kernel(const AssembleParams p)
+{
+    __shared__ double s_val[kShortWarps][kShortCap];     // durations in, starts out
+    __shared__ int s_sn[kShortWarps][kShortCap];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long long t0 = ((long long)blockIdx.x * kShortWarps + warp) * 32;
+    if (t0 >= p.n_tracks) return;
+    const long long n_tags_seen = (long long)p.out->n_tags;
+    if ((long long)p.out->n_fragments > p.capacity || n_tags_seen > p.tag_capacity) return;
+    const long long t = t0 + lane;
+    const bool valid = t < p.n_tracks;
+    const bool parsed = valid && (p.state == nullptr || p.state[t] == HLSMAP_TRACK_PARSED);
+    const long long off = valid ? p.track_off[t] : 0;
+    const long long len = parsed ? p.track_off[t + 1] - off : 0;
+    const long long t_end = t0 + 32 < p.n_tracks ? t0 + 32 : p.n_tracks;
+    const long long run_lo = p.track_off[t0], run_n = p.track_off[t_end] - run_lo;
+    const bool in_smem = run_n <= kShortCap;              // warp-uniform
+    if (in_smem) {
+        for (long long i = lane; i < run_n; i += 32) s_val[warp][i] = p.dur[run_lo + i];
+        __syncwarp();
+    }
+    const double *src = in_smem ? &s_val[warp][off - run_lo] : p.dur + off;
+    double *dst_start = in_smem ? &s_val[warp][off - run_lo] : p.start + off;
+    int *dst_sn = in_smem ? &s_sn[warp][off - run_lo] : p.sn + off;
+    if (valid) p.dur0[t] = len > 0 ? src[0] : __longlong_as_double(0x7ff8000000000000ll);
+    if (len > 0) {
+        // sequence tags of this track (see m3u8_assemble_kernel)
+        const long long tb = p.text_off[t], te = p.text_off[t + 1];
+        const long long none = 0x7fffffffffffffffll;
+        long long e = 0, z = n_tags_seen;
+        if (t < n_tags_seen && p.tag_pos[t] >= tb && (t == 0 || p.tag_pos[t - 1] < tb)) {
+            e = t;
+        } else {
+            while (e < z) {
+                const long long mid = (e + z) >> 1;
+                if (p.tag_pos[mid] < tb) e = mid + 1;
+                else z = mid;
+            }
+        }
+        long long next_tag = (e < n_tags_seen && p.tag_pos[e] < te) ? p.tag_frag[e] : none;
+        long long cur = 0;
+        double total = 0.0;
+        bool overflow = false;
+        for (long long i = 0; i < len; i++) {
+            while (next_tag <= off + i) {
+                cur = p.tag_val[e++];
+                next_tag = (e < n_tags_seen && p.tag_pos[e] < te) ? p.tag_frag[e] : none;
+            }
+            const double d = src[i];
+            dst_start[i] = total;
+            total += d;
+            overflow |= cur > 0x7fffffffll;
+            dst_sn[i] = (int)cur;
+            cur++;
+        }
+        if (overflow) atomicAdd(&p.out->n_unsupported, 1ull);
+    }
+    if (in_smem) {
+        __syncwarp();
+        for (long long i = lane; i < run_n; i += 32) {
+            p.start[run_lo + i] = s_val[warp][i];
+            p.sn[run_lo + i] = s_sn[warp][i];
+        }
+    }
+}
+
 // ---- long tracks: 32 tracks per CTA, a lane per track ------------------------------------------
 // The running sum of a track is a chain nobody can shorten, but 32 lanes can each walk their own
 // track's chain at once instead of all replaying one.  Durations travel through a shared-memory
@@ -980,8 +1053,11 @@ cudaError_t launch_ingest_assemble(const AssembleParams &p, bool warp_per_track,
         m3u8_assemble_kernel<32><<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(p);
     } else if (warp_per_track) {
         m3u8_assemble_tracks_kernel<<<(unsigned)((p.n_tracks + 31) / 32), 32 * kAsmWarps, 0, s>>>(p);
-    } else {
+    } else if (old_warp) {
         m3u8_assemble_kernel<1><<<(unsigned)((p.n_tracks + 255) / 256), 256, 0, s>>>(p);
+    } else {
+        m3u8_assemble_short_kernel<<<(unsigned)((p.n_tracks + 32 * kShortWarps - 1) / (32 * kShortWarps)),
+                                     32 * kShortWarps, 0, s>>>(p);
     }
     return cudaGetLastError();
 }
