@@ -23,7 +23,8 @@
 // track_offsets kernels), so the text is read once and nothing in the heavy kernel ever waits
 // for another CTA.  What is inherently serial -- `start` is a running fp64 sum, which must be
 // added in the reference's order to give the reference's bits -- is left to the assembly: a lane
-// per track (m3u8_assemble_kernel<1> for short tracks, m3u8_assemble_tracks_kernel for long ones).
+// per track (m3u8_assemble_short_kernel for short tracks, m3u8_assemble_tracks_kernel for long ones;
+// m3u8_assemble_kernel is the plain form both replaced, kept behind HLSMAP_ASSEMBLE_WARP).
 #include <cstdlib>
 
 #include "common.cuh"
