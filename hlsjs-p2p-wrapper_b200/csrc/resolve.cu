@@ -74,8 +74,8 @@ template <bool SMALL, int IPT>
 struct SearchSmem {
     Scan::Smem scan;
     unsigned long long mbar;
-    long long red_min[kWarps];
-    long long red_max[kWarps];
+    long long red_min[2][kWarps];     // double buffered: staging passes of one tile alternate
+    long long red_max[2][kWarps];
     unsigned long long warp_cnt[kWarps];
     int warp_heads[kWarps];
     int tile_slot[2];              // next tile id, double buffered across iterations
@@ -212,6 +212,45 @@ __device__ __forceinline__ int upper_bound_from(const Col &col, int lo, int len,
         }
     }
     return upper_bound_ub(col, a, b - a, ub);
+}
+
+// Both bounds of K queries at once: 2*K independent halving chains, the same number of steps for
+// every lane of the warp (the longest track decides), no branches -- so the probes of all chains
+// are in flight together.  Query k searches col[k][0, n[k]) (n[k] = 0: not taking part).  On a
+// sorted NaN-free column `start <= ub` holds on a prefix, so its end found over the whole track
+// equals the one found from the lower bound on.  Every lane of the warp must call this.
+template <int K, bool GLOBAL>
+__device__ __forceinline__ void bounds_interleaved(const double *const (&col)[K], const int (&n)[K],
+                                                   const double (&bg)[K], const double (&ub)[K],
+                                                   int (&l)[K], int (&h)[K])
+{
+    int nl[K], nh[K], mlen = 0;
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+        l[k] = 0;
+        h[k] = 0;
+        nl[k] = n[k];
+        nh[k] = n[k];
+        mlen = max(mlen, n[k]);
+    }
+    mlen = __reduce_max_sync(0xffffffffu, mlen);
+    for (int rem = mlen; rem > 0; rem >>= 1) {
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+            const int hl = nl[k] >> 1, hh = nh[k] >> 1;
+            // a finished chain keeps probing element 0 (its answer is ignored)
+            const double *pl = col[k] + (nl[k] > 0 ? l[k] + hl : 0);
+            const double *ph = col[k] + (nh[k] > 0 ? h[k] + hh : 0);
+            const double xl = GLOBAL ? __ldg(pl) : *pl;
+            const double xh = GLOBAL ? __ldg(ph) : *ph;
+            const bool gl = nl[k] > 0 && !(bg[k] <= xl);
+            const bool gh = nh[k] > 0 && (xh <= ub[k]);
+            l[k] = gl ? l[k] + hl + 1 : l[k];
+            nl[k] = gl ? nl[k] - hl - 1 : hl;
+            h[k] = gh ? h[k] + hh + 1 : h[k];
+            nh[k] = gh ? nh[k] - hh - 1 : hh;
+        }
+    }
 }
 
 __device__ __forceinline__ int warp_excl_scan(int v, int &total)
@@ -472,6 +511,7 @@ resolve_search_kernel(const ResolveParams p)
                     mx = max(mx, off[k] + len[k]);
                 }
             }
+            trace_mark_after(p, tileB, 13, len[0] ^ len[kIpt - 1]);
             if (p.status) {
                 if (full && kIpt == 4) {
                     const unsigned w = (unsigned)st[0] | ((unsigned)st[1] << 8) |
@@ -538,54 +578,92 @@ resolve_search_kernel(const ResolveParams p)
                     cnt[k] = max(h - l, 0);
                 }
             } else {
-                // ---- make the span of start[] this tile needs resident in shared memory -------
-                bool staged = true;
-#pragma unroll
-                for (int d = 16; d > 0; d >>= 1) {
-                    mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, d));
-                    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, d));
-                }
-                if (lane == 0) { sm.red_min[warp] = mn; sm.red_max[warp] = mx; }
-                __syncthreads();
-#pragma unroll
-                for (int w = 0; w < kWarps; w++) {
-                    mn = min(mn, sm.red_min[w]);
-                    mx = max(mx, sm.red_max[w]);
-                }
-                const long long need_lo = mn & ~3ll, need_hi = (mx + 3) & ~3ll;
-                if (mx < 0) {
-                    staged = true;  // nothing to search in this tile
-                } else if (need_lo >= span_lo && need_hi <= span_hi) {
-                    staged = true;  // still resident from the previous tile
-                } else if (need_hi - need_lo <= (long long)p.stage_elems) {
-                    span_lo = need_lo;
-                    span_hi = need_hi;
-                    if (tid == 0) {
-                        const unsigned bytes = (unsigned)((span_hi - span_lo) * 8);
-                        mbar_expect_tx(&sm.mbar, bytes);
-                        bulk_g2s_chunked(dyn_smem, p.start + span_lo, bytes, &sm.mbar);
-                    }
-                    mbar_wait(&sm.mbar, mbar_phase);
-                    mbar_phase ^= 1u;
-                } else {
-                    staged = false;  // span larger than shared memory: search in L2/HBM
-                }
-                // ---- bounds: [lo, lo+cnt) is exactly what the filter keeps ----------------
+                // ---- bounds: [lo, lo+cnt) is exactly what the filter keeps --------------------
+                // The tile's tracks are searched from a shared-memory window of start[].  Usually
+                // one window holds them all; a tile whose tracks span a few windows is done in
+                // several passes (stage the window that begins at the first track still pending,
+                // search every query whose track lies inside, repeat), so a query of such a tile
+                // does not pay L2/HBM latency per probe.  Tracks longer than the window, and tiles
+                // whose tracks lie far apart (queries not grouped by playlist), probe global memory.
+                constexpr int kMaxPasses = 8;
+                bool pend[kIpt];
+                double ub[kIpt];
+                const double *col[kIpt];
+                int nn[kIpt], l[kIpt], h[kIpt];
 #pragma unroll
                 for (int k = 0; k < kIpt; k++) {
-                    const double ub = __dadd_rn(bg[k], du[k]);
-                    int l, h;
-                    if (staged) {
-                        const SmemCol col{s_start + (int)(off[k] - span_lo)};
-                        l = lower_bound_begin(col, 0, len[k], bg[k]);
-                        h = upper_bound_from(col, l, len[k], ub);
-                    } else {
-                        const GmemCol col{p.start + off[k]};
-                        l = lower_bound_begin(col, 0, len[k], bg[k]);
-                        h = upper_bound_from(col, l, len[k], ub);
+                    ub[k] = __dadd_rn(bg[k], du[k]);
+                    pend[k] = st[k] == HLSMAP_ST_OK && len[k] > 0;
+                }
+                for (int pass = 0; pass < kMaxPasses; pass++) {
+                    mn = 0x7fffffffffffffffll;
+                    mx = -1;
+#pragma unroll
+                    for (int k = 0; k < kIpt; k++) {
+                        if (pend[k] && len[k] <= p.stage_elems - 4) {
+                            mn = min(mn, off[k]);
+                            mx = max(mx, off[k] + len[k]);
+                        }
                     }
-                    lo[k] = l;
-                    cnt[k] = max(h - l, 0);
+#pragma unroll
+                    for (int d = 16; d > 0; d >>= 1) {
+                        mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, d));
+                        mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+                    }
+                    if (lane == 0) { sm.red_min[pass & 1][warp] = mn; sm.red_max[pass & 1][warp] = mx; }
+                    __syncthreads();     // also: every thread is done with the previous window
+#pragma unroll
+                    for (int w = 0; w < kWarps; w++) {
+                        mn = min(mn, sm.red_min[pass & 1][w]);
+                        mx = max(mx, sm.red_max[pass & 1][w]);
+                    }
+                    if (mx < 0) break;                  // nothing (left) to stage: CTA-uniform
+                    const long long need_lo = mn & ~3ll, need_all = (mx + 3) & ~3ll;
+                    if (pass == 0 && need_all - need_lo > 4ll * p.stage_elems) break;   // far apart
+                    const long long need_hi = min(need_all, need_lo + (long long)p.stage_elems);
+                    if (!(need_lo >= span_lo && need_hi <= span_hi)) {   // else: still resident
+                        span_lo = need_lo;
+                        span_hi = need_hi;
+                        if (tid == 0) {
+                            const unsigned bytes = (unsigned)((span_hi - span_lo) * 8);
+                            mbar_expect_tx(&sm.mbar, bytes);
+                            bulk_g2s_chunked(dyn_smem, p.start + span_lo, bytes, &sm.mbar);
+                        }
+                        mbar_wait(&sm.mbar, mbar_phase);
+                        mbar_phase ^= 1u;
+                    }
+                    if (pass == 0) trace_mark(p, tileB, 14);
+#pragma unroll
+                    for (int k = 0; k < kIpt; k++) {
+                        // (off >= span_lo: the window starts at the first pending track)
+                        const bool act = pend[k] && len[k] <= p.stage_elems - 4 && off[k] + len[k] <= span_hi;
+                        col[k] = s_start + (act ? (int)(off[k] - span_lo) : 0);
+                        nn[k] = act ? len[k] : 0;
+                    }
+                    bounds_interleaved<kIpt, false>(col, nn, bg, ub, l, h);
+#pragma unroll
+                    for (int k = 0; k < kIpt; k++) {
+                        if (nn[k] > 0) {
+                            lo[k] = l[k];
+                            cnt[k] = max(h[k] - l[k], 0);
+                            pend[k] = false;
+                        }
+                    }
+                    if (need_hi == need_all) break;     // the window held every pending track
+                }
+                // whatever is still pending probes L2/HBM (no lane has any in the common case)
+#pragma unroll
+                for (int k = 0; k < kIpt; k++) {
+                    col[k] = p.start + (pend[k] ? off[k] : 0);
+                    nn[k] = pend[k] ? len[k] : 0;
+                }
+                bounds_interleaved<kIpt, true>(col, nn, bg, ub, l, h);
+#pragma unroll
+                for (int k = 0; k < kIpt; k++) {
+                    if (pend[k]) {
+                        lo[k] = l[k];
+                        cnt[k] = max(h[k] - l[k], 0);
+                    }
                 }
             }
 

@@ -225,6 +225,29 @@ def test_config5_shuffled_queries_span_beyond_window(ctx):
     run_both_paths(ctx, t, q, paths=(N.PATH_SEARCH,))
 
 
+@pytest.mark.parametrize("window_kb", [2, 16, 24])
+def test_config5_tracks_spanning_several_windows(ctx, window_kb, monkeypatch):
+    """A staging window (HLSMAP_STAGE_WINDOW_KB, read at upload) smaller than a tile's tracks:
+    the tile is searched in several staging passes, tracks longer than the window and tiles
+    spread over more than a few windows probe global memory -- same output in every case."""
+    monkeypatch.setenv("HLSMAP_STAGE_WINDOW_KB", str(window_kb))
+    t, q = synth.config5(seed=11, n_playlists=300, queries_per_playlist=100)
+    m = ctx.upload(t)
+    assert m.info()["stage_all"] == 0
+    ref = oracle_list(t, q)
+    assert_same(m.get_segment_list(q.playlist, q.level, q.begin, q.duration), ref, "grouped")
+    m.close()
+    # half-shuffled: runs of grouped queries interleaved with far-away ones
+    rng = np.random.default_rng(window_kb)
+    perm = np.arange(len(q))
+    sel = rng.random(len(q)) < 0.3
+    perm[sel] = rng.permutation(perm[sel])
+    q2 = QueryBatch(q.playlist[perm], q.level[perm], q.begin[perm], q.duration[perm])
+    m = ctx.upload(t)
+    assert_same(m.get_segment_list(q2.playlist, q2.level, q2.begin, q2.duration), oracle_list(t, q2), "mixed")
+    m.close()
+
+
 def test_huge_counts_take_the_cooperative_expansion(ctx):
     """Queries that keep whole 10k-fragment tracks (warp output run > 2048 entries)."""
     t, _, _ = synth.config4(n_views=8)
