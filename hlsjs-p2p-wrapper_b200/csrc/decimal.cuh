@@ -73,10 +73,99 @@ HLSMAP_HD inline DecimalScan scan_decimal(const Get &get, long long p, long long
 }
 
 #if defined(__CUDACC__) || defined(__SIZEOF_INT128__)
+HLSMAP_HD inline int clz64(unsigned long long x)
+{
+#ifdef __CUDA_ARCH__
+    return __clzll((long long)x);
+#else
+    return __builtin_clzll(x);
+#endif
+}
+
+// The 64 leading quotient bits of w / 10^k for k <= 19 (the divisor fits 64 bits), the binary
+// exponent of the quotient and whether a remainder is left.  One floating-point division gives
+// the quotient to within 2^13 units of its last bit; the difference is then settled exactly in
+// integers (a 128-bit remainder, one more small estimate, at most a step or two of fix-up) --
+// a few dozen instructions where the subtract-and-shift division below takes over a thousand.
+// Returns false if an estimate is ever further off than the analysis allows (the caller then
+// divides the slow way; not observed).
+HLSMAP_HD inline bool div_pow10_estimate(unsigned long long w, int k, unsigned long long *q_out, int *e_out,
+                                         bool *rem_out)
+{
+    unsigned long long d = 1;
+    for (int i = 0; i < k; i++) d *= 10ull;
+    const int la = 63 - clz64(w), ld = 63 - clz64(d);
+    const int e0 = la - ld - (((w << (63 - la)) >= (d << (63 - ld))) ? 0 : 1);    // floor(log2(w / d))
+    const int t = 63 - e0;                                                        // w * 2^t / d in [2^63, 2^64)
+    const unsigned __int128 num = (unsigned __int128)w << t;
+#ifdef __CUDA_ARCH__
+    const double x0 = __ddiv_rn(__ull2double_rn(w), __ull2double_rn(d));
+#else
+    const double x0 = (double)w / (double)d;
+#endif
+    unsigned long long xb;
+    memcpy(&xb, &x0, sizeof xb);
+    const int sh = (int)((xb >> 52) & 0x7ffull) - 1075 + t;                       // x0 * 2^t = m * 2^sh
+    const unsigned long long m = (xb & ((1ull << 52) - 1ull)) | (1ull << 52);
+    if (sh < 8 || sh > 12) return false;
+    unsigned long long q = sh == 12 ? ~0ull << 11 : m << sh;                      // (m << 12 would be 2^64)
+    __int128 r = (__int128)(num - (unsigned __int128)q * d);                      // |r| < 2^14 * d
+    // r / d, estimated: r itself fits 64 bits next to a small divisor, r / 2^13 does next to a large one
+    const bool wide = d >= (1ull << 48);
+    const long long rs = wide ? (long long)(r >> 13) : (long long)r;
+    const double scale = wide ? 8192.0 : 1.0;
+#ifdef __CUDA_ARCH__
+    const long long delta = __double2ll_rd(__ddiv_rn(__dmul_rn(__ll2double_rn(rs), scale), __ull2double_rn(d)));
+#else
+    const double de = (double)rs * scale / (double)d;
+    long long delta = (long long)de;
+    if ((double)delta > de) delta--;
+#endif
+    if (delta > (1ll << 20) || delta < -(1ll << 20)) return false;
+    r -= (__int128)delta * (__int128)(unsigned __int128)d;
+    q += (unsigned long long)delta;
+    for (int i = 0; i < 8 && r < 0; i++) {
+        r += (__int128)(unsigned __int128)d;
+        q--;
+    }
+    for (int i = 0; i < 8 && r >= (__int128)(unsigned __int128)d; i++) {
+        r -= (__int128)(unsigned __int128)d;
+        q++;
+    }
+    if (r < 0 || r >= (__int128)(unsigned __int128)d || !(q >> 63)) return false;
+    *q_out = q;
+    *e_out = e0;
+    *rem_out = r != 0;
+    return true;
+}
+
+// 64 quotient bits (the first of them set), the quotient's binary exponent and a sticky flag ->
+// binary64, round to nearest, ties to even.
+HLSMAP_HD inline double round_quotient(unsigned long long q, int e, bool sticky)
+{
+    unsigned long long m = q >> 11;
+    const unsigned long long rest = q & 0x7ffull;
+    if (rest > 0x400ull || (rest == 0x400ull && (sticky || (m & 1ull)))) m++;
+    if (m == (1ull << 53)) {
+        m >>= 1;
+        e++;
+    }
+    const unsigned long long bits = ((unsigned long long)(e + 1023) << 52) | (m & ((1ull << 52) - 1ull));
+    double out;
+    memcpy(&out, &bits, sizeof out);
+    return out;
+}
+
 // w / 10^k (0 <= k <= 38, w != 0) rounded to binary64; `above` = the true value lies
 // strictly above w / 10^k by less than the quotient's last kept bit can resolve.
-HLSMAP_HD inline double div_pow10_rounded(unsigned long long w, int k, bool above)
+HLSMAP_HD inline double div_pow10_rounded(unsigned long long w, int k, bool above, bool allow_estimate = true)
 {
+    if (allow_estimate && k <= 19) {
+        unsigned long long qf;
+        int ef;
+        bool rem;
+        if (div_pow10_estimate(w, k, &qf, &ef, &rem)) return round_quotient(qf, ef, above || rem);
+    }
     unsigned __int128 d = 1, a = w;
     for (int i = 0; i < k; i++) d *= 10u;
     int e = 0;  // value = (a / d) * 2^e with d <= a < 2d
@@ -100,18 +189,7 @@ HLSMAP_HD inline double div_pow10_rounded(unsigned long long w, int k, bool abov
         }
         a <<= 1;
     }
-    const bool sticky = above || a != 0;
-    unsigned long long m = q >> 11;
-    const unsigned long long rest = q & 0x7ffull;
-    if (rest > 0x400ull || (rest == 0x400ull && (sticky || (m & 1ull)))) m++;
-    if (m == (1ull << 53)) {
-        m >>= 1;
-        e++;
-    }
-    const unsigned long long bits = ((unsigned long long)(e + 1023) << 52) | (m & ((1ull << 52) - 1ull));
-    double out;
-    memcpy(&out, &bits, sizeof out);
-    return out;
+    return round_quotient(q, e, above || a != 0);
 }
 
 // false = outside what this converter answers exactly (the caller reports it, loudly).
