@@ -295,9 +295,9 @@ __device__ __forceinline__ int eat_int(const Text &t, long long &q, long long li
 __constant__ double c_json_pow10[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
                                         1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
 
-// `time`: digits [. digits] with at most 15 significant digits and no exponent is one exact IEEE
-// division (both operands are exact doubles); the rest takes the general path.  Returns 0 when the
-// general path has to decide.
+// `time`: digits [. digits] without an exponent and with at most 19 significant digits is read in
+// one walk: up to 15 digits it is one exact IEEE division (both operands are exact doubles), up to
+// 19 the exact integer division of decimal.cuh.  Returns 0 when the general path has to decide.
 __device__ __forceinline__ int eat_plain_decimal(const Text &t, long long &q, long long lim, double *out)
 {
     long long r = q;
@@ -312,7 +312,7 @@ __device__ __forceinline__ int eat_plain_decimal(const Text &t, long long &q, lo
         if (nsig > 0 || c != '0') nsig++;
         w = w * 10ull + (unsigned long long)(c - '0');
         r++;
-        if (nsig > 15) return 0;
+        if (nsig > 19) return 0;
     }
     const int ni = (int)(r - d0);
     if (ni == 0 || (ni > 1 && t(d0) == '0')) return 0;
@@ -325,13 +325,17 @@ __device__ __forceinline__ int eat_plain_decimal(const Text &t, long long &q, lo
             if (nsig > 0 || c != '0') nsig++;
             w = w * 10ull + (unsigned long long)(c - '0');
             r++;
-            if (nsig > 15 || r - f0 > 22) return 0;
+            if (nsig > 19 || r - f0 > 22) return 0;
         }
         frac = (int)(r - f0);
         if (frac == 0) return 0;
     }
     if (r < lim && (t(r) == 'e' || t(r) == 'E')) return 0;
-    const double mag = frac ? __ddiv_rn((double)w, c_json_pow10[frac]) : (double)w;
+    double mag;
+    if (w == 0) mag = 0.0;
+    else if (nsig <= 15) mag = frac ? __ddiv_rn((double)w, c_json_pow10[frac]) : (double)w;
+    else if (frac <= 19) mag = div_pow10_rounded(w, frac, false);
+    else return 0;
     *out = neg ? -mag : mag;
     q = r;
     return 1;
