@@ -157,10 +157,12 @@ HLSMAP_HD inline double round_quotient(unsigned long long q, int e, bool sticky)
 }
 
 // w / 10^k (0 <= k <= 38, w != 0) rounded to binary64; `above` = the true value lies
-// strictly above w / 10^k by less than the quotient's last kept bit can resolve.
-HLSMAP_HD inline double div_pow10_rounded(unsigned long long w, int k, bool above, bool allow_estimate = true)
+// strictly above w / 10^k by less than the quotient's last kept bit can resolve.  ESTIMATE = false
+// leaves the estimated division out (callers for which this path is rare and registers are dear).
+template <bool ESTIMATE = true>
+HLSMAP_HD inline double div_pow10_rounded(unsigned long long w, int k, bool above)
 {
-    if (allow_estimate && k <= 19) {
+    if (ESTIMATE && k <= 19) {
         unsigned long long qf;
         int ef;
         bool rem;
@@ -193,6 +195,7 @@ HLSMAP_HD inline double div_pow10_rounded(unsigned long long w, int k, bool abov
 }
 
 // false = outside what this converter answers exactly (the caller reports it, loudly).
+template <bool ESTIMATE = true>
 HLSMAP_HD inline bool decimal_to_double(const DecimalScan &s, double *out)
 {
     if (s.w == 0) {
@@ -210,12 +213,12 @@ HLSMAP_HD inline bool decimal_to_double(const DecimalScan &s, double *out)
         *out = (double)s.w / den;
         return true;
     }
-    const double lo = div_pow10_rounded(s.w, k, s.sticky);
+    const double lo = div_pow10_rounded<ESTIMATE>(s.w, k, s.sticky);
     if (!s.sticky) {
         *out = lo;
         return true;
     }
-    const double hi = div_pow10_rounded(s.w + 1ull, k, false);  // w < 10^19: no overflow
+    const double hi = div_pow10_rounded<ESTIMATE>(s.w + 1ull, k, false);  // w < 10^19: no overflow
     if (lo != hi) return false;
     *out = lo;
     return true;

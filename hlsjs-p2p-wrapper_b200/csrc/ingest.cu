@@ -90,7 +90,7 @@ __device__ __noinline__ Token classify_at(const TextView &v, long long p, long l
             return t;
         }
         double x = 0.0;
-        t.unsupported = !decimal_to_double(d, &x);
+        t.unsupported = !decimal_to_double<false>(d, &x);   // rare here: the compact division will do
         t.kind = kTokFrag;
         t.bits = __double_as_longlong(x);
         return t;
@@ -143,7 +143,7 @@ __device__ __noinline__ bool decimal_slow(unsigned long long w, int exp10, bool 
     d.sticky = sticky;
     d.run = 1;
     d.is_number = true;
-    return decimal_to_double(d, out);
+    return decimal_to_double<false>(d, out);
 }
 
 __device__ __forceinline__ bool classify_fast(const unsigned char *stext, int pos_rel, int limit, bool limit_is_end,

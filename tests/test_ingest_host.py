@@ -142,7 +142,7 @@ int main() {
     auto check = [&](unsigned long long w, int k, bool above) {
         unsigned long long q; int e; bool rem;
         if (!div_pow10_estimate(w, k, &q, &e, &rem)) fell++;
-        const double a = div_pow10_rounded(w, k, above, true), b = div_pow10_rounded(w, k, above, false);
+        const double a = div_pow10_rounded<true>(w, k, above), b = div_pow10_rounded<false>(w, k, above);
         n++;
         if (memcmp(&a, &b, 8)) { if (bad < 10) printf("MISMATCH w=%llu k=%d above=%d\n", w, k, (int)above); bad++; }
     };
