@@ -42,31 +42,22 @@ struct Shape {
     static_assert(kWords <= kThreads, "one bitmap word per thread at most");
 };
 
-// Expansion records: one per query that kept >= 1 fragment, in query order.
-//   rel = first output slot relative to the tile's output run, src = first kept fragment.
+// Expansion records: one per query that kept >= 1 fragment, in query order.  With rel = the
+// query's first output slot relative to the tile's output run and src = its first kept fragment,
+// output slot q of that query comes from fragment src + (q - rel): the record keeps src - rel.
 template <bool SMALL, int TILE>
 struct RecTable;
 template <int TILE>
-struct RecTable<true, TILE> {   // every fragment index fits an int: one 8-byte record
-    int2 v[TILE];
-    __device__ __forceinline__ void set(int i, int rel, long long src) { v[i] = make_int2(rel, (int)src); }
-    __device__ __forceinline__ void get(int i, int &rel, long long &src) const
-    {
-        const int2 r = v[i];
-        rel = r.x;
-        src = r.y;
-    }
+struct RecTable<true, TILE> {   // every fragment index fits an int
+    int v[TILE];
+    __device__ __forceinline__ void set(int i, int rel, long long src) { v[i] = (int)src - rel; }
+    __device__ __forceinline__ long long fragment_of(int i, int slot) const { return v[i] + slot; }
 };
 template <int TILE>
 struct RecTable<false, TILE> {
-    int rel_[TILE];
-    long long src_[TILE];
-    __device__ __forceinline__ void set(int i, int rel, long long src) { rel_[i] = rel; src_[i] = src; }
-    __device__ __forceinline__ void get(int i, int &rel, long long &src) const
-    {
-        rel = rel_[i];
-        src = src_[i];
-    }
+    long long v[TILE];
+    __device__ __forceinline__ void set(int i, int rel, long long src) { v[i] = src - rel; }
+    __device__ __forceinline__ long long fragment_of(int i, int slot) const { return v[i] + slot; }
 };
 
 // Shared state of one CTA.
@@ -765,10 +756,7 @@ resolve_search_kernel(const ResolveParams p)
                 // slot name the record; its source fragment follows by offset.
                 auto emit = [&](const uint2 hw, int slot, double &t, int &s) {
                     const int r = (int)hw.y + __popc(hw.x & lane_le) - 1;
-                    int rrel;
-                    long long src;
-                    sm.rec.get(r, rrel, src);
-                    src += slot - rrel;
+                    const long long src = sm.rec.fragment_of(r, slot);
                     if (SMALL) {
                         t = s_start[(int)src];
                         s = s_sn[(int)src];
