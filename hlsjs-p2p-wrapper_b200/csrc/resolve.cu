@@ -37,7 +37,7 @@ template <int IPT>
 struct Shape {
     static constexpr int kIpt = IPT;
     static constexpr int kTile = kThreads * IPT;
-    static constexpr int kWindow = IPT >= 4 ? 8192 : 4096;
+    static constexpr int kWindow = 8192;
     static constexpr int kWords = kWindow / 32;   // <= kThreads: one bitmap word per thread
     static_assert(kWords <= kThreads, "one bitmap word per thread at most");
 };
