@@ -323,6 +323,7 @@ __global__ void __launch_bounds__(kThreads, (SMALL && IPT == 2) ? 4 : ((SMALL ||
 resolve_search_kernel(const ResolveParams p)
 {
     using S = Shape<IPT>;
+    constexpr int kClaimSlots = 8 * kThreads;   // the next ticket is drawn this many output slots before the tile's last
     constexpr int kIpt = S::kIpt, kWindow = S::kWindow, kWords = S::kWords;
     extern __shared__ __align__(128) unsigned char dyn_smem[];
     __shared__ SearchSmem<SMALL, IPT> sm;
@@ -768,13 +769,6 @@ resolve_search_kernel(const ResolveParams p)
                 const bool all_fit = (long long)tile_base + total <= p.capacity;   // CTA-uniform
                 for (int w0 = 0; w0 < total; w0 += kWindow) {
                     uint2 *H = sm.hb[hbuf];
-                    if (tid == 0 && haveB && !ticket_pending && w0 + kWindow >= total) {
-                        // Claim the next tile as late as possible -- a claimed but unsearched
-                        // tile stalls the look-back of every later tile -- yet early enough
-                        // for the atomic's round trip to hide behind this last window.
-                        t_new = atomicAdd(&p.ctr->ticket[p.tslot & 1u], 1u);
-                        ticket_pending = true;
-                    }
                     {   // mark where this thread's records start inside the window, rank words
                         int r2 = (int)a_rel;
 #pragma unroll
@@ -809,6 +803,14 @@ resolve_search_kernel(const ResolveParams p)
                     int q = tid;
                     if (all_fit) {
                         for (; q + 3 * kThreads < wend; q += 4 * kThreads) {
+                            if (tid == 0 && haveB && !ticket_pending && w0 + kWindow >= total &&
+                                q + kClaimSlots >= wend) {
+                                // Claim the next tile as late as possible -- a claimed but unsearched
+                                // tile stalls the look-back of every later tile -- yet early enough
+                                // for the atomic's round trip to hide behind the slots still to write.
+                                t_new = atomicAdd(&p.ctr->ticket[p.tslot & 1u], 1u);
+                                ticket_pending = true;
+                            }
                             double t[4];
                             int s[4];
                             uint2 hw[4];
