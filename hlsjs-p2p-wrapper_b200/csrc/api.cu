@@ -83,7 +83,8 @@ struct hlsmap_map {
     int stage_elems = 0;
     size_t stage_smem = 0;
     int grid_search = 0, grid_filter = 0;
-    int ipt = 4;                        // queries per thread of the SMALL search kernel
+    int ipt = 2;                        // queries per thread of the search kernel (tiles of 256 * ipt)
+    int grid_search_wide = 0;           // SMALL maps: grid of the 1024-query-tile variant (0 = not offered)
 };
 
 namespace {
@@ -183,14 +184,14 @@ inline bool al16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) 
 // Tiling of a batch: full tiles of the kernel's 256*ipt queries.  (Trimming the tile size so
 // that every CTA gets a whole number of tiles was measured on B200 and lost: 61 us vs 57 us on
 // the 10^6-query workload -- per-tile fixed costs outweigh the idle tail round.)
-void plan_tiles(const hlsmap_map *map, int path, int64_t nq, int *tile_q, int64_t *n_tiles)
+void plan_tiles(const hlsmap_map *map, int path, int64_t nq, int *tile_q, int64_t *n_tiles, int ipt = 0)
 {
     if (path != HLSMAP_PATH_SEARCH) {
         *tile_q = kFilterTileQueries;
         *n_tiles = (nq + kFilterTileQueries - 1) / kFilterTileQueries;
         return;
     }
-    const int tq = resolve_search_tile(map->info.stage_all != 0, map->ipt);
+    const int tq = resolve_search_tile(map->info.stage_all != 0, ipt ? ipt : map->ipt);
     const int64_t tiles = (nq + tq - 1) / tq;
     *tile_q = tq;
     *n_tiles = tiles;
@@ -433,7 +434,7 @@ static int map_create_impl(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *
     // and a u16 hint grid of `cells` cells per fragment) fits next to the kernel's own
     // shared state, so it is staged once per CTA.  Otherwise the search kernel stages, per
     // tile, the window of the start column its queries touch.
-    int64_t small_limit = 100 * 1024, window = 64 * 1024, cells = 2;
+    int64_t small_limit = 100 * 1024, window = 64 * 1024, cells = 1;
     if (const char *e = getenv("HLSMAP_SMALL_KB")) small_limit = atoll(e) * 1024;
     if (const char *e = getenv("HLSMAP_STAGE_WINDOW_KB")) window = atoll(e) * 1024;
     if (const char *e = getenv("HLSMAP_HINT_CELLS")) cells = atoll(e) > 0 ? atoll(e) : 1;
@@ -484,6 +485,8 @@ static int map_create_impl(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *
     m->ipt = 2;
     if (const char *e = getenv(small ? "HLSMAP_IPT" : "HLSMAP_IPT_GENERAL")) m->ipt = atoi(e) == 4 ? 4 : 2;
     m->grid_search = resolve_search_max_grid(m->stage_smem, small, m->ipt);
+    // SMALL maps also offer 1024-query tiles (3 CTAs/SM): picked per batch, see list_core()
+    if (small && m->ipt == 2 && !getenv("HLSMAP_IPT")) m->grid_search_wide = resolve_search_max_grid(m->stage_smem, true, 4);
     m->grid_filter = resolve_filter_max_grid();
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess)
@@ -661,9 +664,17 @@ static int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
         return HLSMAP_OK;
     }
 
+    // Tile size.  Batches that run back to back (hlsmap_ctx_set_batch_overlap) and give every
+    // CTA two tiles or more take 1024-query tiles on SMALL maps: half as many look-backs and
+    // bitmap builds per query, measured 38.6 us against 39.2 per 10^6-query batch; a batch on
+    // its own keeps 512-query tiles (56 us against 58: its ramp and tail are shorter).
+    int ipt = map->ipt;
+    if (path == HLSMAP_PATH_SEARCH && ctx->overlap && map->grid_search_wide > 0 &&
+        nq >= 2ll * map->grid_search_wide * resolve_search_tile(true, 4))
+        ipt = 4;
     int tile_q = 0;
     int64_t n_tiles = 0;
-    plan_tiles(map, path, nq, &tile_q, &n_tiles);
+    plan_tiles(map, path, nq, &tile_q, &n_tiles, ipt);
     if (n_tiles > 0x7fffffff) return fail(HLSMAP_ERR_INVALID, "batch too large: split it");
     r = prepare_scan(ctx, n_tiles, s);
     if (r) return r;
@@ -696,7 +707,7 @@ static int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
     p.stage_elems = map->stage_elems;
     p.stage_all = map->info.stage_all;
     p.small = map->info.stage_all;
-    p.ipt = map->ipt;
+    p.ipt = ipt;
     p.hint = map->d_hint;
     p.grid = map->d_grid;
     p.grid_padded = map->grid_padded;
@@ -714,7 +725,8 @@ static int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
         p.trace = d_trace;
     }
     if (path == HLSMAP_PATH_SEARCH) {
-        const int grid = (int)(n_tiles < map->grid_search ? n_tiles : map->grid_search);
+        const int max_grid = ipt == map->ipt ? map->grid_search : map->grid_search_wide;
+        const int grid = (int)(n_tiles < max_grid ? n_tiles : max_grid);
         CK(launch_resolve_search(p, grid, map->stage_smem, s, ctx->overlap && d_trace == nullptr));
     } else {
         const int grid = (int)(n_tiles < map->grid_filter ? n_tiles : map->grid_filter);

@@ -347,7 +347,9 @@ def test_overlapping_batches_on_disjoint_buffers(ctx):
     m = ctx.upload(t)
     stream = torch.cuda.Stream(device=dev)
     sets = []
-    for i, nq in enumerate((200_000, 70_001, 333_333, 1_000, 150_000)):
+    # (the 10^6-query batches take the 1024-query-tile variant the library picks for large
+    #  overlapped batches, the others 512-query tiles: both kinds alternate on the same scratch)
+    for i, nq in enumerate((200_000, 1_000_003, 70_001, 333_333, 1_000, 1_000_000, 150_000)):
         _, q = synth.config2(seed=40 + i, n_queries=nq)
         ref = oracle_list(t, q)
         H = int(ref[0][-1])
@@ -360,9 +362,10 @@ def test_overlapping_batches_on_disjoint_buffers(ctx):
     torch.cuda.synchronize()
     ctx.set_batch_overlap(True)
     try:
-        for rep in range(4):                       # 20 launches back to back, no host sync between
+        for rep in range(4):                       # 28 launches back to back, no host sync between
             for s in sets:
-                s["off"].fill_(-1)
+                with torch.cuda.stream(stream):     # on the batches' own stream: ordered before the launch
+                    s["off"].fill_(-1)
                 m.get_segment_list_dev(len(s["q"]), s["pl"].data_ptr(), s["lv"].data_ptr(),
                                        s["bg"].data_ptr(), s["du"].data_ptr(), s["off"].data_ptr(),
                                        s["sn"].data_ptr(), s["tm"].data_ptr(), s["H"],
