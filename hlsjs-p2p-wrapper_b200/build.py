@@ -6,7 +6,10 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
-LIB = os.path.join(CSRC, "libhlsmap.so")
+# HLSMAP_TRACE_BUILD=1 in the environment selects a separate diagnostics library whose search
+# kernel records per-tile phase timestamps (scripts/trace_run.py); the product library has none.
+TRACE = os.environ.get("HLSMAP_TRACE_BUILD") == "1"
+LIB = os.path.join(CSRC, "libhlsmap_trace.so" if TRACE else "libhlsmap.so")
 SOURCES = ["resolve.cu", "views.cu", "ingest.cu", "json.cu", "api.cu"]
 HEADERS = ["common.cuh", "scan.cuh", "decimal.cuh", "dtoa.cuh", "pow10_table.inc"]
 
@@ -35,7 +38,8 @@ def build(force=False, verbose=False):
     """Compile every CUDA source into one shared library; returns its path."""
     if not force and not needs_build():
         return LIB
-    cmd = [_nvcc()] + NVCC_FLAGS + ["-I", INCLUDE, "-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
+    cmd = [_nvcc()] + NVCC_FLAGS + (["-DHLSMAP_TRACE_BUILD=1"] if TRACE else []) + \
+        ["-I", INCLUDE, "-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
     if verbose:
         cmd.insert(1, "-Xptxas")
         cmd.insert(2, "-v")

@@ -16,6 +16,10 @@
 
 using namespace hlsmap;
 
+#ifndef HLSMAP_TRACE_BUILD
+#define HLSMAP_TRACE_BUILD 0
+#endif
+
 namespace {
 
 thread_local std::string g_err;
@@ -48,6 +52,8 @@ struct hlsmap_ctx {
     ScanCounters *ctr = nullptr;        // scan scratch headers, one per scratch set (2)
     DeviceResult *d_result = nullptr;   // results, one per scratch set (2)
     bool overlap = false;               // consecutive search batches may overlap (PDL)
+    bool host_pipeline = true;          // chunked upload/compute/download of large host-pointer calls
+                                        // (HLSMAP_NO_PIPELINE in the environment at context creation turns it off)
     unsigned set_launches[2] = {0, 0};  // kernels launched on each scratch set (ticket slot parity)
     DeviceResult *h_result = nullptr;   // pinned
     unsigned long long *tile_status = nullptr;   // 2 x tile_cap status words (set = epoch & 1)
@@ -227,6 +233,7 @@ int hlsmap_ctx_create(int device, hlsmap_ctx **out)
     hlsmap_ctx *c = new (std::nothrow) hlsmap_ctx();
     if (!c) return fail(HLSMAP_ERR_NOMEM, "out of host memory");
     c->device = device;
+    c->host_pipeline = getenv("HLSMAP_NO_PIPELINE") == nullptr;   // read once, here
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, device));
     if (prop.major < 10) {
@@ -718,12 +725,14 @@ static int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
                (!d_status || (reinterpret_cast<uintptr_t>(d_status) & 3u) == 0);
 
     unsigned long long *d_trace = nullptr;
-    const char *trace_path = getenv("HLSMAP_TRACE");     // experiment: per-tile phase timestamps
+#if HLSMAP_TRACE_BUILD      // diagnostics library only: per-tile phase timestamps into the file HLSMAP_TRACE names
+    const char *trace_path = getenv("HLSMAP_TRACE");
     if (trace_path && path == HLSMAP_PATH_SEARCH) {
         CK(cudaMalloc(&d_trace, (size_t)n_tiles * 128));
         CK(cudaMemsetAsync(d_trace, 0, (size_t)n_tiles * 128, s));
         p.trace = d_trace;
     }
+#endif
     if (path == HLSMAP_PATH_SEARCH) {
         const int max_grid = ipt == map->ipt ? map->grid_search : map->grid_search_wide;
         const int grid = (int)(n_tiles < max_grid ? n_tiles : max_grid);
@@ -734,6 +743,7 @@ static int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
     }
     ctx->set_launches[ctx->epoch & 1u]++;      // only after a successful launch
     ctx->last_launches = 1;
+#if HLSMAP_TRACE_BUILD
     if (d_trace) {
         std::vector<unsigned long long> h((size_t)n_tiles * 16);
         CK(cudaMemcpyAsync(h.data(), d_trace, (size_t)n_tiles * 128, cudaMemcpyDeviceToHost, s));
@@ -744,6 +754,7 @@ static int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
         }
         CK(cudaFree(d_trace));
     }
+#endif
 
     if (result) {
         r = fetch_result(ctx, s, result);
@@ -804,7 +815,7 @@ int hlsmap_get_segment_list(hlsmap_map *map, int64_t nq, const int32_t *playlist
     // Large filling batches go through a chunked pipeline: while chunk c's hits travel to the
     // host, chunk c+1's queries travel to the device (PCIe is full duplex) and its kernel runs.
     constexpr int64_t kChunk = 131072;      // queries per chunk (multiple of 1024: aligned sections)
-    if (fill && nq >= 2 * kChunk && !getenv("HLSMAP_NO_PIPELINE")) {
+    if (fill && nq >= 2 * kChunk && ctx->host_pipeline) {
         int64_t dev_cap = ctx->slot_bytes[6] / 4 < ctx->slot_bytes[7] / 8 ? ctx->slot_bytes[6] / 4
                                                                          : ctx->slot_bytes[7] / 8;
         int64_t want = nq * 16 + 1024;
@@ -1426,12 +1437,14 @@ int hlsmap_view_format(hlsmap_ctx *ctx, int64_t n, const int32_t *level, const i
 // never does.  Its scratch is the fixed array below, which lives in every GPU context that
 // loads the library (about 0.5 MiB per GPU, until the process exits).
 //
-// Layout, in 8-byte words: [0,4) ScanCounters, [8,12) DeviceResult, [32, 32+kNoAllocMaxTiles)
+// Layout, in 8-byte words: [0,5) ScanCounters, [8,12) DeviceResult, [32, 32+kNoAllocMaxTiles)
 // one look-back status word per tile.
 namespace {
 constexpr long long kNoAllocMaxTiles = 65536;
 constexpr int kNoAllocHeaderWords = 32;
 constexpr int kNoAllocMaxDevices = 64;
+static_assert(sizeof(ScanCounters) <= 8 * 8 && sizeof(DeviceResult) <= (kNoAllocHeaderWords - 8) * 8,
+              "no-alloc scratch header layout");
 }  // namespace
 static __device__ __align__(256) unsigned long long g_noalloc_scratch[kNoAllocHeaderWords + kNoAllocMaxTiles];
 

@@ -29,7 +29,8 @@ constexpr unsigned kTrackMonotone = 4u;
 // Per-context scratch header for the single-pass scan kernels.  A context owns TWO scratch
 // sets (header + status words + result) used by alternate launches (set = epoch & 1), so that
 // a batch may start while the previous one is still draining; `owner` is the epoch of the
-// launch currently using the set (0 = free), and ticket[] is double buffered: the host tells
+// launch currently using the set (0 = free; given back by the last CTA of that launch to exit,
+// which `exited` counts), and ticket[] is double buffered: the host tells
 // each launch which of the two counters to use (they alternate per set), and a launch's last
 // tile zeroes the OTHER one, so late ticket fetches of a launch never see the next one's reset.
 struct ScanCounters {
@@ -38,6 +39,8 @@ struct ScanCounters {
     unsigned int owner;
     unsigned long long n_unparsed;
     unsigned long long n_missing;
+    unsigned int exited;      // CTAs of the owning launch that have left
+    unsigned int pad;
 };
 
 // What the last tile of a batch leaves behind for the host.

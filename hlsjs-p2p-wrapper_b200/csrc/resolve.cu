@@ -45,19 +45,25 @@ struct Shape {
 // Expansion records: one per query that kept >= 1 fragment, in query order.  With rel = the
 // query's first output slot relative to the tile's output run and src = its first kept fragment,
 // output slot q of that query comes from fragment src + (q - rel): the record keeps src - rel.
+// SMALL maps keep it as a shared-memory BYTE address: &s_sn[src - rel]; slot q's sn then sits at
+// that address + 4*q and its start at 2 * (that address + 4*q) + (addr(s_start) - 2 * addr(s_sn)):
+// one add per slot, one shift-add more for the time.
 template <bool SMALL, int TILE>
 struct RecTable;
 template <int TILE>
 struct RecTable<true, TILE> {   // every fragment index fits an int
-    int v[TILE];
-    __device__ __forceinline__ void set(int i, int rel, long long src) { v[i] = (int)src - rel; }
-    __device__ __forceinline__ long long fragment_of(int i, int slot) const { return v[i] + slot; }
+    unsigned v[TILE];
+    static constexpr int kShift = 2;
+    __device__ __forceinline__ void set(int i, int rel, long long src, unsigned sn_addr)
+    {
+        v[i] = sn_addr + 4u * (unsigned)((int)src - rel);
+    }
 };
 template <int TILE>
 struct RecTable<false, TILE> {
     long long v[TILE];
-    __device__ __forceinline__ void set(int i, int rel, long long src) { v[i] = src - rel; }
-    __device__ __forceinline__ long long fragment_of(int i, int slot) const { return v[i] + slot; }
+    static constexpr int kShift = 3;
+    __device__ __forceinline__ void set(int i, int rel, long long src, unsigned) { v[i] = src - rel; }
 };
 
 // Shared state of one CTA.
@@ -79,6 +85,29 @@ struct SearchSmem {
 __device__ __forceinline__ unsigned smem_u32(const void *p)
 {
     return (unsigned)__cvta_generic_to_shared(p);
+}
+
+// Loads from a 32-bit shared-memory address plus a compile-time offset (one LDS, no address math).
+template <int IMM>
+__device__ __forceinline__ unsigned lds_u32(unsigned addr)
+{
+    unsigned v;
+    asm("ld.shared.u32 %0, [%1+%2];" : "=r"(v) : "r"(addr), "n"(IMM));
+    return v;
+}
+template <int IMM>
+__device__ __forceinline__ double lds_f64(unsigned addr)
+{
+    double v;
+    asm("ld.shared.f64 %0, [%1+%2];" : "=d"(v) : "r"(addr), "n"(IMM));
+    return v;
+}
+template <int IMM>
+__device__ __forceinline__ long long lds_s64(unsigned addr)
+{
+    long long v;
+    asm("ld.shared.s64 %0, [%1+%2];" : "=l"(v) : "r"(addr), "n"(IMM));
+    return v;
 }
 
 // ---- TMA (bulk async copy) staging of table columns ------------------------------------
@@ -273,13 +302,14 @@ __device__ __forceinline__ unsigned long long warp_excl_scan64(unsigned long lon
 
 }  // namespace
 
-// Hint-grid cell of a time value: monotone non-decreasing in x, NaN -> 0, saturating.  The
-// SAME function places table entries (upload) and query bounds (lookup), so for a sorted
-// NaN-free column  cell(s) < cell(x) => s < x  and  cell(s) > cell(x) => s > x : a bound
-// always lies inside [grid[cell], grid[cell+1]] and is finished there with the filter's own
-// comparison.  The grid narrows the search; it never decides a comparison.
+// Per-tile phase timestamps: diagnostics, compiled in only with -DHLSMAP_TRACE_BUILD=1
+// (scripts/trace_run.py builds such a library); the product build carries none of it.
+#ifndef HLSMAP_TRACE_BUILD
+#define HLSMAP_TRACE_BUILD 0
+#endif
 __device__ __forceinline__ void trace_mark(const ResolveParams &p, int tile, int slot, int who = 0)
 {
+#if HLSMAP_TRACE_BUILD
     if (p.trace != nullptr && threadIdx.x == who) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -290,19 +320,27 @@ __device__ __forceinline__ void trace_mark(const ResolveParams &p, int tile, int
             p.trace[(long long)tile * 16 + 15] = smid;
         }
     }
+#endif
 }
 
 // Same, but issued only once `dep` has been produced (e.g. a loaded value).
 __device__ __forceinline__ void trace_mark_after(const ResolveParams &p, int tile, int slot, int dep,
                                                  int who = 0)
 {
+#if HLSMAP_TRACE_BUILD
     if (p.trace != nullptr && threadIdx.x == who) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t) : "r"(dep));
         p.trace[(long long)tile * 16 + slot] = t;
     }
+#endif
 }
 
+// Hint-grid cell of a time value: monotone non-decreasing in x, NaN -> 0, saturating.  The
+// SAME function places table entries (upload) and query bounds (lookup), so for a sorted
+// NaN-free column  cell(s) < cell(x) => s < x  and  cell(s) > cell(x) => s > x : a bound
+// always lies inside [grid[cell], grid[cell+1]] and is finished there with the filter's own
+// comparison.  The grid narrows the search; it never decides a comparison.
 __device__ __forceinline__ int hint_cell(double x, double t0, double inv, int ncell)
 {
     const int c = __double2int_rd(__dmul_rn(__dsub_rn(x, t0), inv));
@@ -741,31 +779,24 @@ resolve_search_kernel(const ResolveParams p)
             const bool expand = p.sn_out != nullptr && a_cnt_tile > 0 && a_cnt_tile <= 0x7fffffffull;
             if (expand) {
                 const int total = (int)a_cnt_tile;
+                constexpr int kRecShift = RecTable<SMALL, S::kTile>::kShift;
+                const unsigned sn_addr = SMALL ? smem_u32(s_sn) : 0u;
+                // start address of slot q = 2 * (sn address of slot q) + start_bias
+                const unsigned start_bias = SMALL ? smem_u32(s_start) - 2u * sn_addr : 0u;
                 {   // records: one per query that kept >= 1 fragment, in query order
                     int rank = a_rank, rel = (int)a_rel;
 #pragma unroll
                     for (int k = 0; k < kIpt; k++) {
                         if (a_cnt[k] > 0) {
-                            sm.rec.set(rank, rel, a_src[k]);
+                            sm.rec.set(rank, rel, a_src[k], sn_addr);
                             rank++;
                             rel += a_cnt[k];
                         }
                     }
                 }
+                // shared-memory address of the record BEFORE the first one (ranks count from 1 below)
+                const unsigned rec_addr = smem_u32(&sm.rec.v[0]) - (1u << kRecShift);
                 int carried = 0;            // records that start before the current window
-                // Slot q: the word's rank base + the records starting at or before this lane's
-                // slot name the record; its source fragment follows by offset.
-                auto emit = [&](const uint2 hw, int slot, double &t, int &s) {
-                    const int r = (int)hw.y + __popc(hw.x & lane_le) - 1;
-                    const long long src = sm.rec.fragment_of(r, slot);
-                    if (SMALL) {
-                        t = s_start[(int)src];
-                        s = s_sn[(int)src];
-                    } else {
-                        t = __ldg(p.start + src);     // L2-hot: the span was just bulk-copied
-                        s = __ldg(p.sn + src);
-                    }
-                };
                 const bool all_fit = (long long)tile_base + total <= p.capacity;   // CTA-uniform
                 for (int w0 = 0; w0 < total; w0 += kWindow) {
                     uint2 *H = sm.hb[hbuf];
@@ -792,55 +823,93 @@ resolve_search_kernel(const ResolveParams p)
                             before += (w < warp) ? c : 0;
                             all += c;
                         }
-                        if (tid < kWords) H[tid].y = (unsigned)(before + ex);
+                        // .y: where the record that covers the word's first slot lives (the records
+                        // starting at or before a lane's slot are counted on top of it)
+                        if (tid < kWords) H[tid].y = rec_addr + ((unsigned)(before + ex) << kRecShift);
                         carried += all;
                         __syncthreads();
                     }
-                    const int wend = min(total - w0, kWindow);
+                    // (same in every thread; the reduction lets the compiler know, so the loops
+                    // below are uniform and keep their memory descriptors in uniform registers)
+                    if (w0 == 0) trace_mark(p, tileA, 9);
+                    const int wend = __reduce_max_sync(0xffffffffu, min(total - w0, kWindow));
                     const uint2 *hp = H + warp;                // this warp's word, 8 words apart
                     double *tp = p.time_out + ((long long)tile_base + w0 + tid);
                     int *sp = p.sn_out + ((long long)tile_base + w0 + tid);
-                    int q = tid;
-                    if (all_fit) {
-                        for (; q + 3 * kThreads < wend; q += 4 * kThreads) {
-                            if (tid == 0 && haveB && !ticket_pending && w0 + kWindow >= total &&
-                                q + kClaimSlots >= wend) {
-                                // Claim the next tile as late as possible -- a claimed but unsearched
-                                // tile stalls the look-back of every later tile -- yet early enough
-                                // for the atomic's round trip to hide behind the slots still to write.
-                                t_new = atomicAdd(&p.ctr->ticket[p.tslot & 1u], 1u);
-                                ticket_pending = true;
+                    // Slot q of the tile's run: the word's base record + the records starting at or
+                    // before this lane's slot name the record; its source fragment follows by offset.
+                    unsigned slot4 = 4u * (unsigned)(w0 + tid);            // SMALL: 4 * slot
+                    long long slotl = (long long)(w0 + tid);               // general: slot
+                    auto body = [&](auto J4) {      // 4 slots, kThreads apart
+                        constexpr int J = decltype(J4)::value;          // 4 or 1 slots
+                        double t[J];
+                        int sv[J];
+                        uint2 hw[J];
+#pragma unroll
+                        for (int j = 0; j < J; j++) hw[j] = hp[j * kWarps];
+                        if constexpr (SMALL) {
+                            unsigned R[J];
+#pragma unroll
+                            for (int j = 0; j < J; j++)
+                                R[j] = lds_u32<0>(hw[j].y + 4u * (unsigned)__popc(hw[j].x & lane_le)) + slot4;
+                            if constexpr (J == 4) {
+                                sv[0] = (int)lds_u32<0>(R[0]);
+                                sv[1] = (int)lds_u32<4 * kThreads>(R[1]);
+                                sv[2] = (int)lds_u32<8 * kThreads>(R[2]);
+                                sv[J - 1] = (int)lds_u32<12 * kThreads>(R[J - 1]);
+                                t[0] = lds_f64<0>(2u * R[0] + start_bias);
+                                t[1] = lds_f64<8 * kThreads>(2u * R[1] + start_bias);
+                                t[2] = lds_f64<16 * kThreads>(2u * R[2] + start_bias);
+                                t[J - 1] = lds_f64<24 * kThreads>(2u * R[J - 1] + start_bias);
+                            } else {
+                                sv[0] = (int)lds_u32<0>(R[0]);
+                                t[0] = lds_f64<0>(2u * R[0] + start_bias);
                             }
-                            double t[4];
-                            int s[4];
-                            uint2 hw[4];
+                        } else {
 #pragma unroll
-                            for (int j = 0; j < 4; j++) hw[j] = hp[j * kWarps];
+                            for (int j = 0; j < J; j++) {
+                                const long long src =
+                                    lds_s64<0>(hw[j].y + 8u * (unsigned)__popc(hw[j].x & lane_le)) + slotl + j * kThreads;
+                                t[j] = __ldg(p.start + src);      // L2-hot: the span was just bulk-copied
+                                sv[j] = __ldg(p.sn + src);
+                            }
+                        }
+                        if (J == 4 || (long long)tile_base + w0 + (long long)(slotl - w0) < p.capacity) {
 #pragma unroll
-                            for (int j = 0; j < 4; j++) emit(hw[j], w0 + q + j * kThreads, t[j], s[j]);
-#pragma unroll
-                            for (int j = 0; j < 4; j++) {
+                            for (int j = 0; j < J; j++) {
                                 __stcs(tp + j * kThreads, t[j]);   // time = fragment.start (:48)
-                                __stcs(sp + j * kThreads, s[j]);   // sn   = fragment.sn    (:46)
+                                __stcs(sp + j * kThreads, sv[j]);  // sn   = fragment.sn    (:46)
                             }
-                            hp += 4 * kWarps;
-                            tp += 4 * kThreads;
-                            sp += 4 * kThreads;
                         }
+                        hp += J * kWarps;
+                        tp += J * kThreads;
+                        sp += J * kThreads;
+                        slot4 += 4u * J * kThreads;
+                        slotl += J * kThreads;
+                    };
+                    // full rounds of 4 * kThreads slots: the trip count is the same for every thread
+                    const int n_full = all_fit ? wend / (4 * kThreads) : 0;
+                    // Claim the next tile as late as possible -- a claimed but unsearched tile stalls
+                    // the look-back of every later tile -- yet early enough for the atomic's round
+                    // trip to hide behind the slots still to write: kClaimSlots before the tile's last.
+                    const bool claim_here = haveB && w0 + kWindow >= total;
+                    const int n_first = claim_here ? min(n_full, max(0, (wend - kClaimSlots + 4 * kThreads - 1) / (4 * kThreads)))
+                                                   : n_full;
+                    int it = 0;
+#pragma unroll 1
+                    for (; it < n_first; it++) body(std::integral_constant<int, 4>{});
+                    if (claim_here && tid == 0 && !ticket_pending) {
+                        t_new = atomicAdd(&p.ctr->ticket[p.tslot & 1u], 1u);
+                        ticket_pending = true;
                     }
-                    for (; q < wend; q += kThreads) {
-                        double t;
-                        int s;
-                        emit(*hp, w0 + q, t, s);
-                        if ((long long)tile_base + w0 + q < p.capacity) {
-                            __stcs(tp, t);
-                            __stcs(sp, s);
-                        }
-                        hp += kWarps;
-                        tp += kThreads;
-                        sp += kThreads;
-                    }
+#pragma unroll 1
+                    for (; it < n_full; it++) body(std::integral_constant<int, 4>{});
+                    if (w0 == 0) trace_mark(p, tileA, 10);
+                    for (int q = n_full * 4 * kThreads + tid; q < wend; q += kThreads)
+                        body(std::integral_constant<int, 1>{});
+                    if (w0 == 0) trace_mark(p, tileA, 11);
                     __syncthreads();
+                    if (w0 == 0) trace_mark(p, tileA, 12);
                     if (tid < kWords) H[tid].x = 0u;   // next used two windows from now
                     hbuf ^= 1u;
                 }
@@ -883,6 +952,7 @@ resolve_search_kernel(const ResolveParams p)
     }
     // never leave with a bulk copy still landing in this CTA's shared memory
     if (stage_pending) mbar_wait(&sm.mbar, mbar_phase);
+    Scan::leave_set(p.ctr);
 }
 
 // =========================================================================================
@@ -1060,6 +1130,7 @@ resolve_filter_kernel(const ResolveParams p)
 
         if (FScan::tile_done(p.ctr, p.n_tiles)) FScan::finish_batch(p.ctr, p.result, p.tslot);
     }
+    FScan::leave_set(p.ctr);
 }
 
 // =========================================================================================

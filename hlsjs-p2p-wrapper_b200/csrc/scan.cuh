@@ -40,6 +40,7 @@ struct TileScan {
 
     // Called by every CTA before its first ticket: waits until the previous user of this
     // scratch set (two launches back) has wrapped up, then marks the set as this launch's.
+    // Every CTA that calls this must call leave_set() before it exits.
     __device__ static void acquire_set(ScanCounters *ctr, unsigned epoch)
     {
         if (threadIdx.x == 0) {
@@ -185,7 +186,11 @@ struct TileScan {
     }
 
     // Run by the thread tile_done() elected: hand the counters to the host-visible
-    // result and re-arm the scratch header for the next launch.
+    // result and re-arm the scratch header for the next launch.  The set itself stays this
+    // launch's until its last CTA has left (leave_set): a CTA that is dispatched only after
+    // the batch's last tile was finished still finds owner == its own epoch, draws a ticket
+    // past the end and leaves; were the set released here, that late CTA would take it again
+    // and nobody would ever give it back.
     __device__ static void finish_batch(ScanCounters *ctr, DeviceResult *result, unsigned tslot)
     {
         result->n_unparsed = (long long)atomicAdd(&ctr->n_unparsed, 0ull);
@@ -195,7 +200,22 @@ struct TileScan {
         ctr->done = 0u;
         ctr->ticket[(tslot & 1u) ^ 1u] = 0u;       // untouched by this launch's late fetches
         __threadfence();
-        atomicExch(&ctr->owner, 0u);                // the set is free for the launch after next
+    }
+
+    // Called by every CTA as the last thing it does.  The last CTA of the grid to get here
+    // frees the set for the launch after next.
+    __device__ static void leave_set(ScanCounters *ctr)
+    {
+        __syncthreads();                            // this CTA's finish_batch(), if any, is done
+        if (threadIdx.x == 0) {
+            __threadfence();
+            const unsigned old = atomicAdd(&ctr->exited, 1u);
+            if (old == gridDim.x - 1u) {
+                ctr->exited = 0u;
+                __threadfence();
+                atomicExch(&ctr->owner, 0u);
+            }
+        }
     }
 };
 

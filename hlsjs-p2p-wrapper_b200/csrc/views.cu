@@ -304,6 +304,7 @@ view_format_kernel(const FormatParams p)
         }
         if (FmtScan::tile_done(p.ctr, p.n_tiles)) FmtScan::finish_batch(p.ctr, p.result, p.tslot);
     }
+    FmtScan::leave_set(p.ctr);
 }
 
 // ---- the same in three launches, none of which waits for another CTA -----------------------

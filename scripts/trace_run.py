@@ -1,9 +1,14 @@
-"""Experiment: dump per-tile phase timestamps of one search-kernel launch (HLSMAP_TRACE)."""
+"""Experiment: dump per-tile phase timestamps of one search-kernel launch.  Needs the
+diagnostics library: run with HLSMAP_TRACE_BUILD=1 in the environment (builds and loads
+csrc/libhlsmap_trace.so; the product library carries no trace code)."""
 import os, sys
+os.environ["HLSMAP_TRACE_BUILD"] = "1"
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 import hlsjs_p2p_wrapper_b200 as pk
 from hlsjs_p2p_wrapper_b200 import synth
+from hlsjs_p2p_wrapper_b200 import build as _b
+_b.build()
 out = sys.argv[1]
 ctx = pk.Context(0)
 t, q = synth.config5(n_playlists=20000) if os.environ.get('TRACE_WORKLOAD') == 'config5' else synth.config2()

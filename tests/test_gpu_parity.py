@@ -380,3 +380,78 @@ def test_overlapping_batches_on_disjoint_buffers(ctx):
     finally:
         ctx.set_batch_overlap(False)
     m.close()
+
+
+def test_small_batches_behind_big_ones_release_their_scratch_set(ctx):
+    """A batch of two tiles launched while a big batch still holds the SMs: the small grid's early
+    CTA can finish both tiles before its other CTA is even dispatched.  That late CTA must find the
+    scratch set still its own launch's and leave it properly, or the launch after next would wait
+    for the set for ever.  A few thousand alternations on two streams, both kernels of the list
+    form, every small result compared with the oracle; the watchdog turns a hang into a failure."""
+    import threading
+    import torch
+    dev = torch.device("cuda:0")
+    t, _ = synth.config2(n_queries=4)
+    m = ctx.upload(t)
+    s_small, s_big = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+
+    def dev_set(seed, nq):
+        _, q = synth.config2(seed=seed, n_queries=nq)
+        ref = oracle_list(t, q)
+        H = int(ref[0][-1])
+        return {"q": q, "ref": ref, "H": H,
+                "pl": torch.from_numpy(q.playlist).to(dev), "lv": torch.from_numpy(q.level).to(dev),
+                "bg": torch.from_numpy(q.begin).to(dev), "du": torch.from_numpy(q.duration).to(dev),
+                "off": torch.empty(nq + 1, dtype=torch.int32, device=dev),
+                "sn": torch.empty(max(H, 1), dtype=torch.int32, device=dev),
+                "tm": torch.empty(max(H, 1), dtype=torch.float64, device=dev)}
+
+    small = [dev_set(90 + i, nq) for i, nq in enumerate((700, 1024, 513, 1500))]     # 2-3 tiles each
+    big = dev_set(99, 400_000)
+    # a second context on the same GPU keeps the SMs busy with its own batches meanwhile
+    other = pk.Context(0)
+    m2 = other.upload(t)
+
+    def launch(mm, s, stream):
+        mm.get_segment_list_dev(len(s["q"]), s["pl"].data_ptr(), s["lv"].data_ptr(), s["bg"].data_ptr(),
+                                s["du"].data_ptr(), s["off"].data_ptr(), s["sn"].data_ptr(),
+                                s["tm"].data_ptr(), s["H"], stream=stream.cuda_stream)
+
+    done = threading.Event()
+
+    def work():
+        for path in (N.PATH_SEARCH, N.PATH_FILTER):
+            m.set_path(path)
+            ctx.set_batch_overlap(path == N.PATH_SEARCH)
+            reps = 1500 if path == N.PATH_SEARCH else 40
+            for i in range(reps):
+                if i % 8 == 0:
+                    launch(m2, big, s_big)
+                launch(m, small[i % len(small)], s_small)
+            torch.cuda.synchronize()
+            for s in small:
+                assert np.array_equal(s["off"].cpu().numpy().astype(np.int64), s["ref"][0])
+                assert np.array_equal(s["sn"][:s["H"]].cpu().numpy(), s["ref"][2])
+                assert np.array_equal(s["tm"][:s["H"]].cpu().numpy().view(np.uint64), s["ref"][3].view(np.uint64))
+        done.set()
+
+    err = []
+
+    def guarded():
+        try:
+            work()
+        except BaseException as e:      # surfaced below
+            err.append(e)
+            done.set()
+
+    th = threading.Thread(target=guarded, daemon=True)
+    th.start()
+    ok = done.wait(timeout=120)
+    ctx.set_batch_overlap(False)
+    assert ok, "launches hung: a scratch set was never released"
+    if err:
+        raise err[0]
+    m.set_path(N.PATH_AUTO)
+    m2.close()
+    other.close()
+    m.close()
