@@ -90,7 +90,6 @@ struct hlsmap_map {
     size_t stage_smem = 0;
     int grid_search = 0, grid_filter = 0;
     int ipt = 2;                        // queries per thread of the search kernel (tiles of 256 * ipt)
-    int grid_search_wide = 0;           // SMALL maps: grid of the 1024-query-tile variant (0 = not offered)
 };
 
 namespace {
@@ -187,20 +186,21 @@ int pick_path(const hlsmap_map *m)
 
 inline bool al16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
-// Tiling of a batch: full tiles of the kernel's 256*ipt queries.  (Trimming the tile size so
-// that every CTA gets a whole number of tiles was measured on B200 and lost: 61 us vs 57 us on
-// the 10^6-query workload -- per-tile fixed costs outweigh the idle tail round.)
-void plan_tiles(const hlsmap_map *map, int path, int64_t nq, int *tile_q, int64_t *n_tiles, int ipt = 0)
+// Tiling of a batch: full tiles of the kernel's 256*ipt queries.  (Measured on B200 and lost, both
+// against uniform 512-query tiles on the 10^6-query workload: tile size trimmed so that every CTA
+// gets a whole number of tiles, 61 us vs 57 us; the last 15-40 % of a lone batch in tiles of half
+// or a quarter the size, 52-67 us vs 51.7 -- per-tile fixed costs outweigh the idle tail round.)
+struct TilePlan {
+    int tile_q = 0;
+    int64_t n_tiles = 0;
+};
+TilePlan plan_tiles(const hlsmap_map *map, int path, int64_t nq)
 {
-    if (path != HLSMAP_PATH_SEARCH) {
-        *tile_q = kFilterTileQueries;
-        *n_tiles = (nq + kFilterTileQueries - 1) / kFilterTileQueries;
-        return;
-    }
-    const int tq = resolve_search_tile(map->info.stage_all != 0, ipt ? ipt : map->ipt);
-    const int64_t tiles = (nq + tq - 1) / tq;
-    *tile_q = tq;
-    *n_tiles = tiles;
+    TilePlan t;
+    t.tile_q = path == HLSMAP_PATH_SEARCH ? resolve_search_tile(map->info.stage_all != 0, map->ipt)
+                                          : kFilterTileQueries;
+    t.n_tiles = (nq + t.tile_q - 1) / t.tile_q;
+    return t;
 }
 
 }  // namespace
@@ -492,8 +492,6 @@ static int map_create_impl(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *
     m->ipt = 2;
     if (const char *e = getenv(small ? "HLSMAP_IPT" : "HLSMAP_IPT_GENERAL")) m->ipt = atoi(e) == 4 ? 4 : 2;
     m->grid_search = resolve_search_max_grid(m->stage_smem, small, m->ipt);
-    // SMALL maps also offer 1024-query tiles (3 CTAs/SM): picked per batch, see list_core()
-    if (small && m->ipt == 2 && !getenv("HLSMAP_IPT")) m->grid_search_wide = resolve_search_max_grid(m->stage_smem, true, 4);
     m->grid_filter = resolve_filter_max_grid();
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess)
@@ -671,17 +669,12 @@ static int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
         return HLSMAP_OK;
     }
 
-    // Tile size.  Batches that run back to back (hlsmap_ctx_set_batch_overlap) and give every
-    // CTA two tiles or more take 1024-query tiles on SMALL maps: half as many look-backs and
-    // bitmap builds per query, measured 38.6 us against 39.2 per 10^6-query batch; a batch on
-    // its own keeps 512-query tiles (56 us against 58: its ramp and tail are shorter).
-    int ipt = map->ipt;
-    if (path == HLSMAP_PATH_SEARCH && ctx->overlap && map->grid_search_wide > 0 &&
-        nq >= 2ll * map->grid_search_wide * resolve_search_tile(true, 4))
-        ipt = 4;
-    int tile_q = 0;
-    int64_t n_tiles = 0;
-    plan_tiles(map, path, nq, &tile_q, &n_tiles, ipt);
+    // (512-query tiles throughout.  1024-query tiles for large batches run back to back were worth
+    // 1.5 % while every tile paid a CTA-wide look-back; with the look-back done by one warp they
+    // measure the same, 35.6 us against 35.6 per 10^6-query batch, and are 2 us slower alone.)
+    const int ipt = map->ipt;
+    const TilePlan plan = plan_tiles(map, path, nq);
+    const int64_t n_tiles = plan.n_tiles;
     if (n_tiles > 0x7fffffff) return fail(HLSMAP_ERR_INVALID, "batch too large: split it");
     r = prepare_scan(ctx, n_tiles, s);
     if (r) return r;
@@ -709,7 +702,7 @@ static int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
     p.epoch = ctx->epoch;
     p.tslot = ctx->set_launches[ctx->epoch & 1u] & 1u;
     p.n_tiles = (int)n_tiles;
-    p.tile_q = tile_q;
+    p.tile_q = plan.tile_q;
     p.base = base;
     p.stage_elems = map->stage_elems;
     p.stage_all = map->info.stage_all;
@@ -734,8 +727,7 @@ static int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
     }
 #endif
     if (path == HLSMAP_PATH_SEARCH) {
-        const int max_grid = ipt == map->ipt ? map->grid_search : map->grid_search_wide;
-        const int grid = (int)(n_tiles < max_grid ? n_tiles : max_grid);
+        const int grid = (int)(n_tiles < map->grid_search ? n_tiles : map->grid_search);
         CK(launch_resolve_search(p, grid, map->stage_smem, s, ctx->overlap && d_trace == nullptr));
     } else {
         const int grid = (int)(n_tiles < map->grid_filter ? n_tiles : map->grid_filter);
@@ -1492,9 +1484,9 @@ int hlsmap_get_segment_list_noalloc_dev(hlsmap_map *map, int64_t nq, const int32
     cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
 
     const int path = pick_path(map);
-    int tile_q = 0;
-    int64_t n_tiles = 0;
-    plan_tiles(map, path, nq, &tile_q, &n_tiles);
+    const TilePlan plan = plan_tiles(map, path, nq);
+    const int tile_q = plan.tile_q;
+    const int64_t n_tiles = plan.n_tiles;
     if (n_tiles > kNoAllocMaxTiles)
         return fail(HLSMAP_ERR_INVALID,
                     "get_segment_list_noalloc: batch of " + std::to_string(nq) +

@@ -76,6 +76,7 @@ struct SearchSmem {
     unsigned long long warp_cnt[kWarps];
     int warp_heads[kWarps];
     int tile_slot[2];              // next tile id, double buffered across iterations
+    unsigned long long tile_base;  // exclusive prefix of the tile being emitted (from warp 0)
     RecTable<SMALL, Shape<IPT>::kTile> rec;
     // per 32 output slots of the window: .x = bitmap of slots where a record starts,
     // .y = records that start before this word (tile-wide rank base).  Double buffered.
@@ -438,9 +439,10 @@ resolve_search_kernel(const ResolveParams p)
         const bool haveB = tileB < p.n_tiles;
         if (!haveB && tileA < 0) break;
 
-        // tile A's look-back window: load it now, use it after the search (hides the L2 trip)
-        unsigned long long pre[2] = {0ull, 0ull};
-        if (tileA > 0) Scan::template prefetch_window<2>(p.tile_status, tileA, pre);
+        // tile A's look-back window: loaded between B's bounds and B's scan, used after the scan
+        // (hides the L2 trip)
+        unsigned long long pre[1] = {0ull};
+        if (tileA > 0 && !haveB && warp == 0) pre[0] = ld_relaxed_u64(&p.tile_status[max(tileA - 1 - lane, 0)]);
 
         // =====================================================================================
         //  SEARCH tile B
@@ -541,7 +543,7 @@ resolve_search_kernel(const ResolveParams p)
                     mx = max(mx, off[k] + len[k]);
                 }
             }
-            trace_mark_after(p, tileB, 13, len[0] ^ len[kIpt - 1]);
+            if (!SMALL) trace_mark_after(p, tileB, 13, len[0] ^ len[kIpt - 1]);
             if (p.status) {
                 if (full && kIpt == 4) {
                     const unsigned w = (unsigned)st[0] | ((unsigned)st[1] << 8) |
@@ -698,6 +700,7 @@ resolve_search_kernel(const ResolveParams p)
             }
 
             trace_mark_after(p, tileB, 1, cnt[0] ^ cnt[kIpt - 1]);
+            if (tileA > 0 && warp == 0) pre[0] = ld_relaxed_u64(&p.tile_status[max(tileA - 1 - lane, 0)]);
             // ---- fused scan of (hit count, non-empty flag): thread -> warp -> CTA ---------
             unsigned long long tval = 0;
 #pragma unroll
@@ -744,8 +747,51 @@ resolve_search_kernel(const ResolveParams p)
             const long long q_end = min(p.nq, (long long)(tileA + 1) * p.tile_q);
             const bool full = p.vec_ok && q0 + kIpt <= q_end;
             trace_mark(p, tileA, 3);
-            const unsigned long long tile_base =
-                Scan::wait_prefix<2>(sm.scan, p.tile_status, p.epoch, tileA, a_cnt_tile, pre, p.base);
+            // ---- look-back by warp 0 alone, 32 predecessors per step, no CTA barrier; the other
+            //      warps meanwhile lay down the expansion records and the first window's head marks,
+            //      which need no prefix.  One barrier then hands out both.
+            if (warp == 0) {
+#if HLSMAP_TRACE_BUILD
+                int diag = 0;
+                const unsigned long long b = Scan::warp_prefix(p.tile_status, p.epoch, tileA, a_cnt_tile, pre[0], p.base, &diag);
+                if (p.trace != nullptr && lane == 0) p.trace[(long long)tileA * 16 + 7] = (unsigned long long)diag;
+#else
+                const unsigned long long b = Scan::warp_prefix(p.tile_status, p.epoch, tileA, a_cnt_tile, pre[0], p.base);
+#endif
+                if (lane == 0) sm.tile_base = b;
+                if (SMALL) trace_mark_after(p, tileA, 14, (int)b);
+            }
+            const bool expand = p.sn_out != nullptr && a_cnt_tile > 0 && a_cnt_tile <= 0x7fffffffull;
+            constexpr int kRecShift = RecTable<SMALL, S::kTile>::kShift;
+            const unsigned sn_addr = SMALL ? smem_u32(s_sn) : 0u;
+            // start address of slot q = 2 * (sn address of slot q) + start_bias
+            const unsigned start_bias = SMALL ? smem_u32(s_start) - 2u * sn_addr : 0u;
+            // mark where this thread's records start inside the window [w0, w0 + kWindow)
+            auto mark_heads = [&](uint2 *H, int w0) {
+                int r2 = (int)a_rel;
+#pragma unroll
+                for (int k = 0; k < kIpt; k++) {
+                    if (a_cnt[k] > 0) {
+                        const unsigned d = (unsigned)(r2 - w0);
+                        if (d < (unsigned)kWindow) atomicOr(&H[d >> 5].x, 1u << (d & 31));
+                        r2 += a_cnt[k];
+                    }
+                }
+            };
+            if (expand) {   // records: one per query that kept >= 1 fragment, in query order
+                int rank = a_rank, rel = (int)a_rel;
+#pragma unroll
+                for (int k = 0; k < kIpt; k++) {
+                    if (a_cnt[k] > 0) {
+                        sm.rec.set(rank, rel, a_src[k], sn_addr);
+                        rank++;
+                        rel += a_cnt[k];
+                    }
+                }
+                mark_heads(sm.hb[hbuf], 0);
+            }
+            __syncthreads();
+            const unsigned long long tile_base = sm.tile_base;
             trace_mark(p, tileA, 4);
 
             // ---- offsets[q] --------------------------------------------------------------
@@ -776,41 +822,19 @@ resolve_search_kernel(const ResolveParams p)
 
             // ---- expansion: the tile's hits form ONE contiguous output run; the whole CTA
             //      writes it 256 slots at a time whatever the per-query counts (load balanced)
-            const bool expand = p.sn_out != nullptr && a_cnt_tile > 0 && a_cnt_tile <= 0x7fffffffull;
             if (expand) {
                 const int total = (int)a_cnt_tile;
-                constexpr int kRecShift = RecTable<SMALL, S::kTile>::kShift;
-                const unsigned sn_addr = SMALL ? smem_u32(s_sn) : 0u;
-                // start address of slot q = 2 * (sn address of slot q) + start_bias
-                const unsigned start_bias = SMALL ? smem_u32(s_start) - 2u * sn_addr : 0u;
-                {   // records: one per query that kept >= 1 fragment, in query order
-                    int rank = a_rank, rel = (int)a_rel;
-#pragma unroll
-                    for (int k = 0; k < kIpt; k++) {
-                        if (a_cnt[k] > 0) {
-                            sm.rec.set(rank, rel, a_src[k], sn_addr);
-                            rank++;
-                            rel += a_cnt[k];
-                        }
-                    }
-                }
                 // shared-memory address of the record BEFORE the first one (ranks count from 1 below)
                 const unsigned rec_addr = smem_u32(&sm.rec.v[0]) - (1u << kRecShift);
                 int carried = 0;            // records that start before the current window
                 const bool all_fit = (long long)tile_base + total <= p.capacity;   // CTA-uniform
                 for (int w0 = 0; w0 < total; w0 += kWindow) {
                     uint2 *H = sm.hb[hbuf];
-                    {   // mark where this thread's records start inside the window, rank words
-                        int r2 = (int)a_rel;
-#pragma unroll
-                        for (int k = 0; k < kIpt; k++) {
-                            if (a_cnt[k] > 0) {
-                                const unsigned d = (unsigned)(r2 - w0);
-                                if (d < (unsigned)kWindow) atomicOr(&H[d >> 5].x, 1u << (d & 31));
-                                r2 += a_cnt[k];
-                            }
+                    {   // head marks (the first window's are down already), rank words
+                        if (w0 > 0) {
+                            mark_heads(H, w0);
+                            __syncthreads();
                         }
-                        __syncthreads();
                         const int c0 = tid < kWords ? __popc(H[tid].x) : 0;
                         int wsum;
                         const int ex = warp_excl_scan(c0, wsum);
@@ -929,16 +953,6 @@ resolve_search_kernel(const ResolveParams p)
             }
         }
         __syncthreads();       // all global writes of tile A issued; next tile id visible
-        if (tid == kThreads - 1 && tileA >= 0) {
-            // completion count off the critical path: only this thread pays for the fence
-            __threadfence();
-            atomicAdd(&p.ctr->done, 1u);
-            if (tileA == p.n_tiles - 1) {                  // the batch's last tile: wrap up
-                while (ld_relaxed_u32(&p.ctr->done) != (unsigned)p.n_tiles) { }
-                __threadfence();
-                Scan::finish_batch(p.ctr, p.result, p.tslot);
-            }
-        }
         tileA = haveB ? tileB : -1;
         a_rel = b_rel;
         a_cnt_tile = b_cnt_tile;
@@ -952,7 +966,8 @@ resolve_search_kernel(const ResolveParams p)
     }
     // never leave with a bulk copy still landing in this CTA's shared memory
     if (stage_pending) mbar_wait(&sm.mbar, mbar_phase);
-    Scan::leave_set(p.ctr);
+    // the last CTA to leave wraps the batch up (counters -> result, scratch header re-armed)
+    Scan::leave_set(p.ctr, p.result, p.tslot);
 }
 
 // =========================================================================================

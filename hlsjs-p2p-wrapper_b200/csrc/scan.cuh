@@ -163,6 +163,57 @@ struct TileScan {
         return running;
     }
 
+    // The same look-back done by ONE warp, without any CTA barrier: 32 predecessors per step, the
+    // walk ends at the nearest tile that knows its prefix (in the search kernel's pipeline, where a
+    // tile asks one stage after it published, that is 2 steps on average and 1 for half the tiles).
+    // `pre` = status[tile - 1 - lane], loaded ahead of time by this warp (ignored for tile 0).
+    // Every lane gets the result.
+    __device__ static unsigned long long warp_prefix(unsigned long long *status, unsigned epoch, int tile,
+                                                     unsigned long long aggregate, unsigned long long pre,
+                                                     unsigned long long base, int *diag = nullptr)
+    {
+        if (tile == 0) return base;                  // tile 0 published its own prefix
+        int n_windows = 0, n_polls = 0;
+        const int lane = threadIdx.x & 31;
+        const unsigned e = epoch & kEpochMask;
+        const unsigned long long vmask = (1ull << kValueBits) - 1ull;
+        aggregate = aggregate < kSat ? aggregate : kSat;
+        unsigned long long running = 0;
+        int top = tile - 1;
+        unsigned long long w = pre;
+        for (;;) {
+            const int idx = top - lane;
+            int n;                                   // lanes 0..n-1 are summed, then lane n if it is a prefix
+            bool ends;
+            for (;;) {
+                const bool pub = idx < 0 || (unsigned)(w >> 42) == e;
+                const bool isp = idx < 0 || (pub && ((w >> kValueBits) & 3ull) == kStatePrefix);
+                const unsigned m_pub = __ballot_sync(0xffffffffu, pub);
+                const unsigned m_pre = __ballot_sync(0xffffffffu, isp);
+                const int first_unpub = m_pub == 0xffffffffu ? 32 : __ffs(~m_pub) - 1;
+                const int first_pre = m_pre == 0u ? 32 : __ffs(m_pre) - 1;
+                if (first_pre < first_unpub) { n = first_pre; ends = true; break; }
+                if (first_unpub == 32) { n = 31; ends = false; break; }
+                __nanosleep(64);                     // a nearer tile has not published yet
+                n_polls++;
+                if (!pub) w = ld_relaxed_u64(&status[idx]);
+            }
+            n_windows++;
+            unsigned long long c = (lane <= n && idx >= 0) ? (w & vmask) : 0ull;
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
+            running += c;
+            if (ends) break;
+            top -= 32;
+            const int nidx = top - lane;
+            w = nidx >= 0 ? ld_relaxed_u64(&status[nidx]) : 0ull;
+        }
+        running = running < kSat ? running : kSat;
+        if (lane == 0) st_relaxed_u64(&status[tile], make_status(epoch, kStatePrefix, running + aggregate));
+        if (diag) *diag = n_windows | (n_polls << 8);
+        return running;
+    }
+
     __device__ static unsigned long long exclusive_prefix(Smem &s, unsigned long long *status,
                                                           unsigned epoch, int tile,
                                                           unsigned long long aggregate,
@@ -203,14 +254,18 @@ struct TileScan {
     }
 
     // Called by every CTA as the last thing it does.  The last CTA of the grid to get here
-    // frees the set for the launch after next.
-    __device__ static void leave_set(ScanCounters *ctr)
+    // frees the set for the launch after next.  A kernel that does not count finished tiles
+    // (tile_done) passes `result`: the batch is then wrapped up here, where every tile is known
+    // to be done because every CTA has left.
+    __device__ static void leave_set(ScanCounters *ctr, DeviceResult *result = nullptr, unsigned tslot = 0)
     {
         __syncthreads();                            // this CTA's finish_batch(), if any, is done
         if (threadIdx.x == 0) {
             __threadfence();
             const unsigned old = atomicAdd(&ctr->exited, 1u);
             if (old == gridDim.x - 1u) {
+                __threadfence();
+                if (result != nullptr) finish_batch(ctr, result, tslot);
                 ctr->exited = 0u;
                 __threadfence();
                 atomicExch(&ctr->owner, 0u);
