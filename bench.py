@@ -49,6 +49,10 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-other-rows", action="store_true",
                     help="skip the short timings of the rows either side of the path (ingest, JSON)")
+    ap.add_argument("--no-sharded", action="store_true",
+                    help="skip the BASELINE.json configs[4] leg (10^8 queries sharded by playlist, ~2 min at N=1)")
+    ap.add_argument("--config5-chunks", type=int, default=20,
+                    help="corpus chunks of 50 000 playlists for the sharded leg (20 = the full 10^6 playlists)")
     return ap.parse_args()
 
 
@@ -139,8 +143,9 @@ def run_reference(args):
 #  clocks sampling during the timed region
 # ---------------------------------------------------------------------------------------------
 class ClockSampler:
-    """Samples SM clock and throttle reasons through NVML every ~2 ms while the timed region
-    runs (nvidia-smi is far too slow to land a sample inside a few-ms region)."""
+    """Samples SM clock and throttle reasons through NVML every ~0.5 ms while the timed region
+    runs (nvidia-smi is far too slow to land a sample inside a region of a millisecond; the
+    driver's default 20-step run times 0.75 ms)."""
 
     def __init__(self, uuid=None, index=0):
         self.uuid, self.index = uuid, index
@@ -172,13 +177,20 @@ class ClockSampler:
                 self.samples.append((time.perf_counter(),
                                      float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)),
                                      int(get_reasons(h))))
-                self._stop.wait(0.002)
+                self._stop.wait(0.0005)
         except Exception as e:          # no NVML: report that instead of inventing clocks
             self.err = repr(e)
 
     def start(self):
         self._t = threading.Thread(target=self._run, daemon=True)
         self._t.start()
+
+    def wait_first(self, timeout):
+        """Block until NVML has delivered a first sample (or failed): a timed region of a
+        millisecond then still has the clocks read immediately before and after it."""
+        t0 = time.perf_counter()
+        while not self.samples and self.err is None and time.perf_counter() - t0 < timeout:
+            time.sleep(0.01)
 
     def stop(self):
         self._stop.set()
@@ -187,7 +199,11 @@ class ClockSampler:
         bits = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "sw_thermal_slowdown": 0x20,
                 "hw_thermal_slowdown": 0x40, "hw_power_brake_slowdown": 0x80}
         t0, t1 = self.window or (0.0, float("inf"))
-        inside = [s for s in self.samples if t0 <= s[0] <= t1] or self.samples
+        inside = [s for s in self.samples if t0 <= s[0] <= t1]
+        if not inside:       # none landed inside: the last sample before and the first after the region
+            before = [s for s in self.samples if s[0] < t0][-1:]
+            after = [s for s in self.samples if s[0] > t1][:1]
+            inside = before + after or self.samples
         sm = [s[1] for s in inside]
         mask = 0
         for s in inside:
@@ -269,6 +285,305 @@ def other_rows(ctx, torch, peak):
 
 
 
+def list_form_sets(pk, synth, torch, dmap, dev, q0, rank, min_bytes):
+    """Rotating query/result buffer sets for the list form: the same queries in other orders, so
+    successive steps stream through distinct memory whose total is >= min_bytes (> 3x L2)."""
+    nq = len(q0)
+    sets = []
+    while True:
+        q = q0
+        if sets:
+            rng = synth._stream(7000 + rank, len(sets))
+            perm = np.argsort(rng.u32(nq), kind="stable")
+            q = pk.QueryBatch(q0.playlist[perm], q0.level[perm], q0.begin[perm], q0.duration[perm])
+        _, total = dmap.count_segments(q.playlist, q.level, q.begin, q.duration)
+        cap = int(total)
+        sets.append({"q": q, "hits": cap,
+                     "pl": torch.from_numpy(q.playlist).to(dev), "lv": torch.from_numpy(q.level).to(dev),
+                     "bg": torch.from_numpy(q.begin).to(dev), "du": torch.from_numpy(q.duration).to(dev),
+                     "off": torch.empty(nq + 1, dtype=torch.int32, device=dev),
+                     "sn": torch.empty(max(cap, 1), dtype=torch.int32, device=dev),
+                     "tm": torch.empty(max(cap, 1), dtype=torch.float64, device=dev)})
+        per_step = 28 * nq + 12 * cap
+        if len(sets) * per_step >= min_bytes and len(sets) >= 3:
+            return sets, per_step
+
+
+def timed_list_form(torch, ctx, dmap, sets, stream, steps, warmup, barrier=None, count_only=False):
+    """`steps` back-to-back device-resident list-form batches over rotating buffer sets, CUDA events
+    on the launch stream.  -> (region ms, mean hits per step, host issue us per launch)."""
+    nq = len(sets[0]["q"])
+
+    def launch(s):
+        dmap.get_segment_list_dev(nq, s["pl"].data_ptr(), s["lv"].data_ptr(), s["bg"].data_ptr(),
+                                  s["du"].data_ptr(), s["off"].data_ptr(),
+                                  0 if count_only else s["sn"].data_ptr(),
+                                  0 if count_only else s["tm"].data_ptr(),
+                                  0 if count_only else s["hits"], stream=stream)
+    for i in range(warmup):
+        launch(sets[i % len(sets)])
+    torch.cuda.synchronize()
+    t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if barrier:
+        barrier()
+    hits = 0
+    h0 = time.perf_counter()
+    t_begin.record()
+    for i in range(steps):
+        s = sets[i % len(sets)]
+        launch(s)
+        hits += s["hits"]
+    t_end.record()
+    issue_us = (time.perf_counter() - h0) / steps * 1e6
+    if barrier:
+        barrier()
+    else:
+        torch.cuda.synchronize()
+    return t_begin.elapsed_time(t_end), hits / steps, issue_us
+
+
+def path_rows(pk, synth, torch, ctx, dmap, dev, tables, q0, stream, peak, steps, warmup):
+    """Two more device-timed lines for the hot path on the same map (rank 0, N = 1): the look-ahead
+    query class on its own (what the reference's caller asks for: ~30 s windows,
+    hlsjs-p2p-wrapper-private.js:88-89) in list form, and the range form on the headline queries."""
+    import ctypes
+    from hlsjs_p2p_wrapper_b200 import _native as N
+    out = {}
+    nq = len(q0)
+    table_bytes = 12 * len(tables.start)
+    # -- look-ahead class: queries whose duration lies in the 29-31 s band of synth._queries
+    _, big = synth.config2(seed=2, n_queries=int(nq * 1.6))
+    sel = np.nonzero((big.duration >= 29.0) & (big.duration <= 31.0))[0][:nq]
+    ql = pk.QueryBatch(big.playlist[sel], big.level[sel], big.begin[sel], big.duration[sel])
+    if len(ql) == nq:
+        sets, per_step = list_form_sets(pk, synth, torch, dmap, dev, ql, 0, 3 * L2_BYTES)
+        ms, hits, _ = timed_list_form(torch, ctx, dmap, sets, stream, steps, warmup)
+        alg = 28.0 * nq + 12.0 * hits + table_bytes
+        out["list_form_lookahead_mix"] = {
+            "queries": nq, "hits_per_query": hits / nq, "ms_per_step": ms / steps,
+            "queries_per_s": nq * steps / (ms * 1e-3), "algorithmic_bytes_per_launch": alg,
+            "roofline_frac": alg / (ms / steps * 1e-3) / 1e9 / peak, "buffer_sets": len(sets),
+            "what": "the 29-31 s duration class of the same generator (70 % of the headline mix), "
+                    "list form, timed like the headline"}
+        del sets
+    # -- range form (first index + count per query), device-resident, rotating buffers: one batch
+    #    size like the headline's and one large enough that launch overhead stops mattering
+    lib = N.load()
+    v = lambda x: ctypes.c_void_p(x.data_ptr())
+    sp = ctypes.c_void_p(stream)
+    for mult, key in ((1, "range_form_device"), (16, "range_form_device_16x")):
+        n = nq * mult
+        n_sets = max(2, int(np.ceil(3 * L2_BYTES / (33.0 * n))))
+        rs = []
+        for k in range(n_sets):
+            idx = np.concatenate([np.argsort(synth._stream(9000 + k, j).u32(nq), kind="stable") for j in range(mult)])
+            rs.append({"pl": torch.from_numpy(q0.playlist[idx]).to(dev), "lv": torch.from_numpy(q0.level[idx]).to(dev),
+                       "bg": torch.from_numpy(q0.begin[idx]).to(dev), "du": torch.from_numpy(q0.duration[idx]).to(dev),
+                       "first": torch.empty(n, dtype=torch.int32, device=dev),
+                       "count": torch.empty(n, dtype=torch.int32, device=dev),
+                       "st": torch.empty(n, dtype=torch.uint8, device=dev)})
+
+        def launch(r):
+            N.check(lib.hlsmap_get_segment_range_dev(dmap._h, n, v(r["pl"]), v(r["lv"]), v(r["bg"]), v(r["du"]),
+                                                     v(r["first"]), v(r["count"]), v(r["st"]), sp))
+        for i in range(warmup):
+            launch(rs[i % n_sets])
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            launch(rs[i % n_sets])
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        alg = 32.0 * n + table_bytes          # SURVEY 8(d): Q * (24 + 8) + sum F * 12 (the status byte is not counted)
+        out[key] = {
+            "queries": n, "ms_per_step": ms / steps, "queries_per_s": n * steps / (ms * 1e-3),
+            "algorithmic_bytes_per_launch": alg, "roofline_frac": alg / (ms / steps * 1e-3) / 1e9 / peak,
+            "buffer_sets": n_sets, "api": "hlsmap_get_segment_range_dev", "kernel": "range_small_kernel"}
+        del rs
+    return out
+
+
+def sharded_config5(pk, synth, torch, dist, ctx, dev, rank, world, local, peak, n_chunks, gloo):
+    """BASELINE.json configs[4]: 10^8 getSegmentList queries over 10^6 playlists, sharded by
+    contiguous playlist range over the ranks (media-map.js:28,41: a query touches one playlist's one
+    level).  Every rank plans the same boundaries from per-playlist counts (shard.plan_counts),
+    generates only the corpus chunks its range touches, routes each chunk's queries by playlist
+    (shard.split_queries), resolves them on its GPU with inputs resident (CUDA events around one
+    launch per piece after a warm-up launch), and copies its results to the host; rank 0 gathers
+    the shards and merges them (shard.merge) into the global list form.  No collective on the data
+    path: the gather is host-side (gloo point-to-point of host arrays, or nothing at N = 1)."""
+    import oracle
+    from hlsjs_p2p_wrapper_b200 import shard
+    P, QPP = synth.CONFIG5_CHUNK, synth.CONFIG5_QUERIES_PER_PLAYLIST
+    t_all = time.perf_counter()
+    frag_pp = np.concatenate([synth.config5_chunk_fragments_per_playlist(c) for c in range(n_chunks)])
+    bounds = shard.plan_counts(frag_pp, np.full(len(frag_pp), QPP), world)
+    p0, p1 = int(bounds[rank]), int(bounds[rank + 1])
+    pieces = [c for c in range(n_chunks) if max(p0, c * P) < min(p1, (c + 1) * P)]
+    stream = torch.cuda.Stream(device=dev)
+
+    # generate the next chunk on a host thread while the GPU works on this one
+    box = {}
+
+    def gen(c):
+        box[c] = synth.config5_chunk(c)
+    th = None
+    if pieces:
+        th = threading.Thread(target=gen, args=(pieces[0],))
+        th.start()
+    dev_ms, d2h_s, gen_wait_s = 0.0, 0.0, 0.0
+    n_q = n_hits = n_frag = 0
+    alg = 0.0
+    res_off, res_st, res_sn, res_tm = [], [], [], []
+    sample = None
+    ctx.set_batch_overlap(False)
+    for k, c in enumerate(pieces):
+        w0 = time.perf_counter()
+        th.join()
+        gen_wait_s += time.perf_counter() - w0
+        t, q = box.pop(c)
+        if k + 1 < len(pieces):
+            th = threading.Thread(target=gen, args=(pieces[k + 1],))
+            th.start()
+        # this chunk's share of every rank's range; keep ours
+        lb = np.clip(bounds - c * P, 0, P)
+        qs, order = shard.split_queries(P, q, lb)
+        a, b = int(lb[rank]), int(lb[rank + 1])
+        tp, qp = t.slice_playlists(a, b), qs[rank]
+        m = ctx.upload(tp)
+        nq = len(qp)
+        d = {kk: torch.from_numpy(getattr(qp, kk)).to(dev) for kk in ("playlist", "level", "begin", "duration")}
+        _, total = m.count_segments(qp.playlist, qp.level, qp.begin, qp.duration)
+        off = torch.empty(nq + 1, dtype=torch.int32, device=dev)
+        st = torch.empty(nq, dtype=torch.uint8, device=dev)
+        sn = torch.empty(max(total, 1), dtype=torch.int32, device=dev)
+        tm = torch.empty(max(total, 1), dtype=torch.float64, device=dev)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(stream):
+            for i in range(2):
+                if i == 1:
+                    e0.record()
+                m.get_segment_list_dev(nq, d["playlist"].data_ptr(), d["level"].data_ptr(),
+                                       d["begin"].data_ptr(), d["duration"].data_ptr(), off.data_ptr(),
+                                       sn.data_ptr(), tm.data_ptr(), total, d_status=st.data_ptr(),
+                                       stream=stream.cuda_stream)
+            e1.record()
+        torch.cuda.synchronize()
+        dev_ms += e0.elapsed_time(e1)
+        w0 = time.perf_counter()
+        res_off.append(off.cpu().numpy())
+        res_st.append(st.cpu().numpy())
+        res_sn.append(sn[:total].cpu().numpy())
+        res_tm.append(tm[:total].cpu().numpy())
+        d2h_s += time.perf_counter() - w0
+        if sample is None and rank == 0:
+            # parity spot check against the CPU oracle on the first playlists of the first piece
+            ns = min(2000, b - a)
+            tsmp = tp.slice_playlists(0, ns)
+            o_off, o_st, o_sn, o_tm = oracle.get_segment_list_batch(
+                tsmp.playlist_base, tsmp.track_off, tsmp.track_state, tsmp.start, tsmp.sn,
+                qp.playlist[:ns * QPP], qp.level[:ns * QPP], qp.begin[:ns * QPP], qp.duration[:ns * QPP])
+            h = int(o_off[-1])
+            sample = bool(np.array_equal(res_off[-1][:ns * QPP + 1].astype(np.int64), o_off) and
+                          np.array_equal(res_sn[-1][:h], o_sn) and
+                          np.array_equal(res_tm[-1][:h].view(np.uint64), o_tm.view(np.uint64)))
+        n_q += nq
+        n_hits += int(total)
+        n_frag += tp.n_fragments
+        alg += 28.0 * nq + 12.0 * total + 12.0 * tp.n_fragments
+        m.close()
+        del d, off, st, sn, tm
+    # this rank's shard in list form: pieces are in playlist order already
+    counts = np.concatenate([np.diff(o.astype(np.int64)) for o in res_off]) if res_off else np.zeros(0, np.int64)
+    mine = (np.concatenate([[0], np.cumsum(counts)]),
+            np.concatenate(res_st) if res_st else np.zeros(0, np.uint8),
+            np.concatenate(res_sn) if res_sn else np.zeros(0, np.int32),
+            np.concatenate(res_tm) if res_tm else np.zeros(0, np.float64))
+    del res_off, res_st, res_sn, res_tm
+
+    def gather_all(x):
+        if world == 1:
+            return [x]
+        tt = torch.tensor([x], dtype=torch.float64, device=dev)
+        outl = [torch.zeros_like(tt) for _ in range(world)]
+        dist.all_gather(outl, tt)
+        return [float(o.item()) for o in outl]
+    per_rank_ms = gather_all(dev_ms)
+    per_rank_q = gather_all(float(n_q))
+    per_rank_hits = gather_all(float(n_hits))
+    per_rank_alg = gather_all(alg)
+    per_rank_frag = gather_all(float(n_frag))
+    per_rank_d2h = gather_all(d2h_s)
+    per_rank_genwait = gather_all(gen_wait_s)
+
+    # host-side gather to rank 0 (host arrays over gloo), then shard.merge
+    if world > 1:
+        dist.barrier(group=gloo)
+    g0 = time.perf_counter()
+    merged = None
+    if world == 1:
+        shards = [mine]
+    elif rank == 0:
+        shards = [mine]
+        for r in range(1, world):
+            nqr, nhr = int(per_rank_q[r]), int(per_rank_hits[r])
+            bufs = (torch.empty(nqr + 1, dtype=torch.int64), torch.empty(nqr, dtype=torch.uint8),
+                    torch.empty(nhr, dtype=torch.int32), torch.empty(nhr, dtype=torch.float64))
+            for x in bufs:
+                dist.recv(x, src=r, group=gloo)
+            shards.append(tuple(x.numpy() for x in bufs))
+    else:
+        for x in mine:
+            dist.send(torch.from_numpy(np.ascontiguousarray(x)), dst=0, group=gloo)
+        shards = None
+    gather_s = time.perf_counter() - g0
+    merge_s, ok_total = 0.0, None
+    if rank == 0:
+        g1 = time.perf_counter()
+        total_q = int(sum(per_rank_q))
+        merged = shard.merge(shards, np.arange(total_q))       # queries are grouped by playlist: shard order is query order
+        merge_s = time.perf_counter() - g1
+        ok_total = bool(int(merged[0][-1]) == int(sum(per_rank_hits)) and len(merged[2]) == int(sum(per_rank_hits))
+                        and len(merged[0]) == total_q + 1)
+        del merged, shards
+    if world > 1:
+        dist.barrier(group=gloo)
+    if rank != 0:
+        return None
+    worst = max(per_rank_ms)
+    total_q, total_alg = sum(per_rank_q), sum(per_rank_alg)
+    return {
+        "workload": "BASELINE.json configs[4]: %d getSegmentList queries over %d synthetic playlists (3 levels, "
+                    "6-1024 fragments each, 100 queries per playlist, grouped by playlist), sharded by contiguous "
+                    "playlist range over %d GPU(s); corpus = %d chunks of %d playlists, seeds %d.."
+                    % (int(total_q), n_chunks * P, world, n_chunks, P, synth.CONFIG5_SEED0),
+        "metric": METRIC, "unit": UNIT, "value": total_q / (worst * 1e-3), "scaling": "strong",
+        "queries": int(total_q), "hits": int(sum(per_rank_hits)), "fragments": int(sum(per_rank_frag)),
+        "hits_per_query": sum(per_rank_hits) / max(total_q, 1),
+        "bounds": [int(x) for x in bounds],
+        "per_rank_device_ms": per_rank_ms, "per_rank_queries": [int(x) for x in per_rank_q],
+        "per_rank_algorithmic_bytes": per_rank_alg,
+        "byte_imbalance_max_over_mean": max(per_rank_alg) / (total_alg / world),
+        "algorithmic_bytes_per_query": total_alg / max(total_q, 1),
+        "roofline_frac": total_alg / (worst * 1e-3) / 1e9 / (peak * world),
+        "per_rank_roofline_frac": [a / (ms * 1e-3) / 1e9 / peak if ms > 0 else None
+                                   for a, ms in zip(per_rank_alg, per_rank_ms)],
+        "timing": "per piece (a chunk's share of the rank's playlist range, its own uploaded map): one warm-up "
+                  "launch, then CUDA events around one launch on its stream, inputs and outputs resident; "
+                  "summed per rank, value = all queries / max over ranks",
+        "kernel": "resolve_search_kernel<SMALL=0> (tables of a piece: ~0.5 GB, staged per tile)",
+        "d2h_s_max_over_ranks": max(per_rank_d2h), "host_gather_s": gather_s, "host_merge_s": merge_s,
+        "gather": "none (one shard)" if world == 1 else "rank 0 receives every shard's host arrays over gloo "
+                  "(point-to-point), then shard.merge",
+        "merged_totals_ok": ok_total, "parity_sample_vs_oracle_ok": sample,
+        "generation_wait_s_max_over_ranks": max(per_rank_genwait),
+        "wall_s": time.perf_counter() - t_all,
+    }
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -282,9 +597,11 @@ def run_ours(args):
         raise SystemExit("bench.py needs a CUDA device: this engine has no CPU path")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    gloo = None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
+        gloo = dist.new_group(backend="gloo")      # host-side gather of the sharded leg only
 
     def barrier():
         if world > 1:
@@ -305,6 +622,24 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return float(t.item())
 
+    def all_ranks(x):
+        if world == 1:
+            return [x]
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        out = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(out, t)
+        return [float(o.item()) for o in out]
+
+    # clocks: the sampler needs ~0.5 s to bring NVML up; start it before anything else so that
+    # even a 1 ms timed region has samples on either side of it and, with luck, inside
+    try:
+        uuid = str(torch.cuda.get_device_properties(local).uuid)
+    except Exception:
+        uuid = None
+    sampler = ClockSampler(uuid, local)
+    if rank == 0:
+        sampler.start()
+
     ctx = pk.Context(local)
     # every rank owns its own playlist (seeded by rank): sharding by playlist, no exchange
     tables, q0 = synth.config2(seed=2 + 1000 * rank, n_queries=args.queries)
@@ -314,28 +649,8 @@ def run_ours(args):
 
     # Rotating query/result buffer sets: successive steps stream through distinct memory
     # whose total is > 3x L2, so no step finds its inputs or outputs in L2.
-    sets = []
-    per_step_bytes = None
-    n_sets = 0
-    while True:
-        q = q0
-        if n_sets > 0:   # the same queries in another order: distinct memory, same tables
-            rng = synth._stream(7000 + rank, n_sets)
-            perm = np.argsort(rng.u32(nq), kind="stable")
-            q = pk.QueryBatch(q0.playlist[perm], q0.level[perm], q0.begin[perm], q0.duration[perm])
-        _, total = dmap.count_segments(q.playlist, q.level, q.begin, q.duration)
-        cap = int(total)
-        s = {"q": q, "hits": cap,
-             "pl": torch.from_numpy(q.playlist).to(dev), "lv": torch.from_numpy(q.level).to(dev),
-             "bg": torch.from_numpy(q.begin).to(dev), "du": torch.from_numpy(q.duration).to(dev),
-             "off": torch.empty(nq + 1, dtype=torch.int32, device=dev),
-             "sn": torch.empty(cap, dtype=torch.int32, device=dev),
-             "tm": torch.empty(cap, dtype=torch.float64, device=dev)}
-        sets.append(s)
-        n_sets += 1
-        per_step_bytes = 28 * nq + 12 * cap
-        if n_sets * per_step_bytes >= 3 * L2_BYTES and n_sets >= 3:
-            break
+    sets, per_step_bytes = list_form_sets(pk, synth, torch, dmap, dev, q0, rank, 3 * L2_BYTES)
+    n_sets = len(sets)
     torch.cuda.synchronize()
     # an explicit stream: the launches and the CUDA events that time them share it
     tstream = torch.cuda.Stream(device=dev)
@@ -345,49 +660,30 @@ def run_ours(args):
 
     count_only = os.environ.get("HLSMAP_BENCH_COUNT_ONLY") == "1"     # experiment switch
 
-    def launch(s):
-        dmap.get_segment_list_dev(nq, s["pl"].data_ptr(), s["lv"].data_ptr(), s["bg"].data_ptr(),
-                                  s["du"].data_ptr(), s["off"].data_ptr(),
-                                  0 if count_only else s["sn"].data_ptr(),
-                                  0 if count_only else s["tm"].data_ptr(),
-                                  0 if count_only else s["hits"], stream=stream)
-
-    launch(sets[0])
+    s0 = sets[0]
+    dmap.get_segment_list_dev(nq, s0["pl"].data_ptr(), s0["lv"].data_ptr(), s0["bg"].data_ptr(),
+                              s0["du"].data_ptr(), s0["off"].data_ptr(), s0["sn"].data_ptr(),
+                              s0["tm"].data_ptr(), s0["hits"], stream=stream)
     chk = dmap.last_result(stream)
-    assert chk.total_hits == sets[0]["hits"]
+    assert chk.total_hits == s0["hits"]
 
-    try:
-        uuid = str(torch.cuda.get_device_properties(local).uuid)
-    except Exception:
-        uuid = None
-    sampler = ClockSampler(uuid, local)
     if rank == 0:
-        sampler.start()
+        sampler.wait_first(10.0)
     # Consecutive steps use disjoint buffers, so the engine may start step i+1 while step i is
     # still writing its last hits (programmatic dependent launch): a batch's ramp-up then hides
     # behind its predecessor's tail, as it would in a serving loop.
     overlap = os.environ.get("HLSMAP_BENCH_NO_OVERLAP") != "1"
     ctx.set_batch_overlap(overlap)
-    for i in range(args.warmup):
-        launch(sets[i % n_sets])
-    torch.cuda.synchronize()
-    t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
     w0 = time.perf_counter()
-    t_begin.record()
-    hits_timed = 0
-    for i in range(args.steps):
-        s = sets[i % n_sets]
-        launch(s)
-        hits_timed += s["hits"]
-    t_end.record()
-    barrier()
+    my_ms, hits_per_step, issue_us = timed_list_form(torch, ctx, dmap, sets, stream, args.steps, args.warmup,
+                                                     barrier=barrier, count_only=count_only)
     sampler.window = (w0, time.perf_counter())
-    region_ms = max_over_ranks(t_begin.elapsed_time(t_end))
-    clocks = sampler.stop() if rank == 0 else None
+    region_ms = max_over_ranks(my_ms)
+    per_rank_ms = all_ranks(my_ms / args.steps)
+    per_rank_issue_us = all_ranks(issue_us)
     total_queries = sum_over_ranks(float(nq * args.steps))
     value = total_queries / (region_ms * 1e-3)
-    mean_kernel_ms = t_begin.elapsed_time(t_end) / args.steps     # average launch-to-launch time
+    mean_kernel_ms = my_ms / args.steps     # average launch-to-launch time on this rank
 
     # the same kernel timed one launch at a time (no overlap), for reference
     ctx.set_batch_overlap(False)
@@ -396,16 +692,20 @@ def run_ours(args):
           for _ in range(iso_steps)]
     torch.cuda.synchronize()
     for i in range(iso_steps):
+        s = sets[i % n_sets]
         ev[i][0].record()
-        launch(sets[i % n_sets])
+        dmap.get_segment_list_dev(nq, s["pl"].data_ptr(), s["lv"].data_ptr(), s["bg"].data_ptr(),
+                                  s["du"].data_ptr(), s["off"].data_ptr(), s["sn"].data_ptr(),
+                                  s["tm"].data_ptr(), s["hits"], stream=stream)
         ev[i][1].record()
     torch.cuda.synchronize()
     kernel_ms = [a.elapsed_time(b) for a, b in ev]
     ctx.set_batch_overlap(overlap)
+    clocks = sampler.stop() if rank == 0 else None
 
     # roofline of the dominant (only) kernel: algorithmic bytes / mean launch duration
     table_bytes = 12 * info["n_fragments"]
-    alg_bytes = 28.0 * nq + 12.0 * (hits_timed / args.steps) + table_bytes
+    alg_bytes = 28.0 * nq + 12.0 * hits_per_step + table_bytes
     achieved = alg_bytes / (mean_kernel_ms * 1e-3) / 1e9
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
@@ -421,7 +721,6 @@ def run_ours(args):
             traffic = None
 
     # end to end through the host-pointer C ABI call on pinned buffers
-    s0 = sets[0]
     pins = {k: ctx.pinned(shape, dt) for k, shape, dt in (
         ("pl", nq, np.int32), ("lv", nq, np.int32), ("bg", nq, np.float64), ("du", nq, np.float64),
         ("off", nq + 1, np.int32), ("sn", s0["hits"], np.int32), ("tm", s0["hits"], np.float64))}
@@ -442,7 +741,9 @@ def run_ours(args):
     for _ in range(args.e2e_steps):
         r = e2e_step()
     torch.cuda.synchronize()
-    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    my_e2e_s = time.perf_counter() - t0
+    e2e_s = max_over_ranks(my_e2e_s)
+    per_rank_e2e_ms = all_ranks(1e3 * my_e2e_s / args.e2e_steps)
     e2e_value = sum_over_ranks(float(nq * args.e2e_steps)) / e2e_s
     assert int(pins["off"].array[-1]) == s0["hits"] == r.total_hits
     h2d = 24 * nq * world                               # all ranks, per step
@@ -450,29 +751,28 @@ def run_ours(args):
 
     # the same queries through the range form (first index + count per query: 9 B back instead of
     # 12 B per hit) -- what a PCIe-bound deployment would call; reported beside e2e, not instead of it
-    e2e_range = None
-    if rank == 0 and world == 1:
-        import ctypes
-        from hlsjs_p2p_wrapper_b200 import _native as N
-        rp = {k: ctx.pinned(nq, dt) for k, dt in (("first", np.int32), ("count", np.int32), ("st", np.uint8))}
-        pv = lambda a: ctypes.c_void_p(a.ctypes.data)
+    import ctypes
+    from hlsjs_p2p_wrapper_b200 import _native as N
+    rp = {k: ctx.pinned(nq, dt) for k, dt in (("first", np.int32), ("count", np.int32), ("st", np.uint8))}
+    pv = lambda a: ctypes.c_void_p(a.ctypes.data)
 
-        def range_step():
-            N.check(N.load().hlsmap_get_segment_range(dmap._h, nq, pv(pins["pl"].array), pv(pins["lv"].array),
-                                                      pv(pins["bg"].array), pv(pins["du"].array),
-                                                      pv(rp["first"].array), pv(rp["count"].array), pv(rp["st"].array)))
-        for _ in range(3):
-            range_step()
-        t0 = time.perf_counter()
-        for _ in range(args.e2e_steps):
-            range_step()
-        dt_r = time.perf_counter() - t0
-        assert int(rp["count"].array.astype(np.int64).sum()) == s0["hits"]
-        e2e_range = {"value": nq * args.e2e_steps / dt_r, "unit": UNIT, "ms_per_step": 1e3 * dt_r / args.e2e_steps,
-                     "h2d_bytes_per_step": 24 * nq, "d2h_bytes_per_step": 9 * nq,
-                     "api": "hlsmap_get_segment_range (host pointers, pinned)"}
-        for v in rp.values():
-            v.free()
+    def range_step():
+        N.check(N.load().hlsmap_get_segment_range(dmap._h, nq, pv(pins["pl"].array), pv(pins["lv"].array),
+                                                  pv(pins["bg"].array), pv(pins["du"].array),
+                                                  pv(rp["first"].array), pv(rp["count"].array), pv(rp["st"].array)))
+    for _ in range(3):
+        range_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.e2e_steps):
+        range_step()
+    dt_r = max_over_ranks(time.perf_counter() - t0)
+    assert int(rp["count"].array.astype(np.int64).sum()) == s0["hits"]
+    e2e_range = {"value": nq * args.e2e_steps * world / dt_r, "unit": UNIT, "ms_per_step": 1e3 * dt_r / args.e2e_steps,
+                 "h2d_bytes_per_step": 24 * nq * world, "d2h_bytes_per_step": 9 * nq * world,
+                 "api": "hlsmap_get_segment_range (host pointers, pinned)"}
+    for v in rp.values():
+        v.free()
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -486,22 +786,42 @@ def run_ours(args):
     rows = None
     if rank == 0 and world == 1 and not args.no_other_rows:
         try:
-            rows = other_rows(ctx, torch, peak)
+            rows = path_rows(pk, synth, torch, ctx, dmap, dev, tables, q0, stream, peak,
+                             min(args.steps, 200), max(args.warmup, 3))
+            rows.update(other_rows(ctx, torch, peak))
         except Exception as e:                      # never let the extra rows cost the headline line
-            rows = {"error": "%s: %s" % (type(e).__name__, e)}
+            rows = dict(rows or {}, error="%s: %s" % (type(e).__name__, e))
+
+    for p in pins.values():
+        p.free()
+    del sets
+    sharded = None
+    if not args.no_sharded:
+        try:
+            sharded = sharded_config5(pk, synth, torch, dist, ctx, dev, rank, world, local, peak,
+                                      args.config5_chunks, gloo)
+        except Exception as e:
+            if world > 1:
+                raise
+            sharded = {"error": "%s: %s" % (type(e).__name__, e)}
 
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": region_ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": dict(workload_config(args, world),
-                           l2_policy="rotating %d distinct query/result buffer sets, %.0f MB per step, "
+            "config": workload_config(args, world),
+            "details": {"l2_policy": "rotating %d distinct query/result buffer sets, %.0f MB per step, "
                                      "%.0f MB per rotation (> 3x the 126 MB L2): no step finds its "
                                      "inputs or outputs in L2" % (n_sets, per_step_bytes / 1e6,
                                                                   n_sets * per_step_bytes / 1e6),
-                           hits_per_query=hits_timed / args.steps / nq, kernel="resolve_search_kernel",
-                           stage_all=info["stage_all"]),
+                        "hits_per_query": hits_per_step / nq, "kernel": "resolve_search_kernel",
+                        "stage_all": info["stage_all"],
+                        "per_rank_ms_per_step": per_rank_ms,
+                        "host_issue_us_per_launch": per_rank_issue_us,
+                        "host_issue_note": "time.perf_counter around the timed launch loop / steps, per rank: the "
+                                           "Python -> ctypes -> cudaLaunchKernelEx path; the GPU is the limiter "
+                                           "while this stays below ms_per_step"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "frac_of_nominal_8TBs": achieved / 8000.0,
@@ -512,21 +832,23 @@ def run_ours(args):
                          "kernel_ms_isolated_mean": float(np.mean(kernel_ms)),
                          "kernel_ms_isolated_min": float(np.min(kernel_ms)),
                          "frac_isolated": alg_bytes / (float(np.mean(kernel_ms)) * 1e-3) / 1e9 / peak,
-                         "isolated_note": "one launch at a time with the overlap option off: the library then "
-                                          "keeps 512-query tiles (1024-query tiles serve large batches run back "
-                                          "to back, i.e. the timed region)"},
+                         "isolated_note": "one launch at a time with the overlap option off (same kernel, same "
+                                          "512-query tiles): a lone batch pays its own ramp-up and tail"},
             "cpu_baseline": cpu,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": args.e2e_steps,
                     "ms_per_step": 1e3 * e2e_s / args.e2e_steps,
+                    "per_rank_ms_per_step": per_rank_e2e_ms,
                     "api": "hlsmap_get_segment_list (host pointers, pinned)",
-                    "kernel_launches_per_step": e2e_launches},
+                    "kernel_launches_per_step": e2e_launches,
+                    "capacity_note": "the caller's hit buffers were sized from an earlier, untimed count pass "
+                                     "(hlsmap_get_segment_list with NULL hit arrays); a caller that cannot know "
+                                     "the count either pays that pass (24 B/query up, 4 B/query back) or "
+                                     "over-allocates"},
             "gpu_launches": args.steps * world, "clocks": clocks, "node": node_version(),
-            "other_rows": rows, "e2e_range_form": e2e_range,
+            "other_rows": rows, "e2e_range_form": e2e_range, "sharded_config5": sharded,
         }
         print(json.dumps(line))
-    for p in pins.values():
-        p.free()
     dmap.close()
     ctx.close()
     if world > 1:

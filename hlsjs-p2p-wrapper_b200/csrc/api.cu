@@ -947,7 +947,17 @@ int hlsmap_get_segment_range_dev(hlsmap_map *map, int64_t nq, const int32_t *d_p
     p.first = d_first;
     p.count = d_count;
     p.status = d_status;
-    CK(launch_range(p, stream ? (cudaStream_t)stream : ctx->stream));
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    if (map->info.stage_all && pick_path(map) == HLSMAP_PATH_SEARCH) {
+        // the whole map fits shared memory and every column is sorted: staged tables + hint grid
+        const int vec_ok = al16(d_level) && al16(d_begin) && al16(d_duration) && al16(d_first) && al16(d_count) &&
+                           (!d_playlist || al16(d_playlist)) &&
+                           (!d_status || (reinterpret_cast<uintptr_t>(d_status) & 3u) == 0);
+        CK(launch_range_small(p, map->d_hint, map->d_grid, map->n_frag_padded, map->grid_padded,
+                              map->n_tracks_padded, map->n_base_padded, vec_ok, s));
+    } else {
+        CK(launch_range(p, s));
+    }
     ctx->last_launches = 1;
     return HLSMAP_OK;
 }

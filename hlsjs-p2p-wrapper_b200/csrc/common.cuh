@@ -216,6 +216,9 @@ cudaError_t launch_resolve_search(const ResolveParams &p, int grid, size_t smem,
                                   bool overlap_next = false);
 cudaError_t launch_resolve_filter(const ResolveParams &p, int grid, cudaStream_t s);
 cudaError_t launch_range(const RangeParams &p, cudaStream_t s);
+cudaError_t launch_range_small(const RangeParams &p, const TrackHint *hint, const unsigned short *grid,
+                               long long n_frag_padded, int grid_padded, int n_tracks_padded,
+                               int n_base_padded, int vec_ok, cudaStream_t s);
 cudaError_t launch_monotone_check(const double *start, TrackDesc *desc, int n_tracks,
                                   cudaStream_t s);
 cudaError_t launch_segment_duration(const TrackDesc *desc, const int *playlist_base,

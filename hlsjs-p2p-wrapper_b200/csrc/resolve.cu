@@ -348,6 +348,67 @@ __device__ __forceinline__ int hint_cell(double x, double t0, double inv, int nc
     return min(max(c, 0), ncell - 1);
 }
 
+// Bounds of K queries on a map staged in shared memory (SMALL).  Hint grid: each bound is
+// narrowed to one cell before any table probe; the per-query chains are written side by side so
+// they overlap (ILP), and the cell is finished with the filter's own comparisons
+// (media-map.js:44): [lo, lo + cnt) is exactly what the reference loop keeps.
+template <int K>
+__device__ __forceinline__ void small_bounds(const double *s_start, const unsigned short *s_grid,
+                                             const TrackHint *s_hint, const double (&bg)[K],
+                                             const double (&du)[K], const long long (&off)[K],
+                                             const int (&len)[K], const int (&st)[K], const int (&trk)[K],
+                                             int (&lo)[K], int (&cnt)[K])
+{
+    int b0[K], bn[K], u0[K], un[K];
+    double ub[K];
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+        // one fp64 add, round-to-nearest, never contracted: `beginTime + duration`
+        ub[k] = __dadd_rn(bg[k], du[k]);
+        const int4 h0 = *reinterpret_cast<const int4 *>(s_hint + trk[k]);
+        const int4 h1 = *(reinterpret_cast<const int4 *>(s_hint + trk[k]) + 1);
+        const double t0 = __hiloint2double(h0.y, h0.x);
+        const double inv = __hiloint2double(h0.w, h0.z);
+        const bool ok = st[k] == HLSMAP_ST_OK;
+        const int ncell = ok ? h1.y : 1;
+        b0[k] = (ok ? h1.x : 0) + hint_cell(bg[k], t0, inv, ncell);   // grid index
+        u0[k] = (ok ? h1.x : 0) + hint_cell(ub[k], t0, inv, ncell);
+    }
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+        const int gb0 = s_grid[b0[k]], gb1 = s_grid[b0[k] + 1];
+        const int gu0 = s_grid[u0[k]], gu1 = s_grid[u0[k] + 1];
+        b0[k] = gb0; bn[k] = gb1 - gb0;
+        u0[k] = gu0; un[k] = gu1 - gu0;
+    }
+    // two fixed halving steps settle cells of up to 3 fragments without a loop
+#pragma unroll
+    for (int it = 0; it < 2; it++) {
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+            const double *col = s_start + (int)off[k];
+            const int hb_ = bn[k] >> 1, hu_ = un[k] >> 1;
+            const bool gb = bn[k] > 0 && !(bg[k] <= col[b0[k] + hb_]);
+            const bool gu = un[k] > 0 && (col[u0[k] + hu_] <= ub[k]);
+            b0[k] = gb ? b0[k] + hb_ + 1 : b0[k];
+            bn[k] = gb ? bn[k] - hb_ - 1 : hb_;
+            u0[k] = gu ? u0[k] + hu_ + 1 : u0[k];
+            un[k] = gu ? un[k] - hu_ - 1 : hu_;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+        const SmemCol col{s_start + (int)off[k]};
+        int l = b0[k], h = u0[k];
+        if (bn[k] > 0) l = lower_bound_begin(col, l, bn[k], bg[k]);   // crowded cell
+        if (un[k] > 0) h = upper_bound_ub(col, h, un[k], ub[k]);
+        if (bg[k] != bg[k]) l = len[k];       // NaN: `begin <= start` never holds
+        if (st[k] != HLSMAP_ST_OK) { l = 0; h = 0; }
+        lo[k] = l;
+        cnt[k] = max(h - l, 0);
+    }
+}
+
 // =========================================================================================
 //  search kernel.  SMALL = the whole map (start, sn, hint grid) lives in shared memory.
 //
@@ -557,58 +618,7 @@ resolve_search_kernel(const ResolveParams p)
             }
 
             if (SMALL) {
-                // Hint grid: each bound is narrowed to one cell before any table probe; the
-                // per-query chains are written side by side so they overlap (ILP), and the
-                // cell is finished with the filter's own comparisons.
-                int b0[kIpt], bn[kIpt], u0[kIpt], un[kIpt];
-                double ub[kIpt];
-#pragma unroll
-                for (int k = 0; k < kIpt; k++) {
-                    // one fp64 add, round-to-nearest, never contracted: `beginTime + duration`
-                    ub[k] = __dadd_rn(bg[k], du[k]);
-                    const int4 h0 = *reinterpret_cast<const int4 *>(s_hint + trk[k]);
-                    const int4 h1 = *(reinterpret_cast<const int4 *>(s_hint + trk[k]) + 1);
-                    const double t0 = __hiloint2double(h0.y, h0.x);
-                    const double inv = __hiloint2double(h0.w, h0.z);
-                    const bool ok = st[k] == HLSMAP_ST_OK;
-                    const int ncell = ok ? h1.y : 1;
-                    b0[k] = (ok ? h1.x : 0) + hint_cell(bg[k], t0, inv, ncell);   // grid index
-                    u0[k] = (ok ? h1.x : 0) + hint_cell(ub[k], t0, inv, ncell);
-                }
-                trace_mark_after(p, tileB, 7, b0[0] ^ u0[kIpt - 1]);
-#pragma unroll
-                for (int k = 0; k < kIpt; k++) {
-                    const int gb0 = s_grid[b0[k]], gb1 = s_grid[b0[k] + 1];
-                    const int gu0 = s_grid[u0[k]], gu1 = s_grid[u0[k] + 1];
-                    b0[k] = gb0; bn[k] = gb1 - gb0;
-                    u0[k] = gu0; un[k] = gu1 - gu0;
-                }
-                // two fixed halving steps settle cells of up to 3 fragments without a loop
-#pragma unroll
-                for (int it = 0; it < 2; it++) {
-#pragma unroll
-                    for (int k = 0; k < kIpt; k++) {
-                        const double *col = s_start + (int)off[k];
-                        const int hb_ = bn[k] >> 1, hu_ = un[k] >> 1;
-                        const bool gb = bn[k] > 0 && !(bg[k] <= col[b0[k] + hb_]);
-                        const bool gu = un[k] > 0 && (col[u0[k] + hu_] <= ub[k]);
-                        b0[k] = gb ? b0[k] + hb_ + 1 : b0[k];
-                        bn[k] = gb ? bn[k] - hb_ - 1 : hb_;
-                        u0[k] = gu ? u0[k] + hu_ + 1 : u0[k];
-                        un[k] = gu ? un[k] - hu_ - 1 : hu_;
-                    }
-                }
-#pragma unroll
-                for (int k = 0; k < kIpt; k++) {
-                    const SmemCol col{s_start + (int)off[k]};
-                    int l = b0[k], h = u0[k];
-                    if (bn[k] > 0) l = lower_bound_begin(col, l, bn[k], bg[k]);   // crowded cell
-                    if (un[k] > 0) h = upper_bound_ub(col, h, un[k], ub[k]);
-                    if (bg[k] != bg[k]) l = len[k];       // NaN: `begin <= start` never holds
-                    if (st[k] != HLSMAP_ST_OK) { l = 0; h = 0; }
-                    lo[k] = l;
-                    cnt[k] = max(h - l, 0);
-                }
+                small_bounds<kIpt>(s_start, s_grid, s_hint, bg, du, off, len, st, trk, lo, cnt);
             } else {
                 // ---- bounds: [lo, lo+cnt) is exactly what the filter keeps --------------------
                 // The tile's tracks are searched from a shared-memory window of start[].  Usually
@@ -1190,6 +1200,110 @@ range_kernel(const RangeParams p)
     }
 }
 
+// Range form on a map that fits shared memory (SMALL): the same staging and hint-grid search as
+// the list form's kernel, without its scan and expansion.  Every CTA stages start[], the hint grid
+// and the track metadata once (bulk copies, sn[] is not needed), then walks 1024-query tiles
+// grid-stride: four queries per thread, 128-bit loads and stores.
+namespace {
+constexpr int kRangeIpt = 4;
+constexpr int kRangeTile = kThreads * kRangeIpt;
+}  // namespace
+
+__global__ void __launch_bounds__(kThreads)
+range_small_kernel(const RangeParams p, const TrackHint *hint, const unsigned short *grid,
+                   long long n_frag_padded, int grid_padded, int n_tracks_padded, int n_base_padded, int vec_ok)
+{
+    extern __shared__ __align__(128) unsigned char dyn_smem[];
+    __shared__ unsigned long long mbar;
+    const double *s_start = reinterpret_cast<const double *>(dyn_smem);
+    const unsigned short *s_grid = reinterpret_cast<const unsigned short *>(dyn_smem + n_frag_padded * 8);
+    const unsigned char *s_meta = dyn_smem + n_frag_padded * 8 + (long long)grid_padded * 2;
+    const TrackDesc *s_desc = reinterpret_cast<const TrackDesc *>(s_meta);
+    const TrackHint *s_hint = reinterpret_cast<const TrackHint *>(s_meta + (long long)n_tracks_padded * 16);
+    const int *s_base = reinterpret_cast<const int *>(s_meta + (long long)n_tracks_padded * 48);
+    const int tid = threadIdx.x;
+    if (tid == 0) mbar_init(&mbar, 1);
+    __syncthreads();
+    if (tid == 0) {
+        const unsigned b_start = (unsigned)(n_frag_padded * 8), b_grid = (unsigned)(grid_padded * 2);
+        const unsigned b_desc = (unsigned)(n_tracks_padded * 16), b_hint = (unsigned)(n_tracks_padded * 32);
+        const unsigned b_base = (unsigned)(n_base_padded * 4);
+        mbar_expect_tx(&mbar, b_start + b_grid + b_desc + b_hint + b_base);
+        unsigned char *d = dyn_smem;
+        bulk_g2s_chunked(d, p.start, b_start, &mbar); d += b_start;
+        bulk_g2s_chunked(d, grid, b_grid, &mbar); d += b_grid;
+        bulk_g2s_chunked(d, p.desc, b_desc, &mbar); d += b_desc;
+        bulk_g2s_chunked(d, hint, b_hint, &mbar); d += b_hint;
+        bulk_g2s_chunked(d, p.playlist_base, b_base, &mbar);
+    }
+    bool staged = false;
+    const long long n_tiles = (p.nq + kRangeTile - 1) / kRangeTile;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const long long q0 = tile * kRangeTile + (long long)tid * kRangeIpt;
+        const bool full = vec_ok && q0 + kRangeIpt <= p.nq;
+        int pl[kRangeIpt], lv[kRangeIpt];
+        double bg[kRangeIpt], du[kRangeIpt];
+        if (full) {
+            const int4 l4 = __ldcs(reinterpret_cast<const int4 *>(p.q_level + q0));
+            lv[0] = l4.x; lv[1] = l4.y; lv[2] = l4.z; lv[3] = l4.w;
+            if (p.q_playlist) {
+                const int4 p4 = __ldcs(reinterpret_cast<const int4 *>(p.q_playlist + q0));
+                pl[0] = p4.x; pl[1] = p4.y; pl[2] = p4.z; pl[3] = p4.w;
+            } else {
+                pl[0] = pl[1] = pl[2] = pl[3] = 0;
+            }
+#pragma unroll
+            for (int k = 0; k < kRangeIpt; k += 2) {
+                const double2 b2 = __ldcs(reinterpret_cast<const double2 *>(p.q_begin + q0 + k));
+                const double2 d2 = __ldcs(reinterpret_cast<const double2 *>(p.q_duration + q0 + k));
+                bg[k] = b2.x; bg[k + 1] = b2.y;
+                du[k] = d2.x; du[k + 1] = d2.y;
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < kRangeIpt; k++) {
+                const bool in = q0 + k < p.nq;
+                lv[k] = in ? __ldcs(p.q_level + q0 + k) : -1;
+                pl[k] = (in && p.q_playlist) ? __ldcs(p.q_playlist + q0 + k) : 0;
+                bg[k] = in ? __ldcs(p.q_begin + q0 + k) : 0.0;
+                du[k] = in ? __ldcs(p.q_duration + q0 + k) : 0.0;
+            }
+        }
+        if (!staged) {                   // first tile only: the tables have landed
+            mbar_wait(&mbar, 0);
+            staged = true;
+        }
+        long long off[kRangeIpt];
+        int len[kRangeIpt], st[kRangeIpt], trk[kRangeIpt], lo[kRangeIpt], cnt[kRangeIpt];
+#pragma unroll
+        for (int k = 0; k < kRangeIpt; k++) {
+            unsigned fl;
+            st[k] = lookup_track<true>(s_desc, s_base, p.n_playlists, pl[k], lv[k], off[k], len[k], fl, &trk[k]);
+        }
+        small_bounds<kRangeIpt>(s_start, s_grid, s_hint, bg, du, off, len, st, trk, lo, cnt);
+        int first[kRangeIpt];
+#pragma unroll
+        for (int k = 0; k < kRangeIpt; k++) first[k] = cnt[k] > 0 ? lo[k] : -1;
+        if (full) {
+            __stcs(reinterpret_cast<int4 *>(p.first + q0), make_int4(first[0], first[1], first[2], first[3]));
+            __stcs(reinterpret_cast<int4 *>(p.count + q0), make_int4(cnt[0], cnt[1], cnt[2], cnt[3]));
+            if (p.status)
+                *reinterpret_cast<unsigned *>(p.status + q0) =
+                    (unsigned)st[0] | ((unsigned)st[1] << 8) | ((unsigned)st[2] << 16) | ((unsigned)st[3] << 24);
+        } else {
+#pragma unroll
+            for (int k = 0; k < kRangeIpt; k++) {
+                if (q0 + k < p.nq) {
+                    p.first[q0 + k] = first[k];
+                    p.count[q0 + k] = cnt[k];
+                    if (p.status) p.status[q0 + k] = (unsigned char)st[k];
+                }
+            }
+        }
+    }
+    if (!staged) mbar_wait(&mbar, 0);    // never leave with a bulk copy still landing
+}
+
 // =========================================================================================
 //  upload-time monotonicity proof: one warp per track
 // =========================================================================================
@@ -1447,6 +1561,40 @@ cudaError_t launch_resolve_search(const ResolveParams &p, int grid, size_t smem,
 cudaError_t launch_resolve_filter(const ResolveParams &p, int grid, cudaStream_t s)
 {
     resolve_filter_kernel<<<grid, kFThreads, 0, s>>>(p);
+    return cudaGetLastError();
+}
+
+// SMALL maps: the staged kernel.  smem = start + grid + descriptors + hints + playlist index.
+cudaError_t launch_range_small(const RangeParams &p, const TrackHint *hint, const unsigned short *grid,
+                               long long n_frag_padded, int grid_padded, int n_tracks_padded,
+                               int n_base_padded, int vec_ok, cudaStream_t s)
+{
+    const size_t smem = (size_t)(n_frag_padded * 8 + (long long)grid_padded * 2 +
+                                 (long long)n_tracks_padded * 48 + (long long)n_base_padded * 4);
+    // the shared-memory opt-in and the occupancy belong to the current device: remembered per device
+    static size_t configured[64] = {};
+    static int per_sm_of[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const int slot = dev & 63;
+    if (smem != configured[slot]) {
+        cudaError_t e = cudaFuncSetAttribute(range_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        int per_sm = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, range_small_kernel, kThreads, smem) != cudaSuccess ||
+            per_sm < 1)
+            per_sm = 1;
+        configured[slot] = smem;
+        per_sm_of[slot] = per_sm;
+    }
+    long long blocks = (p.nq + kRangeTile - 1) / kRangeTile;
+    int n_sm = 0;
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+    const long long cap = (long long)(n_sm > 0 ? n_sm : 148) * per_sm_of[slot];
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    range_small_kernel<<<(int)blocks, kThreads, smem, s>>>(p, hint, grid, n_frag_padded, grid_padded,
+                                                            n_tracks_padded, n_base_padded, vec_ok);
     return cudaGetLastError();
 }
 

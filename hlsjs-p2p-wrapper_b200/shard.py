@@ -12,14 +12,12 @@ import numpy as np
 from .tables import FragmentTables, QueryBatch
 
 
-def plan(tables: FragmentTables, queries: QueryBatch, n_shards: int):
-    """Contiguous playlist ranges balanced by bytes moved: 12 B per fragment of the shard's
-    tables + 76 B per query (SURVEY.md 8e).  Returns playlist boundaries, length n_shards+1."""
-    p = tables.n_playlists
-    frag_per_pl = np.diff(tables.track_off[tables.playlist_base].astype(np.int64))
-    inb = (queries.playlist >= 0) & (queries.playlist < p)
-    q_per_pl = np.bincount(queries.playlist[inb], minlength=p)[:p]
-    w = 12.0 * frag_per_pl + 76.0 * q_per_pl + 1e-9
+def plan_counts(frag_per_pl, q_per_pl, n_shards: int):
+    """`plan` from per-playlist counts alone (fragments, queries): the tables themselves are not
+    needed to place the boundaries, so a rank can plan before it has generated or loaded anything."""
+    frag_per_pl = np.asarray(frag_per_pl, np.float64)
+    p = len(frag_per_pl)
+    w = 12.0 * frag_per_pl + 76.0 * np.asarray(q_per_pl, np.float64) + 1e-9
     c = np.concatenate([[0.0], np.cumsum(w)])
     targets = c[-1] * np.arange(1, n_shards) / n_shards
     cuts = np.searchsorted(c, targets, side="left")
@@ -27,28 +25,45 @@ def plan(tables: FragmentTables, queries: QueryBatch, n_shards: int):
     return np.maximum.accumulate(bounds)
 
 
-def split(tables: FragmentTables, queries: QueryBatch, bounds):
-    """-> (shards, order): shards[i] = (tables_i, queries_i) with playlist ids re-based;
+def plan(tables: FragmentTables, queries: QueryBatch, n_shards: int):
+    """Contiguous playlist ranges balanced by bytes moved: 12 B per fragment of the shard's
+    tables + 76 B per query (SURVEY.md 8e).  Returns playlist boundaries, length n_shards+1."""
+    p = tables.n_playlists
+    frag_per_pl = np.diff(tables.track_off[tables.playlist_base].astype(np.int64))
+    inb = (queries.playlist >= 0) & (queries.playlist < p)
+    q_per_pl = np.bincount(queries.playlist[inb], minlength=p)[:p]
+    return plan_counts(frag_per_pl, q_per_pl, n_shards)
+
+
+def split_queries(n_playlists: int, queries: QueryBatch, bounds):
+    """-> (query_shards, order): query_shards[i] = the queries of shard i with playlist ids re-based;
     `order` is the permutation that groups the original queries shard by shard.  Queries on
     playlists outside [0, P) go to shard 0 (they resolve to 'missing' there too)."""
     n = len(bounds) - 1
     pl = queries.playlist.astype(np.int64)
     shard_of = np.clip(np.searchsorted(bounds, pl, side="right") - 1, 0, n - 1)
-    outside = (pl < 0) | (pl >= tables.n_playlists)
+    outside = (pl < 0) | (pl >= n_playlists)
     shard_of[outside] = 0
     order = np.argsort(shard_of, kind="stable")
     counts = np.bincount(shard_of, minlength=n)
     starts = np.concatenate([[0], np.cumsum(counts)])
-    shards = []
+    out = []
     for i in range(n):
         idx = order[starts[i]:starts[i + 1]]
-        p0, p1 = int(bounds[i]), int(bounds[i + 1])
-        lp = pl[idx] - p0
+        lp = pl[idx] - int(bounds[i])
         if i == 0:
             lp = np.where(outside[idx], -1, lp)
-        q = QueryBatch(lp.astype(np.int32), queries.level[idx].copy(), queries.begin[idx].copy(),
-                       queries.duration[idx].copy())
-        shards.append((tables.slice_playlists(p0, p1), q))
+        out.append(QueryBatch(lp.astype(np.int32), queries.level[idx].copy(), queries.begin[idx].copy(),
+                              queries.duration[idx].copy()))
+    return out, order
+
+
+def split(tables: FragmentTables, queries: QueryBatch, bounds):
+    """-> (shards, order): shards[i] = (tables_i, queries_i), both re-based to the shard's first
+    playlist; `order` as in split_queries.  (Slices the tables: call it once per upload, and
+    split_queries per batch.)"""
+    qs, order = split_queries(tables.n_playlists, queries, bounds)
+    shards = [(tables.slice_playlists(int(bounds[i]), int(bounds[i + 1])), q) for i, q in enumerate(qs)]
     return shards, order
 
 
@@ -77,6 +92,9 @@ def merge(results, order):
     sn = np.concatenate([r[2] for r in results])
     tm = np.concatenate([r[3] for r in results])
     nq = len(order)
+    if nq == 0 or (order[0] == 0 and order[-1] == nq - 1 and np.all(np.diff(order) == 1)):
+        # queries arrived grouped by shard (e.g. by playlist): shard order IS query order
+        return np.concatenate([[0], np.cumsum(counts)]), status, sn, tm
     inv = np.empty(nq, np.int64)
     inv[order] = np.arange(nq)
     src_off = np.concatenate([[0], np.cumsum(counts)])
@@ -117,18 +135,27 @@ class ShardedMap:
         return self
 
     def get_segment_list(self, queries: QueryBatch):
-        shards, order = split(self.tables, queries, self.bounds)
+        """One batch over all GPUs: route by playlist, one host thread per GPU, gather on the host.
+        An error on any GPU (capacity, out of memory, ...) is re-raised here."""
+        qs, order = split_queries(self.tables.n_playlists, queries, self.bounds)
         out = [None] * len(self.maps)
+        errors = [None] * len(self.maps)
 
         def work(i):
-            q = shards[i][1]
-            r = self.maps[i].get_segment_list(q.playlist, q.level, q.begin, q.duration)
-            out[i] = (r.offsets.astype(np.int64), r.status, r.sn, r.time)
+            try:
+                q = qs[i]
+                r = self.maps[i].get_segment_list(q.playlist, q.level, q.begin, q.duration)
+                out[i] = (r.offsets.astype(np.int64), r.status, r.sn, r.time)
+            except BaseException as e:      # handed to the caller below
+                errors[i] = e
         threads = [threading.Thread(target=work, args=(i,)) for i in range(len(self.maps))]
         for t in threads:
             t.start()
         for t in threads:
             t.join()
+        for e in errors:
+            if e is not None:
+                raise e
         return merge(out, order)
 
     def close(self):

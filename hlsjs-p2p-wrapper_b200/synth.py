@@ -25,12 +25,13 @@ class Mulberry32:
         self.a = np.uint64(seed & 0xFFFFFFFF)
 
     def u32(self, n):
-        k = np.arange(1, n + 1, dtype=np.uint64)
-        a = (self.a + k * np.uint64(0x6D2B79F5)) & _M32
+        # uint32 arrays: numpy's multiply and add wrap modulo 2^32, which is Math.imul / >>> 0
+        k = np.arange(1, n + 1, dtype=np.uint32)
+        a = k * np.uint32(0x6D2B79F5) + np.uint32(int(self.a))
         self.a = np.uint64((int(self.a) + n * 0x6D2B79F5) & 0xFFFFFFFF)
-        t = _imul(a ^ (a >> np.uint64(15)), a | np.uint64(1))
-        t = ((t + _imul(t ^ (t >> np.uint64(7)), t | np.uint64(61))) & _M32) ^ t
-        return (t ^ (t >> np.uint64(14))) & _M32          # uint64 holding u32 values
+        t = (a ^ (a >> np.uint32(15))) * (a | np.uint32(1))
+        t = (t + (t ^ (t >> np.uint32(7))) * (t | np.uint32(61))) ^ t
+        return (t ^ (t >> np.uint32(14))).astype(np.uint64)          # uint64 holding u32 values
 
     def below(self, n, bound):
         """n integers uniform in [0, bound) (modulo bias is irrelevant here)."""
@@ -64,32 +65,28 @@ def _adversarial(rng, n, tables, track, begin, dur):
     """Edge queries: exact boundary hits, rounding sums, negatives, NaN, Inf, -0."""
     kind = rng.below(n, 10).astype(np.int64)
     pick = rng.u32(n).astype(np.int64)
-    off = tables.track_off
-    for i in range(n):
-        t = int(track[i])
-        o, ln = int(off[t]), int(off[t + 1] - off[t])
-        s = tables.start[o + pick[i] % ln] if ln else 0.0
-        k = int(kind[i])
-        if k == 0:      # begin == a start exactly
-            begin[i], dur[i] = s, 30.0
-        elif k == 1:    # begin + duration == a start exactly
-            begin[i], dur[i] = s - 30.0, 30.0
-        elif k == 2:    # a sum that rounds (0.1 + 0.2 style operands are not dyadic)
-            begin[i], dur[i] = s - 0.3, 0.1 + 0.2
-        elif k == 3:    # negative duration -> empty
-            begin[i], dur[i] = s, -1.0
-        elif k == 4:
-            begin[i], dur[i] = float("nan"), 30.0
-        elif k == 5:
-            begin[i], dur[i] = s, float("nan")
-        elif k == 6:
-            begin[i], dur[i] = s, float("inf")
-        elif k == 7:    # -Inf + Inf = NaN upper bound
-            begin[i], dur[i] = float("-inf"), float("inf")
-        elif k == 8:
-            begin[i], dur[i] = -0.0, s
-        else:
-            begin[i], dur[i] = float("-inf"), 1e308
+    off = tables.track_off.astype(np.int64)
+    o, ln = off[track], off[track + 1] - off[track]
+    has = ln > 0
+    s = np.zeros(n)
+    if has.any() and len(tables.start):
+        s[has] = tables.start[o[has] + pick[has] % ln[has]]
+    nan, inf = float("nan"), float("inf")
+    with np.errstate(invalid="ignore"):
+        # 0: begin == a start exactly; 1: begin + duration == a start exactly; 2: a sum that rounds
+        # (0.1 + 0.2 style operands are not dyadic); 3: negative duration -> empty; 4, 5: NaN;
+        # 6: +Inf; 7: -Inf + Inf = NaN upper bound; 8: -0; 9: -Inf with a huge duration
+        b = np.select([kind == 0, kind == 1, kind == 2, kind == 3, kind == 4, kind == 5, kind == 6,
+                       kind == 7, kind == 8],
+                      [s, s - 30.0, s - 0.3, s, np.full(n, nan), s, s, np.full(n, -inf), np.full(n, -0.0)],
+                      default=-inf)
+        d = np.select([kind == 0, kind == 1, kind == 2, kind == 3, kind == 4, kind == 5, kind == 6,
+                       kind == 7, kind == 8],
+                      [np.full(n, 30.0), np.full(n, 30.0), np.full(n, 0.1 + 0.2), np.full(n, -1.0),
+                       np.full(n, 30.0), np.full(n, nan), np.full(n, inf), np.full(n, inf), s],
+                      default=1e308)
+    begin[:] = b
+    dur[:] = d
 
 
 def _queries(rng, tables, playlist, level, total_t, adversarial=True):
@@ -200,6 +197,32 @@ def config5(seed=5, n_playlists=1_000_000, n_levels=3, queries_per_playlist=100,
     playlist = np.repeat(np.arange(n_playlists, dtype=np.int64), queries_per_playlist)
     level = q.below(nq, n_levels).astype(np.int64)
     return tables, _queries(q, tables, playlist, level, total_t, adversarial)
+
+
+# BASELINE.json configs[4] at full size, as every script, test and bench leg builds it: 20 chunks of
+# 50 000 playlists, chunk c drawn from seed CONFIG5_SEED0 + c (a chunk is generated on its own, so a
+# shard needs only the chunks its playlist range touches).  Global playlist id = c * 50 000 + local id.
+CONFIG5_CHUNK = 50_000
+CONFIG5_CHUNKS = 20
+CONFIG5_SEED0 = 1000
+CONFIG5_QUERIES_PER_PLAYLIST = 100
+
+
+def config5_chunk(c, n_playlists=CONFIG5_CHUNK):
+    """Chunk c of the full-size configs[4] corpus: (tables, queries) with chunk-local playlist ids."""
+    return config5(seed=CONFIG5_SEED0 + c, n_playlists=n_playlists,
+                   queries_per_playlist=CONFIG5_QUERIES_PER_PLAYLIST)
+
+
+def config5_chunk_fragments_per_playlist(c, n_playlists=CONFIG5_CHUNK, n_levels=3):
+    """Fragments per playlist of chunk c without building its tables (the first two draws of
+    config5's generator): what shard.plan needs to place the shard boundaries."""
+    rng = _stream(CONFIG5_SEED0 + c, 0)
+    nt = n_playlists * n_levels
+    octave = rng.below(nt, 8).astype(np.int64)
+    base = 6 << octave
+    lens = np.minimum(base + (rng.u32(nt).astype(np.int64) % base), 1024)
+    return lens.reshape(n_playlists, n_levels).sum(axis=1)
 
 
 def hls_mock_tables(level_number=3, defined_level=1, live=False):

@@ -3,9 +3,11 @@
 It exists for hosts that may not call cudaMalloc while they run (real-time threads, plugins
 inside a process that owns all device memory).  Its look-back scratch is a fixed array in the
 library image instead of context memory, so this file checks, through the C ABI, that it
-gives bit-for-bit what the regular device-pointer entry point gives -- on two calls in a row,
-because the second call finds the first call's leftovers in that array -- and that a batch
-beyond the array's capacity is refused with a message instead of overrunning it.
+gives bit-for-bit what the regular device-pointer entry point gives AND what the CPU oracle
+gives (a fault common to both launch paths would otherwise pass) -- on two calls in a row,
+because the second call finds the first call's leftovers in that array -- that a batch beyond
+the array's capacity is refused with a message instead of overrunning it, and, where the box
+has a second GPU, that the array is looked up per device.
 
 Named test_zz_* so pytest collects it last: a failure here cannot hide another test's result
 under `-x`.  It makes its own context, so it also passes alone in a fresh process.
@@ -15,6 +17,7 @@ import ctypes
 import numpy as np
 import pytest
 
+import oracle
 import hlsjs_p2p_wrapper_b200 as pk
 from hlsjs_p2p_wrapper_b200 import synth, _native as N
 from hlsjs_p2p_wrapper_b200.tables import FragmentTables, QueryBatch, TRACK_PARSED
@@ -42,6 +45,17 @@ def _same(torch, a, b, hits):
     assert torch.equal(a["off"], b["off"]) and torch.equal(a["st"], b["st"])
     assert torch.equal(a["sn"][:hits], b["sn"][:hits])
     assert torch.equal(a["tm"][:hits].view(torch.int64), b["tm"][:hits].view(torch.int64))  # bit patterns
+
+
+def _same_as_oracle(t, q, o, hits):
+    """The entry point's device output against the CPU restatement of media-map.js:27-54."""
+    off, status, sn, tm = oracle.get_segment_list_batch(t.playlist_base, t.track_off, t.track_state, t.start,
+                                                        t.sn, q.playlist, q.level, q.begin, q.duration)
+    assert int(off[-1]) == hits
+    assert np.array_equal(o["off"].cpu().numpy().astype(np.int64), off)
+    assert np.array_equal(o["st"].cpu().numpy(), status)
+    assert np.array_equal(o["sn"][:hits].cpu().numpy(), sn)
+    assert np.array_equal(o["tm"][:hits].cpu().numpy().view(np.uint64), tm.view(np.uint64))
 
 
 @pytest.mark.parametrize("which", ["search_small_map", "search_window_map", "filter"])
@@ -80,8 +94,36 @@ def test_noalloc_matches_regular_entry_point_twice_in_a_row(which):
                (ref.total_hits, ref.n_unparsed, ref.n_missing, ref.path)
         assert new.total_hits == total and new.kernel_launches == 1
         _same(torch, ref_o, new_o, int(total))
+        _same_as_oracle(t, q, new_o, int(total))
     m.close()
     ctx.close()
+
+
+def test_noalloc_on_a_second_gpu_uses_that_gpus_array():
+    """The fixed scratch array exists once per GPU and its address is looked up per device: a call
+    on cuda:1 after a call on cuda:0 (and back) must use its own copy.  Needs two visible GPUs."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("one GPU visible: the per-device look-up has nothing to tell apart")
+    t, q = synth.config2(seed=36, n_queries=40_003)
+    ctxs = [pk.Context(0), pk.Context(1)]
+    maps = [c.upload(t) for c in ctxs]
+    _, total = maps[0].count_segments(q.playlist, q.level, q.begin, q.duration)
+    cap = int(total) + 3
+    for which in (0, 1, 0, 1):
+        dev = torch.device("cuda", which)
+        with torch.cuda.device(dev):
+            d, out = _device_batch(torch, dev, q, cap)
+            o = out()
+            stream = torch.cuda.Stream(device=dev)
+            torch.cuda.synchronize(dev)
+            res = _run(maps[which].get_segment_list_noalloc_dev, len(q), d, o, cap, stream.cuda_stream)
+            assert res.total_hits == total
+            _same_as_oracle(t, q, o, int(total))
+    for m in maps:
+        m.close()
+    for c in ctxs:
+        c.close()
 
 
 def test_noalloc_refuses_batches_beyond_its_fixed_scratch():
