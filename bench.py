@@ -311,7 +311,8 @@ def list_form_sets(pk, synth, torch, dmap, dev, q0, rank, min_bytes):
 
 def timed_list_form(torch, ctx, dmap, sets, stream, steps, warmup, barrier=None, count_only=False):
     """`steps` back-to-back device-resident list-form batches over rotating buffer sets, CUDA events
-    on the launch stream.  -> (region ms, mean hits per step, host issue us per launch)."""
+    on the launch stream.  -> (region ms, mean hits per step, host issue us per launch, host time
+    of the first launch call in us, (host t0, host t1) of the timed loop)."""
     nq = len(sets[0]["q"])
 
     def launch(s):
@@ -329,17 +330,21 @@ def timed_list_form(torch, ctx, dmap, sets, stream, steps, warmup, barrier=None,
     hits = 0
     h0 = time.perf_counter()
     t_begin.record()
+    first_us = 0.0
     for i in range(steps):
         s = sets[i % len(sets)]
         launch(s)
+        if i == 0:
+            first_us = (time.perf_counter() - h0) * 1e6
         hits += s["hits"]
     t_end.record()
-    issue_us = (time.perf_counter() - h0) / steps * 1e6
+    h1 = time.perf_counter()
+    issue_us = (h1 - h0) / steps * 1e6
     if barrier:
         barrier()
     else:
         torch.cuda.synchronize()
-    return t_begin.elapsed_time(t_end), hits / steps, issue_us
+    return t_begin.elapsed_time(t_end), hits / steps, issue_us, first_us, (h0, time.perf_counter())
 
 
 def path_rows(pk, synth, torch, ctx, dmap, dev, tables, q0, stream, peak, steps, warmup):
@@ -357,7 +362,7 @@ def path_rows(pk, synth, torch, ctx, dmap, dev, tables, q0, stream, peak, steps,
     ql = pk.QueryBatch(big.playlist[sel], big.level[sel], big.begin[sel], big.duration[sel])
     if len(ql) == nq:
         sets, per_step = list_form_sets(pk, synth, torch, dmap, dev, ql, 0, 3 * L2_BYTES)
-        ms, hits, _ = timed_list_form(torch, ctx, dmap, sets, stream, steps, warmup)
+        ms, hits = timed_list_form(torch, ctx, dmap, sets, stream, steps, warmup)[:2]
         alg = 28.0 * nq + 12.0 * hits + table_bytes
         out["list_form_lookahead_mix"] = {
             "queries": nq, "hits_per_query": hits / nq, "ms_per_step": ms / steps,
@@ -674,13 +679,12 @@ def run_ours(args):
     # behind its predecessor's tail, as it would in a serving loop.
     overlap = os.environ.get("HLSMAP_BENCH_NO_OVERLAP") != "1"
     ctx.set_batch_overlap(overlap)
-    w0 = time.perf_counter()
-    my_ms, hits_per_step, issue_us = timed_list_form(torch, ctx, dmap, sets, stream, args.steps, args.warmup,
-                                                     barrier=barrier, count_only=count_only)
-    sampler.window = (w0, time.perf_counter())
+    my_ms, hits_per_step, issue_us, first_us, sampler.window = timed_list_form(
+        torch, ctx, dmap, sets, stream, args.steps, args.warmup, barrier=barrier, count_only=count_only)
     region_ms = max_over_ranks(my_ms)
     per_rank_ms = all_ranks(my_ms / args.steps)
     per_rank_issue_us = all_ranks(issue_us)
+    per_rank_first_us = all_ranks(first_us)
     total_queries = sum_over_ranks(float(nq * args.steps))
     value = total_queries / (region_ms * 1e-3)
     mean_kernel_ms = my_ms / args.steps     # average launch-to-launch time on this rank
@@ -819,6 +823,7 @@ def run_ours(args):
                         "stage_all": info["stage_all"],
                         "per_rank_ms_per_step": per_rank_ms,
                         "host_issue_us_per_launch": per_rank_issue_us,
+                        "host_first_launch_us": per_rank_first_us,
                         "host_issue_note": "time.perf_counter around the timed launch loop / steps, per rank: the "
                                            "Python -> ctypes -> cudaLaunchKernelEx path; the GPU is the limiter "
                                            "while this stays below ms_per_step"},

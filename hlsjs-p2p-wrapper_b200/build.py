@@ -9,7 +9,12 @@ INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 # HLSMAP_TRACE_BUILD=1 in the environment selects a separate diagnostics library whose search
 # kernel records per-tile phase timestamps (scripts/trace_run.py); the product library has none.
 TRACE = os.environ.get("HLSMAP_TRACE_BUILD") == "1"
-LIB = os.path.join(CSRC, "libhlsmap_trace.so" if TRACE else "libhlsmap.so")
+# Experiments: HLSMAP_VARIANT=name (+ HLSMAP_VARIANT_FLAGS="-DX=1 ...") builds and loads
+# csrc/libhlsmap_<name>.so beside the product library, so one GPU session can compare builds.
+VARIANT = os.environ.get("HLSMAP_VARIANT", "")
+VARIANT_FLAGS = os.environ.get("HLSMAP_VARIANT_FLAGS", "").split()
+LIB = os.path.join(CSRC, "libhlsmap_trace.so" if TRACE else
+                   ("libhlsmap_%s.so" % VARIANT if VARIANT else "libhlsmap.so"))
 SOURCES = ["resolve.cu", "views.cu", "ingest.cu", "json.cu", "api.cu"]
 HEADERS = ["common.cuh", "scan.cuh", "decimal.cuh", "dtoa.cuh", "pow10_table.inc"]
 
@@ -38,7 +43,7 @@ def build(force=False, verbose=False):
     """Compile every CUDA source into one shared library; returns its path."""
     if not force and not needs_build():
         return LIB
-    cmd = [_nvcc()] + NVCC_FLAGS + (["-DHLSMAP_TRACE_BUILD=1"] if TRACE else []) + \
+    cmd = [_nvcc()] + NVCC_FLAGS + (["-DHLSMAP_TRACE_BUILD=1"] if TRACE else []) + VARIANT_FLAGS + \
         ["-I", INCLUDE, "-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
     if verbose:
         cmd.insert(1, "-Xptxas")

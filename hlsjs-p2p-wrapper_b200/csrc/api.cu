@@ -90,6 +90,7 @@ struct hlsmap_map {
     size_t stage_smem = 0;
     int grid_search = 0, grid_filter = 0;
     int ipt = 2;                        // queries per thread of the search kernel (tiles of 256 * ipt)
+    bool sn_contig = false;             // every parsed track numbers its fragments contiguously (proven on the GPU)
 };
 
 namespace {
@@ -411,7 +412,7 @@ static int map_create_impl(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *
         CKM(cudaMemcpyAsync(m->d_sn, sn, sizeof(int) * (size_t)nf, cudaMemcpyDefault, s));
     }
     // monotonicity of every start column, proven on the device (hard part 2)
-    CKM(launch_monotone_check(m->d_start, m->d_desc, n_tracks, s));
+    CKM(launch_monotone_check(m->d_start, m->d_sn, m->d_desc, n_tracks, s));
     if (n_tracks)
         CKM(cudaMemcpyAsync(desc.data(), m->d_desc, sizeof(TrackDesc) * (size_t)n_tracks,
                             cudaMemcpyDeviceToHost, s));
@@ -422,11 +423,13 @@ static int map_create_impl(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *
     m->h_len.resize(n_tracks);
     for (int32_t t = 0; t < n_tracks; t++) m->h_len[t] = (int32_t)(track_offset[t + 1] - track_offset[t]);
     m->h_cap = m->h_len;
-    int mono = 0;
+    int mono = 0, contig = 0;
     for (int32_t t = 0; t < n_tracks; t++) {
         m->h_monotone[t] = (desc[t].flags & kTrackMonotone) ? 1 : 0;
         mono += m->h_monotone[t];
+        contig += (desc[t].flags & kTrackSnContig) ? 1 : 0;
     }
+    m->sn_contig = contig == parsed;
     m->info.n_playlists = n_playlists;
     m->info.n_tracks = n_tracks;
     m->info.n_fragments = nf;
@@ -619,14 +622,16 @@ int hlsmap_map_slide_tracks(hlsmap_map *map, int64_t n, const int32_t *playlist,
     CK(cudaMemcpyAsync(desc.data(), map->d_desc, sizeof(TrackDesc) * (size_t)map->n_tracks,
                        cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
-    int mono = 0;
+    int mono = 0, contig = 0;
     int64_t nf = 0;
     for (int32_t t = 0; t < map->n_tracks; t++) {
         map->h_len[t] = desc[t].len;
         map->h_monotone[t] = (desc[t].flags & kTrackMonotone) ? 1 : 0;
         mono += map->h_monotone[t];
+        contig += (desc[t].flags & kTrackSnContig) ? 1 : 0;
         nf += desc[t].len;
     }
+    map->sn_contig = contig == map->info.n_parsed_tracks;
     map->info.n_fragments = nf;
     map->info.n_monotone_tracks = mono;
     map->info.all_monotone = (mono == map->info.n_parsed_tracks) ? 1 : 0;
@@ -707,6 +712,7 @@ static int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
     p.stage_elems = map->stage_elems;
     p.stage_all = map->info.stage_all;
     p.small = map->info.stage_all;
+    p.sn_contig = (map->sn_contig && !map->info.stage_all) ? 1 : 0;
     p.ipt = ipt;
     p.hint = map->d_hint;
     p.grid = map->d_grid;
@@ -1545,6 +1551,7 @@ int hlsmap_get_segment_list_noalloc_dev(hlsmap_map *map, int64_t nq, const int32
         p.stage_elems = map->stage_elems;
         p.stage_all = map->info.stage_all;
         p.small = map->info.stage_all;
+        p.sn_contig = (map->sn_contig && !map->info.stage_all) ? 1 : 0;
         p.ipt = map->ipt;
         p.hint = map->d_hint;
         p.grid = map->d_grid;

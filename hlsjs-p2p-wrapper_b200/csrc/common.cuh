@@ -25,6 +25,7 @@ struct __align__(16) TrackHint {
 };
 constexpr unsigned kTrackStateMask = 3u;
 constexpr unsigned kTrackMonotone = 4u;
+constexpr unsigned kTrackSnContig = 8u;   // bit 3: sn[i] == sn[0] + i for the whole track (proven at upload)
 
 // Per-context scratch header for the single-pass scan kernels.  A context owns TWO scratch
 // sets (header + status words + result) used by alternate launches (set = epoch & 1), so that
@@ -78,6 +79,7 @@ struct ResolveParams {
     int n_tracks_padded;          // SMALL: descriptors staged in shared memory (>= 1)
     int n_base_padded;            // SMALL: playlist_base ints staged (multiple of 4)
     int small;                    // whole map staged in shared memory + hint grid
+    int sn_contig;                // every parsed track's sn column is contiguous (general kernel computes sn)
     int ipt;                      // queries per thread of the SMALL kernel (2 or 4)
     // queries
     long long nq;
@@ -219,7 +221,7 @@ cudaError_t launch_range(const RangeParams &p, cudaStream_t s);
 cudaError_t launch_range_small(const RangeParams &p, const TrackHint *hint, const unsigned short *grid,
                                long long n_frag_padded, int grid_padded, int n_tracks_padded,
                                int n_base_padded, int vec_ok, cudaStream_t s);
-cudaError_t launch_monotone_check(const double *start, TrackDesc *desc, int n_tracks,
+cudaError_t launch_monotone_check(const double *start, const int *sn, TrackDesc *desc, int n_tracks,
                                   cudaStream_t s);
 cudaError_t launch_segment_duration(const TrackDesc *desc, const int *playlist_base,
                                     int n_playlists, const double *dur0, long long n,

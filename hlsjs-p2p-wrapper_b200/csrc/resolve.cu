@@ -54,16 +54,23 @@ template <int TILE>
 struct RecTable<true, TILE> {   // every fragment index fits an int
     unsigned v[TILE];
     static constexpr int kShift = 2;
-    __device__ __forceinline__ void set(int i, int rel, long long src, unsigned sn_addr)
+    __device__ __forceinline__ void set(int i, int rel, long long src, unsigned sn_addr, int = 0)
     {
         v[i] = sn_addr + 4u * (unsigned)((int)src - rel);
     }
 };
 template <int TILE>
 struct RecTable<false, TILE> {
+    // v = first kept fragment - first slot; sb = sn of the first kept fragment - first slot, for
+    // tracks whose sn column is proven contiguous: slot q's sn is then sb + q
     long long v[TILE];
+    int sb[TILE];
     static constexpr int kShift = 3;
-    __device__ __forceinline__ void set(int i, int rel, long long src, unsigned) { v[i] = src - rel; }
+    __device__ __forceinline__ void set(int i, int rel, long long src, unsigned, int sn_first = 0)
+    {
+        v[i] = src - rel;
+        sb[i] = sn_first - rel;
+    }
 };
 
 // Shared state of one CTA.
@@ -418,10 +425,14 @@ __device__ __forceinline__ void small_bounds(const double *s_start, const unsign
 //  to publish before A asks for them, so the look-back practically never waits, and B's
 //  aggregate is visible to later tiles before A's long emission starts.
 // =========================================================================================
-template <bool SMALL, int IPT>
+// SNC (general kernel only): every parsed track's sn column is proven contiguous (sn[i] = sn[0] + i,
+// established on the GPU at upload), so a hit's sn is computed from its query's first hit instead of
+// being gathered: one L2 read per query with hits in place of one per hit, and sn[] is not streamed.
+template <bool SMALL, int IPT, bool SNC>
 __global__ void __launch_bounds__(kThreads, (SMALL && IPT == 2) ? 4 : ((SMALL || IPT == 2) ? 3 : 2))
 resolve_search_kernel(const ResolveParams p)
 {
+    static_assert(!(SMALL && SNC), "the shared-memory-resident kernel gathers sn from shared memory");
     using S = Shape<IPT>;
     constexpr int kClaimSlots = 8 * kThreads;   // the next ticket is drawn this many output slots before the tile's last
     constexpr int kIpt = S::kIpt, kWindow = S::kWindow, kWords = S::kWords;
@@ -491,9 +502,10 @@ resolve_search_kernel(const ResolveParams p)
     int a_cnt[kIpt];
     using SrcT = typename std::conditional<SMALL, int, long long>::type;
     SrcT a_src[kIpt];
+    int a_snf[kIpt];                 // SNC: sn of each query's first kept fragment
     int a_rank = 0;
 #pragma unroll
-    for (int k = 0; k < kIpt; k++) { a_cnt[k] = 0; a_src[k] = 0; }
+    for (int k = 0; k < kIpt; k++) { a_cnt[k] = 0; a_src[k] = 0; a_snf[k] = 0; }
 
     bool ticket_pending = false;         // thread 0: a ticket was requested for the next tile
     for (;;) {
@@ -505,15 +517,100 @@ resolve_search_kernel(const ResolveParams p)
         unsigned long long pre[1] = {0ull};
         if (tileA > 0 && !haveB && warp == 0) pre[0] = ld_relaxed_u64(&p.tile_status[max(tileA - 1 - lane, 0)]);
 
+        // ---- tile A's look-back, by warp 0 alone, 32 predecessors per step, no CTA barrier.  (Run
+        //      earlier, while tile B's window is landing in the general kernel, it measured the same.)
+        auto lookback = [&]() {
+            if (warp == 0) {
+#if HLSMAP_TRACE_BUILD
+                int diag = 0;
+                const unsigned long long b = Scan::warp_prefix(p.tile_status, p.epoch, tileA, a_cnt_tile, pre[0], p.base, &diag);
+                if (p.trace != nullptr && lane == 0) p.trace[(long long)tileA * 16 + 7] = (unsigned long long)diag;
+#else
+                const unsigned long long b = Scan::warp_prefix(p.tile_status, p.epoch, tileA, a_cnt_tile, pre[0], p.base);
+#endif
+                if (lane == 0) sm.tile_base = b;
+                if (SMALL) trace_mark_after(p, tileA, 14, (int)b);
+            }
+        };
+        unsigned long long tile_base = 0;
+        const bool expand = tileA >= 0 && p.sn_out != nullptr && a_cnt_tile > 0 && a_cnt_tile <= 0x7fffffffull;
+        constexpr int kRecShift = RecTable<SMALL, S::kTile>::kShift;
+        const unsigned sn_addr = SMALL ? smem_u32(s_sn) : 0u;
+        // start address of slot q = 2 * (sn address of slot q) + start_bias
+        const unsigned start_bias = SMALL ? smem_u32(s_start) - 2u * sn_addr : 0u;
+        // mark where this thread's records start inside the window [w0, w0 + kWindow)
+        auto mark_heads = [&](uint2 *H, int w0) {
+            int r2 = (int)a_rel;
+#pragma unroll
+            for (int k = 0; k < kIpt; k++) {
+                if (a_cnt[k] > 0) {
+                    const unsigned d = (unsigned)(r2 - w0);
+                    if (d < (unsigned)kWindow) atomicOr(&H[d >> 5].x, 1u << (d & 31));
+                    r2 += a_cnt[k];
+                }
+            }
+        };
+        // ---- tile A, before its hits can be written: expansion records and the first window's head
+        //      marks (no prefix needed: the other warps lay them down while warp 0 looks back), one
+        //      barrier that hands out both, offsets[]
+        auto emit_prep = [&]() {
+            const long long q0 = (long long)tileA * p.tile_q + tid * kIpt;
+            const long long q_end = min(p.nq, (long long)(tileA + 1) * p.tile_q);
+            const bool full = p.vec_ok && q0 + kIpt <= q_end;
+            trace_mark(p, tileA, 3);
+            lookback();
+            if (expand) {   // records: one per query that kept >= 1 fragment, in query order
+                int rank = a_rank, rel = (int)a_rel;
+#pragma unroll
+                for (int k = 0; k < kIpt; k++) {
+                    if (a_cnt[k] > 0) {
+                        sm.rec.set(rank, rel, a_src[k], sn_addr, a_snf[k]);
+                        rank++;
+                        rel += a_cnt[k];
+                    }
+                }
+                mark_heads(sm.hb[hbuf], 0);
+            }
+            __syncthreads();
+            tile_base = sm.tile_base;
+            trace_mark(p, tileA, 4);
+
+            // ---- offsets[q] --------------------------------------------------------------
+            {
+                unsigned long long run = tile_base + a_rel;
+                int o[kIpt];
+#pragma unroll
+                for (int k = 0; k < kIpt; k++) {
+                    o[k] = (int)run;
+                    run += (unsigned long long)a_cnt[k];
+                }
+                if (full && kIpt == 4) {
+                    __stcs(reinterpret_cast<int4 *>(p.offsets + q0), make_int4(o[0], o[1], o[2], o[kIpt - 1]));
+                } else if (full && kIpt == 2) {
+                    __stcs(reinterpret_cast<int2 *>(p.offsets + q0), make_int2(o[0], o[1]));
+                } else {
+#pragma unroll
+                    for (int k = 0; k < kIpt; k++)
+                        if (q0 + k < q_end) p.offsets[q0 + k] = o[k];
+                }
+            }
+            if (tileA == p.n_tiles - 1 && tid == kThreads - 1) {
+                const unsigned long long total_hits = tile_base + a_cnt_tile;
+                p.offsets[p.nq] = (int)total_hits;
+                p.result->total_hits = (long long)total_hits;
+                p.result->overflow = total_hits > 0x7fffffffull ? 1 : 0;
+            }
+        };
+
         // =====================================================================================
         //  SEARCH tile B
         // =====================================================================================
         long long off[kIpt];
-        int lo[kIpt], cnt[kIpt];
+        int lo[kIpt], cnt[kIpt], snf[kIpt];
         unsigned long long b_rel = 0, b_cnt_tile = 0;
         int b_rank = 0;
 #pragma unroll
-        for (int k = 0; k < kIpt; k++) { off[k] = 0; lo[k] = 0; cnt[k] = 0; }
+        for (int k = 0; k < kIpt; k++) { off[k] = 0; lo[k] = 0; cnt[k] = 0; snf[k] = 0; }
 
         if (haveB) {
             // a tile holds p.tile_q <= 256*kIpt queries; threads past its end idle through the search
@@ -710,6 +807,10 @@ resolve_search_kernel(const ResolveParams p)
             }
 
             trace_mark_after(p, tileB, 1, cnt[0] ^ cnt[kIpt - 1]);
+            if (SNC) {       // consumed one iteration later, when this tile is emitted
+#pragma unroll
+                for (int k = 0; k < kIpt; k++) snf[k] = cnt[k] > 0 ? __ldg(p.sn + off[k] + lo[k]) : 0;
+            }
             if (tileA > 0 && warp == 0) pre[0] = ld_relaxed_u64(&p.tile_status[max(tileA - 1 - lane, 0)]);
             // ---- fused scan of (hit count, non-empty flag): thread -> warp -> CTA ---------
             unsigned long long tval = 0;
@@ -753,82 +854,7 @@ resolve_search_kernel(const ResolveParams p)
         //  EMIT tile A (searched one iteration ago): look-back, offsets, hits
         // =====================================================================================
         if (tileA >= 0) {
-            const long long q0 = (long long)tileA * p.tile_q + tid * kIpt;
-            const long long q_end = min(p.nq, (long long)(tileA + 1) * p.tile_q);
-            const bool full = p.vec_ok && q0 + kIpt <= q_end;
-            trace_mark(p, tileA, 3);
-            // ---- look-back by warp 0 alone, 32 predecessors per step, no CTA barrier; the other
-            //      warps meanwhile lay down the expansion records and the first window's head marks,
-            //      which need no prefix.  One barrier then hands out both.
-            if (warp == 0) {
-#if HLSMAP_TRACE_BUILD
-                int diag = 0;
-                const unsigned long long b = Scan::warp_prefix(p.tile_status, p.epoch, tileA, a_cnt_tile, pre[0], p.base, &diag);
-                if (p.trace != nullptr && lane == 0) p.trace[(long long)tileA * 16 + 7] = (unsigned long long)diag;
-#else
-                const unsigned long long b = Scan::warp_prefix(p.tile_status, p.epoch, tileA, a_cnt_tile, pre[0], p.base);
-#endif
-                if (lane == 0) sm.tile_base = b;
-                if (SMALL) trace_mark_after(p, tileA, 14, (int)b);
-            }
-            const bool expand = p.sn_out != nullptr && a_cnt_tile > 0 && a_cnt_tile <= 0x7fffffffull;
-            constexpr int kRecShift = RecTable<SMALL, S::kTile>::kShift;
-            const unsigned sn_addr = SMALL ? smem_u32(s_sn) : 0u;
-            // start address of slot q = 2 * (sn address of slot q) + start_bias
-            const unsigned start_bias = SMALL ? smem_u32(s_start) - 2u * sn_addr : 0u;
-            // mark where this thread's records start inside the window [w0, w0 + kWindow)
-            auto mark_heads = [&](uint2 *H, int w0) {
-                int r2 = (int)a_rel;
-#pragma unroll
-                for (int k = 0; k < kIpt; k++) {
-                    if (a_cnt[k] > 0) {
-                        const unsigned d = (unsigned)(r2 - w0);
-                        if (d < (unsigned)kWindow) atomicOr(&H[d >> 5].x, 1u << (d & 31));
-                        r2 += a_cnt[k];
-                    }
-                }
-            };
-            if (expand) {   // records: one per query that kept >= 1 fragment, in query order
-                int rank = a_rank, rel = (int)a_rel;
-#pragma unroll
-                for (int k = 0; k < kIpt; k++) {
-                    if (a_cnt[k] > 0) {
-                        sm.rec.set(rank, rel, a_src[k], sn_addr);
-                        rank++;
-                        rel += a_cnt[k];
-                    }
-                }
-                mark_heads(sm.hb[hbuf], 0);
-            }
-            __syncthreads();
-            const unsigned long long tile_base = sm.tile_base;
-            trace_mark(p, tileA, 4);
-
-            // ---- offsets[q] --------------------------------------------------------------
-            {
-                unsigned long long run = tile_base + a_rel;
-                int o[kIpt];
-#pragma unroll
-                for (int k = 0; k < kIpt; k++) {
-                    o[k] = (int)run;
-                    run += (unsigned long long)a_cnt[k];
-                }
-                if (full && kIpt == 4) {
-                    __stcs(reinterpret_cast<int4 *>(p.offsets + q0), make_int4(o[0], o[1], o[2], o[kIpt - 1]));
-                } else if (full && kIpt == 2) {
-                    __stcs(reinterpret_cast<int2 *>(p.offsets + q0), make_int2(o[0], o[1]));
-                } else {
-#pragma unroll
-                    for (int k = 0; k < kIpt; k++)
-                        if (q0 + k < q_end) p.offsets[q0 + k] = o[k];
-                }
-            }
-            if (tileA == p.n_tiles - 1 && tid == kThreads - 1) {
-                const unsigned long long total_hits = tile_base + a_cnt_tile;
-                p.offsets[p.nq] = (int)total_hits;
-                p.result->total_hits = (long long)total_hits;
-                p.result->overflow = total_hits > 0x7fffffffull ? 1 : 0;
-            }
+            emit_prep();
 
             // ---- expansion: the tile's hits form ONE contiguous output run; the whole CTA
             //      writes it 256 slots at a time whatever the per-query counts (load balanced)
@@ -836,6 +862,8 @@ resolve_search_kernel(const ResolveParams p)
                 const int total = (int)a_cnt_tile;
                 // shared-memory address of the record BEFORE the first one (ranks count from 1 below)
                 const unsigned rec_addr = smem_u32(&sm.rec.v[0]) - (1u << kRecShift);
+                unsigned sb_bias = 0;       // general kernel: address of sb[r] = ((address of v[r]) >> 1) + sb_bias
+                if constexpr (!SMALL) sb_bias = smem_u32(&sm.rec.sb[0]) - (smem_u32(&sm.rec.v[0]) >> 1);
                 int carried = 0;            // records that start before the current window
                 const bool all_fit = (long long)tile_base + total <= p.capacity;   // CTA-uniform
                 for (int w0 = 0; w0 < total; w0 += kWindow) {
@@ -874,8 +902,11 @@ resolve_search_kernel(const ResolveParams p)
                     // before this lane's slot name the record; its source fragment follows by offset.
                     unsigned slot4 = 4u * (unsigned)(w0 + tid);            // SMALL: 4 * slot
                     long long slotl = (long long)(w0 + tid);               // general: slot
-                    auto body = [&](auto J4) {      // 4 slots, kThreads apart
-                        constexpr int J = decltype(J4)::value;          // 4 or 1 slots
+                    // slots per thread and round (8 for the general kernel, whose gathers come from L2,
+                    // measured slower: 0.297 ms against 0.289 on a configs[4] chunk)
+                    constexpr int kRound = 4;
+                    auto body = [&](auto JJ) {      // J slots, kThreads apart
+                        constexpr int J = decltype(JJ)::value;          // kRound or 1 slots
                         double t[J];
                         int sv[J];
                         uint2 hw[J];
@@ -902,13 +933,15 @@ resolve_search_kernel(const ResolveParams p)
                         } else {
 #pragma unroll
                             for (int j = 0; j < J; j++) {
-                                const long long src =
-                                    lds_s64<0>(hw[j].y + 8u * (unsigned)__popc(hw[j].x & lane_le)) + slotl + j * kThreads;
+                                const unsigned ra = hw[j].y + 8u * (unsigned)__popc(hw[j].x & lane_le);
+                                const long long src = lds_s64<0>(ra) + slotl + j * kThreads;
                                 t[j] = __ldg(p.start + src);      // L2-hot: the span was just bulk-copied
-                                sv[j] = __ldg(p.sn + src);
+                                // sb[] lies behind v[]: entry r of v at rec_addr + 8 r  <=>  entry r of sb at sb_bias + (that >> 1)
+                                sv[j] = SNC ? (int)lds_u32<0>((ra >> 1) + sb_bias) + (int)slotl + j * kThreads
+                                            : __ldg(p.sn + src);
                             }
                         }
-                        if (J == 4 || (long long)tile_base + w0 + (long long)(slotl - w0) < p.capacity) {
+                        if (J > 1 || (long long)tile_base + w0 + (long long)(slotl - w0) < p.capacity) {
 #pragma unroll
                             for (int j = 0; j < J; j++) {
                                 __stcs(tp + j * kThreads, t[j]);   // time = fragment.start (:48)
@@ -921,25 +954,25 @@ resolve_search_kernel(const ResolveParams p)
                         slot4 += 4u * J * kThreads;
                         slotl += J * kThreads;
                     };
-                    // full rounds of 4 * kThreads slots: the trip count is the same for every thread
-                    const int n_full = all_fit ? wend / (4 * kThreads) : 0;
+                    // full rounds of kRound * kThreads slots: the trip count is the same for every thread
+                    const int n_full = all_fit ? wend / (kRound * kThreads) : 0;
                     // Claim the next tile as late as possible -- a claimed but unsearched tile stalls
                     // the look-back of every later tile -- yet early enough for the atomic's round
                     // trip to hide behind the slots still to write: kClaimSlots before the tile's last.
                     const bool claim_here = haveB && w0 + kWindow >= total;
-                    const int n_first = claim_here ? min(n_full, max(0, (wend - kClaimSlots + 4 * kThreads - 1) / (4 * kThreads)))
+                    const int n_first = claim_here ? min(n_full, max(0, (wend - kClaimSlots + kRound * kThreads - 1) / (kRound * kThreads)))
                                                    : n_full;
                     int it = 0;
 #pragma unroll 1
-                    for (; it < n_first; it++) body(std::integral_constant<int, 4>{});
+                    for (; it < n_first; it++) body(std::integral_constant<int, kRound>{});
                     if (claim_here && tid == 0 && !ticket_pending) {
                         t_new = atomicAdd(&p.ctr->ticket[p.tslot & 1u], 1u);
                         ticket_pending = true;
                     }
 #pragma unroll 1
-                    for (; it < n_full; it++) body(std::integral_constant<int, 4>{});
+                    for (; it < n_full; it++) body(std::integral_constant<int, kRound>{});
                     if (w0 == 0) trace_mark(p, tileA, 10);
-                    for (int q = n_full * 4 * kThreads + tid; q < wend; q += kThreads)
+                    for (int q = n_full * kRound * kThreads + tid; q < wend; q += kThreads)
                         body(std::integral_constant<int, 1>{});
                     if (w0 == 0) trace_mark(p, tileA, 11);
                     __syncthreads();
@@ -971,6 +1004,7 @@ resolve_search_kernel(const ResolveParams p)
         for (int k = 0; k < kIpt; k++) {
             a_cnt[k] = cnt[k];
             a_src[k] = (SrcT)(off[k] + lo[k]);
+            a_snf[k] = snf[k];
         }
         tileB = sm.tile_slot[slot];
     }
@@ -1307,22 +1341,28 @@ range_small_kernel(const RangeParams p, const TrackHint *hint, const unsigned sh
 // =========================================================================================
 //  upload-time monotonicity proof: one warp per track
 // =========================================================================================
+// Also proves, per track, that the sn column is contiguous: sn[i] == sn[0] + i in 32-bit wrap-around
+// arithmetic (what hls.js numbers from #EXT-X-MEDIA-SEQUENCE always is); the search kernel then
+// computes a hit's sn instead of reading it, bit for bit the value stored in the table.
 __global__ void __launch_bounds__(256)
-monotone_check_kernel(const double *__restrict__ start, TrackDesc *desc, int n_tracks)
+monotone_check_kernel(const double *__restrict__ start, const int *__restrict__ sn, TrackDesc *desc, int n_tracks)
 {
     const int lane = threadIdx.x & 31;
     const int wpb = blockDim.x >> 5;
     for (int t = blockIdx.x * wpb + (threadIdx.x >> 5); t < n_tracks; t += gridDim.x * wpb) {
         TrackDesc d = desc[t];
         if ((d.flags & kTrackStateMask) != HLSMAP_TRACK_PARSED) continue;
-        bool bad = false;
+        bool bad = false, gap = false;
+        const unsigned sn0 = d.len > 0 ? (unsigned)sn[d.off] : 0u;
         for (int i = lane; i < d.len; i += 32) {
             const double s = start[d.off + i];
             bad |= (s != s);
             if (i > 0) bad |= (s < start[d.off + i - 1]);
+            gap |= (unsigned)sn[d.off + i] != sn0 + (unsigned)i;
         }
         const unsigned any_bad = __ballot_sync(0xffffffffu, bad);
-        if (lane == 0 && !any_bad) desc[t].flags = d.flags | kTrackMonotone;
+        const unsigned any_gap = __ballot_sync(0xffffffffu, gap);
+        if (lane == 0) desc[t].flags = d.flags | (any_bad ? 0u : kTrackMonotone) | (any_gap ? 0u : kTrackSnContig);
     }
 }
 
@@ -1368,17 +1408,22 @@ slide_tracks_kernel(double *start, int *sn, double *dur0, TrackDesc *desc, long 
         }
         __syncwarp();
         const int len = keep + add;
-        // re-prove monotonicity of the whole column (the search kernel relies on the flag)
-        bool bad = false;
+        // re-prove monotonicity of the whole column and the contiguity of its sn (the search kernel
+        // relies on both flags)
+        bool bad = false, gap = false;
+        const unsigned sn0 = len > 0 ? (unsigned)sn[d.off] : 0u;
         for (int i = lane; i < len; i += 32) {
             const double s = start[d.off + i];
             bad |= (s != s);
             if (i > 0) bad |= (s < start[d.off + i - 1]);
+            gap |= (unsigned)sn[d.off + i] != sn0 + (unsigned)i;
         }
         const unsigned any_bad = __ballot_sync(0xffffffffu, bad);
+        const unsigned any_gap = __ballot_sync(0xffffffffu, gap);
         if (lane == 0) {
-            unsigned fl = d.flags & ~kTrackMonotone;
+            unsigned fl = d.flags & ~(kTrackMonotone | kTrackSnContig);
             if ((fl & kTrackStateMask) == HLSMAP_TRACK_PARSED && !any_bad) fl |= kTrackMonotone;
+            if ((fl & kTrackStateMask) == HLSMAP_TRACK_PARSED && !any_gap) fl |= kTrackSnContig;
             desc[t].len = len;
             desc[t].flags = fl;
             if (new_dur0) dur0[t] = new_dur0[e];
@@ -1500,22 +1545,24 @@ static int sm_count()
     return g_sm_count;
 }
 
-template <bool SMALL, int IPT>
+template <bool SMALL, int IPT, bool SNC>
 static int max_grid_of(size_t smem)
 {
     int per_sm = 0;
-    cudaFuncSetAttribute(resolve_search_kernel<SMALL, IPT>,
+    cudaFuncSetAttribute(resolve_search_kernel<SMALL, IPT, SNC>,
                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resolve_search_kernel<SMALL, IPT>,
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resolve_search_kernel<SMALL, IPT, SNC>,
                                                       kThreads, smem) != cudaSuccess || per_sm < 1)
         per_sm = 1;
     return per_sm * sm_count();
 }
 
+// (both sn variants of the general kernel get their shared-memory opt-in here; their occupancy is the same)
 int resolve_search_max_grid(size_t smem, bool small, int ipt)
 {
-    if (small) return ipt == 2 ? max_grid_of<true, 2>(smem) : max_grid_of<true, 4>(smem);
-    return ipt == 2 ? max_grid_of<false, 2>(smem) : max_grid_of<false, 4>(smem);
+    if (small) return ipt == 2 ? max_grid_of<true, 2, false>(smem) : max_grid_of<true, 4, false>(smem);
+    if (ipt == 2) return min(max_grid_of<false, 2, false>(smem), max_grid_of<false, 2, true>(smem));
+    return min(max_grid_of<false, 4, false>(smem), max_grid_of<false, 4, true>(smem));
 }
 
 int resolve_search_tile(bool small, int ipt) { (void)small; return kThreads * (ipt == 2 ? 2 : 4); }
@@ -1529,7 +1576,7 @@ int resolve_filter_max_grid()
     return per_sm * sm_count();
 }
 
-template <bool SMALL, int IPT>
+template <bool SMALL, int IPT, bool SNC>
 static cudaError_t launch_search_variant(const ResolveParams &p, int grid, size_t smem,
                                          cudaStream_t s, bool overlap_next)
 {
@@ -1543,7 +1590,7 @@ static cudaError_t launch_search_variant(const ResolveParams &p, int grid, size_
     attr[0].val.programmaticStreamSerializationAllowed = overlap_next ? 1 : 0;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, resolve_search_kernel<SMALL, IPT>, p);
+    return cudaLaunchKernelEx(&cfg, resolve_search_kernel<SMALL, IPT, SNC>, p);
 }
 
 // overlap_next: this batch may begin while the previous kernel on the stream is draining.
@@ -1551,10 +1598,12 @@ cudaError_t launch_resolve_search(const ResolveParams &p, int grid, size_t smem,
                                   bool overlap_next)
 {
     cudaError_t e;
-    if (p.small && p.ipt == 2) e = launch_search_variant<true, 2>(p, grid, smem, s, overlap_next);
-    else if (p.small) e = launch_search_variant<true, 4>(p, grid, smem, s, overlap_next);
-    else if (p.ipt == 2) e = launch_search_variant<false, 2>(p, grid, smem, s, overlap_next);
-    else e = launch_search_variant<false, 4>(p, grid, smem, s, overlap_next);
+    if (p.small && p.ipt == 2) e = launch_search_variant<true, 2, false>(p, grid, smem, s, overlap_next);
+    else if (p.small) e = launch_search_variant<true, 4, false>(p, grid, smem, s, overlap_next);
+    else if (p.ipt == 2 && p.sn_contig) e = launch_search_variant<false, 2, true>(p, grid, smem, s, overlap_next);
+    else if (p.ipt == 2) e = launch_search_variant<false, 2, false>(p, grid, smem, s, overlap_next);
+    else if (p.sn_contig) e = launch_search_variant<false, 4, true>(p, grid, smem, s, overlap_next);
+    else e = launch_search_variant<false, 4, false>(p, grid, smem, s, overlap_next);
     return e != cudaSuccess ? e : cudaGetLastError();
 }
 
@@ -1608,14 +1657,14 @@ cudaError_t launch_range(const RangeParams &p, cudaStream_t s)
     return cudaGetLastError();
 }
 
-cudaError_t launch_monotone_check(const double *start, TrackDesc *desc, int n_tracks,
+cudaError_t launch_monotone_check(const double *start, const int *sn, TrackDesc *desc, int n_tracks,
                                   cudaStream_t s)
 {
     if (n_tracks <= 0) return cudaSuccess;
     long long blocks = ((long long)n_tracks + 7) / 8;
     const long long cap = (long long)sm_count() * 8;
     if (blocks > cap) blocks = cap;
-    monotone_check_kernel<<<(int)blocks, 256, 0, s>>>(start, desc, n_tracks);
+    monotone_check_kernel<<<(int)blocks, 256, 0, s>>>(start, sn, desc, n_tracks);
     return cudaGetLastError();
 }
 
