@@ -571,6 +571,19 @@ int hlsmap_map_slide_tracks(hlsmap_map *map, int64_t n, const int32_t *playlist,
     if (n < 0 || (n > 0 && (!level || !drop || !append_offset)))
         return fail(HLSMAP_ERR_INVALID, "slide_tracks: null arrays");
     if (n == 0) return HLSMAP_OK;
+    if (!new_dur0) {
+        // the duration getSegmentDuration returns is the FIRST fragment's (media-map.js:81-87): evicting
+        // at the front, or filling an empty track, changes it, and the reference would read the new one
+        for (int64_t i = 0; i < n; i++) {
+            const int32_t p = playlist ? playlist[i] : 0;
+            const bool known = p >= 0 && p < map->n_playlists && level[i] >= 0 &&
+                               level[i] < map->h_playlist_base[p + 1] - map->h_playlist_base[p];
+            const bool empty = known && map->h_len[map->h_playlist_base[p] + level[i]] == 0;
+            if (drop[i] > 0 || (empty && append_offset[i + 1] > append_offset[i]))
+                return fail(HLSMAP_ERR_INVALID, "slide_tracks: new_dur0 is required when a track's first fragment changes "
+                                                "(drop > 0, or fragments appended to an empty track)");
+        }
+    }
     const int64_t n_new = append_offset[n] - append_offset[0];
     if (append_offset[0] != 0 || n_new < 0 || (n_new > 0 && (!new_start || !new_sn)))
         return fail(HLSMAP_ERR_INVALID, "slide_tracks: bad append_offset / null fragment arrays");
@@ -1890,8 +1903,9 @@ int ingest_core(hlsmap_ctx *ctx, int32_t n_tracks, const uint8_t *d_state, const
     if (h.n_unsupported)
         return fail(HLSMAP_ERR_UNSUPPORTED,
                     "parse_m3u8: " + std::to_string(h.n_unsupported) +
-                        " number(s) outside what the parser converts exactly (more than 19 significant "
-                        "digits with an undecidable tail, or a sequence number beyond int32)");
+                        " item(s) the parser refuses rather than guesses: a number it cannot convert exactly "
+                        "(more than 19 significant digits with an undecidable tail, a sequence number beyond "
+                        "int32), or a tag more than 16384 bytes into its line");
     if (fill && (int64_t)h.n_fragments > capacity)
         return fail(HLSMAP_ERR_CAPACITY, "fragment buffers too small: need " + std::to_string(h.n_fragments) + " entries");
     return HLSMAP_OK;

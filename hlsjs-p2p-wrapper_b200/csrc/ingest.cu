@@ -240,11 +240,24 @@ __device__ __forceinline__ bool classify_fast(const unsigned char *stext, int po
 
 // A '#' in the middle of a line is a match only if nothing before it on the line swallowed it:
 // replay the line from its first byte (global memory; this is the rare path).
+// A line is replayed once per '#' inside it by ONE thread, so the work is quadratic in the line's
+// length: playlist text comes from the network, and one multi-megabyte line packed with tags could
+// stall the kernel for seconds.  No real playlist has lines anywhere near kMaxReplayLine bytes (a
+// segment URI or a key URI is a few hundred); a '#' further than that from its line start is refused
+// (`too_long`, counted in n_unsupported -> HLSMAP_ERR_UNSUPPORTED), never guessed.
+constexpr long long kMaxReplayLine = 16384;
 __device__ __noinline__ bool hidden_by_earlier_match(const unsigned char *text, long long track_lo, long long p,
-                                        long long lim)
+                                        long long lim, bool &too_long)
 {
     long long b = p;
-    while (b > track_lo && text[b - 1] != '\n' && text[b - 1] != '\r') b--;
+    too_long = false;
+    while (b > track_lo && text[b - 1] != '\n' && text[b - 1] != '\r') {
+        b--;
+        if (p - b > kMaxReplayLine) {
+            too_long = true;
+            return true;
+        }
+    }
     TextView v{text, text, 0, 0};
     long long q = b;
     while (q < p) {
@@ -338,7 +351,11 @@ __device__ __forceinline__ int classify_candidate(const IngestParams &p, const S
         bool live = t.kind != kTokNone;
         if (live && pos > tb) {
             const int prev = v(pos - 1);
-            if (prev != '\n' && prev != '\r') live = !hidden_by_earlier_match(p.text, tb, pos, te);
+            if (prev != '\n' && prev != '\r') {
+                bool too_long;
+                live = !hidden_by_earlier_match(p.text, tb, pos, te, too_long);
+                if (too_long && effects) atomicAdd(&p.out->n_unsupported, 1ull);
+            }
         }
         if (live) {
             kind = t.kind;

@@ -187,15 +187,20 @@ def default_context(device=0):
 
 
 class MediaMap:
-    """`new MediaMap(hls)` (media-map.js:6-8).  `hls.levels` is re-read on every call like
-    the reference does (:28,41); its tables are re-uploaded to HBM only when a cheap
-    signature of the level list changes."""
+    """`new MediaMap(hls)` (media-map.js:6-8).  `hls.levels` is re-read on every call like the
+    reference does (:28,41): every call compares the level list -- every fragment's sn and start,
+    every level's url count and first duration -- with what is resident in HBM.  A window that slid
+    (fragments evicted at the front, appended at the back, the rest untouched) is slid in place on
+    the GPU (`slide_tracks`); any other change re-uploads the tables."""
 
     def __init__(self, hls, context=None):
         self.hls = hls
         self._ctx = context
         self._map = None
         self._sig = None
+        self._host = None          # FragmentTables resident on the GPU
+        self._cap = None           # fragments reserved per track at upload (a slide cannot outgrow it)
+        self.refreshes = {"upload": 0, "slide": 0}
 
     # -- batch construction over many players (no per-call snapshotting) --------------------
     @classmethod
@@ -205,24 +210,59 @@ class MediaMap:
         self._sig = "tables"
         return self
 
+    def _upload(self, new):
+        if self._map is not None:
+            self._map.close()
+        self._ctx = self._ctx or default_context()
+        self._map = self._ctx.upload(new)
+        self._host = new
+        self._cap = np.diff(new.track_off).astype(np.int64)
+        self.refreshes["upload"] += 1
+
     def _device_map(self):
         if self._sig == "tables":
             return self._map
-        levels = self.hls.levels
-        sig = []
-        for lv in levels:
-            d = _prop(lv, "details") if lv else None
-            fr = _prop(d, "fragments") if d else None
-            n = len(fr) if fr else 0
-            sig.append((id(lv), id(d), id(fr), n,
-                        (_prop(fr[0], "sn"), _prop(fr[-1], "sn"), _prop(fr[-1], "start")) if n else None))
-        sig = tuple(sig)
-        if sig != self._sig:
-            if self._map is not None:
-                self._map.close()
-            self._ctx = self._ctx or default_context()
-            self._map = self._ctx.upload(FragmentTables.from_hls_levels([levels]))
-            self._sig = sig
+        new = FragmentTables.from_hls_levels([self.hls.levels])
+        old = self._host
+        if old is None or new.n_tracks != old.n_tracks or \
+                not np.array_equal(new.track_state, old.track_state) or \
+                not np.array_equal(new.url_count, old.url_count):
+            self._upload(new)
+            return self._map
+        bits = lambda a: a.view(np.uint64)
+        slides = []
+        for t in range(new.n_tracks):
+            o0, o1, n0, n1 = int(old.track_off[t]), int(old.track_off[t + 1]), int(new.track_off[t]), int(new.track_off[t + 1])
+            osn, ost, nsn, nst = old.sn[o0:o1], old.start[o0:o1], new.sn[n0:n1], new.start[n0:n1]
+            d_old = bits(old.duration[o0:o0 + 1]) if o1 > o0 else None
+            d_new = bits(new.duration[n0:n0 + 1]) if n1 > n0 else None
+            same_dur0 = (d_old is None and d_new is None) or \
+                (d_old is not None and d_new is not None and d_old[0] == d_new[0])
+            if len(osn) == len(nsn) and np.array_equal(osn, nsn) and np.array_equal(bits(ost), bits(nst)) and same_dur0:
+                continue
+            # a slid window?  old[k:] must be the head of new
+            k = None
+            if len(nsn) and len(osn):
+                hit = np.nonzero((osn == nsn[0]) & (bits(ost) == bits(nst)[0]))[0]
+                k = int(hit[0]) if len(hit) else None
+            elif len(nsn) == 0:
+                k = len(osn)
+            keep = len(osn) - k if k is not None else -1
+            ok = k is not None and keep <= len(nsn) and len(nsn) <= self._cap[t] and \
+                np.array_equal(osn[k:], nsn[:keep]) and np.array_equal(bits(ost[k:]), bits(nst[:keep]))
+            if not ok:
+                self._upload(new)
+                return self._map
+            slides.append((t, k, nst[keep:], nsn[keep:], new.duration[n0] if n1 > n0 else np.nan))
+        if slides:
+            aoff = np.concatenate([[0], np.cumsum([len(x[2]) for x in slides])]).astype(np.int64)
+            self._map.slide_tracks(np.zeros(len(slides), np.int32), np.asarray([x[0] for x in slides], np.int32),
+                                   np.asarray([x[1] for x in slides], np.int32), aoff,
+                                   np.concatenate([x[2] for x in slides]) if aoff[-1] else np.zeros(0),
+                                   np.concatenate([x[3] for x in slides]).astype(np.int32) if aoff[-1] else np.zeros(0, np.int32),
+                                   new_dur0=np.asarray([x[4] for x in slides], np.float64))
+            self._host = new
+            self.refreshes["slide"] += 1
         return self._map
 
     def getSegmentTime(self, segmentView):         # media-map.js:14-19
@@ -266,6 +306,12 @@ class MediaMap:
     def getTrackList(self):                        # media-map.js:60-73
         if self._sig != "tables" and not self.hls.levels:
             return []
+        if self._sig != "tables":
+            for lv in self.hls.levels:             # `level.url.length` (:67-68) throws on a falsy level
+                if not lv:
+                    raise JSTypeError("Cannot read property 'url' of undefined")
+                if _prop(lv, "url") is undefined or _prop(lv, "url") is None:
+                    raise JSTypeError("Cannot read property 'length' of undefined")
         lv, ui = self._device_map().get_track_list(0)
         return [TrackView({"level": int(a), "urlId": int(b)}) for a, b in zip(lv, ui)]
 

@@ -135,8 +135,9 @@ int hlsmap_map_set_path(hlsmap_map *map, int path);
  * level.details.fragments on every call (:28,41), so a playlist reload is seen at once.  The
  * batch analogue: for each i, track (playlist[i], level[i]) evicts its first drop[i] fragments
  * and appends new_start/new_sn[append_offset[i] .. append_offset[i+1]) (append_offset[0] = 0);
- * new_dur0[i] (nullable array) becomes the duration of the track's new first fragment
- * (getSegmentDuration).  A track may appear once per call and may not outgrow the fragment
+ * new_dur0[i] becomes the duration of the track's new first fragment (getSegmentDuration);
+ * the array may be NULL only when no listed track changes its first fragment (every drop[i] is 0
+ * and nothing is appended to an empty track), otherwise HLSMAP_ERR_INVALID.  A track may appear once per call and may not outgrow the fragment
  * count it had at hlsmap_map_create (HLSMAP_ERR_CAPACITY).  Monotonicity is re-proven on the
  * GPU for every touched track; a track that stops being sorted routes the map to the filter
  * kernel.  Host pointers; blocks until the tables are updated. */
@@ -305,7 +306,9 @@ int hlsmap_view_from_json(hlsmap_ctx *ctx, int64_t n, const char *chars, const i
  * start / sn / duration  [capacity] out, or all NULL with capacity 0 to only count
  * Numbers the converter cannot round exactly (see csrc/decimal.cuh: more than 19 significant digits
  * whose tail could change the rounding, or a sequence number beyond int32) are never guessed: the
- * call fails with HLSMAP_ERR_UNSUPPORTED and res->n_unsupported says how many there were.
+ * call fails with HLSMAP_ERR_UNSUPPORTED and res->n_unsupported says how many there were.  The same
+ * goes for a '#' more than 16384 bytes into its line: whether an earlier tag on the line hides it is
+ * decided by replaying the line, and that work is bounded.
  * HLSMAP_ERR_CAPACITY: res->n_fragments entries are needed; track_offset / track_live are valid. */
 typedef struct hlsmap_ingest_result {
     int64_t n_fragments;

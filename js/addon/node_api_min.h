@@ -37,6 +37,8 @@ napi_status napi_create_double(napi_env, double, napi_value *);
 napi_status napi_create_external(napi_env, void *data, napi_finalize, void *hint, napi_value *);
 napi_status napi_get_value_external(napi_env, napi_value, void **);
 napi_status napi_get_value_int32(napi_env, napi_value, int32_t *);
+napi_status napi_get_value_int64(napi_env, napi_value, int64_t *);
+napi_status napi_create_external_arraybuffer(napi_env, void *external_data, size_t byte_length, napi_finalize, void *hint, napi_value *result);
 napi_status napi_get_value_bool(napi_env, napi_value, bool *);
 napi_status napi_get_named_property(napi_env, napi_value object, const char *name, napi_value *result);
 napi_status napi_set_named_property(napi_env, napi_value object, const char *name, napi_value value);

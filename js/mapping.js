@@ -54,6 +54,9 @@ SegmentView.packBatch = (ctx, level, urlId, sn) => native.viewPack(ctx, level, u
 SegmentView.unpackBatch = (ctx, wire) => native.viewUnpack(ctx, wire);
 SegmentView.isEqualBatch = (ctx, a, b) => native.viewIsEqual(ctx, a.level, a.urlId, a.sn, b.level, b.urlId, b.sn);
 SegmentView.viewToStringBatch = (ctx, level, urlId, sn) => native.viewFormat(ctx, level, urlId, sn, true);
+SegmentView.isInTrackBatch = (ctx, a, track) => native.viewIsInTrack(ctx, a.level, a.urlId, track.level, track.urlId);
+// toArrayBuffer -> fromArrayBuffer -> isEqual(original) in one pass: {wire: Uint32Array(3n), equal: Uint8Array}
+SegmentView.roundtripBatch = (ctx, level, urlId, sn) => native.viewRoundtrip(ctx, level, urlId, sn);
 
 // ---- MediaMap --------------------------------------------------------------------------------
 const ST_UNPARSED = 1, ST_MISSING = 2, ST_EMPTY = 3;
@@ -87,12 +90,14 @@ function snapshotLevels(levels) {
   return t;
 }
 
-function levelsSignature(levels) {
-  return levels.map((l) => {
-    const fr = l && l.details ? l.details.fragments : null;
-    const n = fr ? fr.length : -1;
-    return n > 0 ? [n, fr[0].sn, fr[n - 1].sn, fr[n - 1].start].join(':') : String(n);
-  }).join('|');
+// Bit pattern view of a Float64Array: NaN starts compare equal to themselves, -0 differs from 0.
+const bitsOf = (f64) => new BigUint64Array(f64.buffer, f64.byteOffset, f64.length);
+
+function sameRun(aSn, aBits, a0, bSn, bBits, b0, n) {
+  for (let i = 0; i < n; i++) {
+    if (aSn[a0 + i] !== bSn[b0 + i] || aBits[a0 + i] !== bBits[b0 + i]) return false;
+  }
+  return true;
 }
 
 class MediaMap {
@@ -100,16 +105,63 @@ class MediaMap {
     this.hls = hls;
     this._device = options && options.device !== undefined ? options.device : 0;
     this._map = null;
-    this._signature = null;
+    this._host = null;                  // the tables resident on the GPU (snapshotLevels form)
+    this._cap = null;                   // fragments reserved per level at upload
+    this.refreshes = { upload: 0, slide: 0 };
   }
 
-  _deviceMap() {                        // the reference reads hls.levels on every call (:28,41)
-    const signature = levelsSignature(this.hls.levels);
-    if (signature !== this._signature) {
-      if (!sharedContext) sharedContext = native.createContext(this._device);
-      if (this._map) native.destroyMap(this._map);
-      this._map = native.createMap(sharedContext, snapshotLevels(this.hls.levels));
-      this._signature = signature;
+  _upload(t) {
+    if (!sharedContext) sharedContext = native.createContext(this._device);
+    if (this._map) native.destroyMap(this._map);
+    this._map = native.createMap(sharedContext, t);
+    this._host = t;
+    this._cap = Array.from({ length: t.trackState.length }, (_, i) => Number(t.trackOffset[i + 1] - t.trackOffset[i]));
+    this.refreshes.upload++;
+    return this._map;
+  }
+
+  // The reference reads hls.levels on every call (:28,41).  Every call therefore compares the level
+  // list -- every fragment's sn and start, every level's url count and first duration -- with what is
+  // resident in HBM.  A window that slid (fragments evicted at the front, appended at the back, the
+  // rest untouched) is slid in place on the GPU (native.slideTracks); anything else re-uploads.
+  _deviceMap() {
+    const t = snapshotLevels(this.hls.levels);
+    const old = this._host;
+    const nT = t.trackState.length;
+    if (!old || old.trackState.length !== nT) return this._upload(t);
+    for (let i = 0; i < nT; i++) {
+      if (t.trackState[i] !== old.trackState[i] || t.urlCount[i] !== old.urlCount[i]) return this._upload(t);
+    }
+    const nb = bitsOf(t.start), ob = bitsOf(old.start), nd = bitsOf(t.duration), od = bitsOf(old.duration);
+    const slides = [];
+    for (let i = 0; i < nT; i++) {
+      const o0 = Number(old.trackOffset[i]), oN = Number(old.trackOffset[i + 1]) - o0;
+      const n0 = Number(t.trackOffset[i]), nN = Number(t.trackOffset[i + 1]) - n0;
+      const sameDur0 = (oN === 0 && nN === 0) || (oN > 0 && nN > 0 && od[o0] === nd[n0]);
+      if (oN === nN && sameDur0 && sameRun(old.sn, ob, o0, t.sn, nb, n0, nN)) continue;
+      let k = -1;                        // old[k..] must be the head of new
+      if (nN === 0) k = oN;
+      else for (let j = 0; j < oN; j++) if (old.sn[o0 + j] === t.sn[n0] && ob[o0 + j] === nb[n0]) { k = j; break; }
+      const keep = oN - k;
+      if (k < 0 || keep > nN || nN > this._cap[i] || !sameRun(old.sn, ob, o0 + k, t.sn, nb, n0, keep)) return this._upload(t);
+      slides.push({ level: i, drop: k, from: n0 + keep, to: n0 + nN, dur0: nN > 0 ? t.duration[n0] : NaN });
+    }
+    if (slides.length) {
+      const n = slides.length;
+      const appendOffset = new BigInt64Array(n + 1);
+      slides.forEach((s, j) => { appendOffset[j + 1] = appendOffset[j] + BigInt(s.to - s.from); });
+      const total = Number(appendOffset[n]);
+      const newStart = new Float64Array(total), newSn = new Int32Array(total);
+      slides.forEach((s, j) => {
+        newStart.set(t.start.subarray(s.from, s.to), Number(appendOffset[j]));
+        newSn.set(t.sn.subarray(s.from, s.to), Number(appendOffset[j]));
+      });
+      native.slideTracks(this._map, {
+        playlist: null, level: Int32Array.from(slides, (s) => s.level), drop: Int32Array.from(slides, (s) => s.drop),
+        appendOffset, newStart, newSn, newDur0: Float64Array.from(slides, (s) => s.dur0),
+      });
+      this._host = t;
+      this.refreshes.slide++;
     }
     return this._map;
   }
@@ -136,6 +188,13 @@ class MediaMap {
   // Added entry point: typed arrays in, typed arrays out, no per-hit objects.
   // queries = {playlist?: Int32Array, level: Int32Array, beginTime: Float64Array, duration: Float64Array}
   // -> {offsets: Int32Array(Q+1), sn: Int32Array(H), time: Float64Array(H), status: Uint8Array(Q)}
+  // Range form of the same query: {first: Int32Array(Q), count: Int32Array(Q), status: Uint8Array(Q)} --
+  // fragment index of the first kept fragment (or -1) and how many follow, 9 bytes back per query.
+  getSegmentRangeBatch(queries) {
+    return native.getSegmentRange(this._deviceMap(), queries.playlist || null, queries.level,
+      queries.beginTime, queries.duration);
+  }
+
   getSegmentListBatch(queries, options) {
     const r = native.getSegmentList(this._deviceMap(), queries.playlist || null, queries.level,
       queries.beginTime, queries.duration);
@@ -148,6 +207,7 @@ class MediaMap {
 
   getTrackList() {                      // media-map.js:60-73
     if (!this.hls.levels) return [];
+    for (const level of this.hls.levels) void level.url.length;   // a falsy level throws a TypeError here (:67-68)
     const r = native.getTrackList(this._deviceMap(), 0);
     return Array.from(r.level, (level, i) => new TrackView({ level, urlId: r.urlId[i] }));
   }
@@ -183,7 +243,20 @@ function segmentViewsFromJSON(chars, offsets) {
   return native.viewFromJson(sharedContext, chars, offsets);
 }
 
+// Typed arrays over pinned host memory (hlsmap_host_alloc): batches built in them reach the GPU
+// without a staging copy.  pinned(Float64Array, n) etc.; the memory is released with the ArrayBuffer.
+function pinned(TypedArray, length, device) {
+  if (!sharedContext) sharedContext = native.createContext(device === undefined ? 0 : device);
+  return new TypedArray(native.hostAlloc(sharedContext, length * TypedArray.BYTES_PER_ELEMENT), 0, length);
+}
+
+// Consecutive getSegmentListBatch calls that share no buffers may overlap on the GPU.
+function setBatchOverlap(enable) {
+  if (!sharedContext) sharedContext = native.createContext(0);
+  native.setBatchOverlap(sharedContext, !!enable);
+}
+
 module.exports = {
   MediaMap, SegmentView, TrackView, native, ST_UNPARSED, ST_MISSING, ST_EMPTY,
-  createMapFromM3u8, segmentViewsToJSON, segmentViewsFromJSON,
+  createMapFromM3u8, segmentViewsToJSON, segmentViewsFromJSON, pinned, setBatchOverlap,
 };

@@ -126,6 +126,25 @@ def test_numbers_that_cannot_be_rounded_exactly_fail_loudly(ctx):
     assert e.value.code == N.ERR_UNSUPPORTED
 
 
+def test_tags_far_into_one_line_are_bounded_work(ctx):
+    """Whether an earlier tag on the same line hides a '#' is decided by replaying the line, one
+    thread per '#': quadratic in the line's length.  Lines up to 16 KB are replayed (and agree with the
+    oracle); a tag further into its line makes the call fail instead of stalling the GPU on a
+    megabyte-long line of tags from the network."""
+    import time
+    line = b"#EXT-X-KEY:" + b"x" * 9000 + b"#EXTINF:5,#EXTINF:6,\n#EXTINF:7,\nseg.ts\n"     # hidden ones: 9 KB in
+    got = ctx.parse_m3u8([line])
+    exp = oracle.parse_m3u8(line, [0, len(line)])
+    _same(got, exp)
+    assert list(got["duration"]) == [7.0]
+    hostile = b"#EXTINF:1," * 250_000 + b"\n#EXTINF:4,\nseg.ts\n"          # one 2.5 MB line of tags
+    t0 = time.perf_counter()
+    with pytest.raises(N.HlsMapError) as e:
+        ctx.parse_m3u8([hostile])
+    assert e.value.code == N.ERR_UNSUPPORTED and "16384" in e.value.message
+    assert time.perf_counter() - t0 < 5.0
+
+
 def test_capacity_protocol_and_empty_inputs(ctx):
     lib = N.load()
     text = b"#EXTINF:1,\n#EXTINF:2,\n#EXTINF:3,\n"

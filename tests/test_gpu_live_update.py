@@ -75,8 +75,15 @@ def test_shrink_grow_and_unsorted_updates(ctx):
             "sn": [t.sn[t.track_off[i]:t.track_off[i + 1]].copy() for i in range(15)]}
     lens = np.diff(t.track_off).astype(np.int64)
     m = ctx.upload(t)
+    # evicting at the front changes the first fragment: its duration has to come along (the reference
+    # would read the new fragments[0].duration, media-map.js:81-87), a missing one is refused
+    with pytest.raises(N.HlsMapError) as e:
+        m.slide_tracks([1, 2], [0, 1], [4, 6], [0, 0, 0], np.zeros(0), np.zeros(0, np.int32))
+    assert e.value.code == N.ERR_INVALID and "new_dur0" in e.value.message
     # shrink track (1,0) to 2 fragments, empty track (2,1), leave the others
-    m.slide_tracks([1, 2], [0, 1], [4, 6], [0, 0, 0], np.zeros(0), np.zeros(0, np.int32))
+    m.slide_tracks([1, 2], [0, 1], [4, 6], [0, 0, 0], np.zeros(0), np.zeros(0, np.int32), new_dur0=[7.5, np.nan])
+    d, st = m.get_segment_duration([1, 2], [0, 1])
+    assert d[0] == 7.5 and st[0] == N.ST_OK and st[1] == N.ST_EMPTY
     host["start"][3], host["sn"][3] = host["start"][3][4:], host["sn"][3][4:]
     host["start"][7], host["sn"][7] = host["start"][7][:0], host["sn"][7][:0]
     lens[3], lens[7] = 2, 0
@@ -92,10 +99,10 @@ def test_shrink_grow_and_unsorted_updates(ctx):
         m.slide_tracks([1], [0], [0], [0, 1], [1e9], [1])
     assert e.value.code == N.ERR_CAPACITY
     with pytest.raises(N.HlsMapError):
-        m.slide_tracks([1, 1], [0, 0], [1, 1], [0, 0, 0], np.zeros(0), np.zeros(0, np.int32))   # twice
+        m.slide_tracks([1, 1], [0, 0], [1, 1], [0, 0, 0], np.zeros(0), np.zeros(0, np.int32), new_dur0=[1.0, 1.0])   # twice
     # an update that breaks the order: the map must fall back to the filter kernel, still exact
     bad = host["start"][0][0] - 50.0
-    m.slide_tracks([0], [0], [1], [0, 1], [bad], [7])
+    m.slide_tracks([0], [0], [1], [0, 1], [bad], [7], new_dur0=[2.0])
     host["start"][0] = np.concatenate([host["start"][0][1:], [bad]])
     host["sn"][0] = np.concatenate([host["sn"][0][1:], [7]]).astype(np.int32)
     assert m.info()["all_monotone"] == 0 and m.monotone_flags()[0] == 0
@@ -104,4 +111,53 @@ def test_shrink_grow_and_unsorted_updates(ctx):
     res = m.get_segment_list(q3.playlist, q3.level, q3.begin, q3.duration)
     assert res.path == N.PATH_FILTER
     _check(m, lens, host, q3)
+    m.close()
+
+
+def test_sequence_numbers_that_stop_being_contiguous(ctx):
+    """The windowed search kernel computes a hit's sn from its query's first hit only while every
+    track numbers its fragments contiguously (proven on the GPU at upload and after every slide).
+    A discontinuity -- at upload, or appended later -- must send it back to reading sn[]: answers
+    stay bit-for-bit the oracle's, including sn values that wrap around INT32."""
+    t, q = synth.config5(seed=21, n_playlists=900, queries_per_playlist=40)     # beyond shared memory
+    nt = t.n_tracks
+    lens = np.diff(t.track_off).astype(np.int64)
+    sn = t.sn.copy()
+    # contiguous runs that wrap: first track starts just below INT32_MAX
+    o0, n0 = int(t.track_off[0]), int(lens[0])
+    sn[o0:o0 + n0] = ((np.arange(n0, dtype=np.int64) + (2 ** 31 - 3) + 2 ** 31) % 2 ** 32 - 2 ** 31).astype(np.int32)
+    tw = FragmentTables(t.playlist_base, t.track_off, t.track_state, t.url_count, t.start, sn, t.duration)
+    m = ctx.upload(tw)
+    assert m.info()["stage_all"] == 0 and m.info()["all_monotone"] == 1
+    ref = _oracle(tw, q)
+    res = m.get_segment_list(q.playlist, q.level, q.begin, q.duration)
+    assert np.array_equal(res.offsets.astype(np.int64), ref[0]) and np.array_equal(res.sn, ref[2])
+    assert np.array_equal(res.time.view(np.uint64), ref[3].view(np.uint64))
+    # a slide that appends a gap in the numbering (an HLS discontinuity in sn) to a few tracks
+    host = {"pbase": t.playlist_base, "state": t.track_state, "urlc": t.url_count,
+            "start": [tw.start[t.track_off[i]:t.track_off[i + 1]].copy() for i in range(nt)],
+            "sn": [tw.sn[t.track_off[i]:t.track_off[i + 1]].copy() for i in range(nt)]}
+    pick = np.array([3, 4, 500, nt - 1])
+    k = np.array([2, 1, 3, 2])
+    aoff = np.concatenate([[0], np.cumsum(k)]).astype(np.int64)
+    ns, nsn = np.empty(aoff[-1]), np.empty(aoff[-1], np.int32)
+    for j, tr in enumerate(pick):
+        last_s, last_sn = host["start"][tr][lens[tr] - 1], int(host["sn"][tr][lens[tr] - 1])
+        add_s = last_s + 3.0 * np.arange(1, k[j] + 1)
+        add_sn = last_sn + 7 + np.arange(1, k[j] + 1)                  # the gap
+        ns[aoff[j]:aoff[j + 1]], nsn[aoff[j]:aoff[j + 1]] = add_s, add_sn
+        host["start"][tr] = np.concatenate([host["start"][tr][k[j]:lens[tr]], add_s])
+        host["sn"][tr] = np.concatenate([host["sn"][tr][k[j]:lens[tr]], add_sn]).astype(np.int32)
+    m.slide_tracks((pick // 3).astype(np.int32), (pick % 3).astype(np.int32), k.astype(np.int32), aoff, ns, nsn,
+                   new_dur0=np.full(len(pick), 3.0))
+    _check(m, lens, host, q)
+    m.close()
+    # and a map that is not contiguous from the start
+    sn2 = t.sn.copy()
+    sn2[::5] += 1000
+    t2 = FragmentTables(t.playlist_base, t.track_off, t.track_state, t.url_count, t.start, sn2, t.duration)
+    m = ctx.upload(t2)
+    ref = _oracle(t2, q)
+    res = m.get_segment_list(q.playlist, q.level, q.begin, q.duration)
+    assert np.array_equal(res.offsets.astype(np.int64), ref[0]) and np.array_equal(res.sn, ref[2])
     m.close()

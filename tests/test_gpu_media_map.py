@@ -164,3 +164,68 @@ def test_batch_entry_point(ctx):
     assert list(res.status) == [1, 0] and list(res.offsets) == [0, 0, 3]
     res = mm.getSegmentListBatch([1, 4], [365.0, 365.0], [33.0, 33.0], strict=False)
     assert list(res.status) == [0, 2] and res.n_missing == 1
+
+
+# ---- hls.levels is read live (media-map.js:28,41): the device copy must never answer from stale tables
+def _levels(n=40, first_sn=100, dur=4.0):
+    frag = lambda i: {"sn": first_sn + i, "start": dur * i, "duration": dur}
+    return [{"url": ["a", "b"], "details": {"fragments": [frag(i) for i in range(n)]}},
+            {"url": ["a"], "details": {"fragments": [frag(i) for i in range(n)]}}]
+
+
+def _sns(mm, level, begin, duration):
+    return [(v.sn, v.time) for v in mm.getSegmentList(TrackView({"level": level, "urlId": 0}), begin, duration)]
+
+
+def test_interior_start_nudge_is_seen(ctx):
+    """hls.js moves fragment starts in place when it aligns PTS: nothing about the list's length,
+    first or last entry changes, and the reference would still see the new value on its next call."""
+    hls = type("Hls", (), {"levels": _levels()})()
+    mm = MediaMap(hls, ctx)
+    assert _sns(mm, 0, 39.0, 6.0) == [(110, 40.0), (111, 44.0)]
+    hls.levels[0]["details"]["fragments"][10]["start"] = 38.5          # interior nudge, same object graph
+    assert _sns(mm, 0, 39.0, 6.0) == [(111, 44.0)]
+    assert _sns(mm, 0, 38.0, 6.5) == [(110, 38.5), (111, 44.0)]
+    assert _sns(mm, 1, 39.0, 6.0) == [(110, 40.0), (111, 44.0)]        # the other level is untouched
+    # url list and first duration are part of what is compared too
+    assert [(t.level, t.urlId) for t in mm.getTrackList()] == [(0, 0), (0, 1), (1, 0)]
+    hls.levels[1]["url"].append("c")
+    assert [(t.level, t.urlId) for t in mm.getTrackList()] == [(0, 0), (0, 1), (1, 0), (1, 1)]
+    hls.levels[0]["details"]["fragments"][0]["duration"] = 3.25
+    assert mm.getSegmentDuration(SegmentView({"sn": 1, "trackView": {"level": 0, "urlId": 0}, "time": 0})) == 3.25
+
+
+def test_sliding_window_is_slid_on_the_gpu_not_reuploaded(ctx):
+    hls = type("Hls", (), {"levels": _levels(n=12)})()
+    mm = MediaMap(hls, ctx)
+    assert _sns(mm, 0, 0.0, 8.0) == [(100, 0.0), (101, 4.0), (102, 8.0)]
+    uploads = mm.refreshes["upload"]
+    for step in range(1, 6):                     # a live reload: two out at the front, two in at the back
+        for lv in hls.levels:
+            fr = lv["details"]["fragments"]
+            last = fr[-1]
+            del fr[:2]
+            fr.extend({"sn": last["sn"] + j, "start": last["start"] + 4.0 * j + 0.125 * step, "duration": 4.0 + step}
+                      for j in (1, 2))
+        got = _sns(mm, 0, 0.0, 1e9)
+        want = [(f["sn"], f["start"]) for f in hls.levels[0]["details"]["fragments"]]
+        assert got == want
+        d = mm.getSegmentDuration(SegmentView({"sn": 1, "trackView": {"level": 1, "urlId": 0}, "time": 0}))
+        assert d == hls.levels[1]["details"]["fragments"][0]["duration"]
+    assert mm.refreshes["upload"] == uploads and mm.refreshes["slide"] == 5
+    # a window that grows beyond what was reserved at upload cannot slide: re-upload, same answers
+    fr = hls.levels[0]["details"]["fragments"]
+    fr.extend({"sn": fr[-1]["sn"] + j, "start": fr[-1]["start"] + 4.0 * j, "duration": 4.0} for j in (1, 2, 3))
+    assert _sns(mm, 0, 0.0, 1e9) == [(f["sn"], f["start"]) for f in fr]
+    assert mm.refreshes["upload"] == uploads + 1
+
+
+def test_get_track_list_throws_on_a_falsy_level(ctx):
+    """media-map.js:66-68 reads level.url.length of every entry of hls.levels: a hole throws a
+    TypeError there, it does not yield an empty track list for that level."""
+    hls = type("Hls", (), {"levels": [_levels()[0], None, _levels()[1]]})()
+    mm = MediaMap(hls, ctx)
+    with pytest.raises(JSTypeError):
+        mm.getTrackList()
+    hls.levels[1] = {"url": []}
+    assert [(t.level, t.urlId) for t in mm.getTrackList()] == [(0, 0), (0, 1), (2, 0)]
