@@ -29,6 +29,14 @@ class MapInfo(ctypes.Structure):
                 ("stage_all", ctypes.c_int32), ("device_bytes", ctypes.c_int64)]
 
 
+class Batch(ctypes.Structure):
+    """hlsmap_batch: one list-form batch of hlsmap_get_segment_list_dev_batches (device pointers)."""
+    _fields_ = [("nq", ctypes.c_int64), ("d_playlist", ctypes.c_void_p), ("d_level", ctypes.c_void_p),
+                ("d_begin", ctypes.c_void_p), ("d_duration", ctypes.c_void_p), ("d_offsets", ctypes.c_void_p),
+                ("d_sn_out", ctypes.c_void_p), ("d_time_out", ctypes.c_void_p), ("hit_capacity", ctypes.c_int64),
+                ("d_status", ctypes.c_void_p)]
+
+
 class IngestResult(ctypes.Structure):
     _fields_ = [("n_fragments", ctypes.c_int64), ("n_sequence_tags", ctypes.c_int64),
                 ("n_unsupported", ctypes.c_int64), ("text_bytes", ctypes.c_int64),
@@ -64,6 +72,7 @@ SYMBOLS = {
     "hlsmap_get_segment_list_dev": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P, _I64, _P, _P, _P]),
     "hlsmap_get_segment_list": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P, _I64, _P, _P]),
     "hlsmap_get_segment_list_noalloc_dev": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P, _I64, _P, _P, _P]),
+    "hlsmap_get_segment_list_dev_batches": (_INT, [_P, _I32, _P, _P, _P]),
     "hlsmap_ctx_last_result": (_INT, [_P, _P, _P]),
     "hlsmap_get_segment_range_dev": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P, _P]),
     "hlsmap_get_segment_range": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P]),

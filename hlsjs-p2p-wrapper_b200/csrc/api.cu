@@ -787,6 +787,22 @@ int hlsmap_get_segment_list_dev(hlsmap_map *map, int64_t nq, const int32_t *d_pl
                      hit_capacity, d_status, stream, result, 0ull);
 }
 
+int hlsmap_get_segment_list_dev_batches(hlsmap_map *map, int32_t n, const hlsmap_batch *batches,
+                                        void *stream, int32_t *n_launched)
+{
+    if (n_launched) *n_launched = 0;
+    if (!map) return fail(HLSMAP_ERR_INVALID, "null map");
+    if (n < 0 || (n > 0 && !batches)) return fail(HLSMAP_ERR_INVALID, "get_segment_list_dev_batches: null batch array");
+    for (int32_t i = 0; i < n; i++) {
+        const hlsmap_batch &b = batches[i];
+        const int r = list_core(map, b.nq, b.d_playlist, b.d_level, b.d_begin, b.d_duration, b.d_offsets,
+                                b.d_sn_out, b.d_time_out, b.hit_capacity, b.d_status, stream, nullptr, 0ull);
+        if (r) return r;
+        if (n_launched) *n_launched = i + 1;
+    }
+    return HLSMAP_OK;
+}
+
 int hlsmap_ctx_last_result(hlsmap_ctx *ctx, void *stream, hlsmap_result *result)
 {
     int r = use_ctx(ctx);

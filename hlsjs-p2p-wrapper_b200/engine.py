@@ -328,6 +328,24 @@ class DeviceMap:
         N.check(code)
         return res
 
+    def get_segment_list_dev_batches(self, batches, stream=None):
+        """Several independent device-pointer batches with one call into the library.  `batches`: a
+        sequence of dicts with nq, d_playlist (or 0), d_level, d_begin, d_duration, d_offsets, d_sn_out,
+        d_time_out, capacity, d_status (optional) -- or a ready-made ctypes array of N.Batch.  Asynchronous;
+        returns the number of batches launched."""
+        if not isinstance(batches, ctypes.Array):
+            arr = (N.Batch * len(batches))()
+            for a, b in zip(arr, batches):
+                a.nq, a.d_playlist, a.d_level = int(b["nq"]), b.get("d_playlist") or None, b["d_level"]
+                a.d_begin, a.d_duration, a.d_offsets = b["d_begin"], b["d_duration"], b["d_offsets"]
+                a.d_sn_out, a.d_time_out = b.get("d_sn_out") or None, b.get("d_time_out") or None
+                a.hit_capacity, a.d_status = int(b.get("capacity", 0)), b.get("d_status") or None
+            batches = arr
+        done = ctypes.c_int32(0)
+        N.check(self._lib.hlsmap_get_segment_list_dev_batches(self._h, len(batches), batches, _stream(stream),
+                                                              ctypes.byref(done)))
+        return done.value
+
     def get_segment_list_noalloc_dev(self, nq, d_playlist, d_level, d_begin, d_duration, d_offsets,
                                      d_sn_out, d_time_out, capacity, d_status=0, stream=None,
                                      sync=True):

@@ -193,6 +193,27 @@ int hlsmap_get_segment_list_noalloc_dev(hlsmap_map *map, int64_t nq, const int32
                                         int32_t *d_sn_out, double *d_time_out,
                                         int64_t hit_capacity, uint8_t *d_status, void *stream,
                                         hlsmap_result *result);
+/* Several independent list-form batches submitted with ONE call (what a serving loop does with the
+ * requests that have queued up): the same as calling hlsmap_get_segment_list_dev for
+ * batches[0..n) in order with result = NULL, without returning to the host language between the
+ * launches.  With hlsmap_ctx_set_batch_overlap the batches overlap on the GPU as consecutive
+ * calls would (they must not share output buffers).  Stops at the first batch that cannot be
+ * launched and returns its error; *n_launched (nullable) = batches issued.  The reference has one
+ * call per query (media-map.js:27); this is that call over many query batches. */
+typedef struct hlsmap_batch {
+    int64_t nq;
+    const int32_t *d_playlist;   /* nullable */
+    const int32_t *d_level;
+    const double *d_begin;
+    const double *d_duration;
+    int32_t *d_offsets;          /* [nq + 1] */
+    int32_t *d_sn_out;           /* nullable together with d_time_out (count only) */
+    double *d_time_out;
+    int64_t hit_capacity;
+    uint8_t *d_status;           /* nullable */
+} hlsmap_batch;
+int hlsmap_get_segment_list_dev_batches(hlsmap_map *map, int32_t n, const hlsmap_batch *batches,
+                                        void *stream, int32_t *n_launched);
 /* Counters of the most recent batch issued through ctx (synchronises its stream). */
 int hlsmap_ctx_last_result(hlsmap_ctx *ctx, void *stream, hlsmap_result *result);
 

@@ -455,3 +455,63 @@ def test_small_batches_behind_big_ones_release_their_scratch_set(ctx):
     m2.close()
     other.close()
     m.close()
+
+
+def test_several_batches_with_one_call(ctx):
+    """hlsmap_get_segment_list_dev_batches: the batches of one call behave like so many calls of
+    hlsmap_get_segment_list_dev -- each bit-for-bit the oracle's answer, with and without overlap
+    between consecutive batches, count-only batches and an empty one among them; a batch that cannot
+    be launched stops the call and says how many were issued."""
+    import torch
+    dev = torch.device("cuda:0")
+    t, _ = synth.config2(n_queries=4)
+    m = ctx.upload(t)
+    stream = torch.cuda.Stream(device=dev)
+    sets = []
+    for i, nq in enumerate((60_000, 0, 1_000_003, 513, 250_000)):
+        _, q = synth.config2(seed=60 + i, n_queries=max(nq, 1))
+        q = QueryBatch(q.playlist[:nq], q.level[:nq], q.begin[:nq], q.duration[:nq])
+        ref = oracle_list(t, q)
+        H = int(ref[0][-1])
+        sets.append({"ref": ref, "H": H, "nq": nq,
+                     "pl": torch.from_numpy(q.playlist).to(dev), "lv": torch.from_numpy(q.level).to(dev),
+                     "bg": torch.from_numpy(q.begin).to(dev), "du": torch.from_numpy(q.duration).to(dev),
+                     "off": torch.full((nq + 1,), -1, dtype=torch.int32, device=dev),
+                     "sn": torch.empty(max(H, 1), dtype=torch.int32, device=dev),
+                     "tm": torch.empty(max(H, 1), dtype=torch.float64, device=dev)})
+    batch = lambda s, fill=True: {"nq": s["nq"], "d_playlist": s["pl"].data_ptr(), "d_level": s["lv"].data_ptr(),
+                                  "d_begin": s["bg"].data_ptr(), "d_duration": s["du"].data_ptr(),
+                                  "d_offsets": s["off"].data_ptr(), "d_sn_out": s["sn"].data_ptr() if fill else 0,
+                                  "d_time_out": s["tm"].data_ptr() if fill else 0, "capacity": s["H"] if fill else 0}
+    torch.cuda.synchronize()
+    for overlap in (False, True):
+        ctx.set_batch_overlap(overlap)
+        try:
+            for s in sets:
+                s["off"].fill_(-1)
+            torch.cuda.synchronize()
+            assert m.get_segment_list_dev_batches([batch(s) for s in sets] * 3, stream.cuda_stream) == 3 * len(sets)
+            last = m.last_result(stream.cuda_stream)
+            assert last.total_hits == sets[-1]["H"]
+            for s in sets:
+                assert np.array_equal(s["off"].cpu().numpy().astype(np.int64), s["ref"][0])
+                assert np.array_equal(s["sn"][:s["H"]].cpu().numpy(), s["ref"][2])
+                assert np.array_equal(s["tm"][:s["H"]].cpu().numpy().view(np.uint64), s["ref"][3].view(np.uint64))
+        finally:
+            ctx.set_batch_overlap(False)
+    # count-only batches size the buffers; a broken batch in the middle stops the call there
+    for s in sets:
+        s["off"].fill_(-1)
+    assert m.get_segment_list_dev_batches([batch(s, fill=False) for s in sets], stream.cuda_stream) == len(sets)
+    torch.cuda.synchronize()
+    assert [int(s["off"][-1].item()) for s in sets] == [s["H"] for s in sets]
+    bad = dict(batch(sets[0]), d_level=0)
+    done = ctypes.c_int32(-1)
+    arr = (N.Batch * 3)()
+    for a, b in zip(arr, (batch(sets[3]), bad, batch(sets[0]))):
+        a.nq, a.d_playlist, a.d_level, a.d_begin, a.d_duration = b["nq"], b["d_playlist"], b["d_level"] or None, b["d_begin"], b["d_duration"]
+        a.d_offsets, a.d_sn_out, a.d_time_out, a.hit_capacity = b["d_offsets"], b["d_sn_out"], b["d_time_out"], b["capacity"]
+    code = N.load().hlsmap_get_segment_list_dev_batches(m._h, 3, arr, ctypes.c_void_p(stream.cuda_stream), ctypes.byref(done))
+    assert code == N.ERR_INVALID and done.value == 1
+    torch.cuda.synchronize()
+    m.close()
