@@ -94,9 +94,7 @@ int hlsmap_ctx_device(const hlsmap_ctx *ctx);
  * on the same stream is still writing its last hits, which hides each batch's ramp-up behind
  * its predecessor's tail.  ONLY legal when consecutive batches are independent: the next batch
  * must not read, or write to, any buffer the previous one is still writing.  Off by default
- * (plain stream order).  The library's own scratch is double-buffered for this.  With the option
- * on, large batches on maps held in shared memory are also cut into 1024-query tiles instead of
- * 512-query ones (same results; better back to back, slightly worse for a batch on its own). */
+ * (plain stream order).  The library's own scratch is double-buffered for this. */
 int hlsmap_ctx_set_batch_overlap(hlsmap_ctx *ctx, int enable);
 /* Block until everything issued through the context's own stream has finished. */
 int hlsmap_ctx_synchronize(hlsmap_ctx *ctx);
