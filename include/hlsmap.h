@@ -170,8 +170,9 @@ int hlsmap_get_segment_list(hlsmap_map *map, int64_t nq, const int32_t *playlist
  * rule, a plugin inside a host process that owns all device memory and forbids allocation
  * from callbacks, a service whose own pool has already taken every byte of HBM.  The
  * regular _dev entry point grows its look-back scratch with cudaMalloc when a batch is
- * larger than any before it; this one never allocates or frees anything, on the device or
- * the host.  Inputs and outputs are still the caller's device buffers; the scratch is a
+ * larger than any before it; this one never allocates or frees device memory, and on the
+ * success path no host memory either (only a failing call builds its error message in a host
+ * string).  Inputs and outputs are still the caller's device buffers; the scratch is a
  * fixed array inside the library image (about 0.5 MiB held by every GPU that loads the
  * library, until exit).
  *   - Limit: 65536 tiles per call.  A tile holds 256 to 4096 queries depending on the map
