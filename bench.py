@@ -280,7 +280,9 @@ def other_rows(ctx, torch, peak):
     alg = 24 * n + total.value
     out["views_json"] = {"views": n, "chars_per_view": total.value / n, "stringify_ms": ms_w,
                          "stringify_views_per_s": n / ms_w * 1e3, "stringify_roofline_frac": alg / ms_w / 1e6 / peak,
-                         "parse_ms": ms_r, "parse_views_per_s": n / ms_r * 1e3, "round_trip_bit_exact": exact}
+                         "parse_ms": ms_r, "parse_views_per_s": n / ms_r * 1e3,
+                         "parse_roofline_frac": (26 * n + total.value) / ms_r / 1e6 / peak,   # text + 4 B offset in, 22 B of columns out
+                         "round_trip_bit_exact": exact}
     return out
 
 

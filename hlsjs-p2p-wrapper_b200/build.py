@@ -16,7 +16,7 @@ VARIANT_FLAGS = os.environ.get("HLSMAP_VARIANT_FLAGS", "").split()
 LIB = os.path.join(CSRC, "libhlsmap_trace.so" if TRACE else
                    ("libhlsmap_%s.so" % VARIANT if VARIANT else "libhlsmap.so"))
 SOURCES = ["resolve.cu", "views.cu", "ingest.cu", "json.cu", "api.cu"]
-HEADERS = ["common.cuh", "scan.cuh", "decimal.cuh", "dtoa.cuh", "pow10_table.inc"]
+HEADERS = ["common.cuh", "scan.cuh", "decimal.cuh", "dtoa.cuh", "swar.cuh", "pow10_table.inc"]
 
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",

@@ -90,6 +90,7 @@ struct hlsmap_map {
     size_t stage_smem = 0;
     int grid_search = 0, grid_filter = 0;
     int ipt = 2;                        // queries per thread of the search kernel (tiles of 256 * ipt)
+    int uniform_levels = 0;             // > 0: every playlist has exactly this many levels
     bool sn_contig = false;             // every parsed track numbers its fragments contiguously (proven on the GPU)
 };
 
@@ -353,6 +354,12 @@ static int map_create_impl(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *
     m->n_frag = nf;
     m->n_frag_padded = ((nf + 3) & ~3ll) + 4;  // bulk copies round spans to 4 elements
     m->h_playlist_base.assign(playlist_track_base, playlist_track_base + n_playlists + 1);
+    if (n_playlists > 0 && n_tracks % n_playlists == 0 && (int64_t)n_tracks / n_playlists <= 1024) {
+        const int32_t per = n_tracks / n_playlists;
+        bool uniform = per > 0;
+        for (int32_t p = 0; p < n_playlists && uniform; p++) uniform = playlist_track_base[p] == p * per;
+        m->uniform_levels = uniform ? per : 0;
+    }
     m->h_url_count.resize(n_tracks);
     for (int32_t t = 0; t < n_tracks; t++) m->h_url_count[t] = url_count ? url_count[t] : 1;
 
@@ -726,6 +733,7 @@ static int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
     p.stage_all = map->info.stage_all;
     p.small = map->info.stage_all;
     p.sn_contig = (map->sn_contig && !map->info.stage_all) ? 1 : 0;
+    p.uniform_levels = map->uniform_levels;
     p.ipt = ipt;
     p.hint = map->d_hint;
     p.grid = map->d_grid;
@@ -1581,6 +1589,7 @@ int hlsmap_get_segment_list_noalloc_dev(hlsmap_map *map, int64_t nq, const int32
         p.stage_all = map->info.stage_all;
         p.small = map->info.stage_all;
         p.sn_contig = (map->sn_contig && !map->info.stage_all) ? 1 : 0;
+        p.uniform_levels = map->uniform_levels;
         p.ipt = map->ipt;
         p.hint = map->d_hint;
         p.grid = map->d_grid;

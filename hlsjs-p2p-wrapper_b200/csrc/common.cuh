@@ -79,6 +79,7 @@ struct ResolveParams {
     int n_tracks_padded;          // SMALL: descriptors staged in shared memory (>= 1)
     int n_base_padded;            // SMALL: playlist_base ints staged (multiple of 4)
     int small;                    // whole map staged in shared memory + hint grid
+    int uniform_levels;           // > 0: every playlist has exactly this many levels (track = playlist * that + level)
     int sn_contig;                // every parsed track's sn column is contiguous (general kernel computes sn)
     int ipt;                      // queries per thread of the SMALL kernel (2 or 4)
     // queries

@@ -8,6 +8,7 @@
 // non-finite `time` printed as null.  Columns in, one string per view out -- and back.
 #include "common.cuh"
 #include "decimal.cuh"
+#include "swar.cuh"
 #include "dtoa.cuh"
 #include "scan.cuh"
 
@@ -295,6 +296,12 @@ __device__ __forceinline__ int eat_int(const Text &t, long long &q, long long li
 __constant__ double c_json_pow10[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
                                         1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
 
+__constant__ unsigned long long c_json_ipow10[20] = {
+    1ull, 10ull, 100ull, 1000ull, 10000ull, 100000ull, 1000000ull, 10000000ull, 100000000ull, 1000000000ull,
+    10000000000ull, 100000000000ull, 1000000000000ull, 10000000000000ull, 100000000000000ull,
+    1000000000000000ull, 10000000000000000ull, 100000000000000000ull, 1000000000000000000ull,
+    10000000000000000000ull};
+
 // `time`: digits [. digits] without an exponent and with at most 19 significant digits is read in
 // one walk: up to 15 digits it is one exact IEEE division (both operands are exact doubles), up to
 // 19 the exact integer division of decimal.cuh.  Returns 0 when the general path has to decide.
@@ -341,41 +348,54 @@ __device__ __forceinline__ int eat_plain_decimal(const Text &t, long long &q, lo
     return 1;
 }
 
-}  // namespace
-
-constexpr int kParseStage = kThreads * kMaxChars;   // what 256 canonical texts can need
-
-__global__ void __launch_bounds__(256)
-view_from_json_kernel(const JsonReadParams p)
-{
-    __shared__ __align__(16) char stage[kParseStage + 16];
-    const long long v0 = (long long)blockIdx.x * blockDim.x, v = v0 + threadIdx.x;
-    // the CTA's texts are one contiguous run of characters: copy it in with coalesced loads
-    const long long v1 = v0 + blockDim.x < p.n ? v0 + blockDim.x : p.n;
-    const long long c_lo = p.offsets[v0], c_hi = p.offsets[v1];
-    const long long a_lo = c_lo & ~15ll;                 // aligned start; never before the buffer's own start
-    const bool staged = p.vec_ok && c_hi - a_lo <= kParseStage;
-    if (staged) {
-        for (long long o = a_lo + 16ll * threadIdx.x; o < c_hi; o += 16ll * blockDim.x) {
-            uint4 w;
-            if (o + 16 <= c_hi) {
-                w = *reinterpret_cast<const uint4 *>(p.chars + o);
-            } else {
-                char tmp[16];
-                for (int k = 0; k < 16; k++) tmp[k] = o + k < c_hi ? p.chars[o + k] : 0;
-                memcpy(&w, tmp, 16);
-            }
-            *reinterpret_cast<uint4 *>(stage + (o - a_lo)) = w;
-        }
+// ---- the canonical text, eight bytes at a time ---------------------------------------------
+// {"sn":<int>,"trackView":{"level":<int>,"urlId":<int>},"time":<number or null>} is what
+// JSON.stringify gives for a SegmentView the constructor built (segment-view.js:22-26).  Its four
+// literals are compared as 64-bit words and its three int32 values read with the SWAR routines of
+// swar.cuh; anything that is not exactly this shape is left to the general reader below, which
+// decides what it is.  Only for texts staged in shared memory.
+struct Stage8 {
+    const char *s;      // shared copy; s[0] is the character at absolute offset lo (16-byte aligned)
+    long long lo;
+    __device__ __forceinline__ unsigned long long operator()(long long p) const
+    {
+        const int r = (int)(p - lo);
+        const unsigned *w = reinterpret_cast<const unsigned *>(s + (r & ~3));
+        const unsigned a = w[0], b = w[1], c = w[2];
+        const unsigned sh = (unsigned)(r & 3) * 8u;
+        return (unsigned long long)__funnelshift_r(a, b, sh) | ((unsigned long long)__funnelshift_r(b, c, sh) << 32);
     }
-    __syncthreads();
-    if (v >= p.n) return;
-    const Text t{p.chars, staged ? stage : nullptr, a_lo};
-    long long q = p.offsets[v];
-    const long long lim = p.offsets[v + 1];
-    int sn = 0, level = 0, url_id = 0, st = HLSMAP_JSON_OK;
-    unsigned flags = 0;
-    double time = __longlong_as_double(0x7ff8000000000000ll);
+};
+
+__host__ __device__ constexpr unsigned long long lit8(const char *c, int n)
+{
+    unsigned long long v = 0;
+    for (int i = 0; i < n && i < 8; i++) v |= (unsigned long long)(unsigned char)c[i] << (8 * i);
+    return v;
+}
+
+// the literal `c` (n <= 24 characters) at q?  Advances q.
+template <int N>
+__device__ __forceinline__ bool eat8(const Stage8 &t, long long &q, long long lim, const char (&c)[N])
+{
+    constexpr int n = N - 1;
+    if (q + n > lim) return false;
+    bool ok = true;
+#pragma unroll
+    for (int o = 0; o < n; o += 8) {
+        const int m = n - o < 8 ? n - o : 8;
+        const unsigned long long mask = m == 8 ? ~0ull : ((1ull << (8 * m)) - 1ull);
+        ok = ok && ((t(q + o) & mask) == lit8(c + o, m));
+    }
+    if (ok) q += n;
+    return ok;
+}
+
+// The general reader: any subset of the properties in constructor order, every JSON number form.
+// Kept out of line so that the canonical fast path of the kernel does not carry its registers.
+__device__ __noinline__ void parse_view_general(const Text &t, long long q, long long lim, int &sn, int &level,
+                                                int &url_id, double &time, unsigned &flags, int &st)
+{
     bool first = true;
     do {
         if (!eat(t, q, lim, "{", 1)) {
@@ -426,6 +446,68 @@ view_from_json_kernel(const JsonReadParams p)
         }
         if (!eat(t, q, lim, "}", 1) || q != lim) st = HLSMAP_JSON_MALFORMED;
     } while (false);
+}
+
+}  // namespace
+
+constexpr int kParseStage = kThreads * kMaxChars;   // what 256 canonical texts can need
+
+__global__ void __launch_bounds__(256)
+view_from_json_kernel(const JsonReadParams p)
+{
+    __shared__ __align__(16) char stage[kParseStage + 16];
+    const long long v0 = (long long)blockIdx.x * blockDim.x, v = v0 + threadIdx.x;
+    // the CTA's texts are one contiguous run of characters: copy it in with coalesced loads
+    const long long v1 = v0 + blockDim.x < p.n ? v0 + blockDim.x : p.n;
+    const long long c_lo = p.offsets[v0], c_hi = p.offsets[v1];
+    const long long a_lo = c_lo & ~15ll;                 // aligned start; never before the buffer's own start
+    const bool staged = p.vec_ok && c_hi - a_lo <= kParseStage;
+    if (staged) {
+        for (long long o = a_lo + 16ll * threadIdx.x; o < c_hi; o += 16ll * blockDim.x) {
+            uint4 w;
+            if (o + 16 <= c_hi) {
+                w = *reinterpret_cast<const uint4 *>(p.chars + o);
+            } else {
+                char tmp[16];
+                for (int k = 0; k < 16; k++) tmp[k] = o + k < c_hi ? p.chars[o + k] : 0;
+                memcpy(&w, tmp, 16);
+            }
+            *reinterpret_cast<uint4 *>(stage + (o - a_lo)) = w;
+        }
+    }
+    __syncthreads();
+    if (v >= p.n) return;
+    const Text t{p.chars, staged ? stage : nullptr, a_lo};
+    long long q = p.offsets[v];
+    const long long lim = p.offsets[v + 1];
+    int sn = 0, level = 0, url_id = 0, st = HLSMAP_JSON_OK;
+    unsigned flags = 0;
+    double time = __longlong_as_double(0x7ff8000000000000ll);
+    if (staged) {       // the canonical full text in a few word operations; otherwise fall through
+        const Stage8 t8{stage, a_lo};
+        long long r = q;
+        int a = 0, b = 0, c = 0;
+        if (eat8(t8, r, lim, "{\"sn\":") && swar_int32(t8, r, lim, &a) &&
+            eat8(t8, r, lim, ",\"trackView\":{\"level\":") && swar_int32(t8, r, lim, &b) &&
+            eat8(t8, r, lim, ",\"urlId\":") && swar_int32(t8, r, lim, &c) && eat8(t8, r, lim, "},\"time\":")) {
+            double x = time;
+            unsigned f = HLSMAP_JSON_HAS_SN | HLSMAP_JSON_HAS_TRACKVIEW | HLSMAP_JSON_HAS_LEVEL |
+                         HLSMAP_JSON_HAS_URLID | HLSMAP_JSON_HAS_TIME;
+            bool ok = true;
+            if (eat8(t8, r, lim, "null")) f |= HLSMAP_JSON_TIME_NULL;
+            else ok = swar_plain_decimal(t8, r, lim, &x, c_json_pow10, c_json_ipow10) || eat_plain_decimal(t, r, lim, &x) != 0;
+            if (ok && eat8(t8, r, lim, "}") && r == lim) {
+                p.sn[v] = a;
+                p.level[v] = b;
+                p.url_id[v] = c;
+                p.time[v] = x;
+                p.flags[v] = (unsigned char)f;
+                p.status[v] = (unsigned char)HLSMAP_JSON_OK;
+                return;
+            }
+        }
+    }
+    parse_view_general(t, q, lim, sn, level, url_id, time, flags, st);
     p.sn[v] = sn;
     p.level[v] = level;
     p.url_id[v] = url_id;

@@ -142,3 +142,139 @@ def test_device_digit_generator_on_the_host(tmp_path):
         assert int(n) == len(s)
     for v in x[:20000]:
         assert oracle.js_number_to_string(float(v)) == js_from_repr(float(v))
+
+
+SWAR_HARNESS = r"""
+#include "swar.cuh"
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+using namespace hlsmap;
+int main() {
+    unsigned long long bad = 0;
+    srand(7);
+    for (long it = 0; it < 3000000; it++) {
+        char s[8];
+        const int nd = rand() % 9;
+        for (int i = 0; i < 8; i++) {
+            if (i < nd) s[i] = (char)('0' + rand() % 10);
+            else { int c; do { c = rand() % 256; } while (i == nd && c >= '0' && c <= '9'); s[i] = (char)c; }
+        }
+        unsigned long long v;
+        memcpy(&v, s, 8);
+        int exp = 0;
+        while (exp < 8 && s[exp] >= '0' && s[exp] <= '9') exp++;
+        if (leading_digits8(v) != exp) bad++;
+        for (int k = 1; k <= exp; k++) {
+            unsigned e = 0;
+            for (int i = 0; i < k; i++) e = e * 10 + (unsigned)(s[i] - '0');
+            if (digits8_value(v, k) != e) bad++;
+        }
+    }
+    printf("%llu\n", bad);
+    return bad != 0;
+}
+"""
+
+
+def test_word_at_a_time_digit_routines_on_the_host(tmp_path):
+    """csrc/swar.cuh (what the JSON reader takes its int32 columns with): the count of leading digit
+    bytes and the value of 1..8 digits of a little-endian word, against byte loops on random words."""
+    src, exe = tmp_path / "s.cpp", tmp_path / "s"
+    src.write_text(SWAR_HARNESS)
+    subprocess.check_call(["g++", "-O2", "-I", CSRC, "-o", str(exe), str(src)])
+    out = subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.strip()
+    assert out == "0"
+
+
+READERS_HARNESS = r"""
+#include "swar.cuh"
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <iostream>
+using namespace hlsmap;
+static const double P10[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
+                               1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+static const unsigned long long IP10[20] = {1ull, 10ull, 100ull, 1000ull, 10000ull, 100000ull, 1000000ull, 10000000ull,
+    100000000ull, 1000000000ull, 10000000000ull, 100000000000ull, 1000000000000ull, 10000000000000ull,
+    100000000000000ull, 1000000000000000ull, 10000000000000000ull, 100000000000000000ull, 1000000000000000000ull,
+    10000000000000000000ull};
+struct Get8 {
+    const char *s;          // zero-padded copy of the text
+    unsigned long long operator()(long long p) const { unsigned long long v; memcpy(&v, s + p, 8); return v; }
+};
+int main() {
+    std::string line;
+    while (std::getline(std::cin, line)) {           // "<i|d> <text>"
+        const char kind = line[0];
+        std::string txt = line.substr(2);
+        const long long lim = (long long)txt.size();
+        std::string padded = txt + std::string(32, '7');     // garbage digits beyond lim must not count
+        Get8 g{padded.c_str()};
+        long long q = 0;
+        if (kind == 'i') {
+            int v = 0;
+            const bool ok = swar_int32(g, q, lim, &v);
+            printf("%d %d %lld\n", ok ? 1 : 0, v, q);
+        } else {
+            double x = 0;
+            const bool ok = swar_plain_decimal(g, q, lim, &x, P10, IP10);
+            unsigned long long b;
+            memcpy(&b, &x, 8);
+            printf("%d %llx %lld\n", ok ? 1 : 0, b, q);
+        }
+    }
+}
+"""
+
+
+def test_word_at_a_time_readers_on_the_host(tmp_path):
+    """swar_int32 / swar_plain_decimal (the JSON reader's fast path) against Python's int() and
+    float(): whenever they accept a text they must give exactly that value and consume exactly the
+    number; shapes they do not cover must be declined, not guessed."""
+    import random
+    src, exe = tmp_path / "r.cpp", tmp_path / "r"
+    src.write_text(READERS_HARNESS)
+    subprocess.check_call(["g++", "-O2", "-I", CSRC, "-o", str(exe), str(src)])
+    rnd = random.Random(11)
+    cases = []
+    ints = [0, 1, -1, 9, 10, 99999999, 100000000, 123456789, 2147483647, -2147483648, 2147483648, -2147483649,
+            4294967296, 99999999999]
+    ints += [rnd.randrange(-2 ** 31, 2 ** 31) for _ in range(20000)]
+    ints += [rnd.randrange(-10 ** k, 10 ** k) for k in range(1, 11) for _ in range(300)]
+    for v in ints:
+        for tail in ("", ",", "}", "x"):
+            cases.append(("i", str(v) + tail, v, len(str(v))))
+    for bad in ("", "-", "01", "-01", "1.5", "1e3", "1E3", "12345678901", "a1", "--1", "+1"):
+        cases.append(("i", bad, None, 0))
+    decs = ["0", "0.5", "12.5", "86399.999", "0.1", "0.30000000000000004", "1234567.123456789012", "9999999.99999999",
+            "0.000001", "5e-7", "1.", ".5", "00.5", "12345678.5", "1.1234567890123456", "0.1234567890123456",
+            "86399.99900000001", "-0.0", "-12.75", "1.5e3", "7", "1234567"]
+    for _ in range(40000):
+        ni, nf = rnd.randrange(1, 8), rnd.randrange(0, 17)
+        ip = str(rnd.randrange(10 ** (ni - 1) if ni > 1 else 0, 10 ** ni))
+        fp = "".join(rnd.choice("0123456789") for _ in range(nf))
+        decs.append(("-" if rnd.random() < 0.1 else "") + ip + ("." + fp if nf else ""))
+    for _ in range(20000):                  # what JSON.stringify prints for playlist times
+        decs.append(repr(rnd.randrange(0, 86400000) / 1000.0 + rnd.choice([0.0, 1e-9, 2.5e-7])))
+    for d in decs:
+        for tail in ("", "}", ",\""):
+            cases.append(("d", d + tail, d, len(d)))
+    inp = "".join("%s %s\n" % (k, t) for k, t, _, _ in cases)
+    out = subprocess.run([str(exe)], input=inp, capture_output=True, text=True, check=True).stdout.split("\n")
+    accepted = {"i": 0, "d": 0}
+    for (kind, text, want, n), ln in zip(cases, out):
+        ok, val, q = ln.split()
+        if ok == "0":
+            continue
+        accepted[kind] += 1
+        assert int(q) == n, (text, ln)
+        if kind == "i":
+            assert want is not None and -2 ** 31 <= want < 2 ** 31 and int(val) == want, (text, ln)
+        else:
+            f = float(want)          # accepted => plain decimal => Python reads the same value
+            assert "e" not in want and "E" not in want, text
+            assert struct.unpack("<Q", struct.pack("<d", f))[0] == int(val, 16), (text, ln)
+    # the shapes the fast path exists for are accepted, not silently pushed to the slow path
+    assert accepted["i"] > 4 * 20000 and accepted["d"] > 3 * 45000
