@@ -90,6 +90,7 @@ struct hlsmap_map {
     size_t stage_smem = 0;
     int grid_search = 0, grid_filter = 0;
     int ipt = 2;                        // queries per thread of the search kernel (tiles of 256 * ipt)
+    int grid_search_wide = 0;           // SMALL maps: grid of the 1024-query-tile variant (0 = not offered)
     int uniform_levels = 0;             // > 0: every playlist has exactly this many levels
     bool sn_contig = false;             // every parsed track numbers its fragments contiguously (proven on the GPU)
 };
@@ -196,10 +197,10 @@ struct TilePlan {
     int tile_q = 0;
     int64_t n_tiles = 0;
 };
-TilePlan plan_tiles(const hlsmap_map *map, int path, int64_t nq)
+TilePlan plan_tiles(const hlsmap_map *map, int path, int64_t nq, int ipt = 0)
 {
     TilePlan t;
-    t.tile_q = path == HLSMAP_PATH_SEARCH ? resolve_search_tile(map->info.stage_all != 0, map->ipt)
+    t.tile_q = path == HLSMAP_PATH_SEARCH ? resolve_search_tile(map->info.stage_all != 0, ipt ? ipt : map->ipt)
                                           : kFilterTileQueries;
     t.n_tiles = (nq + t.tile_q - 1) / t.tile_q;
     return t;
@@ -502,6 +503,8 @@ static int map_create_impl(hlsmap_ctx *ctx, int32_t n_playlists, const int32_t *
     m->ipt = 2;
     if (const char *e = getenv(small ? "HLSMAP_IPT" : "HLSMAP_IPT_GENERAL")) m->ipt = atoi(e) == 4 ? 4 : 2;
     m->grid_search = resolve_search_max_grid(m->stage_smem, small, m->ipt);
+    // SMALL maps also offer 1024-query tiles (3 CTAs/SM): picked per batch, see list_core()
+    if (small && m->ipt == 2 && !getenv("HLSMAP_IPT")) m->grid_search_wide = resolve_search_max_grid(m->stage_smem, true, 4);
     m->grid_filter = resolve_filter_max_grid();
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess)
@@ -694,11 +697,17 @@ static int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
         return HLSMAP_OK;
     }
 
-    // (512-query tiles throughout.  1024-query tiles for large batches run back to back were worth
-    // 1.5 % while every tile paid a CTA-wide look-back; with the look-back done by one warp they
-    // measure the same, 35.6 us against 35.6 per 10^6-query batch, and are 2 us slower alone.)
-    const int ipt = map->ipt;
-    const TilePlan plan = plan_tiles(map, path, nq);
+    // Tile size.  Batches that run back to back (hlsmap_ctx_set_batch_overlap) and give every CTA
+    // two tiles or more take 1024-query tiles on SMALL maps: half as many look-backs and head-mark
+    // builds per query.  Measured per 10^6-query batch: 35.3 us against 36.3 on the bench mix
+    // (12.8 hits per query) and 22.8 against 26.6 on the 30-s look-ahead class (4.6 hits per query),
+    // where the per-tile costs weigh most; a batch on its own keeps 512-query tiles (51.7 us
+    // against 53.6: its ramp and tail are shorter).
+    int ipt = map->ipt;
+    if (path == HLSMAP_PATH_SEARCH && ctx->overlap && map->grid_search_wide > 0 &&
+        nq >= 2ll * map->grid_search_wide * resolve_search_tile(true, 4))
+        ipt = 4;
+    const TilePlan plan = plan_tiles(map, path, nq, ipt);
     const int64_t n_tiles = plan.n_tiles;
     if (n_tiles > 0x7fffffff) return fail(HLSMAP_ERR_INVALID, "batch too large: split it");
     r = prepare_scan(ctx, n_tiles, s);
@@ -754,7 +763,8 @@ static int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
     }
 #endif
     if (path == HLSMAP_PATH_SEARCH) {
-        const int grid = (int)(n_tiles < map->grid_search ? n_tiles : map->grid_search);
+        const int max_grid = ipt == map->ipt ? map->grid_search : map->grid_search_wide;
+        const int grid = (int)(n_tiles < max_grid ? n_tiles : max_grid);
         CK(launch_resolve_search(p, grid, map->stage_smem, s, ctx->overlap && d_trace == nullptr));
     } else {
         const int grid = (int)(n_tiles < map->grid_filter ? n_tiles : map->grid_filter);
