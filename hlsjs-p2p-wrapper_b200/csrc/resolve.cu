@@ -324,6 +324,9 @@ __device__ __forceinline__ unsigned long long warp_excl_scan64(unsigned long lon
 #ifndef HLSMAP_TRACE_BUILD
 #define HLSMAP_TRACE_BUILD 0
 #endif
+#ifndef HLSMAP_GENERAL_CTAS
+#define HLSMAP_GENERAL_CTAS 3     // CTAs per SM the general kernel is compiled for (4: 64 registers, spills; measured slower)
+#endif
 __device__ __forceinline__ void trace_mark(const ResolveParams &p, int tile, int slot, int who = 0)
 {
 #if HLSMAP_TRACE_BUILD
@@ -438,7 +441,7 @@ __device__ __forceinline__ void small_bounds(const double *s_start, const unsign
 // established on the GPU at upload), so a hit's sn is computed from its query's first hit instead of
 // being gathered: one L2 read per query with hits in place of one per hit, and sn[] is not streamed.
 template <bool SMALL, int IPT, bool SNC>
-__global__ void __launch_bounds__(kThreads, (SMALL && IPT == 2) ? 4 : ((SMALL || IPT == 2) ? 3 : 2))
+__global__ void __launch_bounds__(kThreads, (SMALL && IPT == 2) ? 4 : (SMALL ? 3 : (IPT == 2 ? HLSMAP_GENERAL_CTAS : 2)))
 resolve_search_kernel(const ResolveParams p)
 {
     static_assert(!(SMALL && SNC), "the shared-memory-resident kernel gathers sn from shared memory");
@@ -634,7 +637,8 @@ resolve_search_kernel(const ResolveParams p)
                 // window of start[] towards L2 as well -- first / last playlist -> descriptors -> span,
                 // followed by one warp over the iteration -- measured slower: 0.295 against 0.283 ms
                 // per configs[4] chunk; predicating the probes of finished chains in the bounds
-                // measured the same.)
+                // measured the same; staging tile A's window a second time, after B's bounds, so that
+                // A's hits are gathered from shared memory instead of L2: 0.329 ms.)
                 const long long tileC = (long long)tileB + gridDim.x;
                 if (tileC < p.n_tiles) {
                     const long long c0 = tileC * p.tile_q;
