@@ -73,6 +73,7 @@ SYMBOLS = {
     "hlsmap_get_segment_list": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P, _I64, _P, _P]),
     "hlsmap_get_segment_list_noalloc_dev": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P, _I64, _P, _P, _P]),
     "hlsmap_get_segment_list_dev_batches": (_INT, [_P, _I32, _P, _P, _P]),
+    "hlsmap_get_segment_list_dev_batches_timed": (_INT, [_P, _I32, _P, _P, _P, _P, _P]),
     "hlsmap_ctx_last_result": (_INT, [_P, _P, _P]),
     "hlsmap_get_segment_range_dev": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P, _P]),
     "hlsmap_get_segment_range": (_INT, [_P, _I64, _P, _P, _P, _P, _P, _P, _P]),

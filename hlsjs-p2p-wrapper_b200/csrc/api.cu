@@ -808,9 +808,27 @@ int hlsmap_get_segment_list_dev(hlsmap_map *map, int64_t nq, const int32_t *d_pl
 int hlsmap_get_segment_list_dev_batches(hlsmap_map *map, int32_t n, const hlsmap_batch *batches,
                                         void *stream, int32_t *n_launched)
 {
+    return hlsmap_get_segment_list_dev_batches_timed(map, n, batches, stream, nullptr, nullptr, n_launched);
+}
+
+int hlsmap_get_segment_list_dev_batches_timed(hlsmap_map *map, int32_t n, const hlsmap_batch *batches,
+                                              void *stream, void *event_begin, void *event_end,
+                                              int32_t *n_launched)
+{
     if (n_launched) *n_launched = 0;
     if (!map) return fail(HLSMAP_ERR_INVALID, "null map");
     if (n < 0 || (n > 0 && !batches)) return fail(HLSMAP_ERR_INVALID, "get_segment_list_dev_batches: null batch array");
+    {
+        int r = use_ctx(map->ctx);
+        if (r) return r;
+    }
+    cudaStream_t s = stream ? (cudaStream_t)stream : map->ctx->stream;
+    if (event_begin) CK(cudaEventRecord((cudaEvent_t)event_begin, s));
+    struct EndMark {        // the closing event is recorded on every way out
+        void *ev;
+        cudaStream_t s;
+        ~EndMark() { if (ev) cudaEventRecord((cudaEvent_t)ev, s); }
+    } end_mark{event_end, s};
     for (int32_t i = 0; i < n; i++) {
         const hlsmap_batch &b = batches[i];
         const int r = list_core(map, b.nq, b.d_playlist, b.d_level, b.d_begin, b.d_duration, b.d_offsets,

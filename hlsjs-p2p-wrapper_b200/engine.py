@@ -328,11 +328,12 @@ class DeviceMap:
         N.check(code)
         return res
 
-    def get_segment_list_dev_batches(self, batches, stream=None):
+    def get_segment_list_dev_batches(self, batches, stream=None, event_begin=None, event_end=None):
         """Several independent device-pointer batches with one call into the library.  `batches`: a
         sequence of dicts with nq, d_playlist (or 0), d_level, d_begin, d_duration, d_offsets, d_sn_out,
         d_time_out, capacity, d_status (optional) -- or a ready-made ctypes array of N.Batch.  Asynchronous;
-        returns the number of batches launched."""
+        returns the number of batches launched.  event_begin / event_end: raw cudaEvent_t handles (ints)
+        recorded on the stream right before the first and right after the last launch, inside the call."""
         if not isinstance(batches, ctypes.Array):
             arr = (N.Batch * len(batches))()
             for a, b in zip(arr, batches):
@@ -342,8 +343,10 @@ class DeviceMap:
                 a.hit_capacity, a.d_status = int(b.get("capacity", 0)), b.get("d_status") or None
             batches = arr
         done = ctypes.c_int32(0)
-        N.check(self._lib.hlsmap_get_segment_list_dev_batches(self._h, len(batches), batches, _stream(stream),
-                                                              ctypes.byref(done)))
+        N.check(self._lib.hlsmap_get_segment_list_dev_batches_timed(
+            self._h, len(batches), batches, _stream(stream),
+            ctypes.c_void_p(event_begin) if event_begin else None,
+            ctypes.c_void_p(event_end) if event_end else None, ctypes.byref(done)))
         return done.value
 
     def get_segment_list_noalloc_dev(self, nq, d_playlist, d_level, d_begin, d_duration, d_offsets,

@@ -213,6 +213,13 @@ typedef struct hlsmap_batch {
 } hlsmap_batch;
 int hlsmap_get_segment_list_dev_batches(hlsmap_map *map, int32_t n, const hlsmap_batch *batches,
                                         void *stream, int32_t *n_launched);
+/* The same, bracketed by the caller's CUDA events: event_begin (a cudaEvent_t, nullable) is recorded
+ * on the stream immediately before the first launch and event_end (nullable) immediately after the
+ * last, from inside the call -- so that the device time of the n batches can be measured without
+ * the host language's call overhead between "event recorded" and "first kernel issued". */
+int hlsmap_get_segment_list_dev_batches_timed(hlsmap_map *map, int32_t n, const hlsmap_batch *batches,
+                                              void *stream, void *event_begin, void *event_end,
+                                              int32_t *n_launched);
 /* Counters of the most recent batch issued through ctx (synchronises its stream). */
 int hlsmap_ctx_last_result(hlsmap_ctx *ctx, void *stream, hlsmap_result *result);
 

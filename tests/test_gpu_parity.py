@@ -499,6 +499,15 @@ def test_several_batches_with_one_call(ctx):
                 assert np.array_equal(s["tm"][:s["H"]].cpu().numpy().view(np.uint64), s["ref"][3].view(np.uint64))
         finally:
             ctx.set_batch_overlap(False)
+    # the caller's events, recorded inside the call, bracket the batches on their stream
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    e1.record(stream)
+    torch.cuda.synchronize()
+    assert m.get_segment_list_dev_batches([batch(s) for s in sets], stream.cuda_stream,
+                                          event_begin=e0.cuda_event, event_end=e1.cuda_event) == len(sets)
+    torch.cuda.synchronize()
+    assert 0.005 < e0.elapsed_time(e1) < 50.0
     # count-only batches size the buffers; a broken batch in the middle stops the call there
     for s in sets:
         s["off"].fill_(-1)
