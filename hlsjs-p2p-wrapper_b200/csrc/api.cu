@@ -52,6 +52,7 @@ struct hlsmap_ctx {
     ScanCounters *ctr = nullptr;        // scan scratch headers, one per scratch set (2)
     DeviceResult *d_result = nullptr;   // results, one per scratch set (2)
     bool overlap = false;               // consecutive search batches may overlap (PDL)
+    int64_t host_chunk = 262144;        // largest chunk of that pipeline, in queries (HLSMAP_HOST_CHUNK at creation, experiments)
     bool host_pipeline = true;          // chunked upload/compute/download of large host-pointer calls
                                         // (HLSMAP_NO_PIPELINE in the environment at context creation turns it off)
     unsigned set_launches[2] = {0, 0};  // kernels launched on each scratch set (ticket slot parity)
@@ -211,7 +212,7 @@ TilePlan plan_tiles(const hlsmap_map *map, int path, int64_t nq, int ipt = 0)
 extern "C" {
 
 const char *hlsmap_last_error(void) { return g_err.c_str(); }
-int hlsmap_version(void) { return 100; }
+int hlsmap_version(void) { return 200; }
 
 int hlsmap_device_count(void)
 {
@@ -237,6 +238,10 @@ int hlsmap_ctx_create(int device, hlsmap_ctx **out)
     if (!c) return fail(HLSMAP_ERR_NOMEM, "out of host memory");
     c->device = device;
     c->host_pipeline = getenv("HLSMAP_NO_PIPELINE") == nullptr;   // read once, here
+    if (const char *e = getenv("HLSMAP_HOST_CHUNK")) {
+        const long long v = atoll(e);
+        if (v >= 1024) c->host_chunk = (v + 1023) / 1024 * 1024;
+    }
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, device));
     if (prop.major < 10) {
@@ -877,8 +882,14 @@ int hlsmap_get_segment_list(hlsmap_map *map, int64_t nq, const int32_t *playlist
     if (status) { if ((r = ensure_slot(ctx, 5, n1, &v))) return r; d_st = (uint8_t *)v; }
     // Large filling batches go through a chunked pipeline: while chunk c's hits travel to the
     // host, chunk c+1's queries travel to the device (PCIe is full duplex) and its kernel runs.
-    constexpr int64_t kChunk = 131072;      // queries per chunk (multiple of 1024: aligned sections)
+    // Chunks of host_chunk queries (a multiple of 1024: aligned sections).  Few, large copies win:
+    // measured per 10^6-query step 3.10 ms with 262144-query chunks, 3.19 with 131072, 3.39 with
+    // 65536, 3.29 without the pipeline; sizes ramping up from 32768 (the first hits on their way
+    // back sooner, but two more chunks) 3.28.
+    const int64_t kChunk = ctx->host_chunk;
     if (fill && nq >= 2 * kChunk && ctx->host_pipeline) {
+        std::vector<int64_t> cut{0};
+        while (cut.back() < nq) cut.push_back(cut.back() + kChunk < nq ? cut.back() + kChunk : nq);
         int64_t dev_cap = ctx->slot_bytes[6] / 4 < ctx->slot_bytes[7] / 8 ? ctx->slot_bytes[6] / 4
                                                                          : ctx->slot_bytes[7] / 8;
         int64_t want = nq * 16 + 1024;
@@ -888,7 +899,7 @@ int hlsmap_get_segment_list(hlsmap_map *map, int64_t nq, const int32_t *playlist
         if ((r = ensure_slot(ctx, 6, dev_cap * 4, &v))) return r; d_sn = (int *)v;
         if ((r = ensure_slot(ctx, 7, dev_cap * 8, &v))) return r; d_tm = (double *)v;
         auto upload = [&](int64_t c) -> int {
-            const int64_t q0 = c * kChunk, n = nq - q0 < kChunk ? nq - q0 : kChunk;
+            const int64_t q0 = cut[c], n = cut[c + 1] - cut[c];
             if (playlist) CK(cudaMemcpyAsync(d_pl + q0, playlist + q0, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->s_in));
             CK(cudaMemcpyAsync(d_lv + q0, level + q0, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->s_in));
             CK(cudaMemcpyAsync(d_bg + q0, begin + q0, (size_t)n * 8, cudaMemcpyHostToDevice, ctx->s_in));
@@ -896,14 +907,14 @@ int hlsmap_get_segment_list(hlsmap_map *map, int64_t nq, const int32_t *playlist
             CK(cudaEventRecord(ctx->ev_in[c & 1], ctx->s_in));
             return HLSMAP_OK;
         };
-        const int64_t n_chunks = (nq + kChunk - 1) / kChunk;
+        const int64_t n_chunks = (int64_t)cut.size() - 1;
         hlsmap_result acc{};
         unsigned long long base = 0;
         bool overflow_dev = false;
         CK(cudaStreamSynchronize(ctx->s_out));          // earlier downloads are done with the slots
         if ((r = upload(0))) return r;
         for (int64_t c = 0; c < n_chunks; c++) {
-            const int64_t q0 = c * kChunk, n = nq - q0 < kChunk ? nq - q0 : kChunk;
+            const int64_t q0 = cut[c], n = cut[c + 1] - cut[c];
             CK(cudaStreamWaitEvent(s, ctx->ev_in[c & 1], 0));
             if (c + 1 < n_chunks && (r = upload(c + 1))) return r;
             hlsmap_result rc{};

@@ -22,7 +22,7 @@ def test_library_builds_loads_and_exports_every_declared_symbol():
     assert declared == set(N.SYMBOLS), declared ^ set(N.SYMBOLS)
     for name in declared:
         assert getattr(lib, name) is not None
-    assert lib.hlsmap_version() == 100
+    assert lib.hlsmap_version() == 200
     assert isinstance(lib.hlsmap_last_error(), bytes)
 
 

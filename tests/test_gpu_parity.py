@@ -321,7 +321,7 @@ def test_host_pipeline_capacity_and_statuses(ctx):
     """Chunked path: caller capacity one short -> CAPACITY error with the needed total; statuses
     and unparsed / missing tallies accumulate across chunks."""
     t = synth.hls_mock_tables(3, 1, False)              # level 1 parsed, 0 and 2 unparsed
-    nq = 400_000
+    nq = 600_000
     rng = np.random.default_rng(9)
     q = QueryBatch(np.zeros(nq, np.int32), rng.integers(-1, 5, nq).astype(np.int32),
                    rng.integers(0, 2500, nq).astype(np.float64), rng.integers(0, 60, nq).astype(np.float64))
