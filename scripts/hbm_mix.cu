@@ -77,6 +77,121 @@ __global__ void k_write12_bulk(double *o, int *o2, size_t n, double v)
     if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
+// The list form's traffic in the list form's SHAPE, without any of its arithmetic: persistent CTAs take
+// 512-query tiles in order; a tile reads its queries (4 + 8 + 8 B each, three contiguous runs), writes
+// 512 offsets and `hpt` hits as one contiguous run of doubles and one of ints at hpt * tile.
+__global__ void k_mix_tiled(const int *lv, const double *bg, const double *du, int *off, double *tm, int *sn,
+                            size_t n_tiles, int hpt, unsigned *ticket)
+{
+    __shared__ unsigned s_tile;
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+        __syncthreads();
+        const size_t tile = s_tile;
+        if (tile >= n_tiles) break;
+        const size_t q0 = tile * 512 + threadIdx.x * 2;
+        const int2 l = __ldcs(reinterpret_cast<const int2 *>(lv + q0));
+        const double2 b = __ldcs(reinterpret_cast<const double2 *>(bg + q0));
+        const double2 d = __ldcs(reinterpret_cast<const double2 *>(du + q0));
+        const double x = b.x + d.x + b.y + d.y + l.x + l.y;
+        __stcs(reinterpret_cast<int2 *>(off + q0), make_int2((int)q0, (int)q0 + 1));
+        double *t = tm + tile * hpt;
+        int *s = sn + tile * hpt;
+        for (int i = threadIdx.x; i < hpt; i += blockDim.x) {
+            __stcs(t + i, x);
+            __stcs(s + i, i);
+        }
+    }
+}
+
+// The same tiles, their hits written by bulk copies out of shared memory (1024 slots per copy pair,
+// two buffers in flight) instead of by per-thread stores.  hpt must be a multiple of 4 (alignment).
+__global__ void k_mix_tiled_bulk(const int *lv, const double *bg, const double *du, int *off, double *tm, int *sn,
+                                 size_t n_tiles, int hpt, unsigned *ticket)
+{
+    constexpr int CH = 1024;
+    __shared__ __align__(128) double sd[2][CH];
+    __shared__ __align__(128) int si[2][CH];
+    __shared__ unsigned s_tile;
+    int b = 0;
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+        __syncthreads();
+        const size_t tile = s_tile;
+        if (tile >= n_tiles) break;
+        const size_t q0 = tile * 512 + threadIdx.x * 2;
+        const int2 l = __ldcs(reinterpret_cast<const int2 *>(lv + q0));
+        const double2 bb = __ldcs(reinterpret_cast<const double2 *>(bg + q0));
+        const double2 d = __ldcs(reinterpret_cast<const double2 *>(du + q0));
+        const double x = bb.x + d.x + bb.y + d.y + l.x + l.y;
+        __stcs(reinterpret_cast<int2 *>(off + q0), make_int2((int)q0, (int)q0 + 1));
+        double *t = tm + tile * hpt;
+        int *s = sn + tile * hpt;
+        for (int c0 = 0; c0 < hpt; c0 += CH, b ^= 1) {
+            const int n = hpt - c0 < CH ? hpt - c0 : CH;
+            if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            __syncthreads();
+            for (int i = threadIdx.x; i < n; i += blockDim.x) { sd[b][i] = x; si[b][i] = i; }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(t + c0),
+                             "r"((unsigned)__cvta_generic_to_shared(&sd[b][0])), "r"(n * 8) : "memory");
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(s + c0),
+                             "r"((unsigned)__cvta_generic_to_shared(&si[b][0])), "r"(n * 4) : "memory");
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+        }
+    }
+    if (threadIdx.x == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+// ... and with every WARP staging 128 slots of its own and issuing its own pair of small bulk copies
+// (1 KB + 512 B), no CTA barrier in the loop: the granularity a kernel can use whose warps run free.
+__global__ void k_mix_tiled_bulk_warp(const int *lv, const double *bg, const double *du, int *off, double *tm, int *sn,
+                                      size_t n_tiles, int hpt, unsigned *ticket)
+{
+    constexpr int CH = 128;
+    __shared__ __align__(128) double sd[8][2][CH];
+    __shared__ __align__(128) int si[8][2][CH];
+    __shared__ unsigned s_tile;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int b = 0;
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+        __syncthreads();
+        const size_t tile = s_tile;
+        if (tile >= n_tiles) break;
+        const size_t q0 = tile * 512 + threadIdx.x * 2;
+        const int2 l = __ldcs(reinterpret_cast<const int2 *>(lv + q0));
+        const double2 bb = __ldcs(reinterpret_cast<const double2 *>(bg + q0));
+        const double2 d = __ldcs(reinterpret_cast<const double2 *>(du + q0));
+        const double x = bb.x + d.x + bb.y + d.y + l.x + l.y;
+        __stcs(reinterpret_cast<int2 *>(off + q0), make_int2((int)q0, (int)q0 + 1));
+        double *t = tm + tile * hpt;
+        int *s = sn + tile * hpt;
+        for (int c0 = warp * CH; c0 + CH <= hpt; c0 += 8 * CH, b ^= 1) {      // (a ragged end is left out: same bytes +- 1 %)
+            if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 4; j++) { sd[warp][b][lane + 32 * j] = x; si[warp][b][lane + 32 * j] = c0 + j; }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) {
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(t + c0),
+                             "r"((unsigned)__cvta_generic_to_shared(&sd[warp][b][0])), "r"(CH * 8) : "memory");
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(s + c0),
+                             "r"((unsigned)__cvta_generic_to_shared(&si[warp][b][0])), "r"(CH * 4) : "memory");
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+        }
+    }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
 template <class F>
 static float timed(F f, int reps)
 {
@@ -107,6 +222,33 @@ int main()
         float wb = timed([&] { k_write12_bulk<<<grid, th>>>(o, o2, n / 4, 1.0); }, 5);
         printf("{\"ctas_per_sm\": %d, \"write_GBps\": %.0f, \"write_8plus4_GBps\": %.0f, \"write_8plus4_bulk_GBps\": %.0f}\n",
                cps, n / 4 * 8 / w / 1e6, n / 4 * 12 / w12 / 1e6, n / 4 * 12 / wb / 1e6);
+    }
+    {   // 2^22 queries in 512-query tiles, 6537 hits per tile (12.77 per query): 4 CTAs per SM as the kernel runs
+        const size_t nq = (size_t)1 << 22, n_tiles = nq / 512;
+        const int hpt = 6537;
+        unsigned *ticket;
+        cudaMalloc(&ticket, 4);
+        int *lv = reinterpret_cast<int *>(a);
+        double *bg = a + nq, *du = a + 2 * nq;
+        for (int cps : {3, 4, 8}) {
+            float m = timed([&] {
+                cudaMemsetAsync(ticket, 0, 4);
+                k_mix_tiled<<<sms * cps, 256>>>(lv, bg, du, o2 + (n - nq - 16), o, o2, n_tiles, hpt, ticket);
+            }, 5);
+            const int hb = 6536;
+            float mb = timed([&] {
+                cudaMemsetAsync(ticket, 0, 4);
+                k_mix_tiled_bulk<<<sms * cps, 256>>>(lv, bg, du, o2 + (n - nq - 16), o, o2, n_tiles, hb, ticket);
+            }, 5);
+            float mw = timed([&] {
+                cudaMemsetAsync(ticket, 0, 4);
+                k_mix_tiled_bulk_warp<<<sms * cps, 256>>>(lv, bg, du, o2 + (n - nq - 16), o, o2, n_tiles, hb, ticket);
+            }, 5);
+            printf("{\"ctas_per_sm\": %d, \"mix_tiled_like_the_list_form_GBps\": %.0f, \"same_with_bulk_stores_GBps\": %.0f, "
+                   "\"same_with_per_warp_bulk_stores_GBps\": %.0f}\n", cps,
+                   (nq * 28.0 + n_tiles * 12.0 * hpt) / m / 1e6, (nq * 28.0 + n_tiles * 12.0 * hb) / mb / 1e6,
+                   (nq * 28.0 + n_tiles * 12.0 * (hb / 128 * 128)) / mw / 1e6);
+        }
     }
     for (int cps : {4, 8, 16}) {
         const int grid = sms * cps, th = 256;
