@@ -244,6 +244,16 @@ int main()
                 cudaMemsetAsync(ticket, 0, 4);
                 k_mix_tiled_bulk_warp<<<sms * cps, 256>>>(lv, bg, du, o2 + (n - nq - 16), o, o2, n_tiles, hb, ticket);
             }, 5);
+            // the same per-thread stores with every tile's run starting on a line boundary (6528 = 51 * 128
+            // slots per tile), and on a 64-byte boundary of the 8-byte column (6536)
+            for (int h2 : {6528, 6536}) {
+                float ma = timed([&] {
+                    cudaMemsetAsync(ticket, 0, 4);
+                    k_mix_tiled<<<sms * cps, 256>>>(lv, bg, du, o2 + (n - nq - 16), o, o2, n_tiles, h2, ticket);
+                }, 5);
+                printf("{\"ctas_per_sm\": %d, \"hits_per_tile\": %d, \"mix_tiled_per_thread_stores_GBps\": %.0f}\n", cps, h2,
+                       (nq * 28.0 + n_tiles * 12.0 * h2) / ma / 1e6);
+            }
             printf("{\"ctas_per_sm\": %d, \"mix_tiled_like_the_list_form_GBps\": %.0f, \"same_with_bulk_stores_GBps\": %.0f, "
                    "\"same_with_per_warp_bulk_stores_GBps\": %.0f}\n", cps,
                    (nq * 28.0 + n_tiles * 12.0 * hpt) / m / 1e6, (nq * 28.0 + n_tiles * 12.0 * hb) / mb / 1e6,
