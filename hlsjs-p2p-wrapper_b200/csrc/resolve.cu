@@ -331,6 +331,9 @@ __device__ __forceinline__ unsigned long long warp_excl_scan64(unsigned long lon
 #ifndef HLSMAP_TRACE_BUILD
 #define HLSMAP_TRACE_BUILD 0
 #endif
+#ifndef HLSMAP_WIDE_CTAS
+#define HLSMAP_WIDE_CTAS 3        // CTAs per SM the 1024-query variant of the shared-memory kernel is compiled for (4: 64 registers, 36 bytes of spills; 33.5 against 33.1 us per 10^6-query batch, 27.1 against 23.6 on the look-ahead class: 977 tiles over 592 CTAs)
+#endif
 #ifndef HLSMAP_GENERAL_CTAS
 #define HLSMAP_GENERAL_CTAS 3     // CTAs per SM the general kernel is compiled for (4: 64 registers, spills; measured slower)
 #endif
@@ -448,7 +451,7 @@ __device__ __forceinline__ void small_bounds(const double *s_start, const unsign
 // established on the GPU at upload), so a hit's sn is computed from its query's first hit instead of
 // being gathered: one L2 read per query with hits in place of one per hit, and sn[] is not streamed.
 template <bool SMALL, int IPT, bool SNC>
-__global__ void __launch_bounds__(kThreads, (SMALL && IPT == 2) ? 4 : (SMALL ? 3 : (IPT == 2 ? HLSMAP_GENERAL_CTAS : 2)))
+__global__ void __launch_bounds__(kThreads, (SMALL && IPT == 2) ? 4 : (SMALL ? HLSMAP_WIDE_CTAS : (IPT == 2 ? HLSMAP_GENERAL_CTAS : 2)))
 resolve_search_kernel(const ResolveParams p)
 {
     static_assert(!(SMALL && SNC), "the shared-memory-resident kernel gathers sn from shared memory");
