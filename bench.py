@@ -314,9 +314,10 @@ def list_form_sets(pk, synth, torch, dmap, dev, q0, rank, min_bytes):
 def timed_list_form(torch, ctx, dmap, sets, stream, steps, warmup, barrier=None, count_only=False):
     """`steps` back-to-back device-resident list-form batches over rotating buffer sets, CUDA events
     on the launch stream.  The K batches are handed to the library with ONE call
-    (hlsmap_get_segment_list_dev_batches: K launches issued from C), so the host language's
-    per-call cost cannot pace the GPU.  -> (region ms, mean hits per step, host time of that call
-    per launch in us, (host t0, host t1) of the timed region)."""
+    (hlsmap_get_segment_list_dev_batches), so the host language's per-call cost cannot pace the GPU;
+    with batch overlap allowed the library resolves up to 32 of them per kernel launch (one ramp and
+    one tail per launch instead of per batch).  -> (region ms, mean hits per step, host time of that
+    call per batch in us, (host t0, host t1) of the timed region, kernel launches of the call)."""
     from hlsjs_p2p_wrapper_b200 import _native as N
     nq = len(sets[0]["q"])
 
@@ -351,7 +352,9 @@ def timed_list_form(torch, ctx, dmap, sets, stream, steps, warmup, barrier=None,
         barrier()
     else:
         torch.cuda.synchronize()
-    return t_begin.elapsed_time(t_end), hits / steps, issue_us, (h0, time.perf_counter())
+    h1 = time.perf_counter()
+    launches = int(dmap.last_result(stream).kernel_launches)     # of the whole call, counted by the library
+    return t_begin.elapsed_time(t_end), hits / steps, issue_us, (h0, h1), launches
 
 
 def path_rows(pk, synth, torch, ctx, dmap, dev, tables, q0, stream, peak, steps, warmup):
@@ -686,7 +689,7 @@ def run_ours(args):
     # behind its predecessor's tail, as it would in a serving loop.
     overlap = os.environ.get("HLSMAP_BENCH_NO_OVERLAP") != "1"
     ctx.set_batch_overlap(overlap)
-    my_ms, hits_per_step, issue_us, sampler.window = timed_list_form(
+    my_ms, hits_per_step, issue_us, sampler.window, timed_launches = timed_list_form(
         torch, ctx, dmap, sets, stream, args.steps, args.warmup, barrier=barrier, count_only=count_only)
     region_ms = max_over_ranks(my_ms)
     per_rank_ms = all_ranks(my_ms / args.steps)
@@ -835,12 +838,17 @@ def run_ours(args):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "frac_of_nominal_8TBs": achieved / 8000.0,
-                         "algorithmic_bytes_per_launch": alg_bytes,
+                         "algorithmic_bytes_per_batch": alg_bytes,
+                         "algorithmic_bytes_per_launch": alg_bytes * args.steps / max(timed_launches, 1),
                          "kernel_ms_mean": mean_kernel_ms,
-                         "timing": "CUDA events on the launch stream around the %d timed launches, recorded from "
+                         "timing": "CUDA events on the launch stream around the %d timed batches, recorded from "
                                    "inside the one C call that issues them (begin: right before the first launch, "
-                                   "end: right after the last); consecutive launches overlap (programmatic "
-                                   "dependent launch) = %s" % (args.steps, overlap),
+                                   "end: right after the last); consecutive batches may overlap (the caller "
+                                   "promised disjoint buffers) = %s: the library then resolves up to 32 batches "
+                                   "per kernel launch (%d launches for the %d batches) and lets consecutive "
+                                   "launches overlap (programmatic dependent launch); kernel_ms_mean = region / "
+                                   "batches" % (args.steps, overlap, timed_launches, args.steps),
+                         "kernel_launches_timed_region": timed_launches,
                          "kernel_ms_isolated_mean": float(np.mean(kernel_ms)),
                          "kernel_ms_isolated_min": float(np.min(kernel_ms)),
                          "frac_isolated": alg_bytes / (float(np.mean(kernel_ms)) * 1e-3) / 1e9 / peak,
@@ -857,7 +865,7 @@ def run_ours(args):
                                      "(hlsmap_get_segment_list with NULL hit arrays); a caller that cannot know "
                                      "the count either pays that pass (24 B/query up, 4 B/query back) or "
                                      "over-allocates"},
-            "gpu_launches": args.steps * world, "clocks": clocks, "node": node_version(),
+            "gpu_launches": timed_launches * world, "clocks": clocks, "node": node_version(),
             "other_rows": rows, "e2e_range_form": e2e_range, "sharded_config5": sharded,
         }
         print(json.dumps(line))

@@ -54,6 +54,7 @@ struct hlsmap_ctx {
     bool overlap = false;               // consecutive search batches may overlap (PDL)
     int64_t host_chunk = 262144;        // largest chunk of that pipeline, in queries (HLSMAP_HOST_CHUNK at creation, experiments)
     bool host_pipeline = true;          // chunked upload/compute/download of large host-pointer calls
+    bool no_fuse = false;               // HLSMAP_NO_FUSE: a batches call issues one launch per batch even when it may fuse them
                                         // (HLSMAP_NO_PIPELINE in the environment at context creation turns it off)
     unsigned set_launches[2] = {0, 0};  // kernels launched on each scratch set (ticket slot parity)
     DeviceResult *h_result = nullptr;   // pinned
@@ -238,6 +239,7 @@ int hlsmap_ctx_create(int device, hlsmap_ctx **out)
     if (!c) return fail(HLSMAP_ERR_NOMEM, "out of host memory");
     c->device = device;
     c->host_pipeline = getenv("HLSMAP_NO_PIPELINE") == nullptr;   // read once, here
+    c->no_fuse = getenv("HLSMAP_NO_FUSE") != nullptr;             // experiments: one launch per batch of a batches call
     if (const char *e = getenv("HLSMAP_HOST_CHUNK")) {
         const long long v = atoll(e);
         if (v >= 1024) c->host_chunk = (v + 1023) / 1024 * 1024;
@@ -672,7 +674,33 @@ int hlsmap_map_slide_tracks(hlsmap_map *map, int64_t n, const int32_t *playlist,
 // ---------------------------------------------------------------------------------------
 // One batch on `stream`.  `base` = hits produced by earlier chunks of the same logical call:
 // offsets, hit positions and the reported total all include it.
-static int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
+static // The map's tables and the context's scratch, as the list-form kernels take them (after prepare_scan).
+void fill_table_params(ResolveParams &p, const hlsmap_map *map, hlsmap_ctx *ctx)
+{
+    p.desc = map->d_desc;
+    p.playlist_base = map->d_playlist_base;
+    p.n_playlists = map->n_playlists;
+    p.start = map->d_start;
+    p.sn = map->d_sn;
+    p.n_frag_padded = map->n_frag_padded;
+    p.tile_status = status_of(ctx);
+    p.ctr = ctr_of(ctx);
+    p.result = result_of(ctx);
+    p.epoch = ctx->epoch;
+    p.tslot = ctx->set_launches[ctx->epoch & 1u] & 1u;
+    p.stage_elems = map->stage_elems;
+    p.stage_all = map->info.stage_all;
+    p.small = map->info.stage_all;
+    p.sn_contig = (map->sn_contig && !map->info.stage_all) ? 1 : 0;
+    p.uniform_levels = map->uniform_levels;
+    p.hint = map->d_hint;
+    p.grid = map->d_grid;
+    p.grid_padded = map->grid_padded;
+    p.n_tracks_padded = map->n_tracks_padded;
+    p.n_base_padded = map->n_base_padded;
+}
+
+int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
                      const int32_t *d_level, const double *d_begin,
                      const double *d_duration, int32_t *d_offsets, int32_t *d_sn_out,
                      double *d_time_out, int64_t hit_capacity, uint8_t *d_status,
@@ -719,12 +747,7 @@ static int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
     if (r) return r;
 
     ResolveParams p{};
-    p.desc = map->d_desc;
-    p.playlist_base = map->d_playlist_base;
-    p.n_playlists = map->n_playlists;
-    p.start = map->d_start;
-    p.sn = map->d_sn;
-    p.n_frag_padded = map->n_frag_padded;
+    fill_table_params(p, map, ctx);
     p.nq = nq;
     p.q_playlist = d_playlist;
     p.q_level = d_level;
@@ -735,25 +758,10 @@ static int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
     p.time_out = d_time_out;
     p.capacity = d_sn_out ? hit_capacity : 0;
     p.status = d_status;
-    p.tile_status = status_of(ctx);
-    p.ctr = ctr_of(ctx);
-    p.result = result_of(ctx);
-    p.epoch = ctx->epoch;
-    p.tslot = ctx->set_launches[ctx->epoch & 1u] & 1u;
     p.n_tiles = (int)n_tiles;
     p.tile_q = plan.tile_q;
     p.base = base;
-    p.stage_elems = map->stage_elems;
-    p.stage_all = map->info.stage_all;
-    p.small = map->info.stage_all;
-    p.sn_contig = (map->sn_contig && !map->info.stage_all) ? 1 : 0;
-    p.uniform_levels = map->uniform_levels;
     p.ipt = ipt;
-    p.hint = map->d_hint;
-    p.grid = map->d_grid;
-    p.grid_padded = map->grid_padded;
-    p.n_tracks_padded = map->n_tracks_padded;
-    p.n_base_padded = map->n_base_padded;
     p.vec_ok = al16(d_level) && al16(d_begin) && al16(d_duration) && al16(d_offsets) &&
                (!d_playlist || al16(d_playlist)) &&
                (!d_status || (reinterpret_cast<uintptr_t>(d_status) & 3u) == 0);
@@ -800,6 +808,71 @@ static int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
     return HLSMAP_OK;
 }
 
+// n >= 2 non-empty batches with ONE launch of the search kernel (their tiles numbered consecutively;
+// every CTA stages the tables once for all of them): the batches run concurrently, which the caller
+// has allowed with hlsmap_ctx_set_batch_overlap.  Measured on B200, 10^6-query batches on the bench
+// map: 33.0 us per batch as overlapped launches, see BASELINE.md for the fused figure.
+int list_fused(hlsmap_map *map, const hlsmap_batch *bs, int n, void *stream)
+{
+    hlsmap_ctx *ctx = map->ctx;
+    cudaStream_t s = stream ? (cudaStream_t)stream : ctx->stream;
+    int64_t total_q = 0;
+    for (int i = 0; i < n; i++) {
+        const hlsmap_batch &b = bs[i];
+        if (b.nq <= 0 || !b.d_offsets || !b.d_level || !b.d_begin || !b.d_duration)
+            return fail(HLSMAP_ERR_INVALID, "get_segment_list: null query/offset arrays");
+        if ((b.d_sn_out == nullptr) != (b.d_time_out == nullptr))
+            return fail(HLSMAP_ERR_INVALID, "get_segment_list: sn_out and time_out go together");
+        if (b.hit_capacity < 0) return fail(HLSMAP_ERR_INVALID, "negative hit capacity");
+        total_q += b.nq;
+    }
+    ctx->last_path = HLSMAP_PATH_SEARCH;
+    ctx->last_launches = 0;
+    ctx->have_last = true;
+    int ipt = map->ipt;
+    if (map->grid_search_wide > 0 && total_q >= 2ll * map->grid_search_wide * resolve_search_tile(true, 4)) ipt = 4;
+    const int tile_q = resolve_search_tile(map->info.stage_all != 0, ipt);
+
+    ResolveParams p{};
+    BatchDesc fb[kMaxFused] = {};
+    int64_t n_tiles = 0;
+    for (int i = 0; i < n; i++) {
+        const hlsmap_batch &b = bs[i];
+        BatchDesc &d = fb[i];
+        const int64_t t = (b.nq + tile_q - 1) / tile_q;
+        d.q_playlist = b.d_playlist;
+        d.q_level = b.d_level;
+        d.q_begin = b.d_begin;
+        d.q_duration = b.d_duration;
+        d.offsets = b.d_offsets;
+        d.sn_out = b.d_sn_out;
+        d.time_out = b.d_time_out;
+        d.status = b.d_status;
+        d.nq = b.nq;
+        d.capacity = b.d_sn_out ? b.hit_capacity : 0;
+        d.base = 0ull;
+        d.tile_first = (int)n_tiles;
+        d.n_tiles = (int)t;
+        d.vec_ok = al16(b.d_level) && al16(b.d_begin) && al16(b.d_duration) && al16(b.d_offsets) &&
+                   (!b.d_playlist || al16(b.d_playlist)) &&
+                   (!b.d_status || (reinterpret_cast<uintptr_t>(b.d_status) & 3u) == 0);
+        n_tiles += t;
+        if (n_tiles > 0x7fffffff) return fail(HLSMAP_ERR_INVALID, "batches too large: split them");
+    }
+    int r = prepare_scan(ctx, n_tiles, s);
+    if (r) return r;
+    fill_table_params(p, map, ctx);
+    p.n_tiles = (int)n_tiles;
+    p.tile_q = tile_q;
+    p.ipt = ipt;
+    const int max_grid = ipt == map->ipt ? map->grid_search : map->grid_search_wide;
+    const int grid = (int)(n_tiles < max_grid ? n_tiles : max_grid);
+    CK(launch_resolve_search_fused(p, fb, n, grid, map->stage_smem, s, true));
+    ctx->set_launches[ctx->epoch & 1u]++;      // only after a successful launch
+    ctx->last_launches = 1;
+    return HLSMAP_OK;
+}
+
 int hlsmap_get_segment_list_dev(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
                                 const int32_t *d_level, const double *d_begin,
                                 const double *d_duration, int32_t *d_offsets, int32_t *d_sn_out,
@@ -834,13 +907,34 @@ int hlsmap_get_segment_list_dev_batches_timed(hlsmap_map *map, int32_t n, const 
         cudaStream_t s;
         ~EndMark() { if (ev) cudaEventRecord((cudaEvent_t)ev, s); }
     } end_mark{event_end, s};
-    for (int32_t i = 0; i < n; i++) {
-        const hlsmap_batch &b = batches[i];
-        const int r = list_core(map, b.nq, b.d_playlist, b.d_level, b.d_begin, b.d_duration, b.d_offsets,
-                                b.d_sn_out, b.d_time_out, b.hit_capacity, b.d_status, stream, nullptr, 0ull);
+    // Under hlsmap_ctx_set_batch_overlap the caller has promised that consecutive batches are independent:
+    // runs of non-empty batches then go out kMaxFused at a time with one launch each (list_fused).
+    const bool fuse = map->ctx->overlap && pick_path(map) == HLSMAP_PATH_SEARCH && !map->ctx->no_fuse;
+    int launches = 0;
+    for (int32_t i = 0; i < n;) {
+        int g = 0;
+        if (fuse) {      // (a batch that cannot be launched ends the run before it and fails on its own)
+            auto ok = [](const hlsmap_batch &b) {
+                return b.nq > 0 && b.d_offsets && b.d_level && b.d_begin && b.d_duration &&
+                       (b.d_sn_out == nullptr) == (b.d_time_out == nullptr) && b.hit_capacity >= 0;
+            };
+            while (i + g < n && g < kMaxFused && ok(batches[i + g])) g++;
+        }
+        int r;
+        if (g >= 2) {
+            r = list_fused(map, batches + i, g, stream);
+        } else {
+            const hlsmap_batch &b = batches[i];
+            g = 1;
+            r = list_core(map, b.nq, b.d_playlist, b.d_level, b.d_begin, b.d_duration, b.d_offsets,
+                          b.d_sn_out, b.d_time_out, b.hit_capacity, b.d_status, stream, nullptr, 0ull);
+        }
         if (r) return r;
-        if (n_launched) *n_launched = i + 1;
+        launches += map->ctx->last_launches;
+        i += g;
+        if (n_launched) *n_launched = i;
     }
+    if (n > 0) map->ctx->last_launches = launches;     // hlsmap_ctx_last_result: kernel launches of the whole call
     return HLSMAP_OK;
 }
 

@@ -65,6 +65,29 @@ __host__ __device__ inline unsigned long long make_status(unsigned epoch, unsign
            (value & ((1ull << kValueBits) - 1ull));
 }
 
+// One list-form batch inside a launch of the search kernel.  A launch resolves up to kMaxFused
+// independent batches (hlsmap_get_segment_list_dev_batches under hlsmap_ctx_set_batch_overlap): their
+// tiles are numbered consecutively, tickets hand them out in that order, and a CTA stages the tables
+// once for all of them -- n batches cost one ramp and one tail instead of n.
+struct BatchDesc {
+    const int *q_playlist;  // nullable
+    const int *q_level;
+    const double *q_begin;
+    const double *q_duration;
+    int *offsets;           // [nq+1]
+    int *sn_out;            // nullable (count only)
+    double *time_out;
+    unsigned char *status;  // nullable
+    long long nq;
+    long long capacity;
+    unsigned long long base;   // hits produced by earlier chunks of the same call (0 normally)
+    int tile_first;            // the launch-wide number of the batch's first tile
+    int n_tiles;
+    int vec_ok;                // query/offset pointers are 16-byte aligned
+    int pad;
+};
+constexpr int kMaxFused = 32;
+
 struct ResolveParams {
     // tables
     const TrackDesc *desc;
@@ -109,6 +132,15 @@ struct ResolveParams {
     unsigned long long base;  // hits produced by earlier chunks of the same call (0 normally)
     unsigned long long *trace;  // diagnostics: per-tile phase timestamps (HLSMAP_TRACE=file); NULL normally
 };
+// What a launch of the search kernel takes: the launch-wide fields above (n_tiles = the launch's total)
+// and its batches.  NB = 1: one batch, the usual call -- a small parameter block, batch index 0 at
+// compile time; NB = kMaxFused: the fused launches of a batches call.
+template <int NB>
+struct SearchParams : ResolveParams {
+    int n_batches;
+    BatchDesc fb[NB];
+};
+static_assert(sizeof(SearchParams<kMaxFused>) <= 4096, "kernel parameters are limited to 4 KB");
 
 struct RangeParams {
     const TrackDesc *desc;
@@ -217,6 +249,8 @@ cudaError_t launch_view_from_json(const JsonReadParams &p, cudaStream_t s);
 // launchers (resolve.cu)
 cudaError_t launch_resolve_search(const ResolveParams &p, int grid, size_t smem, cudaStream_t s,
                                   bool overlap_next = false);
+cudaError_t launch_resolve_search_fused(const ResolveParams &p, const BatchDesc *b, int n, int grid, size_t smem,
+                                        cudaStream_t s, bool overlap_next);
 cudaError_t launch_resolve_filter(const ResolveParams &p, int grid, cudaStream_t s);
 cudaError_t launch_range(const RangeParams &p, cudaStream_t s);
 cudaError_t launch_range_small(const RangeParams &p, const TrackHint *hint, const unsigned short *grid,

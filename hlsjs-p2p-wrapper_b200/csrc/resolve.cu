@@ -450,12 +450,13 @@ __device__ __forceinline__ void small_bounds(const double *s_start, const unsign
 // SNC (general kernel only): every parsed track's sn column is proven contiguous (sn[i] = sn[0] + i,
 // established on the GPU at upload), so a hit's sn is computed from its query's first hit instead of
 // being gathered: one L2 read per query with hits in place of one per hit, and sn[] is not streamed.
-template <bool SMALL, int IPT, bool SNC>
+template <bool SMALL, int IPT, bool SNC, bool FUSED>
 __global__ void __launch_bounds__(kThreads, (SMALL && IPT == 2) ? 4 : (SMALL ? HLSMAP_WIDE_CTAS : (IPT == 2 ? HLSMAP_GENERAL_CTAS : 2)))
-resolve_search_kernel(const ResolveParams p)
+resolve_search_kernel(const __grid_constant__ SearchParams<FUSED ? kMaxFused : 1> p)
 {
     static_assert(!(SMALL && SNC), "the shared-memory-resident kernel gathers sn from shared memory");
     using S = Shape<IPT>;
+    const int nb = FUSED ? p.n_batches : 1;      // batches in this launch
     constexpr int kClaimSlots = 8 * kThreads;   // the next ticket is drawn this many output slots before the tile's last
     constexpr int kIpt = S::kIpt, kWindow = S::kWindow, kWords = S::kWords;
     extern __shared__ __align__(128) unsigned char dyn_smem[];
@@ -515,7 +516,14 @@ resolve_search_kernel(const ResolveParams p)
     Scan::acquire_set(p.ctr, p.epoch);
     if (tid == 0) sm.tile_slot[0] = (int)atomicAdd(&p.ctr->ticket[p.tslot & 1u], 1u);
     __syncthreads();
-    int tileB = sm.tile_slot[0];
+    // Tickets number the tiles of all the launch's batches consecutively: gB is the ticket, bB the batch
+    // it falls in, tileB the tile's number inside that batch.  (Tickets grow, so bB only moves forward.)
+    int gB = sm.tile_slot[0];
+    int bB = 0;
+    if constexpr (FUSED)
+        while (bB + 1 < nb && gB >= p.fb[bB + 1].tile_first) bB++;
+    int tileB = FUSED ? gB - p.fb[bB].tile_first : gB;
+    int bA = 0;                      // batch of the tile waiting to be emitted
 
     // ---- the tile searched in the previous iteration, waiting to be emitted -----------------
     int tileA = -1;
@@ -530,13 +538,16 @@ resolve_search_kernel(const ResolveParams p)
 
     bool ticket_pending = false;         // thread 0: a ticket was requested for the next tile
     for (;;) {
-        const bool haveB = tileB < p.n_tiles;
+        const bool haveB = gB < p.n_tiles;
         if (!haveB && tileA < 0) break;
+        const BatchDesc &A = p.fb[FUSED ? bA : 0];           // (kernel parameters: constant bank, indexed)
+        const BatchDesc &B = p.fb[FUSED ? bB : 0];
+        unsigned long long *const statusA = FUSED ? p.tile_status + A.tile_first : p.tile_status;
 
         // tile A's look-back window: loaded between B's bounds and B's scan, used after the scan
         // (hides the L2 trip)
         unsigned long long pre[1] = {0ull};
-        if (tileA > 0 && !haveB && warp == 0) pre[0] = ld_relaxed_u64(&p.tile_status[max(tileA - 1 - lane, 0)]);
+        if (tileA > 0 && !haveB && warp == 0) pre[0] = ld_relaxed_u64(&statusA[max(tileA - 1 - lane, 0)]);
 
         // ---- tile A's look-back, by warp 0 alone, 32 predecessors per step, no CTA barrier.  (Run
         //      earlier, while tile B's window is landing in the general kernel, it measured the same.)
@@ -544,17 +555,17 @@ resolve_search_kernel(const ResolveParams p)
             if (warp == 0) {
 #if HLSMAP_TRACE_BUILD
                 int diag = 0;
-                const unsigned long long b = Scan::warp_prefix(p.tile_status, p.epoch, tileA, a_cnt_tile, pre[0], p.base, &diag);
-                if (p.trace != nullptr && lane == 0) p.trace[(long long)tileA * 16 + 7] = (unsigned long long)diag;
+                const unsigned long long b = Scan::warp_prefix(statusA, p.epoch, tileA, a_cnt_tile, pre[0], A.base, &diag);
+                if (p.trace != nullptr && lane == 0) p.trace[(long long)(A.tile_first + tileA) * 16 + 7] = (unsigned long long)diag;
 #else
-                const unsigned long long b = Scan::warp_prefix(p.tile_status, p.epoch, tileA, a_cnt_tile, pre[0], p.base);
+                const unsigned long long b = Scan::warp_prefix(statusA, p.epoch, tileA, a_cnt_tile, pre[0], A.base);
 #endif
                 if (lane == 0) sm.tile_base = b;
-                if (SMALL) trace_mark_after(p, tileA, 14, (int)b);
+                if (SMALL) trace_mark_after(p, A.tile_first + tileA, 14, (int)b);
             }
         };
         unsigned long long tile_base = 0;
-        const bool expand = tileA >= 0 && p.sn_out != nullptr && a_cnt_tile > 0 && a_cnt_tile <= 0x7fffffffull;
+        const bool expand = tileA >= 0 && A.sn_out != nullptr && a_cnt_tile > 0 && a_cnt_tile <= 0x7fffffffull;
         constexpr int kRecShift = RecTable<SMALL, S::kTile>::kShift;
         const unsigned sn_addr = SMALL ? smem_u32(s_sn) : 0u;
         // start address of slot q = 2 * (sn address of slot q) + start_bias
@@ -576,9 +587,9 @@ resolve_search_kernel(const ResolveParams p)
         //      barrier that hands out both, offsets[]
         auto emit_prep = [&]() {
             const long long q0 = (long long)tileA * p.tile_q + tid * kIpt;
-            const long long q_end = min(p.nq, (long long)(tileA + 1) * p.tile_q);
-            const bool full = p.vec_ok && q0 + kIpt <= q_end;
-            trace_mark(p, tileA, 3);
+            const long long q_end = min(A.nq, (long long)(tileA + 1) * p.tile_q);
+            const bool full = A.vec_ok && q0 + kIpt <= q_end;
+            trace_mark(p, A.tile_first + tileA, 3);
             lookback();
             if (expand) {   // records: one per query that kept >= 1 fragment, in query order
                 int rank = a_rank, rel = (int)a_rel;
@@ -594,7 +605,7 @@ resolve_search_kernel(const ResolveParams p)
             }
             __syncthreads();
             tile_base = sm.tile_base;
-            trace_mark(p, tileA, 4);
+            trace_mark(p, A.tile_first + tileA, 4);
 
             // ---- offsets[q] --------------------------------------------------------------
             {
@@ -606,20 +617,22 @@ resolve_search_kernel(const ResolveParams p)
                     run += (unsigned long long)a_cnt[k];
                 }
                 if (full && kIpt == 4) {
-                    __stcs(reinterpret_cast<int4 *>(p.offsets + q0), make_int4(o[0], o[1], o[2], o[kIpt - 1]));
+                    __stcs(reinterpret_cast<int4 *>(A.offsets + q0), make_int4(o[0], o[1], o[2], o[kIpt - 1]));
                 } else if (full && kIpt == 2) {
-                    __stcs(reinterpret_cast<int2 *>(p.offsets + q0), make_int2(o[0], o[1]));
+                    __stcs(reinterpret_cast<int2 *>(A.offsets + q0), make_int2(o[0], o[1]));
                 } else {
 #pragma unroll
                     for (int k = 0; k < kIpt; k++)
-                        if (q0 + k < q_end) p.offsets[q0 + k] = o[k];
+                        if (q0 + k < q_end) A.offsets[q0 + k] = o[k];
                 }
             }
-            if (tileA == p.n_tiles - 1 && tid == kThreads - 1) {
+            if (tileA == A.n_tiles - 1 && tid == kThreads - 1) {
                 const unsigned long long total_hits = tile_base + a_cnt_tile;
-                p.offsets[p.nq] = (int)total_hits;
-                p.result->total_hits = (long long)total_hits;
-                p.result->overflow = total_hits > 0x7fffffffull ? 1 : 0;
+                A.offsets[A.nq] = (int)total_hits;
+                if (!FUSED || bA == nb - 1) {       // the context reports its most recent batch
+                    p.result->total_hits = (long long)total_hits;
+                    p.result->overflow = total_hits > 0x7fffffffull ? 1 : 0;
+                }
             }
         };
 
@@ -637,9 +650,9 @@ resolve_search_kernel(const ResolveParams p)
             // a tile holds p.tile_q <= 256*kIpt queries; threads past its end idle through the search
             const int tq0 = tid * kIpt;
             const long long q0 = (long long)tileB * p.tile_q + tq0;
-            const long long q_end = min(p.nq, (long long)(tileB + 1) * p.tile_q);
-            const bool full = p.vec_ok && q0 + kIpt <= q_end;
-            trace_mark(p, tileB, 0);
+            const long long q_end = min(B.nq, (long long)(tileB + 1) * p.tile_q);
+            const bool full = B.vec_ok && q0 + kIpt <= q_end;
+            trace_mark(p, gB, 0);
             {   // Pull the queries of the tile one grid-width ahead towards L2.  Tiles are handed
                 // out in order, so every tile beyond the first wave is prefetched exactly once,
                 // about one round before whichever CTA claims it loads them.  (Pulling that tile's
@@ -648,17 +661,21 @@ resolve_search_kernel(const ResolveParams p)
                 // per configs[4] chunk; predicating the probes of finished chains in the bounds
                 // measured the same; staging tile A's window a second time, after B's bounds, so that
                 // A's hits are gathered from shared memory instead of L2: 0.329 ms.)
-                const long long tileC = (long long)tileB + gridDim.x;
-                if (tileC < p.n_tiles) {
-                    const long long c0 = tileC * p.tile_q;
-                    const long long cn = min((long long)p.tile_q, p.nq - c0);
+                const long long gC = (long long)gB + gridDim.x;
+                if (gC < p.n_tiles) {
+                    int bC = bB;
+                    if constexpr (FUSED)
+                        while (bC + 1 < nb && gC >= p.fb[bC + 1].tile_first) bC++;
+                    const BatchDesc &C = p.fb[FUSED ? bC : 0];
+                    const long long c0 = (FUSED ? gC - C.tile_first : gC) * p.tile_q;
+                    const long long cn = min((long long)p.tile_q, C.nq - c0);
                     const int l64 = (int)((cn * 8 + 127) >> 7), l32 = (int)((cn * 4 + 127) >> 7);
                     const char *a = nullptr;
-                    if (tid < l64) a = reinterpret_cast<const char *>(p.q_begin + c0) + tid * 128;
-                    else if (tid < 2 * l64) a = reinterpret_cast<const char *>(p.q_duration + c0) + (tid - l64) * 128;
-                    else if (tid < 2 * l64 + l32) a = reinterpret_cast<const char *>(p.q_level + c0) + (tid - 2 * l64) * 128;
-                    else if (tid < 2 * l64 + 2 * l32 && p.q_playlist)
-                        a = reinterpret_cast<const char *>(p.q_playlist + c0) + (tid - 2 * l64 - l32) * 128;
+                    if (tid < l64) a = reinterpret_cast<const char *>(C.q_begin + c0) + tid * 128;
+                    else if (tid < 2 * l64) a = reinterpret_cast<const char *>(C.q_duration + c0) + (tid - l64) * 128;
+                    else if (tid < 2 * l64 + l32) a = reinterpret_cast<const char *>(C.q_level + c0) + (tid - 2 * l64) * 128;
+                    else if (tid < 2 * l64 + 2 * l32 && C.q_playlist)
+                        a = reinterpret_cast<const char *>(C.q_playlist + c0) + (tid - 2 * l64 - l32) * 128;
                     if (a) asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
                 }
             }
@@ -668,28 +685,28 @@ resolve_search_kernel(const ResolveParams p)
             double bg[kIpt], du[kIpt];
             if (full) {
                 if (kIpt == 4) {
-                    const int4 l4 = __ldcs(reinterpret_cast<const int4 *>(p.q_level + q0));
+                    const int4 l4 = __ldcs(reinterpret_cast<const int4 *>(B.q_level + q0));
                     lv[0] = l4.x; lv[1] = l4.y; lv[2] = l4.z; lv[kIpt - 1] = l4.w;
-                    if (p.q_playlist) {
-                        const int4 p4 = __ldcs(reinterpret_cast<const int4 *>(p.q_playlist + q0));
+                    if (B.q_playlist) {
+                        const int4 p4 = __ldcs(reinterpret_cast<const int4 *>(B.q_playlist + q0));
                         pl[0] = p4.x; pl[1] = p4.y; pl[2] = p4.z; pl[kIpt - 1] = p4.w;
                     }
                 } else {
-                    const int2 l2 = __ldcs(reinterpret_cast<const int2 *>(p.q_level + q0));
+                    const int2 l2 = __ldcs(reinterpret_cast<const int2 *>(B.q_level + q0));
                     lv[0] = l2.x; lv[1] = l2.y;
-                    if (p.q_playlist) {
-                        const int2 p2 = __ldcs(reinterpret_cast<const int2 *>(p.q_playlist + q0));
+                    if (B.q_playlist) {
+                        const int2 p2 = __ldcs(reinterpret_cast<const int2 *>(B.q_playlist + q0));
                         pl[0] = p2.x; pl[1] = p2.y;
                     }
                 }
-                if (!p.q_playlist) {
+                if (!B.q_playlist) {
 #pragma unroll
                     for (int k = 0; k < kIpt; k++) pl[k] = 0;
                 }
 #pragma unroll
                 for (int k = 0; k < kIpt; k += 2) {
-                    const double2 b2 = __ldcs(reinterpret_cast<const double2 *>(p.q_begin + q0 + k));
-                    const double2 d2 = __ldcs(reinterpret_cast<const double2 *>(p.q_duration + q0 + k));
+                    const double2 b2 = __ldcs(reinterpret_cast<const double2 *>(B.q_begin + q0 + k));
+                    const double2 d2 = __ldcs(reinterpret_cast<const double2 *>(B.q_duration + q0 + k));
                     bg[k] = b2.x; bg[k + 1] = b2.y;
                     du[k] = d2.x; du[k + 1] = d2.y;
                 }
@@ -697,14 +714,14 @@ resolve_search_kernel(const ResolveParams p)
 #pragma unroll
                 for (int k = 0; k < kIpt; k++) {
                     const bool in = q0 + k < q_end;
-                    lv[k] = in ? __ldcs(p.q_level + q0 + k) : -1;
-                    pl[k] = (in && p.q_playlist) ? __ldcs(p.q_playlist + q0 + k) : 0;
-                    bg[k] = in ? __ldcs(p.q_begin + q0 + k) : 0.0;
-                    du[k] = in ? __ldcs(p.q_duration + q0 + k) : 0.0;
+                    lv[k] = in ? __ldcs(B.q_level + q0 + k) : -1;
+                    pl[k] = (in && B.q_playlist) ? __ldcs(B.q_playlist + q0 + k) : 0;
+                    bg[k] = in ? __ldcs(B.q_begin + q0 + k) : 0.0;
+                    du[k] = in ? __ldcs(B.q_duration + q0 + k) : 0.0;
                 }
             }
 
-            trace_mark_after(p, tileB, 6, lv[0] ^ __double2loint(bg[kIpt - 1]) ^ __double2loint(du[kIpt - 1]));
+            trace_mark_after(p, gB, 6, lv[0] ^ __double2loint(bg[kIpt - 1]) ^ __double2loint(du[kIpt - 1]));
             // ---- resolve (playlist, level) -> fragment table -----------------------------
             if (SMALL && stage_pending) {      // first tile only: tables + metadata have landed
                 mbar_wait(&sm.mbar, mbar_phase);
@@ -728,16 +745,16 @@ resolve_search_kernel(const ResolveParams p)
                     mx = max(mx, off[k] + len[k]);
                 }
             }
-            if (!SMALL) trace_mark_after(p, tileB, 13, len[0] ^ len[kIpt - 1]);
-            if (p.status) {
+            if (!SMALL) trace_mark_after(p, gB, 13, len[0] ^ len[kIpt - 1]);
+            if (B.status) {
                 if (full && kIpt == 4) {
                     const unsigned w = (unsigned)st[0] | ((unsigned)st[1] << 8) |
                                        ((unsigned)st[2] << 16) | ((unsigned)st[kIpt - 1] << 24);
-                    *reinterpret_cast<unsigned *>(p.status + q0) = w;
+                    *reinterpret_cast<unsigned *>(B.status + q0) = w;
                 } else {
 #pragma unroll
                     for (int k = 0; k < kIpt; k++)
-                        if (q0 + k < q_end) p.status[q0 + k] = (unsigned char)st[k];
+                        if (q0 + k < q_end) B.status[q0 + k] = (unsigned char)st[k];
                 }
             }
 
@@ -798,7 +815,7 @@ resolve_search_kernel(const ResolveParams p)
                         mbar_wait(&sm.mbar, mbar_phase);
                         mbar_phase ^= 1u;
                     }
-                    if (pass == 0) trace_mark(p, tileB, 14);
+                    if (pass == 0) trace_mark(p, gB, 14);
 #pragma unroll
                     for (int k = 0; k < kIpt; k++) {
                         // (off >= span_lo: the window starts at the first pending track)
@@ -833,12 +850,12 @@ resolve_search_kernel(const ResolveParams p)
                 }
             }
 
-            trace_mark_after(p, tileB, 1, cnt[0] ^ cnt[kIpt - 1]);
+            trace_mark_after(p, gB, 1, cnt[0] ^ cnt[kIpt - 1]);
             if (SNC) {       // consumed one iteration later, when this tile is emitted
 #pragma unroll
                 for (int k = 0; k < kIpt; k++) snf[k] = cnt[k] > 0 ? __ldg(p.sn + off[k] + lo[k]) : 0;
             }
-            if (tileA > 0 && warp == 0) pre[0] = ld_relaxed_u64(&p.tile_status[max(tileA - 1 - lane, 0)]);
+            if (tileA > 0 && warp == 0) pre[0] = ld_relaxed_u64(&statusA[max(tileA - 1 - lane, 0)]);
             // ---- fused scan of (hit count, non-empty flag): thread -> warp -> CTA ---------
             unsigned long long tval = 0;
 #pragma unroll
@@ -855,14 +872,14 @@ resolve_search_kernel(const ResolveParams p)
                 wbase += (w < warp) ? c : 0ull;
                 tile_tot += c;
             }
-            trace_mark_after(p, tileB, 8, (int)tile_tot);
+            trace_mark_after(p, gB, 8, (int)tile_tot);
             b_cnt_tile = tile_tot & kCntMask;
-            Scan::publish_aggregate(p.tile_status, p.epoch, tileB, b_cnt_tile, p.base);
-            trace_mark(p, tileB, 2);
+            Scan::publish_aggregate(FUSED ? p.tile_status + B.tile_first : p.tile_status, p.epoch, tileB, b_cnt_tile, B.base);
+            trace_mark(p, gB, 2);
             b_rel = (wbase + texcl) & kCntMask;
             b_rank = (int)((wbase + texcl) >> kCntBits);
             {   // rare: fold the unparsed / missing tallies (one atomic per warp when non-zero)
-                const unsigned any = __ballot_sync(0xffffffffu, (n_unp | n_mis) != 0);
+                const unsigned any = __ballot_sync(0xffffffffu, (n_unp | n_mis) != 0 && (!FUSED || bB == nb - 1));
                 if (any) {
 #pragma unroll
                     for (int d = 16; d > 0; d >>= 1) {
@@ -892,7 +909,7 @@ resolve_search_kernel(const ResolveParams p)
                 unsigned sb_bias = 0;       // general kernel: address of sb[r] = ((address of v[r]) >> 1) + sb_bias
                 if constexpr (!SMALL) sb_bias = smem_u32(&sm.rec.sb[0]) - (smem_u32(&sm.rec.v[0]) >> 1);
                 int carried = 0;            // records that start before the current window
-                const bool all_fit = (long long)tile_base + total <= p.capacity;   // CTA-uniform
+                const bool all_fit = (long long)tile_base + total <= A.capacity;   // CTA-uniform
                 for (int w0 = 0; w0 < total; w0 += kWindow) {
                     uint2 *H = sm.hb[hbuf];
                     {   // head marks (the first window's are down already), rank words
@@ -916,7 +933,7 @@ resolve_search_kernel(const ResolveParams p)
                         __syncthreads();
                         carried = sm.carried;
                     }
-                    if (w0 == 0) trace_mark(p, tileA, 9);
+                    if (w0 == 0) trace_mark(p, A.tile_first + tileA, 9);
                     // The run is cut into chunks of kChunk slots that start at multiples of kChunk in the
                     // OUTPUT arrays (slot + a is a multiple of kChunk at a chunk's start): whatever the tile's
                     // first slot, every store instruction of a warp then covers whole 128-byte lines (two of
@@ -943,11 +960,11 @@ resolve_search_kernel(const ResolveParams p)
 #pragma unroll 1
                             for (int j = 0; j < 4; j++) {
                                 const int q = sl + 32 * j;
-                                if (q < 0 || q >= total || (long long)tile_base + q >= p.capacity) continue;
+                                if (q < 0 || q >= total || (long long)tile_base + q >= A.capacity) continue;
                                 const uint2 h = H[(q - w0) >> 5];
                                 const unsigned R = lds_u32<0>(h.y + 4u * (unsigned)__popc(h.x & below)) + 4u * (unsigned)q;
-                                __stcs(p.time_out + ((long long)tile_base + q), lds_f64<0>(2u * R + start_bias));
-                                __stcs(p.sn_out + ((long long)tile_base + q), (int)lds_u32<0>(R));
+                                __stcs(A.time_out + ((long long)tile_base + q), lds_f64<0>(2u * R + start_bias));
+                                __stcs(A.sn_out + ((long long)tile_base + q), (int)lds_u32<0>(R));
                             }
                         } else {        // all four loads first: they come from L2
                             double t[4];
@@ -956,7 +973,7 @@ resolve_search_kernel(const ResolveParams p)
 #pragma unroll
                             for (int j = 0; j < 4; j++) {
                                 const int q = sl + 32 * j;
-                                ok[j] = q >= 0 && q < total && (long long)tile_base + q < p.capacity;
+                                ok[j] = q >= 0 && q < total && (long long)tile_base + q < A.capacity;
                                 t[j] = 0.0;
                                 sv[j] = 0;
                                 if (ok[j]) {
@@ -970,8 +987,8 @@ resolve_search_kernel(const ResolveParams p)
 #pragma unroll
                             for (int j = 0; j < 4; j++) {
                                 if (ok[j]) {
-                                    __stcs(p.time_out + ((long long)tile_base + sl + 32 * j), t[j]);
-                                    __stcs(p.sn_out + ((long long)tile_base + sl + 32 * j), sv[j]);
+                                    __stcs(A.time_out + ((long long)tile_base + sl + 32 * j), t[j]);
+                                    __stcs(A.sn_out + ((long long)tile_base + sl + 32 * j), sv[j]);
                                 }
                             }
                         }
@@ -982,8 +999,8 @@ resolve_search_kernel(const ResolveParams p)
                     int k = f_lo + warp;
                     const int sl0 = k * kChunk - a + lane;
                     const uint2 *hp = H + ((sl0 - w0) >> 5);
-                    double *tp = p.time_out + ((long long)tile_base + sl0);
-                    int *sp = p.sn_out + ((long long)tile_base + sl0);
+                    double *tp = A.time_out + ((long long)tile_base + sl0);
+                    int *sp = A.sn_out + ((long long)tile_base + sl0);
                     unsigned slot4 = 4u * (unsigned)sl0;            // SMALL: 4 * slot
                     long long slotl = (long long)sl0;               // general: slot
                     auto body = [&]() {
@@ -1040,12 +1057,12 @@ resolve_search_kernel(const ResolveParams p)
                     }
 #pragma unroll 1
                     while (k < f_hi) body();
-                    if (w0 == 0) trace_mark(p, tileA, 10);
+                    if (w0 == 0) trace_mark(p, A.tile_first + tileA, 10);
 #pragma unroll 1
                     for (k = f_hi + ((warp - (f_hi - k_lo)) & (kWarps - 1)); k < k_hi; k += kWarps) slow_chunk(k);
-                    if (w0 == 0) trace_mark(p, tileA, 11);
+                    if (w0 == 0) trace_mark(p, A.tile_first + tileA, 11);
                     __syncthreads();
-                    if (w0 == 0) trace_mark(p, tileA, 12);
+                    if (w0 == 0) trace_mark(p, A.tile_first + tileA, 12);
                     if (tid < kWords) H[tid].x = 0u;   // next used two windows from now
                     hbuf ^= 1u;
                 }
@@ -1053,7 +1070,7 @@ resolve_search_kernel(const ResolveParams p)
         }
 
         // ---- rotate the pipeline: B becomes the pending tile --------------------------------
-        if (tileA >= 0) trace_mark(p, tileA, 5);
+        if (tileA >= 0) trace_mark(p, A.tile_first + tileA, 5);
         slot ^= 1u;            // alternate slots: the one read last iteration is not rewritten
         if (tid == 0) {
             if (haveB) {
@@ -1066,6 +1083,7 @@ resolve_search_kernel(const ResolveParams p)
         }
         __syncthreads();       // all global writes of tile A issued; next tile id visible
         tileA = haveB ? tileB : -1;
+        if constexpr (FUSED) bA = bB;
         a_rel = b_rel;
         a_cnt_tile = b_cnt_tile;
         a_rank = b_rank;
@@ -1075,7 +1093,10 @@ resolve_search_kernel(const ResolveParams p)
             a_src[k] = (SrcT)(off[k] + lo[k]);
             a_snf[k] = snf[k];
         }
-        tileB = sm.tile_slot[slot];
+        gB = sm.tile_slot[slot];
+        if constexpr (FUSED)
+            while (bB + 1 < nb && gB >= p.fb[bB + 1].tile_first) bB++;
+        tileB = FUSED ? gB - p.fb[bB].tile_first : gB;
     }
     // never leave with a bulk copy still landing in this CTA's shared memory
     if (stage_pending) mbar_wait(&sm.mbar, mbar_phase);
@@ -1618,9 +1639,11 @@ template <bool SMALL, int IPT, bool SNC>
 static int max_grid_of(size_t smem)
 {
     int per_sm = 0;
-    cudaFuncSetAttribute(resolve_search_kernel<SMALL, IPT, SNC>,
+    cudaFuncSetAttribute(resolve_search_kernel<SMALL, IPT, SNC, false>,
                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resolve_search_kernel<SMALL, IPT, SNC>,
+    cudaFuncSetAttribute(resolve_search_kernel<SMALL, IPT, SNC, true>,
+                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, resolve_search_kernel<SMALL, IPT, SNC, true>,
                                                       kThreads, smem) != cudaSuccess || per_sm < 1)
         per_sm = 1;
     return per_sm * sm_count();
@@ -1645,8 +1668,8 @@ int resolve_filter_max_grid()
     return per_sm * sm_count();
 }
 
-template <bool SMALL, int IPT, bool SNC>
-static cudaError_t launch_search_variant(const ResolveParams &p, int grid, size_t smem,
+template <bool SMALL, int IPT, bool SNC, bool FUSED>
+static cudaError_t launch_search_variant(const SearchParams<FUSED ? kMaxFused : 1> &p, int grid, size_t smem,
                                          cudaStream_t s, bool overlap_next)
 {
     cudaLaunchConfig_t cfg{};
@@ -1659,21 +1682,59 @@ static cudaError_t launch_search_variant(const ResolveParams &p, int grid, size_
     attr[0].val.programmaticStreamSerializationAllowed = overlap_next ? 1 : 0;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, resolve_search_kernel<SMALL, IPT, SNC>, p);
+    return cudaLaunchKernelEx(&cfg, resolve_search_kernel<SMALL, IPT, SNC, FUSED>, p);
 }
 
+template <bool FUSED>
+static cudaError_t launch_search_any(const SearchParams<FUSED ? kMaxFused : 1> &p, int grid, size_t smem,
+                                     cudaStream_t s, bool overlap_next)
+{
+    cudaError_t e;
+    if (p.small && p.ipt == 2) e = launch_search_variant<true, 2, false, FUSED>(p, grid, smem, s, overlap_next);
+    else if (p.small) e = launch_search_variant<true, 4, false, FUSED>(p, grid, smem, s, overlap_next);
+    else if (p.ipt == 2 && p.sn_contig) e = launch_search_variant<false, 2, true, FUSED>(p, grid, smem, s, overlap_next);
+    else if (p.ipt == 2) e = launch_search_variant<false, 2, false, FUSED>(p, grid, smem, s, overlap_next);
+    else if (p.sn_contig) e = launch_search_variant<false, 4, true, FUSED>(p, grid, smem, s, overlap_next);
+    else e = launch_search_variant<false, 4, false, FUSED>(p, grid, smem, s, overlap_next);
+    return e != cudaSuccess ? e : cudaGetLastError();
+}
+
+// One batch, described by the launch-wide fields of p.
 // overlap_next: this batch may begin while the previous kernel on the stream is draining.
 cudaError_t launch_resolve_search(const ResolveParams &p, int grid, size_t smem, cudaStream_t s,
                                   bool overlap_next)
 {
-    cudaError_t e;
-    if (p.small && p.ipt == 2) e = launch_search_variant<true, 2, false>(p, grid, smem, s, overlap_next);
-    else if (p.small) e = launch_search_variant<true, 4, false>(p, grid, smem, s, overlap_next);
-    else if (p.ipt == 2 && p.sn_contig) e = launch_search_variant<false, 2, true>(p, grid, smem, s, overlap_next);
-    else if (p.ipt == 2) e = launch_search_variant<false, 2, false>(p, grid, smem, s, overlap_next);
-    else if (p.sn_contig) e = launch_search_variant<false, 4, true>(p, grid, smem, s, overlap_next);
-    else e = launch_search_variant<false, 4, false>(p, grid, smem, s, overlap_next);
-    return e != cudaSuccess ? e : cudaGetLastError();
+    SearchParams<1> sp{};
+    static_cast<ResolveParams &>(sp) = p;
+    sp.n_batches = 1;
+    BatchDesc &b = sp.fb[0];
+    b.q_playlist = p.q_playlist;
+    b.q_level = p.q_level;
+    b.q_begin = p.q_begin;
+    b.q_duration = p.q_duration;
+    b.offsets = p.offsets;
+    b.sn_out = p.sn_out;
+    b.time_out = p.time_out;
+    b.status = p.status;
+    b.nq = p.nq;
+    b.capacity = p.capacity;
+    b.base = p.base;
+    b.tile_first = 0;
+    b.n_tiles = p.n_tiles;
+    b.vec_ok = p.vec_ok;
+    return launch_search_any<false>(sp, grid, smem, s, overlap_next);
+}
+
+// n <= kMaxFused batches with one launch: p carries the tables, the scratch and the launch's total
+// number of tiles; the batches' own fields are in b[].
+cudaError_t launch_resolve_search_fused(const ResolveParams &p, const BatchDesc *b, int n, int grid, size_t smem,
+                                        cudaStream_t s, bool overlap_next)
+{
+    SearchParams<kMaxFused> sp{};
+    static_cast<ResolveParams &>(sp) = p;
+    sp.n_batches = n;
+    for (int i = 0; i < n; i++) sp.fb[i] = b[i];
+    return launch_search_any<true>(sp, grid, smem, s, overlap_next);
 }
 
 cudaError_t launch_resolve_filter(const ResolveParams &p, int grid, cudaStream_t s)

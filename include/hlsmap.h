@@ -193,12 +193,19 @@ int hlsmap_get_segment_list_noalloc_dev(hlsmap_map *map, int64_t nq, const int32
                                         int64_t hit_capacity, uint8_t *d_status, void *stream,
                                         hlsmap_result *result);
 /* Several independent list-form batches submitted with ONE call (what a serving loop does with the
- * requests that have queued up): the same as calling hlsmap_get_segment_list_dev for
- * batches[0..n) in order with result = NULL, without returning to the host language between the
- * launches.  With hlsmap_ctx_set_batch_overlap the batches overlap on the GPU as consecutive
- * calls would (they must not share output buffers).  Stops at the first batch that cannot be
- * launched and returns its error; *n_launched (nullable) = batches issued.  The reference has one
- * call per query (media-map.js:27); this is that call over many query batches. */
+ * requests that have queued up): the same results as calling hlsmap_get_segment_list_dev for
+ * batches[0..n) in order with result = NULL, without returning to the host language in between.
+ * With hlsmap_ctx_set_batch_overlap (the batches must not share output buffers) runs of up to 32
+ * non-empty batches are resolved by ONE kernel launch each on maps that take the search path --
+ * their tiles are handed out in batch order, every batch keeps its own offsets, capacity and status
+ * column, and the tables are staged once per CTA for the whole run -- so n batches pay one ramp-up
+ * and one tail instead of n (10^6-query batches on a B200: 30.6 us per batch against 33.2 as
+ * overlapping launches); without that option, one launch per batch.  Stops at the first batch
+ * that cannot be launched and returns its error; *n_launched (nullable) = batches issued (a run
+ * ends in front of such a batch, so everything before it has been issued).  Afterwards
+ * hlsmap_ctx_last_result reports the last batch's counters and, in kernel_launches, the launches
+ * of the whole call.  The reference has one call per query (media-map.js:27); this is that call
+ * over many query batches. */
 typedef struct hlsmap_batch {
     int64_t nq;
     const int32_t *d_playlist;   /* nullable */

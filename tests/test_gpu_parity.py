@@ -457,6 +457,96 @@ def test_small_batches_behind_big_ones_release_their_scratch_set(ctx):
     m.close()
 
 
+@pytest.mark.parametrize("which", ["small_map", "large_map"])
+def test_fused_batches_match_the_oracle_batch_by_batch(ctx, which):
+    """Under hlsmap_ctx_set_batch_overlap a batches call resolves runs of up to 32 non-empty batches
+    with ONE kernel launch (their tiles numbered consecutively, each batch with its own look-back
+    chain, buffers, capacity and status column).  Forty batches of mixed sizes -- more than one launch
+    takes, an empty one and a count-only one among them, some with a status column, one with too small a
+    capacity -- on a map that fits shared memory and on one that does not: every batch bit-for-bit the
+    oracle's answer, identical to what one launch per batch (HLSMAP_NO_FUSE) gives, and a broken batch
+    in the middle stops the call exactly there."""
+    import torch
+    dev = torch.device("cuda:0")
+    if which == "small_map":
+        t, _ = synth.config2(n_queries=4)
+        gen = lambda seed, nq: synth.config2(seed=seed, n_queries=nq)[1]
+    else:
+        t, q_all = synth.config5(seed=77, n_playlists=3000, queries_per_playlist=40)
+        def gen(seed, nq):
+            r = np.random.RandomState(seed)
+            i = np.sort(r.randint(0, len(q_all), size=nq))      # (grouped by playlist, as the corpus is)
+            return QueryBatch(q_all.playlist[i], q_all.level[i], q_all.begin[i], q_all.duration[i])
+    m = ctx.upload(t)
+    stream = torch.cuda.Stream(device=dev)
+    sizes = [30_000, 513, 1, 70_001, 0, 1024, 2_049, 120_000] * 5
+    sets = []
+    for i, nq in enumerate(sizes):
+        q = gen(300 + i, max(nq, 1))
+        q = QueryBatch(q.playlist[:nq], q.level[:nq], q.begin[:nq], q.duration[:nq])
+        ref = oracle_list(t, q)
+        H = int(ref[0][-1])
+        count_only = i == 11
+        short = i == 19 and H > 8              # room for fewer hits than the batch has
+        cap = 0 if count_only else (H // 2 if short else H)
+        sets.append({"ref": ref, "H": H, "nq": nq, "cap": cap, "count_only": count_only,
+                     "pl": torch.from_numpy(q.playlist).to(dev), "lv": torch.from_numpy(q.level).to(dev),
+                     "bg": torch.from_numpy(q.begin).to(dev), "du": torch.from_numpy(q.duration).to(dev),
+                     "off": torch.full((nq + 1,), -1, dtype=torch.int32, device=dev),
+                     "sn": torch.full((max(H, 1) + 256,), -7, dtype=torch.int32, device=dev),
+                     "tm": torch.full((max(H, 1) + 256,), -7.0, dtype=torch.float64, device=dev),
+                     "st": torch.full((max(nq, 1),), 99, dtype=torch.uint8, device=dev) if i % 3 == 0 else None})
+    def batch(s):
+        return {"nq": s["nq"], "d_playlist": s["pl"].data_ptr(), "d_level": s["lv"].data_ptr(),
+                "d_begin": s["bg"].data_ptr(), "d_duration": s["du"].data_ptr(), "d_offsets": s["off"].data_ptr(),
+                "d_sn_out": 0 if s["count_only"] else s["sn"].data_ptr(),
+                "d_time_out": 0 if s["count_only"] else s["tm"].data_ptr(), "capacity": s["cap"],
+                "d_status": s["st"].data_ptr() if s["st"] is not None else 0}
+    def check():
+        torch.cuda.synchronize()
+        for s in sets:
+            assert np.array_equal(s["off"].cpu().numpy().astype(np.int64), s["ref"][0])
+            if s["st"] is not None and s["nq"]:
+                assert np.array_equal(s["st"][:s["nq"]].cpu().numpy(), s["ref"][1])
+            if s["count_only"]:
+                continue
+            k = s["cap"]                       # hits beyond the capacity are not written, nothing behind them is touched
+            assert np.array_equal(s["sn"][:k].cpu().numpy(), s["ref"][2][:k])
+            assert np.array_equal(s["tm"][:k].cpu().numpy().view(np.uint64), s["ref"][3][:k].view(np.uint64))
+            assert (s["sn"][k:] == -7).all().item() and (s["tm"][k:] == -7.0).all().item()
+    def reset():
+        for s in sets:
+            s["off"].fill_(-1); s["sn"].fill_(-7); s["tm"].fill_(-7.0)
+            if s["st"] is not None:
+                s["st"].fill_(99)
+        torch.cuda.synchronize()
+    ctx.set_batch_overlap(True)
+    try:
+        for rep in range(3):
+            reset()
+            assert m.get_segment_list_dev_batches([batch(s) for s in sets], stream.cuda_stream) == len(sets)
+            assert m.last_result(stream.cuda_stream).total_hits == sets[-1]["H"]
+            check()
+        # a batch that cannot be launched ends the call in front of it, fused or not
+        reset()
+        bad = dict(batch(sets[5]), d_begin=0)
+        arr = (N.Batch * 9)()
+        for a, b in zip(arr, [batch(s) for s in sets[:4]] + [bad] + [batch(s) for s in sets[5:9]]):
+            a.nq, a.d_playlist, a.d_level, a.d_begin, a.d_duration = b["nq"], b["d_playlist"], b["d_level"], b["d_begin"] or None, b["d_duration"]
+            a.d_offsets, a.d_sn_out, a.d_time_out = b["d_offsets"], b["d_sn_out"] or None, b["d_time_out"] or None
+            a.hit_capacity, a.d_status = b["capacity"], b["d_status"] or None
+        done = ctypes.c_int32(-1)
+        code = N.load().hlsmap_get_segment_list_dev_batches(m._h, 9, arr, ctypes.c_void_p(stream.cuda_stream), ctypes.byref(done))
+        assert code == N.ERR_INVALID and done.value == 4
+        torch.cuda.synchronize()
+        for s in sets[:4]:
+            assert np.array_equal(s["off"].cpu().numpy().astype(np.int64), s["ref"][0])
+        assert int(sets[5]["off"][0].item()) == -1           # nothing behind the broken batch ran
+    finally:
+        ctx.set_batch_overlap(False)
+    m.close()
+
+
 def test_several_batches_with_one_call(ctx):
     """hlsmap_get_segment_list_dev_batches: the batches of one call behave like so many calls of
     hlsmap_get_segment_list_dev -- each bit-for-bit the oracle's answer, with and without overlap
