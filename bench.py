@@ -613,13 +613,19 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     gloo = None
-    if world > 1:
+    # (diagnostics: HLSMAP_BENCH_PG1=1 brings NCCL up in a one-rank run, to see what its presence costs)
+    pg1 = world == 1 and os.environ.get("HLSMAP_BENCH_PG1") == "1"
+    if world > 1 or pg1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
-        gloo = dist.new_group(backend="gloo")      # host-side gather of the sharded leg only
+        if pg1:
+            os.environ.setdefault("MASTER_PORT", "29533")
+            dist.init_process_group("nccl", device_id=dev, rank=0, world_size=1)
+        else:
+            dist.init_process_group("nccl", device_id=dev)
+            gloo = dist.new_group(backend="gloo")      # host-side gather of the sharded leg only
 
     def barrier():
-        if world > 1:
+        if world > 1 or pg1:
             dist.barrier(device_ids=[local])
         torch.cuda.synchronize()
 

@@ -131,24 +131,36 @@ int ensure_slot(hlsmap_ctx *ctx, int i, int64_t bytes, void **out, cudaStream_t 
     return HLSMAP_OK;
 }
 
+// Room for the status words of n_tiles tiles in each of the two scratch sets.  Grows by reallocating
+// (stream synchronisation, cudaFree, cudaMalloc, a clearing memset): callers that time what follows
+// reserve first.  The first allocation holds 65536 tiles (2 MiB), which most callers never outgrow.
+int reserve_tiles(hlsmap_ctx *ctx, int64_t n_tiles, cudaStream_t s)
+{
+    if (n_tiles <= ctx->tile_cap) return HLSMAP_OK;
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (s != ctx->stream) CK(cudaStreamSynchronize(s));
+    if (ctx->tile_status) CK(cudaFree(ctx->tile_status));
+    ctx->tile_status = nullptr;
+    int64_t cap = n_tiles + n_tiles / 2 + 1024;
+    if (cap < 65536) cap = 65536;
+    cudaError_t e = cudaMalloc(&ctx->tile_status, (size_t)cap * 16);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        ctx->tile_cap = 0;
+        return fail(HLSMAP_ERR_NOMEM, "cudaMalloc of tile status failed");
+    }
+    ctx->tile_cap = cap;
+    CK(cudaMemsetAsync(ctx->tile_status, 0, (size_t)cap * 16, s));
+    return HLSMAP_OK;
+}
+
 // Scratch for a scan batch of n_tiles tiles; bumps the launch epoch.  Launches alternate
 // between two scratch sets (epoch & 1) so that a batch may start while its predecessor drains.
 int prepare_scan(hlsmap_ctx *ctx, int64_t n_tiles, cudaStream_t s)
 {
-    if (n_tiles > ctx->tile_cap) {
-        CK(cudaStreamSynchronize(ctx->stream));
-        if (s != ctx->stream) CK(cudaStreamSynchronize(s));
-        if (ctx->tile_status) CK(cudaFree(ctx->tile_status));
-        ctx->tile_status = nullptr;
-        const int64_t cap = n_tiles + n_tiles / 2 + 1024;
-        cudaError_t e = cudaMalloc(&ctx->tile_status, (size_t)cap * 16);
-        if (e != cudaSuccess) {
-            cudaGetLastError();
-            ctx->tile_cap = 0;
-            return fail(HLSMAP_ERR_NOMEM, "cudaMalloc of tile status failed");
-        }
-        ctx->tile_cap = cap;
-        CK(cudaMemsetAsync(ctx->tile_status, 0, (size_t)cap * 16, s));
+    {
+        const int r = reserve_tiles(ctx, n_tiles, s);
+        if (r) return r;
     }
     ctx->epoch++;
     if (ctx->epoch > kEpochMask) {  // epoch 0 means "never written": wipe and restart
@@ -901,6 +913,22 @@ int hlsmap_get_segment_list_dev_batches_timed(hlsmap_map *map, int32_t n, const 
         if (r) return r;
     }
     cudaStream_t s = stream ? (cudaStream_t)stream : map->ctx->stream;
+    const bool fuse = map->ctx->overlap && pick_path(map) == HLSMAP_PATH_SEARCH && !map->ctx->no_fuse;
+    if (fuse && n > 1) {
+        // scratch for the largest launch of the call, before the caller's opening event: growing it
+        // means a reallocation, which is set-up and not part of the batches' device time
+        const int tile_q = resolve_search_tile(map->info.stage_all != 0, map->ipt);     // (the smaller tile: an upper bound)
+        int64_t most = 0, run = 0;
+        for (int32_t i = 0, g = 0; i < n; i++) {
+            if (batches[i].nq <= 0 || g == kMaxFused) { run = 0; g = 0; }
+            if (batches[i].nq > 0) { run += (batches[i].nq + tile_q - 1) / tile_q; g++; }
+            if (run > most) most = run;
+        }
+        if (most <= 0x7fffffff) {
+            const int r = reserve_tiles(map->ctx, most, s);
+            if (r) return r;
+        }
+    }
     if (event_begin) CK(cudaEventRecord((cudaEvent_t)event_begin, s));
     struct EndMark {        // the closing event is recorded on every way out
         void *ev;
@@ -909,7 +937,6 @@ int hlsmap_get_segment_list_dev_batches_timed(hlsmap_map *map, int32_t n, const 
     } end_mark{event_end, s};
     // Under hlsmap_ctx_set_batch_overlap the caller has promised that consecutive batches are independent:
     // runs of non-empty batches then go out kMaxFused at a time with one launch each (list_fused).
-    const bool fuse = map->ctx->overlap && pick_path(map) == HLSMAP_PATH_SEARCH && !map->ctx->no_fuse;
     int launches = 0;
     for (int32_t i = 0; i < n;) {
         int g = 0;
