@@ -54,6 +54,7 @@ struct hlsmap_ctx {
     bool overlap = false;               // consecutive search batches may overlap (PDL)
     int64_t host_chunk = 262144;        // largest chunk of that pipeline, in queries (HLSMAP_HOST_CHUNK at creation, experiments)
     bool host_pipeline = true;          // chunked upload/compute/download of large host-pointer calls
+    void *begin_event = nullptr;        // a batches call's opening cudaEvent_t, recorded right before its first launch
     bool no_fuse = false;               // HLSMAP_NO_FUSE: a batches call issues one launch per batch even when it may fuse them
                                         // (HLSMAP_NO_PIPELINE in the environment at context creation turns it off)
     unsigned set_launches[2] = {0, 0};  // kernels launched on each scratch set (ticket slot parity)
@@ -129,6 +130,16 @@ int ensure_slot(hlsmap_ctx *ctx, int i, int64_t bytes, void **out, cudaStream_t 
     }
     *out = ctx->slot[i];
     return HLSMAP_OK;
+}
+
+// The opening event of a timed batches call goes onto the stream immediately before the call's first
+// launch (after the host-side preparation, which would otherwise count as device time on an idle stream).
+inline void mark_begin(hlsmap_ctx *ctx, cudaStream_t s)
+{
+    if (ctx->begin_event) {
+        cudaEventRecord((cudaEvent_t)ctx->begin_event, s);
+        ctx->begin_event = nullptr;
+    }
 }
 
 // Room for the status words of n_tiles tiles in each of the two scratch sets.  Grows by reallocating
@@ -736,6 +747,7 @@ int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
     if (nq == 0) {
         r = prepare_scan(ctx, 0, s);        // moves to the other scratch set
         if (r) return r;
+        mark_begin(ctx, s);
         CK(cudaMemsetAsync(d_offsets, 0, sizeof(int32_t), s));
         CK(cudaMemsetAsync(result_of(ctx), 0, sizeof(DeviceResult), s));
         if (result) return fetch_result(ctx, s, result);
@@ -787,6 +799,7 @@ int list_core(hlsmap_map *map, int64_t nq, const int32_t *d_playlist,
         p.trace = d_trace;
     }
 #endif
+    mark_begin(ctx, s);
     if (path == HLSMAP_PATH_SEARCH) {
         const int max_grid = ipt == map->ipt ? map->grid_search : map->grid_search_wide;
         const int grid = (int)(n_tiles < max_grid ? n_tiles : max_grid);
@@ -879,6 +892,7 @@ int list_fused(hlsmap_map *map, const hlsmap_batch *bs, int n, void *stream)
     p.ipt = ipt;
     const int max_grid = ipt == map->ipt ? map->grid_search : map->grid_search_wide;
     const int grid = (int)(n_tiles < max_grid ? n_tiles : max_grid);
+    mark_begin(ctx, s);
     CK(launch_resolve_search_fused(p, fb, n, grid, map->stage_smem, s, true));
     ctx->set_launches[ctx->epoch & 1u]++;      // only after a successful launch
     ctx->last_launches = 1;
@@ -929,12 +943,17 @@ int hlsmap_get_segment_list_dev_batches_timed(hlsmap_map *map, int32_t n, const 
             if (r) return r;
         }
     }
-    if (event_begin) CK(cudaEventRecord((cudaEvent_t)event_begin, s));
-    struct EndMark {        // the closing event is recorded on every way out
+    map->ctx->begin_event = event_begin;     // recorded right before the first launch (mark_begin)
+    struct EndMark {        // both events are recorded on every way out
+        hlsmap_ctx *ctx;
         void *ev;
         cudaStream_t s;
-        ~EndMark() { if (ev) cudaEventRecord((cudaEvent_t)ev, s); }
-    } end_mark{event_end, s};
+        ~EndMark()
+        {
+            mark_begin(ctx, s);               // (no launch happened: an empty or refused call)
+            if (ev) cudaEventRecord((cudaEvent_t)ev, s);
+        }
+    } end_mark{map->ctx, event_end, s};
     // Under hlsmap_ctx_set_batch_overlap the caller has promised that consecutive batches are independent:
     // runs of non-empty batches then go out kMaxFused at a time with one launch each (list_fused).
     int launches = 0;
