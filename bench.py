@@ -704,6 +704,13 @@ def run_ours(args):
     value = total_queries / (region_ms * 1e-3)
     mean_kernel_ms = my_ms / args.steps     # average launch-to-launch time on this rank
 
+    # the same batches as one launch per batch (overlapping launches, no fusing), for reference
+    unfused_ms = None
+    if overlap and not count_only:
+        ctx.set_batch_overlap(2)
+        unfused_ms = timed_list_form(torch, ctx, dmap, sets, stream, args.steps, args.warmup)[0] / args.steps
+        ctx.set_batch_overlap(overlap)
+
     # the same kernel timed one launch at a time (no overlap), for reference
     ctx.set_batch_overlap(False)
     iso_steps = min(args.steps, 200)
@@ -855,6 +862,11 @@ def run_ours(args):
                                    "launches overlap (programmatic dependent launch); kernel_ms_mean = region / "
                                    "batches" % (args.steps, overlap, timed_launches, args.steps),
                          "kernel_launches_timed_region": timed_launches,
+                         "one_launch_per_batch": None if unfused_ms is None else {
+                             "kernel_ms_mean": unfused_ms, "frac": alg_bytes / (unfused_ms * 1e-3) / 1e9 / peak,
+                             "note": "the same %d batches through the same call with "
+                                     "hlsmap_ctx_set_batch_overlap(ctx, 2): consecutive launches overlap, "
+                                     "one launch per batch (rank 0)" % args.steps},
                          "kernel_ms_isolated_mean": float(np.mean(kernel_ms)),
                          "kernel_ms_isolated_min": float(np.min(kernel_ms)),
                          "frac_isolated": alg_bytes / (float(np.mean(kernel_ms)) * 1e-3) / 1e9 / peak,

@@ -55,6 +55,7 @@ struct hlsmap_ctx {
     int64_t host_chunk = 262144;        // largest chunk of that pipeline, in queries (HLSMAP_HOST_CHUNK at creation, experiments)
     bool host_pipeline = true;          // chunked upload/compute/download of large host-pointer calls
     void *begin_event = nullptr;        // a batches call's opening cudaEvent_t, recorded right before its first launch
+    bool env_no_fuse = false;
     bool no_fuse = false;               // HLSMAP_NO_FUSE: a batches call issues one launch per batch even when it may fuse them
                                         // (HLSMAP_NO_PIPELINE in the environment at context creation turns it off)
     unsigned set_launches[2] = {0, 0};  // kernels launched on each scratch set (ticket slot parity)
@@ -262,7 +263,8 @@ int hlsmap_ctx_create(int device, hlsmap_ctx **out)
     if (!c) return fail(HLSMAP_ERR_NOMEM, "out of host memory");
     c->device = device;
     c->host_pipeline = getenv("HLSMAP_NO_PIPELINE") == nullptr;   // read once, here
-    c->no_fuse = getenv("HLSMAP_NO_FUSE") != nullptr;             // experiments: one launch per batch of a batches call
+    c->env_no_fuse = getenv("HLSMAP_NO_FUSE") != nullptr;         // experiments: one launch per batch of a batches call
+    c->no_fuse = c->env_no_fuse;
     if (const char *e = getenv("HLSMAP_HOST_CHUNK")) {
         const long long v = atoll(e);
         if (v >= 1024) c->host_chunk = (v + 1023) / 1024 * 1024;
@@ -315,6 +317,7 @@ int hlsmap_ctx_set_batch_overlap(hlsmap_ctx *ctx, int enable)
 {
     if (!ctx) return fail(HLSMAP_ERR_INVALID, "null context");
     ctx->overlap = enable != 0;
+    ctx->no_fuse = ctx->env_no_fuse || enable == 2;      // 2: overlapping launches, one per batch
     return HLSMAP_OK;
 }
 
@@ -710,7 +713,7 @@ void fill_table_params(ResolveParams &p, const hlsmap_map *map, hlsmap_ctx *ctx)
     p.ctr = ctr_of(ctx);
     p.result = result_of(ctx);
     p.epoch = ctx->epoch;
-    p.tslot = ctx->set_launches[ctx->epoch & 1u] & 1u;
+    p.tslot = ctx->set_launches[ctx->epoch & 1u];
     p.stage_elems = map->stage_elems;
     p.stage_all = map->info.stage_all;
     p.small = map->info.stage_all;
@@ -1477,7 +1480,7 @@ int hlsmap_view_format_dev(hlsmap_ctx *ctx, int64_t n, const int32_t *d_level,
     p.ctr = ctr_of(ctx);
     p.result = result_of(ctx);
     p.epoch = ctx->epoch;
-    p.tslot = ctx->set_launches[ctx->epoch & 1u] & 1u;
+    p.tslot = ctx->set_launches[ctx->epoch & 1u];
     p.n_tiles = (int)n_tiles;
     if (single_pass) {
         const int maxg = view_format_max_grid();

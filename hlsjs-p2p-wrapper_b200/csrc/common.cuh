@@ -29,15 +29,15 @@ constexpr unsigned kTrackSnContig = 8u;   // bit 3: sn[i] == sn[0] + i for the w
 
 // Per-context scratch header for the single-pass scan kernels.  A context owns TWO scratch
 // sets (header + status words + result) used by alternate launches (set = epoch & 1), so that
-// a batch may start while the previous one is still draining; `owner` is the epoch of the
-// launch currently using the set (0 = free; given back by the last CTA of that launch to exit,
-// which `exited` counts), and ticket[] is double buffered: the host tells
+// a batch may start while the previous one is still draining; the launches on a set are numbered
+// and take it in that order (`turn`: how many have finished with it; passed on by the last CTA of
+// a launch to exit, which `exited` counts), and ticket[] is double buffered: the host tells
 // each launch which of the two counters to use (they alternate per set), and a launch's last
 // tile zeroes the OTHER one, so late ticket fetches of a launch never see the next one's reset.
 struct ScanCounters {
     unsigned int ticket[2];
     unsigned int done;
-    unsigned int owner;
+    unsigned int turn;        // launches that have finished with this set (the next one to use it has seq == turn)
     unsigned long long n_unparsed;
     unsigned long long n_missing;
     unsigned int exited;      // CTAs of the owning launch that have left
@@ -122,7 +122,7 @@ struct ResolveParams {
     ScanCounters *ctr;
     DeviceResult *result;
     unsigned epoch;
-    unsigned tslot;         // which ticket counter of the set this launch uses (0 / 1)
+    unsigned tslot;         // the launch's number on its scratch set (0, 1, 2, ...); its low bit picks the ticket counter
     int n_tiles;
     // staging
     int stage_elems;  // capacity of the shared-memory copy of start[], in doubles

@@ -513,7 +513,7 @@ resolve_search_kernel(const __grid_constant__ SearchParams<FUSED ? kMaxFused : 1
     // Programmatic dependent launch: let the next batch's CTAs take the slots this grid frees
     // while it drains (only takes effect when the host launched with that attribute).
     asm volatile("griddepcontrol.launch_dependents;");
-    Scan::acquire_set(p.ctr, p.epoch);
+    Scan::acquire_set(p.ctr, p.tslot);
     if (tid == 0) sm.tile_slot[0] = (int)atomicAdd(&p.ctr->ticket[p.tslot & 1u], 1u);
     __syncthreads();
     // Tickets number the tiles of all the launch's batches consecutively: gB is the ticket, bB the batch
@@ -1101,7 +1101,7 @@ resolve_search_kernel(const __grid_constant__ SearchParams<FUSED ? kMaxFused : 1
     // never leave with a bulk copy still landing in this CTA's shared memory
     if (stage_pending) mbar_wait(&sm.mbar, mbar_phase);
     // the last CTA to leave wraps the batch up (counters -> result, scratch header re-armed)
-    Scan::leave_set(p.ctr, p.result, p.tslot);
+    Scan::leave_set(p.ctr, p.tslot, p.result);
 }
 
 // =========================================================================================
@@ -1167,7 +1167,7 @@ resolve_filter_kernel(const ResolveParams p)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned lane_lt = (1u << lane) - 1u;
 
-    FScan::acquire_set(p.ctr, p.epoch);
+    FScan::acquire_set(p.ctr, p.tslot);
     for (;;) {
         const int tile = FScan::next_tile(scan, p.ctr, p.tslot);
         if (tile >= p.n_tiles) break;
@@ -1279,7 +1279,7 @@ resolve_filter_kernel(const ResolveParams p)
 
         if (FScan::tile_done(p.ctr, p.n_tiles)) FScan::finish_batch(p.ctr, p.result, p.tslot);
     }
-    FScan::leave_set(p.ctr);
+    FScan::leave_set(p.ctr, p.tslot);
 }
 
 // =========================================================================================

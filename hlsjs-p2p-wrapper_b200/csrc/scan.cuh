@@ -38,18 +38,19 @@ struct TileScan {
         unsigned long long warp_sum[NW];
     };
 
-    // Called by every CTA before its first ticket: waits until the previous user of this
-    // scratch set (two launches back) has wrapped up, then marks the set as this launch's.
+    // Called by every CTA before its first ticket.  The launches on a scratch set are numbered by the
+    // host (seq = 0, 1, 2, ...; its low bit also picks the launch's ticket counter) and take the set
+    // strictly in that order: `turn` is the number of launches that have finished with it, and a
+    // launch's CTAs wait here until it is theirs.  (An earlier build handed the set to whichever
+    // waiting launch won a compare-and-swap on an owner word: with several small launches in flight
+    // under programmatic dependent launch, the launch after next could take the set first, draw from
+    // a ticket counter nobody had reset yet, find no tiles and leave its batch untouched.)
     // Every CTA that calls this must call leave_set() before it exits.
-    __device__ static void acquire_set(ScanCounters *ctr, unsigned epoch)
+    __device__ static void acquire_set(ScanCounters *ctr, unsigned seq)
     {
         if (threadIdx.x == 0) {
-            const unsigned e = epoch & kEpochMask;
-            for (;;) {
-                const unsigned o = atomicCAS(&ctr->owner, 0u, e);
-                if (o == 0u || o == e) break;
-                __nanosleep(256);
-            }
+            while (*reinterpret_cast<volatile unsigned *>(&ctr->turn) != seq) __nanosleep(256);
+            __threadfence();
         }
         __syncthreads();
     }
@@ -239,9 +240,9 @@ struct TileScan {
     // Run by the thread tile_done() elected: hand the counters to the host-visible
     // result and re-arm the scratch header for the next launch.  The set itself stays this
     // launch's until its last CTA has left (leave_set): a CTA that is dispatched only after
-    // the batch's last tile was finished still finds owner == its own epoch, draws a ticket
-    // past the end and leaves; were the set released here, that late CTA would take it again
-    // and nobody would ever give it back.
+    // the batch's last tile was finished still finds turn == its launch's number, draws a ticket
+    // past the end and leaves; were the set passed on here, that late CTA would wait for a turn
+    // that has gone by.
     __device__ static void finish_batch(ScanCounters *ctr, DeviceResult *result, unsigned tslot)
     {
         result->n_unparsed = (long long)atomicAdd(&ctr->n_unparsed, 0ull);
@@ -254,10 +255,10 @@ struct TileScan {
     }
 
     // Called by every CTA as the last thing it does.  The last CTA of the grid to get here
-    // frees the set for the launch after next.  A kernel that does not count finished tiles
-    // (tile_done) passes `result`: the batch is then wrapped up here, where every tile is known
-    // to be done because every CTA has left.
-    __device__ static void leave_set(ScanCounters *ctr, DeviceResult *result = nullptr, unsigned tslot = 0)
+    // passes the set on to the next launch on it (turn = seq + 1).  A kernel that does not count
+    // finished tiles (tile_done) passes `result`: the batch is then wrapped up here, where every
+    // tile is known to be done because every CTA has left.
+    __device__ static void leave_set(ScanCounters *ctr, unsigned seq, DeviceResult *result = nullptr)
     {
         __syncthreads();                            // this CTA's finish_batch(), if any, is done
         if (threadIdx.x == 0) {
@@ -265,10 +266,10 @@ struct TileScan {
             const unsigned old = atomicAdd(&ctr->exited, 1u);
             if (old == gridDim.x - 1u) {
                 __threadfence();
-                if (result != nullptr) finish_batch(ctr, result, tslot);
+                if (result != nullptr) finish_batch(ctr, result, seq);
                 ctr->exited = 0u;
                 __threadfence();
-                atomicExch(&ctr->owner, 0u);
+                atomicExch(&ctr->turn, seq + 1u);
             }
         }
     }

@@ -220,7 +220,7 @@ view_format_kernel(const FormatParams p)
     __shared__ __align__(16) char buf[kFormatTileViews * kFmtMaxChars + 16];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-    FmtScan::acquire_set(p.ctr, p.epoch);
+    FmtScan::acquire_set(p.ctr, p.tslot);
     for (;;) {
         const int tile = FmtScan::next_tile(scan, p.ctr, p.tslot);
         if (tile >= p.n_tiles) break;
@@ -304,7 +304,7 @@ view_format_kernel(const FormatParams p)
         }
         if (FmtScan::tile_done(p.ctr, p.n_tiles)) FmtScan::finish_batch(p.ctr, p.result, p.tslot);
     }
-    FmtScan::leave_set(p.ctr);
+    FmtScan::leave_set(p.ctr, p.tslot);
 }
 
 // ---- the same in three launches, none of which waits for another CTA -----------------------

@@ -60,8 +60,9 @@ class Context:
 
     def set_batch_overlap(self, enable=True):
         """Allow consecutive, independent device-pointer batches to overlap (the next one starts
-        while the previous one drains).  The caller guarantees they share no output buffers."""
-        N.check(self._lib.hlsmap_ctx_set_batch_overlap(self._h, int(bool(enable))))
+        while the previous one drains).  The caller guarantees they share no output buffers.
+        enable=2: overlapping launches, but a batches call keeps one launch per batch (no fusing)."""
+        N.check(self._lib.hlsmap_ctx_set_batch_overlap(self._h, 2 if enable == 2 else int(bool(enable))))
 
     def synchronize(self):
         N.check(self._lib.hlsmap_ctx_synchronize(self._h))

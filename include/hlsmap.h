@@ -94,7 +94,9 @@ int hlsmap_ctx_device(const hlsmap_ctx *ctx);
  * on the same stream is still writing its last hits, which hides each batch's ramp-up behind
  * its predecessor's tail.  ONLY legal when consecutive batches are independent: the next batch
  * must not read, or write to, any buffer the previous one is still writing.  Off by default
- * (plain stream order).  The library's own scratch is double-buffered for this. */
+ * (plain stream order).  The library's own scratch is double-buffered for this.  With enable = 1
+ * hlsmap_get_segment_list_dev_batches additionally resolves runs of batches with one launch (see
+ * there); enable = 2 keeps one (overlapping) launch per batch. */
 int hlsmap_ctx_set_batch_overlap(hlsmap_ctx *ctx, int enable);
 /* Block until everything issued through the context's own stream has finished. */
 int hlsmap_ctx_synchronize(hlsmap_ctx *ctx);

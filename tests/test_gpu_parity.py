@@ -522,11 +522,18 @@ def test_fused_batches_match_the_oracle_batch_by_batch(ctx, which):
         torch.cuda.synchronize()
     ctx.set_batch_overlap(True)
     try:
-        for rep in range(3):
+        launches = {}
+        for mode in (1, 1, 2, 1):               # 1: runs of batches fused into one launch; 2: one launch per batch
+            ctx.set_batch_overlap(mode)
             reset()
             assert m.get_segment_list_dev_batches([batch(s) for s in sets], stream.cuda_stream) == len(sets)
-            assert m.last_result(stream.cuda_stream).total_hits == sets[-1]["H"]
+            last = m.last_result(stream.cuda_stream)
+            assert last.total_hits == sets[-1]["H"]
+            launches[mode] = last.kernel_launches          # of the whole call
             check()
+        assert launches[2] == sum(1 for s in sets if s["nq"] > 0)
+        assert launches[1] == 6                             # the six runs between the five empty batches
+        ctx.set_batch_overlap(True)
         # a batch that cannot be launched ends the call in front of it, fused or not
         reset()
         bad = dict(batch(sets[5]), d_begin=0)
