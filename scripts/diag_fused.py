@@ -1,3 +1,6 @@
+"""Forty mixed-size list-form batches through hlsmap_get_segment_list_dev_batches, alternately fused (overlap mode 1)
+and as one overlapping launch per batch (mode 2); prints which batches differ from the oracle and which were left
+untouched.  (How the out-of-order hand-over of the scratch sets was found; tests/test_gpu_parity.py now covers it.)"""
 import sys, os, ctypes
 import numpy as np, torch
 sys.path.insert(0, "/root/repo")
