@@ -52,5 +52,54 @@ ctx.view_roundtrip(lv, ui, sn)
 o, c = ctx.view_format(lv, ui, sn)
 eo, ec = oracle.view_format(lv, ui, sn)
 assert c.tobytes() == ec.tobytes()
+
+
+def fused(t, gen):
+    """device-pointer batches through the batches call: fused into one launch (mode 1) and one launch each (mode 2)"""
+    import torch
+    dev = torch.device("cuda:0")
+    m = ctx.upload(t)
+    sets = []
+    for i, nq in enumerate((3001, 700, 1, 2049, 5000)):
+        qq = gen(i, nq)
+        ref = oracle.get_segment_list_batch(t.playlist_base, t.track_off, t.track_state, t.start, t.sn,
+                                            qq.playlist, qq.level, qq.begin, qq.duration)
+        H = int(ref[0][-1])
+        sets.append({"ref": ref, "H": H, "nq": nq,
+                     "pl": torch.from_numpy(qq.playlist).to(dev), "lv": torch.from_numpy(qq.level).to(dev),
+                     "bg": torch.from_numpy(qq.begin).to(dev), "du": torch.from_numpy(qq.duration).to(dev),
+                     "off": torch.empty(nq + 1, dtype=torch.int32, device=dev),
+                     "sn": torch.empty(max(H, 1), dtype=torch.int32, device=dev),
+                     "tm": torch.empty(max(H, 1), dtype=torch.float64, device=dev)})
+    batches = [{"nq": s["nq"], "d_playlist": s["pl"].data_ptr(), "d_level": s["lv"].data_ptr(),
+                "d_begin": s["bg"].data_ptr(), "d_duration": s["du"].data_ptr(), "d_offsets": s["off"].data_ptr(),
+                "d_sn_out": s["sn"].data_ptr(), "d_time_out": s["tm"].data_ptr(), "capacity": s["H"]} for s in sets]
+    for mode in (1, 2):
+        ctx.set_batch_overlap(mode)
+        for s in sets:
+            s["off"].fill_(-1)
+        torch.cuda.synchronize()
+        assert m.get_segment_list_dev_batches(batches) == len(sets)
+        m.last_result()
+        torch.cuda.synchronize()
+        for s in sets:
+            assert np.array_equal(s["off"].cpu().numpy().astype(np.int64), s["ref"][0])
+            assert np.array_equal(s["sn"][:s["H"]].cpu().numpy(), s["ref"][2])
+            assert np.array_equal(s["tm"][:s["H"]].cpu().numpy().view(np.uint64), s["ref"][3].view(np.uint64))
+    ctx.set_batch_overlap(False)
+    m.close()
+
+
+t, _ = synth.config2(n_queries=4)
+fused(t, lambda i, nq: synth.config2(seed=500 + i, n_queries=nq)[1])
+t, qa = synth.config5(n_playlists=60, queries_per_playlist=120)
+
+
+def pick(i, nq):
+    j = np.sort(np.random.RandomState(i).randint(0, len(qa), size=nq))
+    return QueryBatch(qa.playlist[j], qa.level[j], qa.begin[j], qa.duration[j])
+
+
+fused(t, pick)
 ctx.close()
 print("sanitize case ok")
